@@ -1,0 +1,191 @@
+/*
+ * uhdr_b200.h — C ABI of the B200-native gain-map hot path.
+ *
+ * Drop-in boundary for the three protected members of the reference's `ultrahdr::UltraHdr`
+ * (reference lib/include/ultrahdr/ultrahdr.h:348-350 generateGainMap, :370-372 applyGainMap,
+ * :381 toneMap; definitions lib/src/ultrahdr.cpp:185-358, :360-515, :517-558) plus the "next"
+ * row N1 `JpegR::convertYuv` (lib/src/jpegr.cpp:1132-1206). Plain pointers and sizes only: no
+ * C++ types, no torch types, no CUDA types (streams travel as `void*`).
+ *
+ * Every entry point returns the SAME integer values as the reference's `status_t`
+ * (ultrahdr.h:91-120) and performs the reference's argument checks in the reference's order
+ * before any CUDA call, so argument-validation behaviour is identical with or without a GPU.
+ *
+ * Memory kinds
+ *   *_host entry points  : all `data` / `chroma_data` pointers are HOST pointers (pageable or
+ *                          pinned). Synchronous, blocking, re-entrant — same contract as the
+ *                          reference members. Copies host<->device inside the call.
+ *   *_dev entry points   : all plane pointers are DEVICE pointers on the current CUDA device;
+ *                          the call only enqueues work on `stream` (a cudaStream_t passed as
+ *                          void*, NULL = legacy default stream) and returns without syncing.
+ *   *_batch_dev          : the same for `n` independent images in ONE launch.
+ */
+#ifndef UHDR_B200_H
+#define UHDR_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define UHDRB200_ABI_VERSION 1
+
+/* ---- enums: numeric values identical to the reference (ultrahdr.h:36-75) ---- */
+enum {
+  UHDRB200_COLORGAMUT_UNSPECIFIED = -1,
+  UHDRB200_COLORGAMUT_BT709 = 0,
+  UHDRB200_COLORGAMUT_P3 = 1,
+  UHDRB200_COLORGAMUT_BT2100 = 2
+};
+enum {
+  UHDRB200_TF_UNSPECIFIED = -1,
+  UHDRB200_TF_LINEAR = 0,
+  UHDRB200_TF_HLG = 1,
+  UHDRB200_TF_PQ = 2,
+  UHDRB200_TF_SRGB = 3
+};
+enum {
+  UHDRB200_OUTPUT_UNSPECIFIED = -1,
+  UHDRB200_OUTPUT_SDR = 0,               /* RGBA8888; see uhdrb200_sdr_to_rgba8888_* (row N3) */
+  UHDRB200_OUTPUT_HDR_LINEAR = 1,        /* RGBA F16, 8 B/px */
+  UHDRB200_OUTPUT_HDR_PQ = 2,            /* RGBA1010102, 4 B/px */
+  UHDRB200_OUTPUT_HDR_HLG = 3,           /* RGBA1010102, 4 B/px */
+  UHDRB200_OUTPUT_HDR_LINEAR_RGB_10BIT = 4 /* three planar u16 planes R,G,B */
+};
+enum {
+  UHDRB200_PIX_FMT_UNSPECIFIED = -1,
+  UHDRB200_PIX_FMT_P010 = 0,
+  UHDRB200_PIX_FMT_YUV420 = 1,
+  UHDRB200_PIX_FMT_MONOCHROME = 2,
+  UHDRB200_PIX_FMT_RGBA8888 = 3,
+  UHDRB200_PIX_FMT_RGBAF16 = 4,
+  UHDRB200_PIX_FMT_RGBA1010102 = 5
+};
+
+/* ---- status codes: numeric values identical to the reference status_t (ultrahdr.h:91-120) ---- */
+enum {
+  UHDRB200_NO_ERROR = 0,
+  UHDRB200_UNKNOWN_ERROR = -1,
+  UHDRB200_ERROR_BAD_PTR = -10001,
+  UHDRB200_ERROR_UNSUPPORTED_WIDTH_HEIGHT = -10002,
+  UHDRB200_ERROR_INVALID_COLORGAMUT = -10003,
+  UHDRB200_ERROR_INVALID_STRIDE = -10004,
+  UHDRB200_ERROR_INVALID_TRANS_FUNC = -10005,
+  UHDRB200_ERROR_RESOLUTION_MISMATCH = -10006,
+  UHDRB200_ERROR_INVALID_OUTPUT_FORMAT = -10009,
+  UHDRB200_ERROR_BAD_METADATA = -10010,
+  UHDRB200_ERROR_UNSUPPORTED_MAP_SCALE_FACTOR = -20008,
+  UHDRB200_ERROR_INSUFFICIENT_RESOURCE = -20009, /* also: no CUDA device / CUDA failure */
+  UHDRB200_ERROR_UNSUPPORTED_FEATURE = -30000
+};
+
+/*
+ * POD mirror of `ultrahdr_uncompressed_struct` (ultrahdr.h:152-180): same field order and types
+ * (the reference enums are plain `int`-sized), so on LP64 the two layouts are identical and the
+ * C++ shim can pass the reference struct straight through.
+ * Strides are in PIXELS (P010 chroma stride in uint16 elements), exactly as in the reference.
+ */
+typedef struct uhdrb200_image {
+  void* data;
+  size_t width;
+  size_t height;
+  int32_t colorGamut;
+  void* chroma_data;
+  size_t luma_stride;
+  size_t chroma_stride;
+  int32_t pixelFormat;
+} uhdrb200_image;
+
+/*
+ * POD flattening of `ultrahdr_metadata_struct` (ultrahdr.h:129-146). The reference member
+ * `std::string version` becomes a fixed char array; applyGainMap compares it with "1.0"
+ * (kGainMapVersion, ultrahdr.h:210) like ultrahdr.cpp:369-372.
+ */
+typedef struct uhdrb200_metadata {
+  char version[8];
+  float maxContentBoost;
+  float minContentBoost;
+  float gamma;
+  float offsetSdr;
+  float offsetHdr;
+  float hdrCapacityMin;
+  float hdrCapacityMax;
+} uhdrb200_metadata;
+
+/* ---- numeric mode ---- */
+enum {
+  /* default: follows the reference AS BUILT (analytic transfer functions; the USE_*_LUT macros
+   * of jpegr.cpp:33-38 are invisible to ultrahdr.cpp). */
+  UHDRB200_MODE_ANALYTIC = 0
+};
+
+/* ---- library / device management ---- */
+int uhdrb200_abi_version(void);
+/* number of CUDA devices visible, 0 if none / no driver. Never fails. */
+int uhdrb200_device_count(void);
+/* binds the calling thread to `device` and creates its context lazily. */
+int uhdrb200_init(int device);
+void uhdrb200_shutdown(void);
+/* last CUDA error string seen by the calling thread ("" if none). */
+const char* uhdrb200_last_error(void);
+/* pinned host memory helpers (full-speed DMA for the *_host entry points). */
+void* uhdrb200_host_alloc(size_t bytes);
+void uhdrb200_host_free(void* p);
+/* frees a gain map returned by uhdrb200_generate_gainmap_host (malloc-compatible). */
+void uhdrb200_free(void* p);
+/* number of kernel launches issued by this library in the calling process (monotonic). */
+uint64_t uhdrb200_launch_count(void);
+
+/* ---- A1: UltraHdr::generateGainMap (ultrahdr.cpp:185-358) ---- */
+/* Host planes. On success dest->data is a malloc'ed map_w*map_h buffer owned by the caller
+ * (release with uhdrb200_free); metadata is fully overwritten (ultrahdr.cpp:250-257). */
+int uhdrb200_generate_gainmap_host(const uhdrb200_image* yuv420, const uhdrb200_image* p010,
+                                   int hdr_tf, uhdrb200_metadata* metadata, uhdrb200_image* dest,
+                                   int sdr_is_601);
+/* Same, but writes the map into caller memory `map_buf` (>= (w/4)*(h/4) bytes); used by the C++
+ * shim, which must hand the reference callers a new[]-allocated buffer (jpegr.cpp:207-208). */
+int uhdrb200_generate_gainmap_host_into(const uhdrb200_image* yuv420, const uhdrb200_image* p010,
+                                        int hdr_tf, uhdrb200_metadata* metadata,
+                                        uhdrb200_image* dest, int sdr_is_601, void* map_buf,
+                                        size_t map_buf_bytes);
+/* Device planes; dest->data must point to a device buffer of (w/4)*(h/4) bytes. Async. */
+int uhdrb200_generate_gainmap_dev(const uhdrb200_image* yuv420, const uhdrb200_image* p010,
+                                  int hdr_tf, uhdrb200_metadata* metadata, uhdrb200_image* dest,
+                                  int sdr_is_601, void* stream);
+
+/* ---- A2: UltraHdr::applyGainMap (ultrahdr.cpp:360-515) ---- */
+int uhdrb200_apply_gainmap_host(const uhdrb200_image* yuv420, const uhdrb200_image* gainmap,
+                                const uhdrb200_metadata* metadata, int output_format,
+                                float max_display_boost, uhdrb200_image* dest);
+int uhdrb200_apply_gainmap_dev(const uhdrb200_image* yuv420, const uhdrb200_image* gainmap,
+                               const uhdrb200_metadata* metadata, int output_format,
+                               float max_display_boost, uhdrb200_image* dest, void* stream);
+
+/* ---- A3: UltraHdr::toneMap (ultrahdr.cpp:517-558) ---- */
+int uhdrb200_tonemap_host(const uhdrb200_image* src, uhdrb200_image* dest);
+int uhdrb200_tonemap_dev(const uhdrb200_image* src, uhdrb200_image* dest, void* stream);
+
+/* ---- batched device-resident variants: n independent images, ONE launch each ----
+ * Arrays of n descriptors (host memory, read during the call); all images of a batch must share
+ * width/height/strides layout class, gamuts, transfer function / output format. */
+int uhdrb200_generate_gainmap_batch_dev(int n, const uhdrb200_image* yuv420, const uhdrb200_image* p010,
+                                        int hdr_tf, uhdrb200_metadata* metadata,
+                                        uhdrb200_image* dest, int sdr_is_601, void* stream);
+int uhdrb200_apply_gainmap_batch_dev(int n, const uhdrb200_image* yuv420, const uhdrb200_image* gainmap,
+                                     const uhdrb200_metadata* metadata, int output_format,
+                                     float max_display_boost, uhdrb200_image* dest, void* stream);
+int uhdrb200_tonemap_batch_dev(int n, const uhdrb200_image* src, uhdrb200_image* dest,
+                               void* stream);
+
+/* ---- N1: JpegR::convertYuv (jpegr.cpp:1132-1206) + transformYuv420 (gainmapmath.cpp:483-520):
+ * in-place YUV420 re-encode between BT.709 / BT.601(P3) / BT.2100 matrices. ---- */
+int uhdrb200_convert_yuv_host(uhdrb200_image* image, int src_encoding, int dest_encoding);
+int uhdrb200_convert_yuv_dev(uhdrb200_image* image, int src_encoding, int dest_encoding,
+                             void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* UHDR_B200_H */
