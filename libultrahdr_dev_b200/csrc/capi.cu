@@ -1,0 +1,692 @@
+// capi.cu — the C ABI of include/uhdr_b200.h: argument validation in the reference's order
+// (lib/src/ultrahdr.cpp:189-202, 245-247, 364-406, 518-523; lib/src/jpegr.cpp:1134-1140), plane
+// staging for the host-pointer entry points, and kernel launches on CUDA streams (which replace
+// the reference's JobQueue + <=4 worker threads, ultrahdr.cpp:131-183, 304-354, 500-513).
+//
+// There is NO CPU fallback: without a usable CUDA device every compute entry point returns
+// UHDRB200_ERROR_INSUFFICIENT_RESOURCE and uhdrb200_last_error() says why.
+#include <atomic>
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <map>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "../../include/uhdr_b200.h"
+#include "uhdr_kernels.cuh"
+#include "uhdr_math.cuh"
+
+namespace {
+using namespace uhdr;
+
+std::atomic<uint64_t> g_launches{0};
+
+// ---------------------------------------------------------------- per-thread context
+struct DevBuf {
+  void* p = nullptr;
+  size_t cap = 0;
+};
+constexpr int kRing = 16;
+struct BatchSlot {
+  Planes* host = nullptr;  // pinned
+  Planes* dev = nullptr;
+  int cap = 0;
+  cudaEvent_t done = nullptr;
+};
+struct Ctx {
+  int device = -1;  // -1: not bound yet
+  bool ready = false;
+  cudaStream_t stream = nullptr;
+  DevBuf buf[8];  // staging planes of the *_host entry points
+  BatchSlot ring[kRing];
+  int ring_next = 0;
+  std::string err;
+};
+thread_local Ctx t_ctx;
+
+int fail(cudaError_t e, const char* what) {
+  char msg[256];
+  snprintf(msg, sizeof msg, "%s: %s", what, cudaGetErrorString(e));
+  t_ctx.err = msg;
+  cudaGetLastError();  // clear the sticky-less error state
+  return UHDRB200_ERROR_INSUFFICIENT_RESOURCE;
+}
+#define CU(call)                                   \
+  do {                                             \
+    cudaError_t e__ = (call);                      \
+    if (e__ != cudaSuccess) return fail(e__, #call); \
+  } while (0)
+
+int ensure_ctx() {
+  Ctx& c = t_ctx;
+  if (c.ready) {
+    CU(cudaSetDevice(c.device));
+    return 0;
+  }
+  int n = 0;
+  cudaError_t e = cudaGetDeviceCount(&n);
+  if (e != cudaSuccess || n == 0) {
+    t_ctx.err = std::string("no CUDA device: ") + (e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0");
+    cudaGetLastError();
+    return UHDRB200_ERROR_INSUFFICIENT_RESOURCE;
+  }
+  if (c.device < 0) {
+    int cur = 0;
+    if (cudaGetDevice(&cur) != cudaSuccess) cur = 0;
+    c.device = cur;
+  }
+  CU(cudaSetDevice(c.device));
+  CU(cudaStreamCreateWithFlags(&c.stream, cudaStreamNonBlocking));
+  c.ready = true;
+  return 0;
+}
+
+int reserve(DevBuf& b, size_t bytes) {
+  if (bytes <= b.cap) return 0;
+  if (b.p) cudaFree(b.p);
+  b.p = nullptr;
+  b.cap = 0;
+  size_t cap = (bytes + (size_t(1) << 20)) & ~((size_t(1) << 20) - 1);
+  CU(cudaMalloc(&b.p, cap));
+  b.cap = cap;
+  return 0;
+}
+
+// ---------------------------------------------------------------- IDW tables (gainmapmath.h:184-228, gainmapmath.cpp:69-110)
+// Built on the host with the reference's float arithmetic, cached on the device per (device, scale).
+float idw_dist(float x1, float x2, float y1, float y2) {
+  return sqrtf(((y2 - y1) * (y2 - y1)) + (x2 - x1) * (x2 - x1));
+}
+void idw_fill(float* w, int s, int inc_r, int inc_b) {
+  for (int y = 0; y < s; y++)
+    for (int x = 0; x < s; x++) {
+      float px = ((float)x) / s, py = ((float)y) / s;
+      int cx = (int)floorf(px), cy = (int)floorf(py);
+      int nx = cx + inc_r, ny = cy + inc_b;
+      float* o = w + (y * s + x) * 4;
+      float d1 = idw_dist(px, (float)cx, py, (float)cy);
+      if (d1 == 0) {
+        o[0] = 1.f; o[1] = 0.f; o[2] = 0.f; o[3] = 0.f;
+        continue;
+      }
+      float w1 = 1.f / d1;
+      float w2 = 1.f / idw_dist(px, (float)cx, py, (float)ny);
+      float w3 = 1.f / idw_dist(px, (float)nx, py, (float)cy);
+      float w4 = 1.f / idw_dist(px, (float)nx, py, (float)ny);
+      float tot = w1 + w2 + w3 + w4;
+      o[0] = w1 / tot; o[1] = w2 / tot; o[2] = w3 / tot; o[3] = w4 / tot;
+    }
+}
+std::mutex g_idw_mu;
+std::map<std::pair<int, int>, float*> g_idw;  // (device, scale) -> device tables [4][s][s][4]
+
+int get_idw(int device, int scale, const float** out) {
+  std::lock_guard<std::mutex> lk(g_idw_mu);
+  auto it = g_idw.find({device, scale});
+  if (it != g_idw.end()) {
+    *out = it->second;
+    return 0;
+  }
+  const size_t n = (size_t)scale * scale * 4;
+  std::vector<float> h(4 * n);
+  idw_fill(h.data() + 0 * n, scale, 1, 1);  // mWeights
+  idw_fill(h.data() + 1 * n, scale, 0, 1);  // mWeightsNR
+  idw_fill(h.data() + 2 * n, scale, 1, 0);  // mWeightsNB
+  idw_fill(h.data() + 3 * n, scale, 0, 0);  // mWeightsC
+  float* d = nullptr;
+  CU(cudaMalloc(&d, h.size() * sizeof(float)));
+  CU(cudaMemcpy(d, h.data(), h.size() * sizeof(float), cudaMemcpyHostToDevice));
+  g_idw[{device, scale}] = d;
+  *out = d;
+  return 0;
+}
+
+// ---------------------------------------------------------------- batch descriptor staging
+// A launch over n>1 images reads its per-image plane pointers from a small device array. Slots
+// come from a ring guarded by events so an async caller can have kRing launches in flight.
+int stage_batch(const std::vector<Planes>& v, cudaStream_t s, const Planes** dev, BatchSlot** slot_out) {
+  Ctx& c = t_ctx;
+  BatchSlot& sl = c.ring[c.ring_next];
+  c.ring_next = (c.ring_next + 1) % kRing;
+  if (sl.done) CU(cudaEventSynchronize(sl.done));
+  else CU(cudaEventCreateWithFlags(&sl.done, cudaEventDisableTiming));
+  if ((int)v.size() > sl.cap) {
+    if (sl.host) cudaFreeHost(sl.host);
+    if (sl.dev) cudaFree(sl.dev);
+    sl.host = nullptr; sl.dev = nullptr; sl.cap = 0;
+    int cap = 64;
+    while (cap < (int)v.size()) cap *= 2;
+    CU(cudaHostAlloc((void**)&sl.host, sizeof(Planes) * cap, cudaHostAllocDefault));
+    CU(cudaMalloc((void**)&sl.dev, sizeof(Planes) * cap));
+    sl.cap = cap;
+  }
+  memcpy(sl.host, v.data(), sizeof(Planes) * v.size());
+  CU(cudaMemcpyAsync(sl.dev, sl.host, sizeof(Planes) * v.size(), cudaMemcpyHostToDevice, s));
+  *dev = sl.dev;
+  *slot_out = &sl;
+  return 0;
+}
+
+bool same_layout(const uhdrb200_image& a, const uhdrb200_image& b) {
+  return a.width == b.width && a.height == b.height && a.luma_stride == b.luma_stride &&
+         a.chroma_stride == b.chroma_stride && a.colorGamut == b.colorGamut;
+}
+
+}  // namespace
+
+// ================================================================ validation (no CUDA involved)
+namespace {
+
+// ultrahdr.cpp:189-202, then :222-248 for the transfer function, :267-302 for gamut ranges.
+int validate_generate(const uhdrb200_image* sdr, const uhdrb200_image* hdr, int hdr_tf,
+                      const uhdrb200_metadata* md, const uhdrb200_image* dest) {
+  if (!sdr || !hdr || !md || !dest || !sdr->data || !sdr->chroma_data || !hdr->data || !hdr->chroma_data)
+    return UHDRB200_ERROR_BAD_PTR;
+  if (sdr->width != hdr->width || sdr->height != hdr->height) return UHDRB200_ERROR_RESOLUTION_MISMATCH;
+  if (sdr->colorGamut == UHDRB200_COLORGAMUT_UNSPECIFIED || hdr->colorGamut == UHDRB200_COLORGAMUT_UNSPECIFIED)
+    return UHDRB200_ERROR_INVALID_COLORGAMUT;
+  if (hdr_tf != UHDRB200_TF_LINEAR && hdr_tf != UHDRB200_TF_HLG && hdr_tf != UHDRB200_TF_PQ)
+    return UHDRB200_ERROR_INVALID_TRANS_FUNC;
+  if (sdr->colorGamut < 0 || sdr->colorGamut > 2 || hdr->colorGamut < 0 || hdr->colorGamut > 2)
+    return UHDRB200_ERROR_INVALID_COLORGAMUT;
+  return UHDRB200_NO_ERROR;
+}
+
+// ultrahdr.cpp:250-257
+void fill_metadata(uhdrb200_metadata* md, int hdr_tf) {
+  const float white = hdr_tf == UHDRB200_TF_PQ ? 10000.0f : 1000.0f;  // kPqMaxNits / kHlgMaxNits
+  memset(md->version, 0, sizeof md->version);
+  memcpy(md->version, "1.0", 3);  // kGainMapVersion
+  md->maxContentBoost = white / 203.0f;  // kSdrWhiteNits
+  md->minContentBoost = 1.0f;
+  md->gamma = 1.0f;
+  md->offsetSdr = 0.0f;
+  md->offsetHdr = 0.0f;
+  md->hdrCapacityMin = 1.0f;
+  md->hdrCapacityMax = md->maxContentBoost;
+}
+
+// ultrahdr.cpp:209-216 (data pointer is set by the caller of this helper)
+void fill_map_desc(uhdrb200_image* dest, size_t mw, size_t mh) {
+  dest->width = mw;
+  dest->height = mh;
+  dest->colorGamut = UHDRB200_COLORGAMUT_UNSPECIFIED;
+  dest->luma_stride = mw;
+  dest->chroma_data = nullptr;
+  dest->chroma_stride = 0;
+  dest->pixelFormat = UHDRB200_PIX_FMT_MONOCHROME;
+}
+
+// ultrahdr.cpp:364-406
+int validate_apply(const uhdrb200_image* sdr, const uhdrb200_image* map, const uhdrb200_metadata* md,
+                   const uhdrb200_image* dest) {
+  if (!sdr || !map || !md || !dest || !sdr->data || !sdr->chroma_data || !map->data) return UHDRB200_ERROR_BAD_PTR;
+  if (strncmp(md->version, "1.0", sizeof md->version) != 0) return UHDRB200_ERROR_BAD_METADATA;
+  if (md->gamma != 1.0f) return UHDRB200_ERROR_BAD_METADATA;
+  if (md->offsetSdr != 0.0f || md->offsetHdr != 0.0f) return UHDRB200_ERROR_BAD_METADATA;
+  if (md->hdrCapacityMin != md->minContentBoost || md->hdrCapacityMax != md->maxContentBoost)
+    return UHDRB200_ERROR_BAD_METADATA;
+  if (map->width == 0 || map->height == 0) return UHDRB200_ERROR_UNSUPPORTED_MAP_SCALE_FACTOR;  // the reference would divide by zero
+  if (sdr->width % map->width != 0 || sdr->height % map->height != 0) return UHDRB200_ERROR_UNSUPPORTED_MAP_SCALE_FACTOR;
+  if (sdr->width * map->height != sdr->height * map->width) return UHDRB200_ERROR_UNSUPPORTED_MAP_SCALE_FACTOR;
+  return UHDRB200_NO_ERROR;
+}
+
+// ultrahdr.cpp:518-523 (+ null plane pointers, which the reference would dereference)
+int validate_tonemap(const uhdrb200_image* src, const uhdrb200_image* dest) {
+  if (!src || !dest) return UHDRB200_ERROR_BAD_PTR;
+  if (src->width != dest->width || src->height != dest->height) return UHDRB200_ERROR_RESOLUTION_MISMATCH;
+  if (!src->data || !src->chroma_data || !dest->data || !dest->chroma_data) return UHDRB200_ERROR_BAD_PTR;
+  return UHDRB200_NO_ERROR;
+}
+
+bool fits_int(size_t v) { return v <= (size_t)0x7fffffff; }
+
+Geometry geometry_of(const uhdrb200_image* sdr, const uhdrb200_image* hdr) {
+  Geometry g;
+  memset(&g, 0, sizeof g);
+  const uhdrb200_image* any = sdr ? sdr : hdr;
+  g.width = (int)any->width;
+  g.height = (int)any->height;
+  if (sdr) {
+    g.sdr_luma_stride = (int)sdr->luma_stride;
+    g.sdr_chroma_stride = (int)sdr->chroma_stride;
+  }
+  if (hdr) {
+    g.hdr_luma_stride = (int)(hdr->luma_stride == 0 ? hdr->width : hdr->luma_stride);  // gainmapmath.cpp:585
+    g.hdr_chroma_stride = (int)hdr->chroma_stride;
+  }
+  return g;
+}
+void set_sdr_planes(Planes& pl, const uhdrb200_image& im) {
+  pl.sdr_y = im.data;
+  pl.sdr_u = im.chroma_data;
+  pl.sdr_v = (const uint8_t*)im.chroma_data + im.chroma_stride * (im.height / 2);  // gainmapmath.cpp:568
+}
+
+// ================================================================ device-pointer cores
+int generate_core(int n, const uhdrb200_image* sdr, const uhdrb200_image* hdr, int hdr_tf,
+                  uhdrb200_metadata* md, uhdrb200_image* dest, int sdr_is_601, cudaStream_t s) {
+  if (n <= 0) return UHDRB200_NO_ERROR;
+  if (!sdr || !hdr || !md || !dest) return UHDRB200_ERROR_BAD_PTR;
+  for (int i = 0; i < n; i++) {
+    int st = validate_generate(&sdr[i], &hdr[i], hdr_tf, &md[i], &dest[i]);
+    if (st) return st;
+    if (!dest[i].data) return UHDRB200_ERROR_BAD_PTR;
+    if (i && (!same_layout(sdr[i], sdr[0]) || !same_layout(hdr[i], hdr[0]))) return UHDRB200_ERROR_RESOLUTION_MISMATCH;
+  }
+  if (!fits_int(sdr[0].width) || !fits_int(sdr[0].height) || !fits_int(sdr[0].luma_stride) || !fits_int(hdr[0].luma_stride))
+    return UHDRB200_ERROR_UNSUPPORTED_WIDTH_HEIGHT;
+  int st = ensure_ctx();
+  if (st) return st;
+  GenerateParams p;
+  memset(&p, 0, sizeof p);
+  p.g = geometry_of(&sdr[0], &hdr[0]);
+  p.g.map_scale = 4;  // kMapDimensionScaleFactor, ultrahdr.h:213
+  p.g.map_width = p.g.width / 4;
+  p.g.map_height = p.g.height / 4;
+  p.sdr_k = yuv_coefs(sdr_is_601 ? 1 : sdr[0].colorGamut);  // ultrahdr.cpp:267-286
+  p.hdr_k = yuv_coefs(hdr[0].colorGamut);                   // ultrahdr.cpp:288-302
+  p.luma = luma_coefs(sdr[0].colorGamut);
+  p.gamut = gamut_matrix(sdr[0].colorGamut, hdr[0].colorGamut);  // ultrahdr.cpp:262-263
+  p.use_gamut = sdr[0].colorGamut != hdr[0].colorGamut;
+  p.hdr_tf = hdr_tf;
+  p.hdr_white_nits = hdr_tf == UHDRB200_TF_PQ ? 10000.0f : 1000.0f;
+  std::vector<Planes> v(n);
+  bool vec = true;
+  for (int i = 0; i < n; i++) {
+    fill_metadata(&md[i], hdr_tf);
+    fill_map_desc(&dest[i], (size_t)p.g.map_width, (size_t)p.g.map_height);
+    memset(&v[i], 0, sizeof(Planes));
+    set_sdr_planes(v[i], sdr[i]);
+    v[i].hdr_y = hdr[i].data;
+    v[i].hdr_uv = hdr[i].chroma_data;
+    v[i].out = dest[i].data;
+    vec = vec && generate_vec_ok(p.g, v[i]);
+  }
+  p.min_boost = md[0].minContentBoost;
+  p.max_boost = md[0].maxContentBoost;
+  p.log2_min = (float)log2((double)p.min_boost);  // ultrahdr.cpp:259-260
+  p.log2_max = (float)log2((double)p.max_boost);
+  {  // gainmapmath.cpp:539-540 for gain == min / max, in double like the reference
+    const double den = (double)(p.log2_max - p.log2_min);
+    p.code_at_min = (int)(uint8_t)((log2((double)p.min_boost) - (double)p.log2_min) / den * 255.0);
+    p.code_at_max = (int)(uint8_t)((log2((double)p.max_boost) - (double)p.log2_min) / den * 255.0);
+  }
+  BatchSlot* slot = nullptr;
+  if (n == 1) p.single = v[0];
+  else if ((st = stage_batch(v, s, &p.batch, &slot))) return st;
+  cudaError_t e = launch_generate_impl(p, n, vec, s);
+  if (slot) cudaEventRecord(slot->done, s);
+  if (e != cudaSuccess) return fail(e, "generate kernel launch");
+  g_launches++;
+  return UHDRB200_NO_ERROR;
+}
+
+int apply_core(int n, const uhdrb200_image* sdr, const uhdrb200_image* map, const uhdrb200_metadata* md,
+               int fmt, float max_display_boost, uhdrb200_image* dest, cudaStream_t s) {
+  if (n <= 0) return UHDRB200_NO_ERROR;
+  if (!sdr || !map || !md || !dest) return UHDRB200_ERROR_BAD_PTR;
+  for (int i = 0; i < n; i++) {
+    int st = validate_apply(&sdr[i], &map[i], md, &dest[i]);
+    if (st) return st;
+    if (!dest[i].data) return UHDRB200_ERROR_BAD_PTR;
+    if (i && (!same_layout(sdr[i], sdr[0]) || map[i].width != map[0].width || map[i].height != map[0].height))
+      return UHDRB200_ERROR_RESOLUTION_MISMATCH;
+  }
+  if (!fits_int(sdr[0].width) || !fits_int(sdr[0].height) || !fits_int(sdr[0].luma_stride))
+    return UHDRB200_ERROR_UNSUPPORTED_WIDTH_HEIGHT;
+  for (int i = 0; i < n; i++) {  // ultrahdr.cpp:411-413
+    dest[i].width = sdr[i].width;
+    dest[i].height = sdr[i].height;
+    dest[i].colorGamut = sdr[i].colorGamut;
+  }
+  if (fmt != UHDRB200_OUTPUT_HDR_LINEAR && fmt != UHDRB200_OUTPUT_HDR_PQ && fmt != UHDRB200_OUTPUT_HDR_HLG &&
+      fmt != UHDRB200_OUTPUT_HDR_LINEAR_RGB_10BIT)
+    return UHDRB200_NO_ERROR;  // ultrahdr.cpp:491-493: nothing is written, NO_ERROR
+  int st = ensure_ctx();
+  if (st) return st;
+  ApplyParams p;
+  memset(&p, 0, sizeof p);
+  p.g = geometry_of(&sdr[0], nullptr);
+  p.g.map_width = (int)map[0].width;
+  p.g.map_height = (int)map[0].height;
+  p.g.map_scale = (int)(sdr[0].width / map[0].width);  // ultrahdr.cpp:409
+  p.output_format = fmt;
+  p.log2_min = (float)log2((double)md->minContentBoost);
+  p.log2_max = (float)log2((double)md->maxContentBoost);
+  p.max_boost = md->maxContentBoost;
+  p.display_boost = max_display_boost < md->maxContentBoost ? max_display_boost : md->maxContentBoost;  // :415
+  p.inv_display_boost = 1.0f / p.display_boost;
+  if ((st = get_idw(t_ctx.device, p.g.map_scale, &p.idw))) return st;
+  std::vector<Planes> v(n);
+  bool vec = true;
+  for (int i = 0; i < n; i++) {
+    memset(&v[i], 0, sizeof(Planes));
+    set_sdr_planes(v[i], sdr[i]);
+    v[i].map_in = map[i].data;
+    v[i].out = dest[i].data;
+    vec = vec && apply_vec_ok(p.g, v[i]);
+  }
+  BatchSlot* slot = nullptr;
+  if (n == 1) p.single = v[0];
+  else if ((st = stage_batch(v, s, &p.batch, &slot))) return st;
+  cudaError_t e = launch_apply_impl(p, n, vec, s);
+  if (slot) cudaEventRecord(slot->done, s);
+  if (e != cudaSuccess) return fail(e, "apply kernel launch");
+  g_launches++;
+  return UHDRB200_NO_ERROR;
+}
+
+int tonemap_core(int n, const uhdrb200_image* src, uhdrb200_image* dest, cudaStream_t s) {
+  if (n <= 0) return UHDRB200_NO_ERROR;
+  if (!src || !dest) return UHDRB200_ERROR_BAD_PTR;
+  for (int i = 0; i < n; i++) {
+    int st = validate_tonemap(&src[i], &dest[i]);
+    if (st) return st;
+    if (i && (!same_layout(src[i], src[0]) || dest[i].luma_stride != dest[0].luma_stride ||
+              dest[i].chroma_stride != dest[0].chroma_stride))
+      return UHDRB200_ERROR_RESOLUTION_MISMATCH;
+  }
+  if (!fits_int(src[0].width) || !fits_int(src[0].height) || !fits_int(src[0].luma_stride) || !fits_int(dest[0].luma_stride))
+    return UHDRB200_ERROR_UNSUPPORTED_WIDTH_HEIGHT;
+  int st = ensure_ctx();
+  if (st) return st;
+  ToneMapParams p;
+  memset(&p, 0, sizeof p);
+  p.g = geometry_of(nullptr, &src[0]);
+  p.g.hdr_luma_stride = (int)src[0].luma_stride;  // toneMap uses the stride as given, ultrahdr.cpp:527
+  p.g.dst_luma_stride = (int)dest[0].luma_stride;
+  p.g.dst_chroma_stride = (int)dest[0].chroma_stride;
+  std::vector<Planes> v(n);
+  bool vec = true;
+  for (int i = 0; i < n; i++) {
+    memset(&v[i], 0, sizeof(Planes));
+    v[i].hdr_y = src[i].data;
+    v[i].hdr_uv = src[i].chroma_data;
+    v[i].out = dest[i].data;
+    v[i].out_u = dest[i].chroma_data;
+    v[i].out_v = (uint8_t*)dest[i].chroma_data + dest[i].chroma_stride * dest[i].height / 2;  // ultrahdr.cpp:539-540
+    vec = vec && tonemap_vec_ok(p.g, v[i]);
+    dest[i].colorGamut = src[i].colorGamut;  // ultrahdr.cpp:556
+  }
+  BatchSlot* slot = nullptr;
+  if (n == 1) p.single = v[0];
+  else if ((st = stage_batch(v, s, &p.batch, &slot))) return st;
+  cudaError_t e = launch_tonemap_impl(p, n, vec, s);
+  if (slot) cudaEventRecord(slot->done, s);
+  if (e != cudaSuccess) return fail(e, "toneMap kernel launch");
+  g_launches++;
+  return UHDRB200_NO_ERROR;
+}
+
+// jpegr.cpp:1134-1195: selector; identity conversions return NO_ERROR without touching the image
+int convert_yuv_core(uhdrb200_image* im, int src_enc, int dst_enc, cudaStream_t s) {
+  if (!im) return UHDRB200_ERROR_BAD_PTR;
+  if (src_enc == UHDRB200_COLORGAMUT_UNSPECIFIED || dst_enc == UHDRB200_COLORGAMUT_UNSPECIFIED)
+    return UHDRB200_ERROR_INVALID_COLORGAMUT;
+  if (src_enc < 0 || src_enc > 2 || dst_enc < 0 || dst_enc > 2) return UHDRB200_ERROR_INVALID_COLORGAMUT;
+  if (src_enc == dst_enc) return UHDRB200_NO_ERROR;
+  if (!im->data || !im->chroma_data) return UHDRB200_ERROR_BAD_PTR;
+  // gainmapmath.cpp:447-481; [src][dst]
+  static const float M[3][3][9] = {
+      {{0}, {1.0f, 0.101579f, 0.196076f, 0.0f, 0.989854f, -0.110653f, 0.0f, -0.072453f, 0.983398f},
+       {1.0f, -0.016969f, 0.096312f, 0.0f, 0.995306f, -0.051192f, 0.0f, 0.011507f, 1.002637f}},
+      {{1.0f, -0.118188f, -0.212685f, 0.0f, 1.018640f, 0.114618f, 0.0f, 0.075049f, 1.025327f}, {0},
+       {1.0f, -0.128245f, -0.115879f, 0.0f, 1.010016f, 0.061592f, 0.0f, 0.086969f, 1.029350f}},
+      {{1.0f, 0.018149f, -0.095132f, 0.0f, 1.004123f, 0.051267f, 0.0f, -0.011524f, 0.996782f},
+       {1.0f, 0.117887f, 0.105521f, 0.0f, 0.995211f, -0.059549f, 0.0f, -0.084085f, 0.976518f}, {0}}};
+  int st = ensure_ctx();
+  if (st) return st;
+  ConvertYuvParams p;
+  memset(&p, 0, sizeof p);
+  p.g = geometry_of(im, nullptr);
+  memcpy(p.m, M[src_enc][dst_enc], sizeof p.m);
+  set_sdr_planes(p.single, *im);
+  p.single.sdr_v = (const uint8_t*)im->chroma_data + im->chroma_stride * im->height / 2;  // gainmapmath.cpp:507
+  cudaError_t e = launch_convert_yuv_impl(p, 1, convert_yuv_vec_ok(p.g, p.single), s);
+  if (e != cudaSuccess) return fail(e, "convertYuv kernel launch");
+  g_launches++;
+  return UHDRB200_NO_ERROR;
+}
+
+}  // namespace
+
+// ================================================================ host-pointer staging helpers
+namespace {
+
+size_t yuv420_luma_bytes(const uhdrb200_image& im) { return im.height ? im.luma_stride * (im.height - 1) + im.width : 0; }
+size_t yuv420_chroma_bytes(const uhdrb200_image& im) {  // U rows followed by V rows at +chroma_stride*(h/2)
+  size_t ch = im.height / 2;
+  return ch ? im.chroma_stride * ch + im.chroma_stride * (ch - 1) + im.width / 2 : 0;
+}
+size_t p010_luma_stride(const uhdrb200_image& im) { return im.luma_stride == 0 ? im.width : im.luma_stride; }
+size_t p010_luma_bytes(const uhdrb200_image& im) { return im.height ? 2 * (p010_luma_stride(im) * (im.height - 1) + im.width) : 0; }
+size_t p010_chroma_bytes(const uhdrb200_image& im) {
+  size_t ch = im.height / 2;
+  return ch ? 2 * (im.chroma_stride * (ch - 1) + (im.width & ~(size_t)1)) : 0;
+}
+
+int upload(DevBuf& b, const void* host, size_t bytes, cudaStream_t s) {
+  int st = reserve(b, bytes ? bytes : 1);
+  if (st) return st;
+  if (bytes) CU(cudaMemcpyAsync(b.p, host, bytes, cudaMemcpyHostToDevice, s));
+  return 0;
+}
+
+int generate_host(const uhdrb200_image* sdr, const uhdrb200_image* hdr, int hdr_tf, uhdrb200_metadata* md,
+                  uhdrb200_image* dest, int sdr_is_601, void* map_buf, size_t map_buf_bytes, bool own_alloc) {
+  int st = validate_generate(sdr, hdr, hdr_tf, md, dest);
+  if (st) return st;
+  if ((st = ensure_ctx())) return st;
+  Ctx& c = t_ctx;
+  const size_t mw = sdr->width / 4, mh = sdr->height / 4, mbytes = mw * mh;
+  if (!own_alloc && (!map_buf || map_buf_bytes < mbytes)) return -20004;  // ERROR_ULTRAHDR_BUFFER_TOO_SMALL
+  if ((st = upload(c.buf[0], sdr->data, yuv420_luma_bytes(*sdr), c.stream))) return st;
+  if ((st = upload(c.buf[1], sdr->chroma_data, yuv420_chroma_bytes(*sdr), c.stream))) return st;
+  if ((st = upload(c.buf[2], hdr->data, p010_luma_bytes(*hdr), c.stream))) return st;
+  if ((st = upload(c.buf[3], hdr->chroma_data, p010_chroma_bytes(*hdr), c.stream))) return st;
+  if ((st = reserve(c.buf[4], mbytes ? mbytes : 1))) return st;
+  uhdrb200_image dsdr = *sdr, dhdr = *hdr, ddst;
+  memset(&ddst, 0, sizeof ddst);
+  dsdr.data = c.buf[0].p; dsdr.chroma_data = c.buf[1].p;
+  dhdr.data = c.buf[2].p; dhdr.chroma_data = c.buf[3].p;
+  ddst.data = c.buf[4].p;
+  if ((st = generate_core(1, &dsdr, &dhdr, hdr_tf, md, &ddst, sdr_is_601, c.stream))) return st;
+  void* out = own_alloc ? malloc(mbytes ? mbytes : 1) : map_buf;
+  if (!out) return UHDRB200_ERROR_INSUFFICIENT_RESOURCE;
+  cudaError_t e = mbytes ? cudaMemcpyAsync(out, c.buf[4].p, mbytes, cudaMemcpyDeviceToHost, c.stream) : cudaSuccess;
+  if (e == cudaSuccess) e = cudaStreamSynchronize(c.stream);
+  if (e != cudaSuccess) {
+    if (own_alloc) free(out);
+    return fail(e, "generateGainMap device->host");
+  }
+  fill_map_desc(dest, mw, mh);
+  dest->data = out;
+  return UHDRB200_NO_ERROR;
+}
+
+size_t out_bpp(int fmt) {
+  switch (fmt) {
+    case UHDRB200_OUTPUT_HDR_LINEAR: return 8;
+    case UHDRB200_OUTPUT_HDR_PQ:
+    case UHDRB200_OUTPUT_HDR_HLG: return 4;
+    case UHDRB200_OUTPUT_HDR_LINEAR_RGB_10BIT: return 6;
+    default: return 0;
+  }
+}
+
+int apply_host(const uhdrb200_image* sdr, const uhdrb200_image* map, const uhdrb200_metadata* md, int fmt,
+               float max_display_boost, uhdrb200_image* dest) {
+  int st = validate_apply(sdr, map, md, dest);
+  if (st) return st;
+  const size_t obytes = sdr->width * sdr->height * out_bpp(fmt);
+  if (obytes == 0) {  // unknown format: reference sets the dims and writes nothing (ultrahdr.cpp:411-413, 491-493)
+    dest->width = sdr->width; dest->height = sdr->height; dest->colorGamut = sdr->colorGamut;
+    return UHDRB200_NO_ERROR;
+  }
+  if (!dest->data) return UHDRB200_ERROR_BAD_PTR;
+  if ((st = ensure_ctx())) return st;
+  Ctx& c = t_ctx;
+  if ((st = upload(c.buf[0], sdr->data, yuv420_luma_bytes(*sdr), c.stream))) return st;
+  if ((st = upload(c.buf[1], sdr->chroma_data, yuv420_chroma_bytes(*sdr), c.stream))) return st;
+  if ((st = upload(c.buf[5], map->data, map->width * map->height, c.stream))) return st;
+  if ((st = reserve(c.buf[4], obytes))) return st;
+  uhdrb200_image dsdr = *sdr, dmap = *map, ddst = *dest;
+  dsdr.data = c.buf[0].p; dsdr.chroma_data = c.buf[1].p;
+  dmap.data = c.buf[5].p;
+  ddst.data = c.buf[4].p;
+  if ((st = apply_core(1, &dsdr, &dmap, md, fmt, max_display_boost, &ddst, c.stream))) return st;
+  CU(cudaMemcpyAsync(dest->data, c.buf[4].p, obytes, cudaMemcpyDeviceToHost, c.stream));
+  CU(cudaStreamSynchronize(c.stream));
+  dest->width = sdr->width; dest->height = sdr->height; dest->colorGamut = sdr->colorGamut;
+  return UHDRB200_NO_ERROR;
+}
+
+int tonemap_host(const uhdrb200_image* src, uhdrb200_image* dest) {
+  int st = validate_tonemap(src, dest);
+  if (st) return st;
+  if ((st = ensure_ctx())) return st;
+  Ctx& c = t_ctx;
+  uhdrb200_image s2 = *src;  // toneMap reads luma_stride as given (no 0 -> width fallback, ultrahdr.cpp:527)
+  const size_t ly = src->height ? 2 * (src->luma_stride * (src->height - 1) + src->width) : 0;
+  const size_t dl = dest->luma_stride * dest->height;               // rows are written out to the stride
+  const size_t dc = 2 * (dest->chroma_stride * (dest->height / 2));  // U rows then V rows
+  if ((st = upload(c.buf[2], src->data, ly, c.stream))) return st;
+  if ((st = upload(c.buf[3], src->chroma_data, p010_chroma_bytes(*src), c.stream))) return st;
+  if ((st = reserve(c.buf[6], dl ? dl : 1)) || (st = reserve(c.buf[7], dc ? dc : 1))) return st;
+  uhdrb200_image dd = *dest;
+  s2.data = c.buf[2].p; s2.chroma_data = c.buf[3].p;
+  dd.data = c.buf[6].p; dd.chroma_data = c.buf[7].p;
+  if ((st = tonemap_core(1, &s2, &dd, c.stream))) return st;
+  // stride tails of the last rows are part of the reference's writes (memset to the stride)
+  if (dl) CU(cudaMemcpyAsync(dest->data, c.buf[6].p, dl, cudaMemcpyDeviceToHost, c.stream));
+  if (dc) CU(cudaMemcpyAsync(dest->chroma_data, c.buf[7].p, dc, cudaMemcpyDeviceToHost, c.stream));
+  CU(cudaStreamSynchronize(c.stream));
+  dest->colorGamut = src->colorGamut;
+  return UHDRB200_NO_ERROR;
+}
+
+int convert_yuv_host(uhdrb200_image* im, int src_enc, int dst_enc) {
+  if (!im) return UHDRB200_ERROR_BAD_PTR;
+  if (src_enc == UHDRB200_COLORGAMUT_UNSPECIFIED || dst_enc == UHDRB200_COLORGAMUT_UNSPECIFIED)
+    return UHDRB200_ERROR_INVALID_COLORGAMUT;
+  if (src_enc < 0 || src_enc > 2 || dst_enc < 0 || dst_enc > 2) return UHDRB200_ERROR_INVALID_COLORGAMUT;
+  if (src_enc == dst_enc) return UHDRB200_NO_ERROR;
+  if (!im->data || !im->chroma_data) return UHDRB200_ERROR_BAD_PTR;
+  int st = ensure_ctx();
+  if (st) return st;
+  Ctx& c = t_ctx;
+  const size_t lb = yuv420_luma_bytes(*im), cb = yuv420_chroma_bytes(*im);
+  if ((st = upload(c.buf[0], im->data, lb, c.stream))) return st;
+  if ((st = upload(c.buf[1], im->chroma_data, cb, c.stream))) return st;
+  uhdrb200_image d = *im;
+  d.data = c.buf[0].p; d.chroma_data = c.buf[1].p;
+  if ((st = convert_yuv_core(&d, src_enc, dst_enc, c.stream))) return st;
+  if (lb) CU(cudaMemcpyAsync(im->data, c.buf[0].p, lb, cudaMemcpyDeviceToHost, c.stream));
+  if (cb) CU(cudaMemcpyAsync(im->chroma_data, c.buf[1].p, cb, cudaMemcpyDeviceToHost, c.stream));
+  CU(cudaStreamSynchronize(c.stream));
+  return UHDRB200_NO_ERROR;
+}
+
+}  // namespace
+
+// ================================================================ extern "C"
+extern "C" {
+
+int uhdrb200_abi_version(void) { return UHDRB200_ABI_VERSION; }
+int uhdrb200_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+  return n;
+}
+int uhdrb200_init(int device) {
+  Ctx& c = t_ctx;
+  if (c.ready && c.device != device) {  // rebind: drop the old stream, keep it simple
+    cudaSetDevice(c.device);
+    for (auto& b : c.buf) { if (b.p) cudaFree(b.p); b = DevBuf(); }
+    if (c.stream) cudaStreamDestroy(c.stream);
+    c.stream = nullptr;
+    c.ready = false;
+  }
+  c.device = device;
+  return ensure_ctx();
+}
+void uhdrb200_shutdown(void) {
+  Ctx& c = t_ctx;
+  if (!c.ready) return;
+  cudaSetDevice(c.device);
+  cudaStreamSynchronize(c.stream);
+  for (auto& b : c.buf) { if (b.p) cudaFree(b.p); b = DevBuf(); }
+  for (auto& s : c.ring) {
+    if (s.host) cudaFreeHost(s.host);
+    if (s.dev) cudaFree(s.dev);
+    if (s.done) cudaEventDestroy(s.done);
+    s = BatchSlot();
+  }
+  cudaStreamDestroy(c.stream);
+  c.stream = nullptr;
+  c.ready = false;
+}
+const char* uhdrb200_last_error(void) { return t_ctx.err.c_str(); }
+void* uhdrb200_host_alloc(size_t bytes) {
+  void* p = nullptr;
+  if (ensure_ctx()) return nullptr;
+  if (cudaHostAlloc(&p, bytes, cudaHostAllocDefault) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+  return p;
+}
+void uhdrb200_host_free(void* p) { if (p) cudaFreeHost(p); }
+void uhdrb200_free(void* p) { free(p); }
+uint64_t uhdrb200_launch_count(void) { return g_launches.load(); }
+
+int uhdrb200_generate_gainmap_host(const uhdrb200_image* yuv420, const uhdrb200_image* p010, int hdr_tf,
+                                   uhdrb200_metadata* metadata, uhdrb200_image* dest, int sdr_is_601) {
+  return generate_host(yuv420, p010, hdr_tf, metadata, dest, sdr_is_601, nullptr, 0, true);
+}
+int uhdrb200_generate_gainmap_host_into(const uhdrb200_image* yuv420, const uhdrb200_image* p010, int hdr_tf,
+                                        uhdrb200_metadata* metadata, uhdrb200_image* dest, int sdr_is_601,
+                                        void* map_buf, size_t map_buf_bytes) {
+  return generate_host(yuv420, p010, hdr_tf, metadata, dest, sdr_is_601, map_buf, map_buf_bytes, false);
+}
+int uhdrb200_generate_gainmap_dev(const uhdrb200_image* yuv420, const uhdrb200_image* p010, int hdr_tf,
+                                  uhdrb200_metadata* metadata, uhdrb200_image* dest, int sdr_is_601, void* stream) {
+  return generate_core(1, yuv420, p010, hdr_tf, metadata, dest, sdr_is_601, (cudaStream_t)stream);
+}
+int uhdrb200_generate_gainmap_batch_dev(int n, const uhdrb200_image* yuv420, const uhdrb200_image* p010, int hdr_tf,
+                                        uhdrb200_metadata* metadata, uhdrb200_image* dest, int sdr_is_601,
+                                        void* stream) {
+  return generate_core(n, yuv420, p010, hdr_tf, metadata, dest, sdr_is_601, (cudaStream_t)stream);
+}
+int uhdrb200_apply_gainmap_host(const uhdrb200_image* yuv420, const uhdrb200_image* gainmap,
+                                const uhdrb200_metadata* metadata, int output_format, float max_display_boost,
+                                uhdrb200_image* dest) {
+  return apply_host(yuv420, gainmap, metadata, output_format, max_display_boost, dest);
+}
+int uhdrb200_apply_gainmap_dev(const uhdrb200_image* yuv420, const uhdrb200_image* gainmap,
+                               const uhdrb200_metadata* metadata, int output_format, float max_display_boost,
+                               uhdrb200_image* dest, void* stream) {
+  return apply_core(1, yuv420, gainmap, metadata, output_format, max_display_boost, dest, (cudaStream_t)stream);
+}
+int uhdrb200_apply_gainmap_batch_dev(int n, const uhdrb200_image* yuv420, const uhdrb200_image* gainmap,
+                                     const uhdrb200_metadata* metadata, int output_format, float max_display_boost,
+                                     uhdrb200_image* dest, void* stream) {
+  return apply_core(n, yuv420, gainmap, metadata, output_format, max_display_boost, dest, (cudaStream_t)stream);
+}
+int uhdrb200_tonemap_host(const uhdrb200_image* src, uhdrb200_image* dest) { return tonemap_host(src, dest); }
+int uhdrb200_tonemap_dev(const uhdrb200_image* src, uhdrb200_image* dest, void* stream) {
+  return tonemap_core(1, src, dest, (cudaStream_t)stream);
+}
+int uhdrb200_tonemap_batch_dev(int n, const uhdrb200_image* src, uhdrb200_image* dest, void* stream) {
+  return tonemap_core(n, src, dest, (cudaStream_t)stream);
+}
+int uhdrb200_convert_yuv_host(uhdrb200_image* image, int src_encoding, int dest_encoding) {
+  return convert_yuv_host(image, src_encoding, dest_encoding);
+}
+int uhdrb200_convert_yuv_dev(uhdrb200_image* image, int src_encoding, int dest_encoding, void* stream) {
+  return convert_yuv_core(image, src_encoding, dest_encoding, (cudaStream_t)stream);
+}
+
+}  // extern "C"

@@ -1,0 +1,106 @@
+// convert_yuv.cu — N1: JpegR::convertYuv (reference lib/src/jpegr.cpp:1132-1206) +
+// transformYuv420 (lib/src/gainmapmath.cpp:483-520) on sm_100a: in-place re-encode of a YUV420
+// image between the BT.709 / BT.601 / BT.2100 YUV matrices, per 2x2 quad: each of the 4 pixels is
+// transformed with the quad's (U,V), luma is written back rounded (+0.5, clip), chroma gets the
+// average of the 4 transformed (U,V).
+//
+// One thread = two horizontally adjacent quads (4 px x 2 rows): 32-bit luma loads/stores, 16-bit
+// chroma loads/stores. In place, so plain (coherent) loads; every byte is read and written by the
+// same thread only. HBM-bound: 1.5 B/px read + 1.5 B/px written.
+#include "uhdr_kernels.cuh"
+#include "uhdr_math.cuh"
+
+namespace uhdr {
+namespace {
+
+__device__ __forceinline__ uint32_t to_u8(float v) {  // static_cast<uint8_t>(CLIP3(v, 0, 255))
+  v = v < 0.0f ? 0.0f : (v > 255.0f ? 255.0f : v);
+  return __float2uint_rz(v);
+}
+
+struct Quad { uint32_t y[2][2]; uint32_t u, v; };
+
+__device__ __forceinline__ void transform_quad(const float* m, Quad& q) {
+  const float uf = (float)((int)q.u - 128) * (1 / 255.0f), vf = (float)((int)q.v - 128) * (1 / 255.0f);
+  float su = 0.f, sv = 0.f;
+  bool first = true;
+#pragma unroll
+  for (int r = 0; r < 2; r++)
+#pragma unroll
+    for (int c = 0; c < 2; c++) {  // order yuv1..yuv4 = (0,0),(1,0),(0,1),(1,1) in (x,y): gainmapmath.cpp:485-488
+      const float yf = (float)q.y[r][c] * (1 / 255.0f);
+      const float ny = m[0] * yf + m[1] * uf + m[2] * vf;
+      const float nu = m[3] * yf + m[4] * uf + m[5] * vf;
+      const float nv = m[6] * yf + m[7] * uf + m[8] * vf;
+      if (first) { su = nu; sv = nv; first = false; } else { su += nu; sv += nv; }
+      q.y[r][c] = to_u8(ny * 255.0f + 0.5f);
+    }
+  q.u = to_u8(su / 4.0f * 255.0f + 128.0f + 0.5f);
+  q.v = to_u8(sv / 4.0f * 255.0f + 128.0f + 0.5f);
+}
+
+template <bool VEC>
+__global__ void __launch_bounds__(256) convert_yuv_kernel(ConvertYuvParams p) {
+  const Geometry& g = p.g;
+  const int x0 = (blockIdx.x * 32 + threadIdx.x) * 4;
+  const int y0 = (blockIdx.y * 8 + threadIdx.y) * 2;
+  const int cw = g.width / 2, ch = g.height / 2;
+  if ((x0 >> 1) >= cw || (y0 >> 1) >= ch) return;
+  const Planes pl = p.batch ? p.batch[blockIdx.z] : p.single;
+  uint8_t* yp = (uint8_t*)pl.sdr_y + (size_t)y0 * g.sdr_luma_stride + x0;
+  uint8_t* up = (uint8_t*)pl.sdr_u + (size_t)(y0 >> 1) * g.sdr_chroma_stride + (x0 >> 1);
+  uint8_t* vp = (uint8_t*)pl.sdr_v + (size_t)(y0 >> 1) * g.sdr_chroma_stride + (x0 >> 1);
+  const int nq = VEC ? 2 : min(2, cw - (x0 >> 1));
+  Quad q[2];
+  if (VEC) {
+    uint32_t a = *reinterpret_cast<uint32_t*>(yp), b = *reinterpret_cast<uint32_t*>(yp + g.sdr_luma_stride);
+    uint32_t c = *reinterpret_cast<uint16_t*>(up), d = *reinterpret_cast<uint16_t*>(vp);
+#pragma unroll
+    for (int k = 0; k < 2; k++) {
+      q[k].y[0][0] = (a >> (16 * k)) & 0xff; q[k].y[0][1] = (a >> (16 * k + 8)) & 0xff;
+      q[k].y[1][0] = (b >> (16 * k)) & 0xff; q[k].y[1][1] = (b >> (16 * k + 8)) & 0xff;
+      q[k].u = (c >> (8 * k)) & 0xff; q[k].v = (d >> (8 * k)) & 0xff;
+    }
+  } else {
+    for (int k = 0; k < nq; k++) {
+      for (int r = 0; r < 2; r++)
+        for (int c = 0; c < 2; c++) q[k].y[r][c] = yp[(size_t)r * g.sdr_luma_stride + 2 * k + c];
+      q[k].u = up[k]; q[k].v = vp[k];
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < 2; k++) if (k < nq) transform_quad(p.m, q[k]);
+  if (VEC) {
+    uint32_t a = q[0].y[0][0] | (q[0].y[0][1] << 8) | (q[1].y[0][0] << 16) | (q[1].y[0][1] << 24);
+    uint32_t b = q[0].y[1][0] | (q[0].y[1][1] << 8) | (q[1].y[1][0] << 16) | (q[1].y[1][1] << 24);
+    *reinterpret_cast<uint32_t*>(yp) = a;
+    *reinterpret_cast<uint32_t*>(yp + g.sdr_luma_stride) = b;
+    *reinterpret_cast<uint16_t*>(up) = (uint16_t)(q[0].u | (q[1].u << 8));
+    *reinterpret_cast<uint16_t*>(vp) = (uint16_t)(q[0].v | (q[1].v << 8));
+  } else {
+    for (int k = 0; k < nq; k++) {
+      for (int r = 0; r < 2; r++)
+        for (int c = 0; c < 2; c++) yp[(size_t)r * g.sdr_luma_stride + 2 * k + c] = (uint8_t)q[k].y[r][c];
+      up[k] = (uint8_t)q[k].u; vp[k] = (uint8_t)q[k].v;
+    }
+  }
+}
+
+bool aligned(const void* q, size_t a) { return (reinterpret_cast<uintptr_t>(q) & (a - 1)) == 0; }
+}  // namespace
+
+bool convert_yuv_vec_ok(const Geometry& g, const Planes& pl) {
+  return g.width % 4 == 0 && aligned(pl.sdr_y, 4) && aligned(pl.sdr_u, 2) && aligned(pl.sdr_v, 2) &&
+         g.sdr_luma_stride % 4 == 0 && g.sdr_chroma_stride % 2 == 0;
+}
+
+cudaError_t launch_convert_yuv_impl(const ConvertYuvParams& p, int n, bool vec, cudaStream_t s) {
+  if (p.g.width < 2 || p.g.height < 2 || n == 0) return cudaSuccess;
+  dim3 block(32, 8, 1);
+  dim3 grid((p.g.width + 127) / 128, (p.g.height + 15) / 16, n);
+  if (vec) convert_yuv_kernel<true><<<grid, block, 0, s>>>(p);
+  else convert_yuv_kernel<false><<<grid, block, 0, s>>>(p);
+  return cudaGetLastError();
+}
+
+}  // namespace uhdr
