@@ -1,0 +1,375 @@
+#!/usr/bin/env python
+"""bench.py — gain-map hot path throughput on B200 (BASELINE.json metric: "Gain-map generate/apply
+Mpix/s (4K, 1-8 B200) and % of HBM BW peak").
+
+A step = one pass of the hot path over one batch of synthetic 4K image pairs on every GPU:
+generateGainMap (P010 HLG BT.2100 + YUV420 BT.709 -> u8 map) followed by applyGainMap (YUV420 +
+that map -> RGBA1010102 HLG, max_display_boost = FLT_MAX), i.e. BASELINE config 5 (whose
+single-image form is configs 1-2 at 3840x2160). Images are independent, so N GPUs = N ranks, each
+with its own batch, no collective on the data path (weak scaling).
+
+  value      whole-job Mpix/s (full-resolution pixels through generate+apply), inputs resident
+             in HBM, CUDA events on the launch stream, max over ranks.
+  e2e        the same metric through the host-pointer C ABI (what the reference-side shim calls):
+             pinned HOST planes in, host map + host RGBA1010102 out, copies inside the timing.
+  roofline   the dominant kernel (apply: 5.5625 algorithmic B/px) against MEASURED_PEAKS.json.
+  cpu_baseline  the reference's own CPU code (oracle/_ref, built from /root/reference by
+             oracle/Makefile) on this box's host cores, bounded sample. Checker-side only.
+
+`--impl reference` times that CPU code alone (rank 0 only) on the same config/metric.
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+W, H = 3840, 2160
+MW, MH = W // 4, H // 4
+PIX = W * H
+FLT_MAX = 3.4028234663852886e38
+GEN_BPP = 4.5625    # P010 3 B + 420 1.5 B read, 1/16 B written
+APPLY_BPP = 5.5625  # 420 1.5 B + map 1/16 B read, RGBA1010102 4 B written
+METRIC = "gain-map generate+apply throughput (4K)"
+UNIT = "Mpix/s"
+
+
+def host_cores():
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+# ------------------------------------------------------------------------------------ CPU arms
+def cpu_worker(n_images, seed, tag):
+    """Child process: the reference CPU path (<=4 threads, ultrahdr.cpp:304,500) over n_images
+    4K pairs: generate (HLG, 2100->709) + apply -> RGBA1010102 HLG. Prints elapsed seconds."""
+    import numpy as np
+
+    from libultrahdr_dev_b200 import abi, synth
+    from oracle.pyoracle import CpuImpl
+
+    impl = CpuImpl.reference() if tag == "reference" else CpuImpl.oracle()
+    sdr_b, hdr_b = synth.uniform_pair(W, H, seed)
+    sdr = abi.host_yuv420(sdr_b, W, H, abi.COLORGAMUT_BT709)
+    hdr = abi.host_p010(hdr_b, W, H, abi.COLORGAMUT_BT2100)
+    sys.stdout.write("ready\n")
+    sys.stdout.flush()
+    sys.stdin.readline()
+    t0 = time.perf_counter()
+    for _ in range(n_images):
+        st, mp, md, _ = impl.generate_gainmap(sdr, hdr, abi.TF_HLG)
+        assert st == 0
+        st, out, _ = impl.apply_gainmap(sdr, abi.host_map(mp, MW, MH), md, abi.OUTPUT_HDR_HLG, FLT_MAX)
+        assert st == 0
+    sys.stdout.write(json.dumps({"s": time.perf_counter() - t0, "sum": int(out[:4096].sum())}) + "\n")
+    sys.stdout.flush()
+
+
+def cpu_arm(images_per_worker, workers=None):
+    """Runs `workers` concurrent reference processes; returns (Mpix/s, info dict)."""
+    from oracle.pyoracle import CpuImpl
+
+    tag = "reference" if CpuImpl.have_reference() else "port"
+    cores = host_cores()
+    threads_per = min(cores, 4) if tag == "reference" else 1
+    if workers is None:
+        workers = max(1, cores // threads_per)
+    procs = [subprocess.Popen([sys.executable, os.path.abspath(__file__), "--cpu-worker", str(images_per_worker),
+                               str(0xB200 + i), tag], stdin=subprocess.PIPE, stdout=subprocess.PIPE, text=True, cwd=ROOT)
+             for i in range(workers)]
+    for p in procs:
+        assert p.stdout.readline().strip() == "ready"
+    t0 = time.perf_counter()
+    for p in procs:
+        p.stdin.write("go\n")
+        p.stdin.flush()
+    for p in procs:
+        json.loads(p.stdout.readline())
+    dt = time.perf_counter() - t0
+    for p in procs:
+        p.wait()
+    n = workers * images_per_worker
+    return n * PIX / dt / 1e6, {
+        "kind": tag, "cores": workers * threads_per, "host_cores": cores,
+        "sample": f"{n} synthetic 3840x2160 pairs (generate HLG 2100->709 + apply->RGBA1010102 HLG), "
+                  f"{workers} concurrent processes x {threads_per} threads (reference caps a call at 4 threads), {dt:.1f} s",
+        "seconds": dt, "images": n}
+
+
+# ------------------------------------------------------------------------------------ clocks
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.rows, self.proc = [], None
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.th = threading.Thread(target=self._read, daemon=True)
+            self.th.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append((time.perf_counter(), [c.strip() for c in line.split(",")]))
+
+    def window(self, t0, t1):
+        rows = [r for t, r in self.rows if t0 <= t <= t1] or [r for _, r in self.rows[-3:]]
+        sm = sorted(float(r[0]) for r in rows if r and r[0].replace(".", "").isdigit())
+        reasons = set()
+        for r in rows:
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        mx = [float(r[1]) for r in rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx[0] if mx else None,
+                "reasons": sorted(reasons), "samples": len(rows)}
+
+    def stop(self):
+        if self.proc:
+            self.proc.terminate()
+
+
+# ------------------------------------------------------------------------------------ GPU arm
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--batch", type=int, default=256, help="4K pairs per step per GPU (device-resident)")
+    ap.add_argument("--e2e-images", type=int, default=16, help="4K pairs per e2e step per GPU (host planes)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-images", type=int, default=2, help="images per CPU worker process in the CPU arms")
+    ap.add_argument("--cpu-worker", nargs=3, metavar=("N", "SEED", "TAG"))
+    a = ap.parse_args()
+    if a.cpu_worker:
+        return cpu_worker(int(a.cpu_worker[0]), int(a.cpu_worker[1]), a.cpu_worker[2])
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    config = {"workload": "BASELINE config 5 flavour: batch of synthetic 3840x2160 P010(HLG,BT.2100)+YUV420(BT.709) pairs, "
+                          "generateGainMap then applyGainMap->RGBA1010102 HLG (max_display_boost=FLT_MAX), image-sharded",
+              "width": W, "height": H, "map_scale": 4, "images_per_step_per_gpu": a.batch,
+              "l2": "inputs+outputs per step >> 126 MB L2 (no flush needed)", "mode": "analytic (reference as built)"}
+
+    if a.impl == "reference":
+        if rank != 0:
+            return
+        steps = max(1, a.steps)
+        vals = []
+        for _ in range(a.warmup and 1):
+            cpu_arm(1)
+        info = None
+        t_all = 0.0
+        n_all = 0
+        for _ in range(steps):
+            v, info = cpu_arm(a.cpu_images)
+            vals.append(v)
+            t_all += info["seconds"]
+            n_all += info["images"]
+            if t_all > 150:
+                break
+        value = n_all * PIX / t_all / 1e6
+        info.update(value=value, unit=UNIT)
+        print(json.dumps({"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": a.gpus,
+                          "steps": len(vals), "warmup": 1 if a.warmup else 0, "ms_per_step": 1e3 * t_all / len(vals),
+                          "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+                          "data": "synthetic", "config": config, "cpu_baseline": info, "gpu_launches": 0,
+                          "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+        return
+
+    import numpy as np
+    import torch
+
+    from libultrahdr_dev_b200 import abi, api, synth
+
+    lib = api.load_library()  # raises when the CUDA library is missing: no CPU fallback
+    if not torch.cuda.is_available() or lib.uhdrb200_device_count() < 1:
+        raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback")
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    dev = torch.device("cuda", local)
+    uh = api.JpegR(lib)
+    assert lib.uhdrb200_init(local) == 0, lib.uhdrb200_last_error()
+
+    # ---- CPU baseline first (rank 0, N=1 only), before the GPU is busy
+    cpu_info = None
+    if world == 1 and not a.no_cpu_baseline:
+        v, cpu_info = cpu_arm(a.cpu_images)
+        cpu_info.update(value=v, unit=UNIT)
+
+    # ---- synthetic inputs: K distinct natural pairs, replicated into B device slots
+    B, K = a.batch, 4
+    pairs = [synth.natural_pair(W, H, rank * K + i, abi.TF_HLG, abi.COLORGAMUT_BT709, abi.COLORGAMUT_BT2100) for i in range(K)]
+    sdr_len, hdr_len = abi.yuv420_size(W, H), abi.p010_size(W, H)
+    d_sdr = torch.empty((B, sdr_len), dtype=torch.uint8, device=dev)
+    d_hdr = torch.empty((B, hdr_len), dtype=torch.int16, device=dev)
+    d_map = torch.zeros((B, MW * MH), dtype=torch.uint8, device=dev)
+    d_out = torch.zeros((B, PIX), dtype=torch.int32, device=dev)
+    for i in range(K):
+        s = torch.from_numpy(pairs[i][0]).to(dev)
+        h = torch.from_numpy(pairs[i][1].view(np.int16)).to(dev)
+        d_sdr[i::K] = s
+        d_hdr[i::K] = h
+    torch.cuda.synchronize()
+
+    Img = abi.Image * B
+    sdrs, hdrs, maps, outs = Img(), Img(), Img(), Img()
+    mds = (abi.Metadata * B)()
+    for i in range(B):
+        for arr, base, fmt, gam in ((sdrs, d_sdr[i].data_ptr(), abi.PIX_FMT_YUV420, abi.COLORGAMUT_BT709),):
+            arr[i].data, arr[i].chroma_data = base, base + W * H
+            arr[i].width, arr[i].height, arr[i].colorGamut = W, H, gam
+            arr[i].luma_stride, arr[i].chroma_stride, arr[i].pixelFormat = W, W // 2, fmt
+        hb = d_hdr[i].data_ptr()
+        hdrs[i].data, hdrs[i].chroma_data = hb, hb + 2 * W * H
+        hdrs[i].width, hdrs[i].height, hdrs[i].colorGamut = W, H, abi.COLORGAMUT_BT2100
+        hdrs[i].luma_stride, hdrs[i].chroma_stride, hdrs[i].pixelFormat = W, W, abi.PIX_FMT_P010
+        maps[i].data = d_map[i].data_ptr()
+        maps[i].width, maps[i].height, maps[i].luma_stride = MW, MH, MW
+        maps[i].pixelFormat = abi.PIX_FMT_MONOCHROME
+        outs[i].data = d_out[i].data_ptr()
+    md = abi.default_metadata(1000.0 / 203.0)
+    stream = torch.cuda.current_stream().cuda_stream
+
+    def step():
+        assert uh.generateGainMapBatch(B, sdrs, hdrs, abi.TF_HLG, mds, maps, False, stream) == 0
+        assert uh.applyGainMapBatch(B, sdrs, maps, md, abi.OUTPUT_HDR_HLG, FLT_MAX, outs, stream) == 0
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(a.warmup, 3)):
+        step()
+    barrier()
+    clocks = ClockSampler(local) if rank == 0 else None
+    time.sleep(0.25)
+    n0 = lib.uhdrb200_launch_count()
+    ev = [[torch.cuda.Event(enable_timing=True) for _ in range(3)] for _ in range(a.steps)]
+    barrier()
+    t0 = time.perf_counter()
+    for k in range(a.steps):
+        ev[k][0].record()
+        assert uh.generateGainMapBatch(B, sdrs, hdrs, abi.TF_HLG, mds, maps, False, stream) == 0
+        ev[k][1].record()
+        assert uh.applyGainMapBatch(B, sdrs, maps, md, abi.OUTPUT_HDR_HLG, FLT_MAX, outs, stream) == 0
+        ev[k][2].record()
+    barrier()
+    t1 = time.perf_counter()
+    launches = lib.uhdrb200_launch_count() - n0
+    total_ms = ev[0][0].elapsed_time(ev[-1][2])
+    gen_ms = sum(e[0].elapsed_time(e[1]) for e in ev) / a.steps
+    app_ms = sum(e[1].elapsed_time(e[2]) for e in ev) / a.steps
+    clk = clocks.window(t0, t1) if clocks else None
+
+    # ---- e2e: host planes -> C ABI host entry points -> host results (copies inside the timing)
+    E = a.e2e_images
+    KH = 4
+    host_bufs = []
+    for i in range(KH):
+        ps = lib.uhdrb200_host_alloc(sdr_len)
+        ph = lib.uhdrb200_host_alloc(hdr_len * 2)
+        po = lib.uhdrb200_host_alloc(PIX * 4)
+        pm = lib.uhdrb200_host_alloc(MW * MH)
+        assert ps and ph and po and pm, "pinned allocation failed"
+        C.memmove(ps, pairs[i % K][0].ctypes.data, sdr_len)
+        C.memmove(ph, pairs[i % K][1].ctypes.data, hdr_len * 2)
+        s_img, h_img, m_img, o_img = abi.Image(), abi.Image(), abi.Image(), abi.Image()
+        s_img.data, s_img.chroma_data = ps, ps + W * H
+        s_img.width, s_img.height, s_img.colorGamut = W, H, abi.COLORGAMUT_BT709
+        s_img.luma_stride, s_img.chroma_stride, s_img.pixelFormat = W, W // 2, abi.PIX_FMT_YUV420
+        h_img.data, h_img.chroma_data = ph, ph + 2 * W * H
+        h_img.width, h_img.height, h_img.colorGamut = W, H, abi.COLORGAMUT_BT2100
+        h_img.luma_stride, h_img.chroma_stride, h_img.pixelFormat = W, W, abi.PIX_FMT_P010
+        o_img.data = po
+        host_bufs.append((s_img, h_img, m_img, o_img, pm))
+
+    def e2e_step():
+        for i in range(E):
+            s_img, h_img, m_img, o_img, pm = host_bufs[i % KH]
+            mdh = abi.Metadata()
+            st = lib.uhdrb200_generate_gainmap_host_into(C.byref(s_img), C.byref(h_img), abi.TF_HLG, C.byref(mdh),
+                                                         C.byref(m_img), 0, pm, MW * MH)
+            assert st == 0, lib.uhdrb200_last_error()
+            st = lib.uhdrb200_apply_gainmap_host(C.byref(s_img), C.byref(m_img), C.byref(mdh), abi.OUTPUT_HDR_HLG,
+                                                 FLT_MAX, C.byref(o_img))
+            assert st == 0, lib.uhdrb200_last_error()
+
+    e2e_steps = max(2, min(a.steps, 5))
+    e2e_step()
+    barrier()
+    te0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        e2e_step()
+    barrier()
+    e2e_s = time.perf_counter() - te0
+    h2d = E * (sdr_len + hdr_len * 2 + sdr_len + MW * MH)  # generate: SDR+HDR planes; apply: SDR planes + map
+    d2h = E * (MW * MH + PIX * 4)
+
+    times = torch.tensor([total_ms, e2e_s * 1e3, gen_ms, app_ms], dtype=torch.float64, device=dev)
+    if dist is not None:
+        dist.all_reduce(times, op=dist.ReduceOp.MAX)
+    total_ms, e2e_ms, gen_ms, app_ms = [float(x) for x in times.tolist()]
+    if clocks:
+        clocks.stop()
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+    if rank != 0:
+        return
+
+    peaks, peak_src = None, "fallback (B200_PROFILING.md)"
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            peaks = json.load(f)
+        peak, peak_src = float(peaks["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except (OSError, KeyError, ValueError):
+        peak = 6650.0
+    app_gbs = B * PIX * APPLY_BPP / (app_ms * 1e-3) / 1e9
+    gen_gbs = B * PIX * GEN_BPP / (gen_ms * 1e-3) / 1e9
+    value = world * B * PIX * a.steps / (total_ms * 1e-3) / 1e6
+    out = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3),
+        "ms_per_step": total_ms / a.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": f"synthetic ({K} distinct seeded natural pairs per rank replicated into {B} device slots)",
+        "config": config,
+        "roofline": {"bound": "hbm", "kernel": "apply_kernel (applyGainMap -> RGBA1010102 HLG)", "achieved": app_gbs,
+                     "peak": peak, "unit": "GB/s", "frac": app_gbs / peak, "traffic": None, "peak_source": peak_src,
+                     "ms_per_launch": app_ms, "algorithmic_bytes_per_launch": B * PIX * APPLY_BPP},
+        "roofline_generate": {"bound": "hbm", "kernel": "generate_kernel", "achieved": gen_gbs, "peak": peak,
+                              "unit": "GB/s", "frac": gen_gbs / peak, "ms_per_launch": gen_ms,
+                              "algorithmic_bytes_per_launch": B * PIX * GEN_BPP},
+        "stage_mpix_s": {"generate": B * PIX / gen_ms / 1e3, "apply": B * PIX / app_ms / 1e3},
+        "e2e": {"value": world * E * PIX * e2e_steps / (e2e_ms * 1e-3) / 1e6, "unit": UNIT, "h2d_bytes_per_step": h2d,
+                "d2h_bytes_per_step": d2h, "images_per_step_per_gpu": E, "steps": e2e_steps,
+                "api": "uhdrb200_generate_gainmap_host_into + uhdrb200_apply_gainmap_host, pinned host planes"},
+        "gpu_launches": int(launches),
+        "clocks": clk,
+    }
+    if cpu_info:
+        out["cpu_baseline"] = cpu_info
+    print(json.dumps(out))
+
+
+if __name__ == "__main__":
+    main()
