@@ -138,6 +138,12 @@ void uhdrb200_free(void* p);
 /* number of kernel launches issued by this library in the calling process (monotonic). */
 uint64_t uhdrb200_launch_count(void);
 
+/* applyGainMap kernel selection (process-wide): AUTO uses the table-driven kernel whenever the
+ * layout allows it (map scale 4, 4-aligned planes) and the generic kernel otherwise; GENERIC forces
+ * the generic kernel (any integer scale factor, MUFU-evaluated transfer functions). */
+enum { UHDRB200_APPLY_AUTO = 0, UHDRB200_APPLY_GENERIC = 1 };
+int uhdrb200_set_apply_mode(int mode);
+
 /* ---- A1: UltraHdr::generateGainMap (ultrahdr.cpp:185-358) ---- */
 /* Host planes. On success dest->data is a malloc'ed map_w*map_h buffer owned by the caller
  * (release with uhdrb200_free); metadata is fully overwritten (ultrahdr.cpp:250-257). */

@@ -1,0 +1,249 @@
+// apply_fast.cu — A2 fast path: UltraHdr::applyGainMap (reference lib/src/ultrahdr.cpp:427-496) for
+// the layout every decode produces (map scale factor 4 = kMapDimensionScaleFactor, 4-aligned
+// planes), restructured so that it is bound by instruction issue / HBM instead of the SFU:
+//
+//   * one thread = one gain-map cell = 4x4 pixels: the four surrounding map samples, the 2x2
+//     chroma samples and the cell's plane pointers are fetched once per 16 pixels; luma comes in
+//     as four 32-bit loads (a warp reads 128 contiguous bytes per row) and the packed output
+//     leaves as 128-bit stores (a warp writes 512 contiguous bytes per row).
+//   * the Shepard-IDW weights of the interior table (gainmapmath.h:184-228) sit in the kernel
+//     parameter block, i.e. in the constant bank: with the 4x4 loop fully unrolled every weight
+//     is an immediate constant-bank operand of an FFMA. Cells on the right/bottom map border
+//     (tables NR/NB/C, gainmapmath.cpp:710-716) read their weights from global memory.
+//   * srgbInvOetf (3 pow per pixel in the reference) and hlgOetf/pqOetf (sqrt/log or 9 pow per
+//     pixel) are piecewise-linear tables in shared memory on log-spaced segments: the float's
+//     exponent/mantissa bits are the index, one 64-bit LDS + one FFMA per evaluation. The tables
+//     (built in double on the host, tables.cu) are staged with one TMA bulk copy per block and the
+//     blocks are persistent (grid = SMs x resident blocks, grid-stride over 128x32-pixel tiles).
+//   * the gain factor 2^(logBoost * displayBoost / maxContentBoost) / displayBoost
+//     (gainmapmath.cpp:550-555, ultrahdr.cpp:451) is one FFMA + one MUFU.EX2 per pixel.
+#include "uhdr_io.cuh"
+#include "uhdr_kernels.cuh"
+#include "uhdr_math.cuh"
+
+namespace uhdr {
+namespace {
+
+constexpr int kThreads = 256;
+constexpr int kTileCellsX = 32, kTileCellsY = 8;
+
+enum { kPack1010102 = 0, kPackF16 = 1, kPackPlanar10 = 2 };
+
+// value = a + b * x on the segment selected by the float's bits; `tab` is pre-biased by -base
+template <int SHIFT>
+__device__ __forceinline__ float seg_eval(const float2* __restrict__ tab, float x) {
+  const float2 ab = tab[__float_as_uint(x) >> SHIFT];
+  return fmaf(ab.y, x, ab.x);
+}
+
+__device__ __forceinline__ float ex2_fast(float x) {
+  float r;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+}
+
+// PACK selects the output packing; MASK (RGBA1010102 only) keeps the reference's `& 0x3ff` wrap for
+// codes above 1023, which can only occur when displayBoost < maxContentBoost.
+// The RGBA1010102 kernel holds its tables in STATIC shared memory (S 12 KB + O 28 KB + 1 KB) so
+// that a lookup address is `mask(bits >> n) + link-time constant` (no base-register add); the
+// linear-output kernels use a 4x finer S table (48 KB, dynamic shared memory) and no O table.
+template <int PACK, bool MASK>
+__global__ void __launch_bounds__(kThreads, 3) apply_fast_kernel(const __grid_constant__ ApplyFastParams p) {
+  constexpr bool kHasO = PACK == kPack1010102;
+  constexpr int kSB = kHasO ? kSBits : kSBitsHi;
+  constexpr int kSN = kHasO ? kSEntries : kSEntriesHi;
+  constexpr int kSBs = kHasO ? kSBase : kSBaseHi;
+  extern __shared__ __align__(16) uint8_t smem_dyn[];
+  __shared__ __align__(16) float2 sS_static[kHasO ? kSEntries : 1];
+  __shared__ __align__(16) float2 sO_static[kHasO ? kOEntries : 1];
+  __shared__ __align__(16) float sE[256];
+  __shared__ __align__(8) uint64_t bar;
+  float2* sS = kHasO ? sS_static : reinterpret_cast<float2*>(smem_dyn);
+  float2* sO = sO_static;
+  const int tid = threadIdx.x;
+
+  // ---- stage the tables: one elected thread issues the TMA bulk copies, everyone waits on the mbarrier
+  if (tid == 0) mbar_init(&bar, 1);
+  __syncthreads();
+  if (tid == 0) {
+    constexpr uint32_t sb = kSN * sizeof(float2), ob = kOEntries * sizeof(float2), eb = 256 * sizeof(float);
+    mbar_expect_tx(&bar, sb + eb + (kHasO ? ob : 0));
+    bulk_g2s(sS, kHasO ? p.tab.s : p.tab.s_hi, sb, &bar);
+    if (kHasO) bulk_g2s(sO, p.output_format == 3 ? p.tab.o_hlg : p.tab.o_pq, ob, &bar);
+    bulk_g2s(sE, p.tab.e255, eb, &bar);
+  }
+  mbar_wait(&bar, 0);
+  const float2* tS = sS - kSBs;    // index = bits >> (23 - kSB)
+  const float2* tO = sO - kOBase;  // index = bits >> (23 - kOBits)
+
+  const Geometry& g = p.g;
+  const int mw = g.map_width, mh = g.map_height;
+  const int tiles_per_image = p.tiles_x * p.tiles_y;
+  const float k601_cr = 1.402f, k601_cb = 1.772f;
+  const float k601_gcb = 0.114f * 1.772f / 0.587f, k601_gcr = 0.299f * 1.402f / 0.587f;  // gainmapmath.cpp:195-196
+  const float kT1 = (float)(1.0 / 1.055), kT0 = (float)(0.055 / 1.055);
+  const size_t npix = (size_t)g.width * g.height;
+
+  for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
+    const int z = tile / tiles_per_image;
+    const int rem = tile - z * tiles_per_image;
+    const int ty = rem / p.tiles_x, tx = rem - ty * p.tiles_x;
+    const int cx = tx * kTileCellsX + (tid & 31), cy = ty * kTileCellsY + (tid >> 5);
+    if (cx >= mw || cy >= mh) continue;
+    const Planes* pl = p.batch ? p.batch + z : &p.single;
+    const uint8_t* yp = (const uint8_t*)pl->sdr_y + (size_t)(4 * cy) * g.sdr_luma_stride + 4 * cx;
+    const uint8_t* up = (const uint8_t*)pl->sdr_u + (size_t)(2 * cy) * g.sdr_chroma_stride + 2 * cx;
+    const uint8_t* vp = (const uint8_t*)pl->sdr_v + (size_t)(2 * cy) * g.sdr_chroma_stride + 2 * cx;
+    const uint8_t* map = (const uint8_t*)pl->map_in;
+    uint8_t* outp = (uint8_t*)pl->out;
+
+    // ---- all global loads of the cell first
+    uint32_t yw[4], uw[2], vw[2];
+#pragma unroll
+    for (int r = 0; r < 4; r++) yw[r] = ldg4(yp + (size_t)r * g.sdr_luma_stride);
+#pragma unroll
+    for (int r = 0; r < 2; r++) {
+      uw[r] = ldg2(up + (size_t)r * g.sdr_chroma_stride);
+      vw[r] = ldg2(vp + (size_t)r * g.sdr_chroma_stride);
+    }
+    const int cxr = min(cx + 1, mw - 1), cyb = min(cy + 1, mh - 1);  // gainmapmath.cpp:690-697
+    const uint32_t b1 = __ldg(map + cx + cy * mw), b2 = __ldg(map + cx + cyb * mw);
+    const uint32_t b3 = __ldg(map + cxr + cy * mw), b4 = __ldg(map + cxr + cyb * mw);
+    const float e1 = sE[b1], e2 = sE[b2], e3 = sE[b3], e4 = sE[b4];  // e1=(xl,yl) e2=(xl,yu) e3=(xu,yl) e4=(xu,yu)
+
+    // ---- gain factor of the 16 pixels
+    float f[16];
+    if (cx + 1 < mw && cy + 1 < mh) {
+#pragma unroll
+      for (int i = 0; i < 16; i++) {
+        float gain = e1 * p.w[i][0];
+        gain = fmaf(e2, p.w[i][1], gain);
+        gain = fmaf(e3, p.w[i][2], gain);
+        gain = fmaf(e4, p.w[i][3], gain);
+        f[i] = ex2_fast(fmaf(gain, p.A, p.B));
+      }
+    } else {  // map border: tables NR (1), NB (2), C (3)
+      const int t = (cx + 1 < mw) ? 2 : ((cy + 1 < mh) ? 1 : 3);
+      const float4* wt = reinterpret_cast<const float4*>(p.idw) + t * 16;
+#pragma unroll
+      for (int i = 0; i < 16; i++) {
+        const float4 w = __ldg(wt + i);
+        float gain = e1 * w.x;
+        gain = fmaf(e2, w.y, gain);
+        gain = fmaf(e3, w.z, gain);
+        gain = fmaf(e4, w.w, gain);
+        f[i] = ex2_fast(fmaf(gain, p.A, p.B));
+      }
+    }
+
+    // ---- chroma terms of the four 2x2 quads: R = y + cr*v, G = y - gcb*u - gcr*v, B = y + cb*u (always BT.601, ultrahdr.cpp:430-431)
+    float rv[2][2], gq[2][2], bu[2][2];
+#pragma unroll
+    for (int r = 0; r < 2; r++)
+#pragma unroll
+      for (int c = 0; c < 2; c++) {
+        const float u = (float)((int)((uw[r] >> (8 * c)) & 0xff) - 128) * (1 / 255.0f);
+        const float v = (float)((int)((vw[r] >> (8 * c)) & 0xff) - 128) * (1 / 255.0f);
+        rv[r][c] = k601_cr * v;
+        gq[r][c] = -(k601_gcb * u + k601_gcr * v);
+        bu[r][c] = k601_cb * u;
+      }
+
+#pragma unroll
+    for (int r = 0; r < 4; r++) {
+      uint32_t px[4][3];  // 10-bit codes or half bits
+#pragma unroll
+      for (int i = 0; i < 4; i++) {
+        const float yf = (float)((yw[r] >> (8 * i)) & 0xff);
+        const float fi = f[r * 4 + i];
+        const float cR = __saturatef(fmaf(yf, 1 / 255.0f, rv[r >> 1][i >> 1]));
+        const float cG = __saturatef(fmaf(yf, 1 / 255.0f, gq[r >> 1][i >> 1]));
+        const float cB = __saturatef(fmaf(yf, 1 / 255.0f, bu[r >> 1][i >> 1]));
+        const float sR = seg_eval<23 - kSB>(tS, fmaf(cR, kT1, kT0));
+        const float sG = seg_eval<23 - kSB>(tS, fmaf(cG, kT1, kT0));
+        const float sB = seg_eval<23 - kSB>(tS, fmaf(cB, kT1, kT0));
+        if (PACK == kPack1010102) {
+          px[i][0] = __float2uint_rz(seg_eval<23 - kOBits>(tO, fmaf(sR, fi, p.e0)));
+          px[i][1] = __float2uint_rz(seg_eval<23 - kOBits>(tO, fmaf(sG, fi, p.e0)));
+          px[i][2] = __float2uint_rz(seg_eval<23 - kOBits>(tO, fmaf(sB, fi, p.e0)));
+          if (MASK) { px[i][0] &= 0x3ffu; px[i][1] &= 0x3ffu; px[i][2] &= 0x3ffu; }
+        } else if (PACK == kPackF16) {
+          px[i][0] = float_to_half_ref(sR * fi);
+          px[i][1] = float_to_half_ref(sG * fi);
+          px[i][2] = float_to_half_ref(sB * fi);
+        } else {
+          px[i][0] = to_10bit(sR * fi);
+          px[i][1] = to_10bit(sG * fi);
+          px[i][2] = to_10bit(sB * fi);
+        }
+      }
+      const size_t pix = (size_t)(4 * cy + r) * g.width + 4 * cx;
+      if (PACK == kPack1010102) {  // colorToRgba1010102, gainmapmath.cpp:722-727
+        uint32_t w[4];
+#pragma unroll
+        for (int i = 0; i < 4; i++) w[i] = (px[i][0] + (px[i][1] << 10) + (px[i][2] << 20)) | 0xC0000000u;  // codes <= 1023: + == |
+        stg16(outp + pix * 4, make_uint4(w[0], w[1], w[2], w[3]));
+      } else if (PACK == kPackF16) {  // colorToRgbaF16, gainmapmath.cpp:729-732
+        uint32_t w[8];
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+          w[2 * i] = px[i][0] | (px[i][1] << 16);
+          w[2 * i + 1] = px[i][2] | (0x3C00u << 16);
+        }
+        stg16(outp + pix * 8, make_uint4(w[0], w[1], w[2], w[3]));
+        stg16(outp + pix * 8 + 16, make_uint4(w[4], w[5], w[6], w[7]));
+      } else {  // three planar u16 planes, ultrahdr.cpp:460-468
+#pragma unroll
+        for (int ch = 0; ch < 3; ch++)
+          stg8(outp + (ch * npix + pix) * 2, make_uint2(px[0][ch] | (px[1][ch] << 16), px[2][ch] | (px[3][ch] << 16)));
+      }
+    }
+  }
+}
+
+bool aligned(const void* q, size_t a) { return (reinterpret_cast<uintptr_t>(q) & (a - 1)) == 0; }
+
+template <int PACK, bool MASK>
+cudaError_t launch(const ApplyFastParams& p, cudaStream_t s) {
+  const size_t smem = PACK == kPack1010102 ? 0 : kSEntriesHi * sizeof(float2);
+  static int sms_of[64], per_sm_of[64];  // per device, filled on first use (benign race: same values)
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  dev &= 63;
+  if (per_sm_of[dev] == 0) {
+    int n_sm = 0, n = 0;
+    if ((e = cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev)) != cudaSuccess) return e;
+    if (smem && (e = cudaFuncSetAttribute(apply_fast_kernel<PACK, MASK>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess) return e;
+    if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, apply_fast_kernel<PACK, MASK>, kThreads, smem)) != cudaSuccess) return e;
+    sms_of[dev] = n_sm;
+    per_sm_of[dev] = n > 0 ? n : 1;
+  }
+  const int sms = sms_of[dev], per_sm = per_sm_of[dev];
+  const int grid = p.n_tiles < sms * per_sm ? p.n_tiles : sms * per_sm;
+  apply_fast_kernel<PACK, MASK><<<grid, kThreads, smem, s>>>(p);
+  return cudaGetLastError();
+}
+
+}  // namespace
+
+bool apply_fast_ok(const Geometry& g, const Planes& pl) {
+  return g.map_scale == 4 && g.width % 4 == 0 && g.height % 4 == 0 && g.map_width * 4 == g.width &&
+         g.map_height * 4 == g.height && aligned(pl.sdr_y, 4) && aligned(pl.sdr_u, 2) && aligned(pl.sdr_v, 2) &&
+         aligned(pl.out, 16) && g.sdr_luma_stride % 4 == 0 && g.sdr_chroma_stride % 2 == 0 &&
+         ((size_t)g.width * g.height * 2) % 8 == 0;
+}
+
+cudaError_t launch_apply_fast_impl(ApplyFastParams& p, int n, cudaStream_t s) {
+  if (p.g.width == 0 || p.g.height == 0 || n == 0) return cudaSuccess;
+  p.tiles_x = (p.g.map_width + kTileCellsX - 1) / kTileCellsX;
+  p.tiles_y = (p.g.map_height + kTileCellsY - 1) / kTileCellsY;
+  p.n_tiles = p.tiles_x * p.tiles_y * n;
+  switch (p.output_format) {
+    case 1: return launch<kPackF16, false>(p, s);
+    case 4: return launch<kPackPlanar10, false>(p, s);
+    default: return p.need_mask ? launch<kPack1010102, true>(p, s) : launch<kPack1010102, false>(p, s);
+  }
+}
+
+}  // namespace uhdr

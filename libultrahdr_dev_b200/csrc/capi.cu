@@ -23,6 +23,7 @@ namespace {
 using namespace uhdr;
 
 std::atomic<uint64_t> g_launches{0};
+std::atomic<int> g_apply_mode{0};  // 0 auto (table-driven fast path when eligible), 1 force the generic kernel
 
 // ---------------------------------------------------------------- per-thread context
 struct DevBuf {
@@ -141,6 +142,39 @@ int get_idw(int device, int scale, const float** out) {
   CU(cudaMemcpy(d, h.data(), h.size() * sizeof(float), cudaMemcpyHostToDevice));
   g_idw[{device, scale}] = d;
   *out = d;
+  return 0;
+}
+
+// ---------------------------------------------------------------- transfer-function tables of the fast apply path
+std::map<int, ApplyTables> g_tables;  // device -> device-resident tables (guarded by g_idw_mu)
+
+int get_apply_tables(int device, ApplyTables* out) {
+  std::lock_guard<std::mutex> lk(g_idw_mu);
+  auto it = g_tables.find(device);
+  if (it != g_tables.end()) {
+    *out = it->second;
+    return 0;
+  }
+  const size_t n2 = (size_t)kSEntries + (size_t)kSEntriesHi + 2 * (size_t)kOEntries;
+  std::vector<float2> h2(n2);
+  std::vector<float> e255(256);
+  float2* hs = h2.data();
+  float2* hs_hi = hs + kSEntries;
+  float2* ho_hlg = hs_hi + kSEntriesHi;
+  float2* ho_pq = ho_hlg + kOEntries;
+  build_apply_tables(hs, hs_hi, ho_hlg, ho_pq, e255.data());
+  char* d = nullptr;
+  CU(cudaMalloc((void**)&d, n2 * sizeof(float2) + 256 * sizeof(float)));
+  CU(cudaMemcpy(d, h2.data(), n2 * sizeof(float2), cudaMemcpyHostToDevice));
+  CU(cudaMemcpy(d + n2 * sizeof(float2), e255.data(), 256 * sizeof(float), cudaMemcpyHostToDevice));
+  ApplyTables t;
+  t.s = (const float2*)d;
+  t.s_hi = t.s + kSEntries;
+  t.o_hlg = t.s_hi + kSEntriesHi;
+  t.o_pq = t.o_hlg + kOEntries;
+  t.e255 = (const float*)(d + n2 * sizeof(float2));
+  g_tables[device] = t;
+  *out = t;
   return 0;
 }
 
@@ -371,10 +405,39 @@ int apply_core(int n, const uhdrb200_image* sdr, const uhdrb200_image* map, cons
     v[i].out = dest[i].data;
     vec = vec && apply_vec_ok(p.g, v[i]);
   }
+  // Fast path (apply_fast.cu): map scale 4, 4-aligned planes, and a gain factor
+  // f = 2^(gain*A + B) (gain in [0,1]) small enough for the OETF table range.
+  bool fast = g_apply_mode != 1;
+  for (int i = 0; i < n && fast; i++) fast = apply_fast_ok(p.g, v[i]);
+  const double k = (double)p.display_boost / (double)p.max_boost;
+  const double A = ((double)p.log2_max - (double)p.log2_min) * k;
+  const double B = (double)p.log2_min * k - log2((double)p.display_boost);
+  const double fmax = exp2(A > 0 ? A + B : B);
+  if (!(fmax < 3.9) || !(p.display_boost > 0.0f) || !std::isfinite(A) || !std::isfinite(B)) fast = false;
   BatchSlot* slot = nullptr;
-  if (n == 1) p.single = v[0];
-  else if ((st = stage_batch(v, s, &p.batch, &slot))) return st;
-  cudaError_t e = launch_apply_impl(p, n, vec, s);
+  const Planes* batch = nullptr;
+  if (n > 1 && (st = stage_batch(v, s, &batch, &slot))) return st;
+  cudaError_t e;
+  if (fast) {
+    ApplyFastParams f;
+    memset(&f, 0, sizeof f);
+    f.g = p.g;
+    f.output_format = fmt;
+    f.A = (float)A;
+    f.B = (float)B;
+    f.e0 = (float)ldexp(1.0, kOLoExp);
+    f.need_mask = fmax > 1.0005 ? 1 : 0;  // at f <= 1.0005 no 10-bit code can reach 1024
+    idw_fill(&f.w[0][0], 4, 1, 1);  // ShepardsIDW::mWeights for scale 4
+    f.idw = p.idw;
+    if ((st = get_apply_tables(t_ctx.device, &f.tab))) return st;
+    f.single = v[0];
+    f.batch = batch;
+    e = launch_apply_fast_impl(f, n, s);
+  } else {
+    p.single = v[0];
+    p.batch = batch;
+    e = launch_apply_impl(p, n, vec, s);
+  }
   if (slot) cudaEventRecord(slot->done, s);
   if (e != cudaSuccess) return fail(e, "apply kernel launch");
   g_launches++;
@@ -641,6 +704,11 @@ void* uhdrb200_host_alloc(size_t bytes) {
 void uhdrb200_host_free(void* p) { if (p) cudaFreeHost(p); }
 void uhdrb200_free(void* p) { free(p); }
 uint64_t uhdrb200_launch_count(void) { return g_launches.load(); }
+int uhdrb200_set_apply_mode(int mode) {
+  if (mode != UHDRB200_APPLY_AUTO && mode != UHDRB200_APPLY_GENERIC) return UHDRB200_ERROR_UNSUPPORTED_FEATURE;
+  g_apply_mode = mode;
+  return UHDRB200_NO_ERROR;
+}
 
 int uhdrb200_generate_gainmap_host(const uhdrb200_image* yuv420, const uhdrb200_image* p010, int hdr_tf,
                                    uhdrb200_metadata* metadata, uhdrb200_image* dest, int sdr_is_601) {

@@ -1,0 +1,94 @@
+// tables.cu — host-side construction (double precision) of the shared-memory transfer-function
+// tables used by apply_fast.cu. Each table is piecewise linear on log-spaced segments (a float's
+// exponent + top mantissa bits pick the segment); per segment the line interpolates the target
+// at the two Chebyshev nodes, which halves the maximum error of an end-point chord.
+//
+// Targets follow the reference's formulas evaluated in double, as the reference itself does under
+// g++/glibc (DESIGN.md "numerics"): srgbInvOetf gainmapmath.cpp:149-155, hlgOetf :259-267,
+// pqOetf :309-314. Measured against the oracle the tables give >= 99.9 % exact 10-bit codes and
+// never more than 1 LSB (tests/test_gpu_parity.py).
+#include <cmath>
+#include <cstdint>
+#include <cstring>
+
+#include "uhdr_kernels.cuh"
+
+namespace uhdr {
+namespace {
+
+double srgb_inv_of_t(double t) {  // t = (c + 0.055) / 1.055
+  const double c = t * 1.055 - 0.055;
+  if (c <= 0.04045) return c / 12.92;
+  return pow(t, 2.4);
+}
+double hlg_oetf_d(double e) {
+  const double a = 0.17883277, b = 0.28466892, c = 0.55991073;
+  if (e <= 1.0 / 12.0) return sqrt(3.0 * (e < 0 ? 0 : e));
+  return a * log(12.0 * e - b) + c;
+}
+double pq_oetf_d(double e) {
+  if (e <= 0.0) return 0.0;
+  const double m1 = 2610.0 / 16384.0, m2 = 2523.0 / 4096.0 * 128.0;
+  const double c1 = 3424.0 / 4096.0, c2 = 2413.0 / 4096.0 * 32.0, c3 = 2392.0 / 4096.0 * 32.0;
+  const double p = pow(e, m1);
+  return pow((c1 + c2 * p) / (1.0 + c3 * p), m2);
+}
+
+float bits_to_float(uint32_t b) {
+  float f;
+  memcpy(&f, &b, 4);
+  return f;
+}
+
+template <class F>
+void fill(float2* tab, int lo_exp, int hi_exp, int bits, F fn) {
+  const int n = (hi_exp - lo_exp) << bits;
+  const uint32_t step = 1u << (23 - bits);
+  const double k = sqrt(2.0) / 4.0;
+  for (int i = 0; i < n; i++) {
+    const uint32_t b0 = ((uint32_t)(lo_exp + 127) << 23) + (uint32_t)i * step;
+    const double x0 = bits_to_float(b0), x1 = bits_to_float(b0 + step), h = x1 - x0;
+    const double n0 = x0 + h * (0.5 - k), n1 = x0 + h * (0.5 + k);
+    const double f0 = fn(n0), f1 = fn(n1);
+    const double slope = (f1 - f0) / (n1 - n0);
+    tab[i].x = (float)(f0 - slope * n0);
+    tab[i].y = (float)slope;
+  }
+}
+
+// S table: segments that lie wholly inside the linear part of srgbInvOetf get the exact line
+// (c / 12.92 with c = 1.055 t - 0.055), with the intercept rounded UP so that c = 0 (t = t0, the
+// float the kernel computes for it) evaluates to +0 or a positive value below 2^-25, never to a
+// negative number: floatToHalf (gainmapmath.h:136-147) would turn that into 0x8000.
+void fill_s(float2* tab, int bits) {
+  fill(tab, kSLoExp, kSHiExp, bits, srgb_inv_of_t);
+  const float k1 = (float)(1.0 / 1.055), k0 = (float)(0.055 / 1.055);
+  const float t0 = fmaf(0.0f, k1, k0);
+  const float t_kink = (float)((0.04045 + 0.055) / 1.055);
+  const float b = (float)(1.055 / 12.92);
+  const double a_exact = -(double)b * (double)t0;
+  float a = (float)a_exact;
+  if ((double)a < a_exact) a = nextafterf(a, 1.0f);
+  const int n = (kSHiExp - kSLoExp) << bits;
+  const uint32_t step = 1u << (23 - bits);
+  for (int i = 0; i < n; i++) {
+    const uint32_t b0 = ((uint32_t)(kSLoExp + 127) << 23) + (uint32_t)i * step;
+    if (bits_to_float(b0 + step) <= t_kink) {
+      tab[i].x = a;
+      tab[i].y = b;
+    }
+  }
+}
+
+}  // namespace
+
+void build_apply_tables(float2* s, float2* s_hi, float2* o_hlg, float2* o_pq, float* e255) {
+  fill_s(s, kSBits);
+  fill_s(s_hi, kSBitsHi);
+  const double e0 = ldexp(1.0, kOLoExp);
+  fill(o_hlg, kOLoExp, kOHiExp, kOBits, [e0](double x) { return 1023.0 * hlg_oetf_d(x - e0); });
+  fill(o_pq, kOLoExp, kOHiExp, kOBits, [e0](double x) { return 1023.0 * pq_oetf_d(x - e0); });
+  for (int i = 0; i < 256; i++) e255[i] = (float)i / 255.0f;  // gainmapmath.cpp:700-703
+}
+
+}  // namespace uhdr

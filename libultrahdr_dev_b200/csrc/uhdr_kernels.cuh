@@ -57,6 +57,46 @@ struct ApplyParams {
   const Planes* batch;
 };
 
+// ---- table-driven fast path of applyGainMap (apply_fast.cu) ----
+// Piecewise-linear tables on log-spaced segments: a float's exponent and top mantissa bits select
+// the segment ((bits >> (23 - kBits)) - base), value = a + b * x. Built on the host in double
+// (tables.cu), staged into shared memory by a TMA bulk copy.
+//   S table: x = t = (c + 0.055) / 1.055 in [2^kSLoExp, 2^kSHiExp)  ->  srgbInvOetf(c)   (gainmapmath.cpp:149-155)
+//   O table: x = e + 2^kOLoExp       in [2^kOLoExp, 2^kOHiExp)  ->  1023 * hlgOetf(e) or 1023 * pqOetf(e)
+//            (gainmapmath.cpp:259-267, 309-314; the 1023 of colorToRgba1010102, :722-727, is folded in)
+constexpr int kSLoExp = -5, kSHiExp = 1;
+constexpr int kSBits = 8;    // RGBA1010102 kernel: 12 KB, with the 28 KB O table in static shared memory
+constexpr int kSBitsHi = 10; // linear outputs (RGBA F16, planar 10-bit): 48 KB, no O table needed
+constexpr int kOLoExp = -26, kOHiExp = 2, kOBits = 7;
+constexpr int kSEntries = (kSHiExp - kSLoExp) << kSBits;      // 1536 float2
+constexpr int kSEntriesHi = (kSHiExp - kSLoExp) << kSBitsHi;  // 6144 float2
+constexpr int kOEntries = (kOHiExp - kOLoExp) << kOBits;      // 3584 float2
+constexpr int kSBase = (kSLoExp + 127) << kSBits;
+constexpr int kSBaseHi = (kSLoExp + 127) << kSBitsHi;
+constexpr int kOBase = (kOLoExp + 127) << kOBits;
+
+struct ApplyTables {       // device pointers, one set per device
+  const float2* s;         // kSEntries
+  const float2* s_hi;      // kSEntriesHi
+  const float2* o_hlg;     // kOEntries
+  const float2* o_pq;      // kOEntries
+  const float* e255;       // 256 floats: i / 255.0f, correctly rounded (gainmapmath.cpp:700-703)
+};
+
+struct ApplyFastParams {
+  Geometry g;              // map_scale == 4, width % 4 == 0, height % 4 == 0
+  int output_format;
+  float A, B;              // gain factor f = 2^(gain * A + B) = 2^(logBoost * displayBoost / maxContentBoost) / displayBoost
+  float e0;                // 2^kOLoExp
+  int need_mask;           // 1 when 10-bit codes can exceed 1023 (displayBoost < maxContentBoost): `& 0x3ff` wraps like the reference
+  float w[16][4];          // interior IDW weights [oy * 4 + ox][k] (ShepardsIDW::mWeights, gainmapmath.h:184-228)
+  const float* idw;        // all four tables (device), used by the cells on the right/bottom map border
+  ApplyTables tab;
+  int tiles_x, tiles_y, n_tiles;  // tiles of 32 x 8 map cells (128 x 32 pixels)
+  Planes single;
+  const Planes* batch;
+};
+
 struct ToneMapParams {
   Geometry g;
   Planes single;
@@ -78,6 +118,11 @@ bool tonemap_vec_ok(const Geometry& g, const Planes& pl);
 bool convert_yuv_vec_ok(const Geometry& g, const Planes& pl);
 cudaError_t launch_generate_impl(const GenerateParams& p, int n, bool vec, cudaStream_t s);
 cudaError_t launch_apply_impl(const ApplyParams& p, int n, bool vec, cudaStream_t s);
+// fast path: scale 4, vector-aligned planes, gain factor bounded so that e + e0 < 2^kOHiExp
+bool apply_fast_ok(const Geometry& g, const Planes& pl);
+cudaError_t launch_apply_fast_impl(ApplyFastParams& p, int n, cudaStream_t s);
+// host: fills the double-precision-built tables (tables.cu)
+void build_apply_tables(float2* s, float2* s_hi, float2* o_hlg, float2* o_pq, float* e255);
 cudaError_t launch_tonemap_impl(const ToneMapParams& p, int n, bool vec, cudaStream_t s);
 cudaError_t launch_convert_yuv_impl(const ConvertYuvParams& p, int n, bool vec, cudaStream_t s);
 
