@@ -35,7 +35,8 @@ def build(force=False, verbose=False):
     """Compile every kernel for sm_100a into one shared library. Returns its path."""
     if not force and up_to_date():
         return LIB
-    cmd = [_nvcc()] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", LIB] + [os.path.join(CSRC, f) for f in SOURCES]
+    extra = os.environ.get("UHDR_NVCC_EXTRA", "").split()  # experiments only, e.g. -DUHDR_APPLY_MUFU_CHANNELS=2
+    cmd = [_nvcc()] + NVCC_FLAGS + extra + (["-Xptxas", "-v"] if verbose else []) + ["-o", LIB] + [os.path.join(CSRC, f) for f in SOURCES]
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:
         raise RuntimeError("nvcc failed:\n" + r.stdout + r.stderr)

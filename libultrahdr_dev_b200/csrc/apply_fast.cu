@@ -24,16 +24,48 @@
 namespace uhdr {
 namespace {
 
+#ifndef UHDR_APPLY_MUFU_CHANNELS
+#define UHDR_APPLY_MUFU_CHANNELS 2  // colour channels whose srgbInvOetf runs on the XU pipe (lg2/ex2) instead of the smem table
+#endif
+#ifndef UHDR_APPLY_MIN_BLOCKS
+#define UHDR_APPLY_MIN_BLOCKS 3
+#endif
 constexpr int kThreads = 256;
 constexpr int kTileCellsX = 32, kTileCellsY = 8;
 
 enum { kPack1010102 = 0, kPackF16 = 1, kPackPlanar10 = 2 };
 
-// value = a + b * x on the segment selected by the float's bits; `tab` is pre-biased by -base
+// log-spaced table: value = a + b * x on the segment selected by the float's bits; `tab` is pre-biased by -base
 template <int SHIFT>
 __device__ __forceinline__ float seg_eval(const float2* __restrict__ tab, float x) {
   const float2 ab = tab[__float_as_uint(x) >> SHIFT];
   return fmaf(ab.y, x, ab.x);
+}
+
+// uniform table over [0,1] with SEGS segments: floor(c * SEGS) lands in the low mantissa bits of
+// c * SEGS + 2^23 rounded toward -inf (one FFMA.RM); `biased` = shared address of the table minus
+// 8 * 0x4B000000 (mod 2^32), so the entry address is one shift-add (LEA) away.
+template <int SEGS>
+__device__ __forceinline__ float uni_eval(uint32_t biased, float c) {
+  float m;
+  asm("fma.rm.f32 %0, %1, %2, 0f4B000000;" : "=f"(m) : "f"(c), "f"((float)SEGS));
+  float a, b;
+  asm volatile("ld.shared.v2.f32 {%0,%1}, [%2];" : "=f"(a), "=f"(b) : "r"(biased + (__float_as_uint(m) << 3)));
+  return fmaf(b, c, a);
+}
+
+// floor(v) for 0 <= v < 2^22 as an integer in the low mantissa bits: one FADD with round-to-minus-
+// infinity on the FMA pipe instead of an F2I on the (quarter-rate) XU pipe.
+__device__ __forceinline__ uint32_t floor_bits(float v) {
+  float r;
+  asm("add.rm.f32 %0, %1, 0f4B000000;" : "=f"(r) : "f"(v));  // + 2^23
+  return __float_as_uint(r);
+}
+
+// srgbInvOetf (gainmapmath.cpp:149-155) on the XU pipe: 2 MUFU, ~4e-7 relative
+__device__ __forceinline__ float srgb_inv_mufu(float c) {
+  const float pw = mufu_ex2(2.4f * mufu_lg2(fmaf(c, (float)(1.0 / 1.055), (float)(0.055 / 1.055))));
+  return c <= 0.04045f ? c * (float)(1.0 / 12.92) : pw;
 }
 
 __device__ __forceinline__ float ex2_fast(float x) {
@@ -48,11 +80,10 @@ __device__ __forceinline__ float ex2_fast(float x) {
 // that a lookup address is `mask(bits >> n) + link-time constant` (no base-register add); the
 // linear-output kernels use a 4x finer S table (48 KB, dynamic shared memory) and no O table.
 template <int PACK, bool MASK>
-__global__ void __launch_bounds__(kThreads, 3) apply_fast_kernel(const __grid_constant__ ApplyFastParams p) {
+__global__ void __launch_bounds__(kThreads, UHDR_APPLY_MIN_BLOCKS) apply_fast_kernel(const __grid_constant__ ApplyFastParams p) {
   constexpr bool kHasO = PACK == kPack1010102;
-  constexpr int kSB = kHasO ? kSBits : kSBitsHi;
+  constexpr int kSSeg = kHasO ? kSSegs : kSSegsHi;
   constexpr int kSN = kHasO ? kSEntries : kSEntriesHi;
-  constexpr int kSBs = kHasO ? kSBase : kSBaseHi;
   extern __shared__ __align__(16) uint8_t smem_dyn[];
   __shared__ __align__(16) float2 sS_static[kHasO ? kSEntries : 1];
   __shared__ __align__(16) float2 sO_static[kHasO ? kOEntries : 1];
@@ -73,7 +104,9 @@ __global__ void __launch_bounds__(kThreads, 3) apply_fast_kernel(const __grid_co
     bulk_g2s(sE, p.tab.e255, eb, &bar);
   }
   mbar_wait(&bar, 0);
-  const float2* tS = sS - kSBs;    // index = bits >> (23 - kSB)
+  // p.s_bias = 8 * 0x4B000000 (mod 2^32) comes from the parameter block so that it stays a run-time value and the
+  // entry address is one LEA: (bits << 3) + tS
+  const uint32_t tS = smem_u32(sS) - p.s_bias;
   const float2* tO = sO - kOBase;  // index = bits >> (23 - kOBits)
 
   const Geometry& g = p.g;
@@ -81,49 +114,82 @@ __global__ void __launch_bounds__(kThreads, 3) apply_fast_kernel(const __grid_co
   const int tiles_per_image = p.tiles_x * p.tiles_y;
   const float k601_cr = 1.402f, k601_cb = 1.772f;
   const float k601_gcb = 0.114f * 1.772f / 0.587f, k601_gcr = 0.299f * 1.402f / 0.587f;  // gainmapmath.cpp:195-196
-  const float kT1 = (float)(1.0 / 1.055), kT0 = (float)(0.055 / 1.055);
   const size_t npix = (size_t)g.width * g.height;
 
+  // tile -> (image z, tile row ty, tile column tx), advanced incrementally: no division in the loop
+  const uint32_t tiles_x = p.tiles_x, tiles_y = p.tiles_y;
+  uint32_t tx, ty, z, dtx, dty, dz;
+  {
+    const uint32_t b0 = blockIdx.x, st = gridDim.x;
+    z = b0 / tiles_per_image;
+    uint32_t rem = b0 - z * tiles_per_image;
+    ty = rem / tiles_x;
+    tx = rem - ty * tiles_x;
+    dz = st / tiles_per_image;
+    rem = st - dz * tiles_per_image;
+    dty = rem / tiles_x;
+    dtx = rem - dty * tiles_x;
+  }
+  const uint32_t ls = g.sdr_luma_stride, cs = g.sdr_chroma_stride;
+
   for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
-    const int z = tile / tiles_per_image;
-    const int rem = tile - z * tiles_per_image;
-    const int ty = rem / p.tiles_x, tx = rem - ty * p.tiles_x;
-    const int cx = tx * kTileCellsX + (tid & 31), cy = ty * kTileCellsY + (tid >> 5);
-    if (cx >= mw || cy >= mh) continue;
-    const Planes* pl = p.batch ? p.batch + z : &p.single;
-    const uint8_t* yp = (const uint8_t*)pl->sdr_y + (size_t)(4 * cy) * g.sdr_luma_stride + 4 * cx;
-    const uint8_t* up = (const uint8_t*)pl->sdr_u + (size_t)(2 * cy) * g.sdr_chroma_stride + 2 * cx;
-    const uint8_t* vp = (const uint8_t*)pl->sdr_v + (size_t)(2 * cy) * g.sdr_chroma_stride + 2 * cx;
-    const uint8_t* map = (const uint8_t*)pl->map_in;
-    uint8_t* outp = (uint8_t*)pl->out;
+    const uint32_t cx = tx * kTileCellsX + (tid & 31), cy = ty * kTileCellsY + (tid >> 5);
+    const uint32_t zi = z;
+    tx += dtx;
+    if (tx >= tiles_x) { tx -= tiles_x; ty++; }
+    ty += dty;
+    if (ty >= tiles_y) { ty -= tiles_y; z++; }
+    z += dz;
+    if (cx >= (uint32_t)mw || cy >= (uint32_t)mh) continue;
+    const uint8_t *sdr_y, *sdr_u, *sdr_v, *map;
+    uint8_t* outp;
+    if (p.batch) {
+      const Planes* pl = p.batch + zi;
+      sdr_y = (const uint8_t*)__ldg((const unsigned long long*)&pl->sdr_y);
+      sdr_u = (const uint8_t*)__ldg((const unsigned long long*)&pl->sdr_u);
+      sdr_v = (const uint8_t*)__ldg((const unsigned long long*)&pl->sdr_v);
+      map = (const uint8_t*)__ldg((const unsigned long long*)&pl->map_in);
+      outp = (uint8_t*)__ldg((const unsigned long long*)&pl->out);
+    } else {
+      sdr_y = (const uint8_t*)p.single.sdr_y;
+      sdr_u = (const uint8_t*)p.single.sdr_u;
+      sdr_v = (const uint8_t*)p.single.sdr_v;
+      map = (const uint8_t*)p.single.map_in;
+      outp = (uint8_t*)p.single.out;
+    }
+    // 32-bit offsets inside a plane (planes are < 4 GB: width, height <= 2^15 after the capi checks)
+    const uint8_t* yp = sdr_y + (4u * cy * ls + 4u * cx);
+    const uint32_t coff = 2u * cy * cs + 2u * cx;
+    const uint8_t* up = sdr_u + coff;
+    const uint8_t* vp = sdr_v + coff;
 
     // ---- all global loads of the cell first
     uint32_t yw[4], uw[2], vw[2];
 #pragma unroll
-    for (int r = 0; r < 4; r++) yw[r] = ldg4(yp + (size_t)r * g.sdr_luma_stride);
+    for (int r = 0; r < 4; r++) yw[r] = ldg4(yp + r * ls);
 #pragma unroll
     for (int r = 0; r < 2; r++) {
-      uw[r] = ldg2(up + (size_t)r * g.sdr_chroma_stride);
-      vw[r] = ldg2(vp + (size_t)r * g.sdr_chroma_stride);
+      uw[r] = ldg2(up + r * cs);
+      vw[r] = ldg2(vp + r * cs);
     }
-    const int cxr = min(cx + 1, mw - 1), cyb = min(cy + 1, mh - 1);  // gainmapmath.cpp:690-697
-    const uint32_t b1 = __ldg(map + cx + cy * mw), b2 = __ldg(map + cx + cyb * mw);
-    const uint32_t b3 = __ldg(map + cxr + cy * mw), b4 = __ldg(map + cxr + cyb * mw);
+    const uint32_t cxr = min(cx + 1, (uint32_t)mw - 1), cyb = min(cy + 1, (uint32_t)mh - 1);  // gainmapmath.cpp:690-697
+    const uint32_t b1 = __ldg(map + (cx + cy * mw)), b2 = __ldg(map + (cx + cyb * mw));
+    const uint32_t b3 = __ldg(map + (cxr + cy * mw)), b4 = __ldg(map + (cxr + cyb * mw));
     const float e1 = sE[b1], e2 = sE[b2], e3 = sE[b3], e4 = sE[b4];  // e1=(xl,yl) e2=(xl,yu) e3=(xu,yl) e4=(xu,yu)
 
-    // ---- gain factor of the 16 pixels
+    // ---- gain factor of the 16 pixels: f = 2^(gain * A + B); p.w holds the IDW weights times A
     float f[16];
-    if (cx + 1 < mw && cy + 1 < mh) {
+    if (cx + 1 < (uint32_t)mw && cy + 1 < (uint32_t)mh) {
 #pragma unroll
       for (int i = 0; i < 16; i++) {
-        float gain = e1 * p.w[i][0];
-        gain = fmaf(e2, p.w[i][1], gain);
-        gain = fmaf(e3, p.w[i][2], gain);
-        gain = fmaf(e4, p.w[i][3], gain);
-        f[i] = ex2_fast(fmaf(gain, p.A, p.B));
+        float ex = fmaf(e1, p.w[i][0], p.B);
+        ex = fmaf(e2, p.w[i][1], ex);
+        ex = fmaf(e3, p.w[i][2], ex);
+        ex = fmaf(e4, p.w[i][3], ex);
+        f[i] = ex2_fast(ex);
       }
     } else {  // map border: tables NR (1), NB (2), C (3)
-      const int t = (cx + 1 < mw) ? 2 : ((cy + 1 < mh) ? 1 : 3);
+      const int t = (cx + 1 < (uint32_t)mw) ? 2 : ((cy + 1 < (uint32_t)mh) ? 1 : 3);
       const float4* wt = reinterpret_cast<const float4*>(p.idw) + t * 16;
 #pragma unroll
       for (int i = 0; i < 16; i++) {
@@ -159,13 +225,15 @@ __global__ void __launch_bounds__(kThreads, 3) apply_fast_kernel(const __grid_co
         const float cR = __saturatef(fmaf(yf, 1 / 255.0f, rv[r >> 1][i >> 1]));
         const float cG = __saturatef(fmaf(yf, 1 / 255.0f, gq[r >> 1][i >> 1]));
         const float cB = __saturatef(fmaf(yf, 1 / 255.0f, bu[r >> 1][i >> 1]));
-        const float sR = seg_eval<23 - kSB>(tS, fmaf(cR, kT1, kT0));
-        const float sG = seg_eval<23 - kSB>(tS, fmaf(cG, kT1, kT0));
-        const float sB = seg_eval<23 - kSB>(tS, fmaf(cB, kT1, kT0));
+        constexpr int kX = kHasO ? UHDR_APPLY_MUFU_CHANNELS : 0;
+        const float sR = kX >= 2 ? srgb_inv_mufu(cR) : uni_eval<kSSeg>(tS, cR);
+        const float sG = kX >= 3 ? srgb_inv_mufu(cG) : uni_eval<kSSeg>(tS, cG);
+        const float sB = kX >= 1 ? srgb_inv_mufu(cB) : uni_eval<kSSeg>(tS, cB);
         if (PACK == kPack1010102) {
-          px[i][0] = __float2uint_rz(seg_eval<23 - kOBits>(tO, fmaf(sR, fi, p.e0)));
-          px[i][1] = __float2uint_rz(seg_eval<23 - kOBits>(tO, fmaf(sG, fi, p.e0)));
-          px[i][2] = __float2uint_rz(seg_eval<23 - kOBits>(tO, fmaf(sB, fi, p.e0)));
+          // the O table is >= 0 everywhere (tables.cu), so floor == the reference's truncation
+          px[i][0] = floor_bits(seg_eval<23 - kOBits>(tO, fmaf(sR, fi, p.e0)));
+          px[i][1] = floor_bits(seg_eval<23 - kOBits>(tO, fmaf(sG, fi, p.e0)));
+          px[i][2] = floor_bits(seg_eval<23 - kOBits>(tO, fmaf(sB, fi, p.e0)));
           if (MASK) { px[i][0] &= 0x3ffu; px[i][1] &= 0x3ffu; px[i][2] &= 0x3ffu; }
         } else if (PACK == kPackF16) {
           px[i][0] = float_to_half_ref(sR * fi);
@@ -177,11 +245,15 @@ __global__ void __launch_bounds__(kThreads, 3) apply_fast_kernel(const __grid_co
           px[i][2] = to_10bit(sB * fi);
         }
       }
-      const size_t pix = (size_t)(4 * cy + r) * g.width + 4 * cx;
+      const size_t pix = (size_t)((4u * cy + r) * (uint32_t)g.width + 4u * cx);
       if (PACK == kPack1010102) {  // colorToRgba1010102, gainmapmath.cpp:722-727
         uint32_t w[4];
+        // px = 0x4B000000 + code (or the masked code); codes <= 1023, so the fields do not overlap and
+        // "| alpha" and the removal of the float bias fold into one additive constant
+        constexpr uint32_t kBias = MASK ? 0u : (0x4B000000u + (0x4B000000u << 10) + (0x4B000000u << 20));
+        constexpr uint32_t kAdd = 0xC0000000u - kBias;
 #pragma unroll
-        for (int i = 0; i < 4; i++) w[i] = (px[i][0] + (px[i][1] << 10) + (px[i][2] << 20)) | 0xC0000000u;  // codes <= 1023: + == |
+        for (int i = 0; i < 4; i++) w[i] = px[i][0] + (px[i][1] << 10) + (px[i][2] << 20) + kAdd;
         stg16(outp + pix * 4, make_uint4(w[0], w[1], w[2], w[3]));
       } else if (PACK == kPackF16) {  // colorToRgbaF16, gainmapmath.cpp:729-732
         uint32_t w[8];
@@ -231,7 +303,8 @@ bool apply_fast_ok(const Geometry& g, const Planes& pl) {
   return g.map_scale == 4 && g.width % 4 == 0 && g.height % 4 == 0 && g.map_width * 4 == g.width &&
          g.map_height * 4 == g.height && aligned(pl.sdr_y, 4) && aligned(pl.sdr_u, 2) && aligned(pl.sdr_v, 2) &&
          aligned(pl.out, 16) && g.sdr_luma_stride % 4 == 0 && g.sdr_chroma_stride % 2 == 0 &&
-         ((size_t)g.width * g.height * 2) % 8 == 0;
+         ((size_t)g.width * g.height * 2) % 8 == 0 && (uint64_t)g.height * (uint64_t)g.sdr_luma_stride < (1ull << 31) &&
+         (uint64_t)g.height * (uint64_t)g.width < (1ull << 31);
 }
 
 cudaError_t launch_apply_fast_impl(ApplyFastParams& p, int n, cudaStream_t s) {

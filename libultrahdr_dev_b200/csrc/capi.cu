@@ -426,8 +426,11 @@ int apply_core(int n, const uhdrb200_image* sdr, const uhdrb200_image* map, cons
     f.A = (float)A;
     f.B = (float)B;
     f.e0 = (float)ldexp(1.0, kOLoExp);
+    f.s_bias = 0x4B000000u << 3;
     f.need_mask = fmax > 1.0005 ? 1 : 0;  // at f <= 1.0005 no 10-bit code can reach 1024
-    idw_fill(&f.w[0][0], 4, 1, 1);  // ShepardsIDW::mWeights for scale 4
+    idw_fill(&f.w[0][0], 4, 1, 1);  // ShepardsIDW::mWeights for scale 4 ...
+    for (int i = 0; i < 16; i++)
+      for (int c = 0; c < 4; c++) f.w[i][c] = (float)((double)f.w[i][c] * A);  // ... pre-multiplied by A
     f.idw = p.idw;
     if ((st = get_apply_tables(t_ctx.device, &f.tab))) return st;
     f.single = v[0];

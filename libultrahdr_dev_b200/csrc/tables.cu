@@ -16,11 +16,6 @@
 namespace uhdr {
 namespace {
 
-double srgb_inv_of_t(double t) {  // t = (c + 0.055) / 1.055
-  const double c = t * 1.055 - 0.055;
-  if (c <= 0.04045) return c / 12.92;
-  return pow(t, 2.4);
-}
 double hlg_oetf_d(double e) {
   const double a = 0.17883277, b = 0.28466892, c = 0.55991073;
   if (e <= 1.0 / 12.0) return sqrt(3.0 * (e < 0 ? 0 : e));
@@ -41,7 +36,7 @@ float bits_to_float(uint32_t b) {
 }
 
 template <class F>
-void fill(float2* tab, int lo_exp, int hi_exp, int bits, F fn) {
+void fill(float2* tab, int lo_exp, int hi_exp, int bits, F fn, bool nonneg = false) {
   const int n = (hi_exp - lo_exp) << bits;
   const uint32_t step = 1u << (23 - bits);
   const double k = sqrt(2.0) / 4.0;
@@ -53,41 +48,48 @@ void fill(float2* tab, int lo_exp, int hi_exp, int bits, F fn) {
     const double slope = (f1 - f0) / (n1 - n0);
     tab[i].x = (float)(f0 - slope * n0);
     tab[i].y = (float)slope;
+    if (nonneg) {  // lift the line so that it is >= 0 at both ends of its segment (first segments only)
+      const double lo = fmin((double)tab[i].x + (double)tab[i].y * x0, (double)tab[i].x + (double)tab[i].y * x1);
+      if (lo < 0) {
+        float a = (float)((double)tab[i].x - lo);
+        while ((double)a + (double)tab[i].y * x0 < 0 || (double)a + (double)tab[i].y * x1 < 0) a = nextafterf(a, 1e30f);
+        tab[i].x = a;
+      }
+    }
   }
 }
 
-// S table: segments that lie wholly inside the linear part of srgbInvOetf get the exact line
-// (c / 12.92 with c = 1.055 t - 0.055), with the intercept rounded UP so that c = 0 (t = t0, the
-// float the kernel computes for it) evaluates to +0 or a positive value below 2^-25, never to a
-// negative number: floatToHalf (gainmapmath.h:136-147) would turn that into 0x8000.
-void fill_s(float2* tab, int bits) {
-  fill(tab, kSLoExp, kSHiExp, bits, srgb_inv_of_t);
-  const float k1 = (float)(1.0 / 1.055), k0 = (float)(0.055 / 1.055);
-  const float t0 = fmaf(0.0f, k1, k0);
-  const float t_kink = (float)((0.04045 + 0.055) / 1.055);
-  const float b = (float)(1.055 / 12.92);
-  const double a_exact = -(double)b * (double)t0;
-  float a = (float)a_exact;
-  if ((double)a < a_exact) a = nextafterf(a, 1.0f);
-  const int n = (kSHiExp - kSLoExp) << bits;
-  const uint32_t step = 1u << (23 - bits);
-  for (int i = 0; i < n; i++) {
-    const uint32_t b0 = ((uint32_t)(kSLoExp + 127) << 23) + (uint32_t)i * step;
-    if (bits_to_float(b0 + step) <= t_kink) {
-      tab[i].x = a;
-      tab[i].y = b;
+double srgb_inv_d(double c) { return c <= 0.04045 ? c / 12.92 : pow((c + 0.055) / 1.055, 2.4); }
+
+// S table on uniform segments of c in [0,1]. Segments wholly inside the linear part of
+// srgbInvOetf hold the exact line (a = 0, so c = 0 gives exactly +0: floatToHalf,
+// gainmapmath.h:136-147, would turn a negative zero-ish value into 0x8000).
+void fill_s(float2* tab, int segs, int entries) {
+  const double k = sqrt(2.0) / 4.0, h = 1.0 / segs;
+  for (int i = 0; i < segs; i++) {
+    const double x0 = i * h, x1 = (i + 1) * h;
+    if (x1 <= 0.04045) {
+      tab[i].x = 0.0f;
+      tab[i].y = (float)(1.0 / 12.92);
+      continue;
     }
+    const double n0 = x0 + h * (0.5 - k), n1 = x0 + h * (0.5 + k);
+    const double f0 = srgb_inv_d(n0), f1 = srgb_inv_d(n1);
+    const double slope = (f1 - f0) / (n1 - n0);
+    tab[i].x = (float)(f0 - slope * n0);
+    tab[i].y = (float)slope;
   }
+  for (int i = segs; i < entries; i++) tab[i] = tab[segs - 1];  // c == 1.0 lands on index `segs`
 }
 
 }  // namespace
 
 void build_apply_tables(float2* s, float2* s_hi, float2* o_hlg, float2* o_pq, float* e255) {
-  fill_s(s, kSBits);
-  fill_s(s_hi, kSBitsHi);
+  fill_s(s, kSSegs, kSEntries);
+  fill_s(s_hi, kSSegsHi, kSEntriesHi);
   const double e0 = ldexp(1.0, kOLoExp);
-  fill(o_hlg, kOLoExp, kOHiExp, kOBits, [e0](double x) { return 1023.0 * hlg_oetf_d(x - e0); });
-  fill(o_pq, kOLoExp, kOHiExp, kOBits, [e0](double x) { return 1023.0 * pq_oetf_d(x - e0); });
+  fill(o_hlg, kOLoExp, kOHiExp, kOBits, [e0](double x) { return 1023.0 * hlg_oetf_d(x - e0); }, true);
+  fill(o_pq, kOLoExp, kOHiExp, kOBits, [e0](double x) { return 1023.0 * pq_oetf_d(x - e0); }, true);
   for (int i = 0; i < 256; i++) e255[i] = (float)i / 255.0f;  // gainmapmath.cpp:700-703
 }
 

@@ -58,21 +58,19 @@ struct ApplyParams {
 };
 
 // ---- table-driven fast path of applyGainMap (apply_fast.cu) ----
-// Piecewise-linear tables on log-spaced segments: a float's exponent and top mantissa bits select
-// the segment ((bits >> (23 - kBits)) - base), value = a + b * x. Built on the host in double
-// (tables.cu), staged into shared memory by a TMA bulk copy.
-//   S table: x = t = (c + 0.055) / 1.055 in [2^kSLoExp, 2^kSHiExp)  ->  srgbInvOetf(c)   (gainmapmath.cpp:149-155)
-//   O table: x = e + 2^kOLoExp       in [2^kOLoExp, 2^kOHiExp)  ->  1023 * hlgOetf(e) or 1023 * pqOetf(e)
-//            (gainmapmath.cpp:259-267, 309-314; the 1023 of colorToRgba1010102, :722-727, is folded in)
-constexpr int kSLoExp = -5, kSHiExp = 1;
-constexpr int kSBits = 8;    // RGBA1010102 kernel: 12 KB, with the 28 KB O table in static shared memory
-constexpr int kSBitsHi = 10; // linear outputs (RGBA F16, planar 10-bit): 48 KB, no O table needed
+// Piecewise-linear tables (value = a + b * x per segment), built on the host in double
+// (tables.cu) and staged into shared memory by a TMA bulk copy.
+//   S table: srgbInvOetf (gainmapmath.cpp:149-155) on UNIFORM segments of c in [0,1]:
+//            index = floor(c * kSSegs) comes out of one FFMA with round-to-minus-infinity.
+//   O table: x = e + 2^kOLoExp in [2^kOLoExp, 2^kOHiExp) -> 1023 * hlgOetf(e) or 1023 * pqOetf(e)
+//            (gainmapmath.cpp:259-267, 309-314; the 1023 of colorToRgba1010102, :722-727, is folded in) on
+//            LOG-spaced segments: the float's exponent and top kOBits mantissa bits are the index.
+constexpr int kSSegs = 1536;      // RGBA1010102 kernel: 12 KB, next to the 28 KB O table in static shared memory
+constexpr int kSSegsHi = 6144;    // linear outputs (RGBA F16, planar 10-bit) need relative accuracy: 48 KB, no O table
+constexpr int kSEntries = kSSegs + 2;      // + entry for c == 1.0, padded to a 16-byte multiple
+constexpr int kSEntriesHi = kSSegsHi + 2;
 constexpr int kOLoExp = -26, kOHiExp = 2, kOBits = 7;
-constexpr int kSEntries = (kSHiExp - kSLoExp) << kSBits;      // 1536 float2
-constexpr int kSEntriesHi = (kSHiExp - kSLoExp) << kSBitsHi;  // 6144 float2
 constexpr int kOEntries = (kOHiExp - kOLoExp) << kOBits;      // 3584 float2
-constexpr int kSBase = (kSLoExp + 127) << kSBits;
-constexpr int kSBaseHi = (kSLoExp + 127) << kSBitsHi;
 constexpr int kOBase = (kOLoExp + 127) << kOBits;
 
 struct ApplyTables {       // device pointers, one set per device
@@ -88,8 +86,9 @@ struct ApplyFastParams {
   int output_format;
   float A, B;              // gain factor f = 2^(gain * A + B) = 2^(logBoost * displayBoost / maxContentBoost) / displayBoost
   float e0;                // 2^kOLoExp
+  uint32_t s_bias;         // 0x4B000000 << 3 (see uni_eval in apply_fast.cu)
   int need_mask;           // 1 when 10-bit codes can exceed 1023 (displayBoost < maxContentBoost): `& 0x3ff` wraps like the reference
-  float w[16][4];          // interior IDW weights [oy * 4 + ox][k] (ShepardsIDW::mWeights, gainmapmath.h:184-228)
+  float w[16][4];          // A x interior IDW weights [oy * 4 + ox][k] (ShepardsIDW::mWeights, gainmapmath.h:184-228)
   const float* idw;        // all four tables (device), used by the cells on the right/bottom map border
   ApplyTables tab;
   int tiles_x, tiles_y, n_tiles;  // tiles of 32 x 8 map cells (128 x 32 pixels)
