@@ -151,8 +151,9 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--batch", type=int, default=256, help="4K pairs per step per GPU (device-resident)")
     ap.add_argument("--e2e-images", type=int, default=16, help="4K pairs per e2e step per GPU (host planes)")
+    ap.add_argument("--e2e-threads", type=int, default=4, help="host threads calling the synchronous host-pointer API concurrently")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--cpu-images", type=int, default=2, help="images per CPU worker process in the CPU arms")
+    ap.add_argument("--cpu-images", type=int, default=24, help="images per CPU worker process in the CPU arms")
     ap.add_argument("--cpu-worker", nargs=3, metavar=("N", "SEED", "TAG"))
     a = ap.parse_args()
     if a.cpu_worker:
@@ -284,7 +285,7 @@ def main():
 
     # ---- e2e: host planes -> C ABI host entry points -> host results (copies inside the timing)
     E = a.e2e_images
-    KH = 4
+    KH = max(4, a.e2e_threads)  # one private set of pinned buffers per in-flight image
     host_bufs = []
     for i in range(KH):
         ps = lib.uhdrb200_host_alloc(sdr_len)
@@ -304,16 +305,28 @@ def main():
         o_img.data = po
         host_bufs.append((s_img, h_img, m_img, o_img, pm))
 
+    # Each host thread owns a CUDA stream + staging buffers inside the library (thread-local context), so T
+    # threads calling the synchronous reference-style entry points overlap H2D, kernels and D2H of different
+    # images — what a multi-threaded server on top of the drop-in API gets. ctypes releases the GIL in the calls.
+    import concurrent.futures as cf
+
+    T = max(1, a.e2e_threads)
+    pool = cf.ThreadPoolExecutor(T, initializer=lambda: lib.uhdrb200_init(local))
+
+    def e2e_one(i):
+        s_img, h_img, m_img, o_img, pm = host_bufs[i % KH]
+        mdh, m_loc = abi.Metadata(), abi.Image()
+        st = lib.uhdrb200_generate_gainmap_host_into(C.byref(s_img), C.byref(h_img), abi.TF_HLG, C.byref(mdh),
+                                                     C.byref(m_loc), 0, pm, MW * MH)
+        assert st == 0, lib.uhdrb200_last_error()
+        o_loc = abi.Image()
+        o_loc.data = o_img.data
+        st = lib.uhdrb200_apply_gainmap_host(C.byref(s_img), C.byref(m_loc), C.byref(mdh), abi.OUTPUT_HDR_HLG,
+                                             FLT_MAX, C.byref(o_loc))
+        assert st == 0, lib.uhdrb200_last_error()
+
     def e2e_step():
-        for i in range(E):
-            s_img, h_img, m_img, o_img, pm = host_bufs[i % KH]
-            mdh = abi.Metadata()
-            st = lib.uhdrb200_generate_gainmap_host_into(C.byref(s_img), C.byref(h_img), abi.TF_HLG, C.byref(mdh),
-                                                         C.byref(m_img), 0, pm, MW * MH)
-            assert st == 0, lib.uhdrb200_last_error()
-            st = lib.uhdrb200_apply_gainmap_host(C.byref(s_img), C.byref(m_img), C.byref(mdh), abi.OUTPUT_HDR_HLG,
-                                                 FLT_MAX, C.byref(o_img))
-            assert st == 0, lib.uhdrb200_last_error()
+        list(pool.map(e2e_one, range(E)))
 
     e2e_steps = max(2, min(a.steps, 5))
     e2e_step()
@@ -362,7 +375,8 @@ def main():
         "stage_mpix_s": {"generate": B * PIX / gen_ms / 1e3, "apply": B * PIX / app_ms / 1e3},
         "e2e": {"value": world * E * PIX * e2e_steps / (e2e_ms * 1e-3) / 1e6, "unit": UNIT, "h2d_bytes_per_step": h2d,
                 "d2h_bytes_per_step": d2h, "images_per_step_per_gpu": E, "steps": e2e_steps,
-                "api": "uhdrb200_generate_gainmap_host_into + uhdrb200_apply_gainmap_host, pinned host planes"},
+                "host_threads": T,
+                "api": "uhdrb200_generate_gainmap_host_into + uhdrb200_apply_gainmap_host (synchronous, reference-style), pinned host planes"},
         "gpu_launches": int(launches),
         "clocks": clk,
     }

@@ -5,37 +5,15 @@
 // HBM-bound (4.5625 B/px: 3 B P010 + 1.5 B 420 read, 1/16 B written). A warp covers 128 image
 // columns, so every row request is one fully coalesced 256 B (P010 Y/UV), 128 B (420 Y) or 64 B
 // (420 U, V) segment; the 14 independent loads per thread are issued before any use.
-// The 4x4 box average reproduces the reference's float accumulation order exactly
-// (gainmapmath.cpp:605-615: dy-major, dx-minor, one division at the end), so the only deviation
-// from the reference is the fp32 transcendental chain (~1e-6 relative, see uhdr_math.cuh).
+// The 4x4 box average (gainmapmath.cpp:605-615) is an exact integer sum (dp4a / dp2a) converted
+// once; with the fp32 transcendental chain (~1e-6 relative, uhdr_math.cuh) that is the only
+// deviation from the reference: map bytes +-1 LSB, >= 99.9 % exact.
+#include "uhdr_io.cuh"
 #include "uhdr_kernels.cuh"
 #include "uhdr_math.cuh"
 
 namespace uhdr {
 namespace {
-
-__device__ __forceinline__ uint2 ldg8(const void* p) {
-  uint2 r;
-  asm volatile("ld.global.nc.L1::no_allocate.v2.u32 {%0,%1}, [%2];" : "=r"(r.x), "=r"(r.y) : "l"(p));
-  return r;
-}
-__device__ __forceinline__ uint32_t ldg4(const void* p) {
-  uint32_t r;
-  asm volatile("ld.global.nc.L1::no_allocate.u32 %0, [%1];" : "=r"(r) : "l"(p));
-  return r;
-}
-__device__ __forceinline__ uint32_t ldg2(const void* p) {
-  uint16_t r;
-  asm volatile("ld.global.nc.L1::no_allocate.u16 %0, [%1];" : "=h"(r) : "l"(p));
-  return r;
-}
-
-// getYuv420Pixel scaling, gainmapmath.cpp:579-580
-__device__ __forceinline__ float sdr_luma(uint32_t v) { return (float)v * (1 / 255.0f); }
-__device__ __forceinline__ float sdr_chroma(uint32_t v) { return (float)((int)v - 128) * (1 / 255.0f); }
-// getP010Pixel scaling, gainmapmath.cpp:593-600 (no limited-range clamp)
-__device__ __forceinline__ float hdr_luma(uint32_t v16) { return (float)((int)(v16 >> 6) - 64) * (1 / 876.0f); }
-__device__ __forceinline__ float hdr_chroma(uint32_t v16) { return (float)((int)(v16 >> 6) - 64) * (1 / 896.0f) - 0.5f; }
 
 template <bool VEC>
 __global__ void __launch_bounds__(256) generate_kernel(GenerateParams p) {
@@ -45,9 +23,11 @@ __global__ void __launch_bounds__(256) generate_kernel(GenerateParams p) {
   if (mx >= g.map_width || my >= g.map_height) return;
   const Planes pl = p.batch ? p.batch[blockIdx.z] : p.single;
 
-  // ---- gather the raw samples of the 4x4 block (all loads first) ----
-  uint32_t sy[4][4], su[2][2], sv[2][2];  // [row][col]
-  uint32_t hy[4][4], hu[2][2], hv[2][2];
+  // ---- gather the raw samples of the 4x4 block as packed words (all loads first) ----
+  uint32_t sy[4];      // 4 x u8 luma per row
+  uint32_t su[2], sv[2];  // 2 x u8 chroma per chroma row (low 16 bits)
+  uint2 hy[4];         // 4 x u16 luma per row
+  uint2 huv[2];        // U0 V0 | U1 V1 per chroma row
   const int x0 = mx * 4, y0 = my * 4;
   {
     const uint8_t* y8 = (const uint8_t*)pl.sdr_y + (size_t)y0 * g.sdr_luma_stride + x0;
@@ -56,60 +36,64 @@ __global__ void __launch_bounds__(256) generate_kernel(GenerateParams p) {
     const uint16_t* y16 = (const uint16_t*)pl.hdr_y + (size_t)y0 * g.hdr_luma_stride + x0;
     const uint16_t* uv16 = (const uint16_t*)pl.hdr_uv + (size_t)(y0 >> 1) * g.hdr_chroma_stride + x0;
     if (VEC) {
-      uint2 a[4], c[2];
-      uint32_t b[4], d[2], e[2];
 #pragma unroll
-      for (int r = 0; r < 4; r++) a[r] = ldg8(y16 + (size_t)r * g.hdr_luma_stride);
+      for (int r = 0; r < 4; r++) hy[r] = ldg8(y16 + (size_t)r * g.hdr_luma_stride);
 #pragma unroll
-      for (int r = 0; r < 2; r++) c[r] = ldg8(uv16 + (size_t)r * g.hdr_chroma_stride);
+      for (int r = 0; r < 2; r++) huv[r] = ldg8(uv16 + (size_t)r * g.hdr_chroma_stride);
 #pragma unroll
-      for (int r = 0; r < 4; r++) b[r] = ldg4(y8 + (size_t)r * g.sdr_luma_stride);
+      for (int r = 0; r < 4; r++) sy[r] = ldg4(y8 + (size_t)r * g.sdr_luma_stride);
 #pragma unroll
       for (int r = 0; r < 2; r++) {
-        d[r] = ldg2(u8 + (size_t)r * g.sdr_chroma_stride);
-        e[r] = ldg2(v8 + (size_t)r * g.sdr_chroma_stride);
-      }
-#pragma unroll
-      for (int r = 0; r < 4; r++) {
-        hy[r][0] = a[r].x & 0xffff; hy[r][1] = a[r].x >> 16; hy[r][2] = a[r].y & 0xffff; hy[r][3] = a[r].y >> 16;
-        sy[r][0] = b[r] & 0xff; sy[r][1] = (b[r] >> 8) & 0xff; sy[r][2] = (b[r] >> 16) & 0xff; sy[r][3] = b[r] >> 24;
-      }
-#pragma unroll
-      for (int r = 0; r < 2; r++) {
-        hu[r][0] = c[r].x & 0xffff; hv[r][0] = c[r].x >> 16; hu[r][1] = c[r].y & 0xffff; hv[r][1] = c[r].y >> 16;
-        su[r][0] = d[r] & 0xff; su[r][1] = d[r] >> 8; sv[r][0] = e[r] & 0xff; sv[r][1] = e[r] >> 8;
+        su[r] = ldg2(u8 + (size_t)r * g.sdr_chroma_stride);
+        sv[r] = ldg2(v8 + (size_t)r * g.sdr_chroma_stride);
       }
     } else {
 #pragma unroll
-      for (int r = 0; r < 4; r++)
+      for (int r = 0; r < 4; r++) {
+        const uint16_t* h = y16 + (size_t)r * g.hdr_luma_stride;
+        const uint8_t* q = y8 + (size_t)r * g.sdr_luma_stride;
+        hy[r] = make_uint2((uint32_t)h[0] | ((uint32_t)h[1] << 16), (uint32_t)h[2] | ((uint32_t)h[3] << 16));
+        sy[r] = (uint32_t)q[0] | ((uint32_t)q[1] << 8) | ((uint32_t)q[2] << 16) | ((uint32_t)q[3] << 24);
+      }
 #pragma unroll
-        for (int c = 0; c < 4; c++) {
-          hy[r][c] = y16[(size_t)r * g.hdr_luma_stride + c];
-          sy[r][c] = y8[(size_t)r * g.sdr_luma_stride + c];
-        }
-#pragma unroll
-      for (int r = 0; r < 2; r++)
-#pragma unroll
-        for (int c = 0; c < 2; c++) {
-          hu[r][c] = uv16[(size_t)r * g.hdr_chroma_stride + 2 * c];
-          hv[r][c] = uv16[(size_t)r * g.hdr_chroma_stride + 2 * c + 1];
-          su[r][c] = u8[(size_t)r * g.sdr_chroma_stride + c];
-          sv[r][c] = v8[(size_t)r * g.sdr_chroma_stride + c];
-        }
+      for (int r = 0; r < 2; r++) {
+        const uint16_t* h = uv16 + (size_t)r * g.hdr_chroma_stride;
+        huv[r] = make_uint2((uint32_t)h[0] | ((uint32_t)h[1] << 16), (uint32_t)h[2] | ((uint32_t)h[3] << 16));
+        su[r] = (uint32_t)u8[(size_t)r * g.sdr_chroma_stride] | ((uint32_t)u8[(size_t)r * g.sdr_chroma_stride + 1] << 8);
+        sv[r] = (uint32_t)v8[(size_t)r * g.sdr_chroma_stride] | ((uint32_t)v8[(size_t)r * g.sdr_chroma_stride + 1] << 8);
+      }
     }
   }
 
-  // ---- 4x4 box averages in the reference's accumulation order (samplePixels) ----
-  Color3 s = {0.f, 0.f, 0.f}, h = {0.f, 0.f, 0.f};
+  // ---- 4x4 box averages (samplePixels, gainmapmath.cpp:605-615) ----
+  // The reference sums 16 float-converted samples sequentially and divides by 16. Here the
+  // samples are summed EXACTLY as integers (byte / 16-bit dot products with 1) and converted
+  // once: the result differs from the reference's float accumulation by a few 1e-7 relative,
+  // far inside the +-1 LSB contract (measured exact-match fraction in tests/ and DESIGN.md),
+  // and it removes ~300 unpack/convert/add instructions per map pixel from an issue-bound kernel.
+  // Each chroma sample covers 4 of the 16 pixels, so chroma averages are sums of 4 samples / 4.
+  uint32_t ys = 0, us, vs, yh = 0, uh = 0, vh = 0;
 #pragma unroll
-  for (int r = 0; r < 4; r++)
+  for (int r = 0; r < 4; r++) {
+    ys = __dp4a(sy[r], 0x01010101u, ys);
+    yh = __dp2a_lo(hy[r].x & 0xFFC0FFC0u, 0x0101u, yh);  // 10 MSBs only (getP010Pixel: >> 6)
+    yh = __dp2a_lo(hy[r].y & 0xFFC0FFC0u, 0x0101u, yh);
+  }
+  us = __dp4a(su[0] | (su[1] << 16), 0x01010101u, 0u);
+  vs = __dp4a(sv[0] | (sv[1] << 16), 0x01010101u, 0u);
 #pragma unroll
-    for (int c = 0; c < 4; c++) {
-      s.r += sdr_luma(sy[r][c]); s.g += sdr_chroma(su[r >> 1][c >> 1]); s.b += sdr_chroma(sv[r >> 1][c >> 1]);
-      h.r += hdr_luma(hy[r][c]); h.g += hdr_chroma(hu[r >> 1][c >> 1]); h.b += hdr_chroma(hv[r >> 1][c >> 1]);
-    }
-  s.r *= 0.0625f; s.g *= 0.0625f; s.b *= 0.0625f;  // "/16.0f" is exact either way
-  h.r *= 0.0625f; h.g *= 0.0625f; h.b *= 0.0625f;
+  for (int r = 0; r < 2; r++) {
+    const uint32_t a = huv[r].x & 0xFFC0FFC0u, b = huv[r].y & 0xFFC0FFC0u;
+    uh += (a & 0xFFFFu) + (b & 0xFFFFu);
+    vh += (a >> 16) + (b >> 16);
+  }
+  Color3 s, h;
+  s.r = (float)ys * (1.0f / (255.0f * 16.0f));                    // y / 255
+  s.g = (float)((int)us - 4 * 128) * (1.0f / (255.0f * 4.0f));        // (u - 128) / 255
+  s.b = (float)((int)vs - 4 * 128) * (1.0f / (255.0f * 4.0f));
+  h.r = (float)((int)(yh >> 6) - 16 * 64) * (1.0f / (876.0f * 16.0f));  // (y - 64) / 876, no range clamp
+  h.g = fmaf((float)((int)(uh >> 6) - 4 * 64), 1.0f / (896.0f * 4.0f), -0.5f);  // (u - 64) / 896 - 0.5
+  h.b = fmaf((float)((int)(vh >> 6) - 4 * 64), 1.0f / (896.0f * 4.0f), -0.5f);
 
   // ---- SDR: YUV->RGB, sRGB^-1, luminance * 203 (ultrahdr.cpp:316-324) ----
   const LumaCoefs lk = p.luma;
