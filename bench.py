@@ -153,6 +153,7 @@ def main():
     ap.add_argument("--e2e-images", type=int, default=16, help="4K pairs per e2e step per GPU (host planes)")
     ap.add_argument("--e2e-threads", type=int, default=4, help="host threads calling the synchronous host-pointer API concurrently")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-other-stages", action="store_true", help="skip the per-kernel rooflines of the other stages")
     ap.add_argument("--cpu-images", type=int, default=24, help="images per CPU worker process in the CPU arms")
     ap.add_argument("--cpu-worker", nargs=3, metavar=("N", "SEED", "TAG"))
     a = ap.parse_args()
@@ -283,6 +284,49 @@ def main():
     app_ms = sum(e[1].elapsed_time(e[2]) for e in ev) / a.steps
     clk = clocks.window(t0, t1) if clocks else None
 
+    # ---- the other kernels of the path (not part of `value`): per-kernel roofline on the same batch, rank 0 only
+    other = {}
+    if rank == 0 and not a.no_other_stages:
+        Bo = min(B, 32)
+        d_tm = torch.zeros((Bo, sdr_len), dtype=torch.uint8, device=dev)
+        tms = (abi.Image * Bo)()
+        for i in range(Bo):
+            tb = d_tm[i].data_ptr()
+            tms[i].data, tms[i].chroma_data = tb, tb + W * H
+            tms[i].width, tms[i].height, tms[i].colorGamut = W, H, abi.COLORGAMUT_UNSPECIFIED
+            tms[i].luma_stride, tms[i].chroma_stride, tms[i].pixelFormat = W, W // 2, abi.PIX_FMT_YUV420
+        d_big = torch.zeros((Bo, PIX * 8), dtype=torch.uint8, device=dev)
+        bigs = (abi.Image * Bo)()
+        for i in range(Bo):
+            bigs[i].data = d_big[i].data_ptr()
+        md_pq = abi.default_metadata(10000.0 / 203.0)
+
+        def timed(fn, bpp, iters=5):
+            for _ in range(2):
+                assert fn() == 0
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(iters):
+                fn()
+            e1.record()
+            torch.cuda.synchronize()
+            ms = e0.elapsed_time(e1) / iters
+            gbs = Bo * PIX * bpp / (ms * 1e-3) / 1e9
+            return {"mpix_s": Bo * PIX / ms / 1e3, "achieved_gbs": gbs, "algorithmic_bytes_per_px": bpp, "ms_per_launch": ms,
+                    "images_per_launch": Bo}
+
+        other["tonemap"] = timed(lambda: uh.toneMapBatch(Bo, hdrs, tms, stream), 4.5)
+        other["api0_fused_tonemap_generate"] = timed(lambda: uh.toneMapGenerateGainMapBatch(Bo, hdrs, abi.TF_HLG, tms, mds, maps, stream), 4.5625)
+        other["generate_pq_p3"] = timed(lambda: uh.generateGainMapBatch(Bo, sdrs, hdrs, abi.TF_PQ, mds, maps, False, stream), GEN_BPP)
+        assert uh.generateGainMapBatch(Bo, sdrs, hdrs, abi.TF_HLG, mds, maps, False, stream) == 0  # restore HLG maps
+        other["apply_rgba_f16_linear"] = timed(lambda: uh.applyGainMapBatch(Bo, sdrs, maps, md, abi.OUTPUT_HDR_LINEAR, FLT_MAX, bigs, stream), 9.5625)
+        other["apply_1010102_pq"] = timed(lambda: uh.applyGainMapBatch(Bo, sdrs, maps, md_pq, abi.OUTPUT_HDR_PQ, FLT_MAX, bigs, stream), APPLY_BPP)
+        other["apply_planar_10bit"] = timed(lambda: uh.applyGainMapBatch(Bo, sdrs, maps, md, abi.OUTPUT_HDR_LINEAR_RGB_10BIT, FLT_MAX, bigs, stream), 7.5625)
+        assert lib.uhdrb200_set_apply_mode(abi.APPLY_GENERIC) == 0
+        other["apply_1010102_hlg_generic_kernel"] = timed(lambda: uh.applyGainMapBatch(Bo, sdrs, maps, md, abi.OUTPUT_HDR_HLG, FLT_MAX, bigs, stream), APPLY_BPP, 2)
+        assert lib.uhdrb200_set_apply_mode(abi.APPLY_AUTO) == 0
+        del d_tm, d_big
+
     # ---- e2e: host planes -> C ABI host entry points -> host results (copies inside the timing)
     E = a.e2e_images
     KH = max(4, a.e2e_threads)  # one private set of pinned buffers per in-flight image
@@ -377,6 +421,7 @@ def main():
                 "d2h_bytes_per_step": d2h, "images_per_step_per_gpu": E, "steps": e2e_steps,
                 "host_threads": T,
                 "api": "uhdrb200_generate_gainmap_host_into + uhdrb200_apply_gainmap_host (synchronous, reference-style), pinned host planes"},
+        "other_stages": {k: dict(v, frac_of_hbm_peak=v["achieved_gbs"] / peak) for k, v in other.items()},
         "gpu_launches": int(launches),
         "clocks": clk,
     }

@@ -27,6 +27,9 @@ namespace {
 #ifndef UHDR_APPLY_MUFU_CHANNELS
 #define UHDR_APPLY_MUFU_CHANNELS 2  // colour channels whose srgbInvOetf runs on the XU pipe (lg2/ex2) instead of the smem table
 #endif
+#ifndef UHDR_APPLY_MUFU_CHANNELS_LINEAR
+#define UHDR_APPLY_MUFU_CHANNELS_LINEAR 2  // same, for the linear-output kernels (RGBA F16, planar 10-bit)
+#endif
 #ifndef UHDR_APPLY_MIN_BLOCKS
 #define UHDR_APPLY_MIN_BLOCKS 3
 #endif
@@ -225,7 +228,7 @@ __global__ void __launch_bounds__(kThreads, UHDR_APPLY_MIN_BLOCKS) apply_fast_ke
         const float cR = __saturatef(fmaf(yf, 1 / 255.0f, rv[r >> 1][i >> 1]));
         const float cG = __saturatef(fmaf(yf, 1 / 255.0f, gq[r >> 1][i >> 1]));
         const float cB = __saturatef(fmaf(yf, 1 / 255.0f, bu[r >> 1][i >> 1]));
-        constexpr int kX = kHasO ? UHDR_APPLY_MUFU_CHANNELS : 0;
+        constexpr int kX = kHasO ? UHDR_APPLY_MUFU_CHANNELS : UHDR_APPLY_MUFU_CHANNELS_LINEAR;
         const float sR = kX >= 2 ? srgb_inv_mufu(cR) : uni_eval<kSSeg>(tS, cR);
         const float sG = kX >= 3 ? srgb_inv_mufu(cG) : uni_eval<kSSeg>(tS, cG);
         const float sB = kX >= 1 ? srgb_inv_mufu(cB) : uni_eval<kSSeg>(tS, cB);
@@ -236,9 +239,23 @@ __global__ void __launch_bounds__(kThreads, UHDR_APPLY_MIN_BLOCKS) apply_fast_ke
           px[i][2] = floor_bits(seg_eval<23 - kOBits>(tO, fmaf(sB, fi, p.e0)));
           if (MASK) { px[i][0] &= 0x3ffu; px[i][1] &= 0x3ffu; px[i][2] &= 0x3ffu; }
         } else if (PACK == kPackF16) {
-          px[i][0] = float_to_half_ref(sR * fi);
-          px[i][1] = float_to_half_ref(sG * fi);
-          px[i][2] = float_to_half_ref(sB * fi);
+          // floatToHalf (gainmapmath.h:136-147). Values here are in [0, 4): for the normal-half range
+          // (exponent field of bits + 0x1000 >= 113) the routine reduces to a shift and a re-bias;
+          // darker values (half subnormals, flush to zero) take the full bit-exact routine.
+          const float eR = sR * fi, eG = sG * fi, eB = sB * fi;
+          const uint32_t bR = __float_as_uint(eR) + 0x1000u, bG = __float_as_uint(eG) + 0x1000u, bB = __float_as_uint(eB) + 0x1000u;
+          if (min(bR, min(bG, bB)) >= 0x38800000u) {
+            px[i][0] = (bR >> 13) - 0x1C000u;
+            px[i][1] = (bG >> 13) - 0x1C000u;
+            px[i][2] = (bB >> 13) - 0x1C000u;
+          } else {  // per channel: normal / flushed to zero (exponent field <= 101) / half subnormal (rare)
+            px[i][0] = bR >= 0x38800000u ? (bR >> 13) - 0x1C000u : 0u;
+            px[i][1] = bG >= 0x38800000u ? (bG >> 13) - 0x1C000u : 0u;
+            px[i][2] = bB >= 0x38800000u ? (bB >> 13) - 0x1C000u : 0u;
+            if (bR - 0x33000000u < 0x05800000u) px[i][0] = float_to_half_ref(eR);
+            if (bG - 0x33000000u < 0x05800000u) px[i][1] = float_to_half_ref(eG);
+            if (bB - 0x33000000u < 0x05800000u) px[i][2] = float_to_half_ref(eB);
+          }
         } else {
           px[i][0] = to_10bit(sR * fi);
           px[i][1] = to_10bit(sG * fi);

@@ -303,7 +303,7 @@ void set_sdr_planes(Planes& pl, const uhdrb200_image& im) {
 
 // ================================================================ device-pointer cores
 int generate_core(int n, const uhdrb200_image* sdr, const uhdrb200_image* hdr, int hdr_tf,
-                  uhdrb200_metadata* md, uhdrb200_image* dest, int sdr_is_601, cudaStream_t s) {
+                  uhdrb200_metadata* md, uhdrb200_image* dest, int sdr_is_601, cudaStream_t s, bool fused = false) {
   if (n <= 0) return UHDRB200_NO_ERROR;
   if (!sdr || !hdr || !md || !dest) return UHDRB200_ERROR_BAD_PTR;
   for (int i = 0; i < n; i++) {
@@ -353,7 +353,7 @@ int generate_core(int n, const uhdrb200_image* sdr, const uhdrb200_image* hdr, i
   BatchSlot* slot = nullptr;
   if (n == 1) p.single = v[0];
   else if ((st = stage_batch(v, s, &p.batch, &slot))) return st;
-  cudaError_t e = launch_generate_impl(p, n, vec, s);
+  cudaError_t e = fused ? launch_api0_fused_impl(p, n, s) : launch_generate_impl(p, n, vec, s);
   if (slot) cudaEventRecord(slot->done, s);
   if (e != cudaSuccess) return fail(e, "generate kernel launch");
   g_launches++;
@@ -519,6 +519,39 @@ int convert_yuv_core(uhdrb200_image* im, int src_enc, int dst_enc, cudaStream_t 
   return UHDRB200_NO_ERROR;
 }
 
+// API-0 (jpegr.cpp:167-225): toneMap(hdr -> sdr) then generateGainMap(sdr, hdr). One fused launch when the
+// layout allows it (width, height % 4 == 0, vector-aligned planes), else the two kernels back to back.
+int api0_core(int n, const uhdrb200_image* hdr, int hdr_tf, uhdrb200_image* sdr, uhdrb200_metadata* md,
+              uhdrb200_image* dest, cudaStream_t s) {
+  if (n <= 0) return UHDRB200_NO_ERROR;
+  if (!hdr || !sdr || !md || !dest) return UHDRB200_ERROR_BAD_PTR;
+  for (int i = 0; i < n; i++) {
+    int st = validate_tonemap(&hdr[i], &sdr[i]);
+    if (st) return st;
+    uhdrb200_image tmp = sdr[i];
+    tmp.colorGamut = hdr[i].colorGamut;  // what toneMap would have set (ultrahdr.cpp:556)
+    if ((st = validate_generate(&tmp, &hdr[i], hdr_tf, &md[i], &dest[i]))) return st;
+    if (!dest[i].data) return UHDRB200_ERROR_BAD_PTR;
+  }
+  bool fused = true;
+  for (int i = 0; i < n && fused; i++) {
+    Geometry g = geometry_of(&sdr[i], &hdr[i]);
+    Planes pl;
+    memset(&pl, 0, sizeof pl);
+    set_sdr_planes(pl, sdr[i]);
+    pl.hdr_y = hdr[i].data;
+    pl.hdr_uv = hdr[i].chroma_data;
+    fused = api0_fused_ok(g, pl) && hdr[i].luma_stride != 0 && (i == 0 || same_layout(sdr[i], sdr[0]));
+  }
+  if (!fused) {
+    int st = tonemap_core(n, hdr, sdr, s);
+    if (st) return st;
+    return generate_core(n, sdr, hdr, hdr_tf, md, dest, 0, s);
+  }
+  for (int i = 0; i < n; i++) sdr[i].colorGamut = hdr[i].colorGamut;
+  return generate_core(n, sdr, hdr, hdr_tf, md, dest, 0, s, true);
+}
+
 }  // namespace
 
 // ================================================================ host-pointer staging helpers
@@ -658,6 +691,38 @@ int convert_yuv_host(uhdrb200_image* im, int src_enc, int dst_enc) {
   return UHDRB200_NO_ERROR;
 }
 
+int api0_host(const uhdrb200_image* hdr, int hdr_tf, uhdrb200_image* sdr, uhdrb200_metadata* md, uhdrb200_image* dest,
+              void* map_buf, size_t map_buf_bytes) {
+  int st = validate_tonemap(hdr, sdr);
+  if (st) return st;
+  uhdrb200_image tmp = *sdr;
+  tmp.colorGamut = hdr->colorGamut;
+  if ((st = validate_generate(&tmp, hdr, hdr_tf, md, dest))) return st;
+  const size_t mw = hdr->width / 4, mh = hdr->height / 4, mbytes = mw * mh;
+  if (!map_buf || map_buf_bytes < mbytes) return -20004;  // ERROR_ULTRAHDR_BUFFER_TOO_SMALL
+  if ((st = ensure_ctx())) return st;
+  Ctx& c = t_ctx;
+  const size_t ly = hdr->height ? 2 * (hdr->luma_stride * (hdr->height - 1) + hdr->width) : 0;
+  const size_t dl = sdr->luma_stride * sdr->height, dc = 2 * (sdr->chroma_stride * (sdr->height / 2));
+  if ((st = upload(c.buf[2], hdr->data, ly, c.stream))) return st;
+  if ((st = upload(c.buf[3], hdr->chroma_data, p010_chroma_bytes(*hdr), c.stream))) return st;
+  if ((st = reserve(c.buf[6], dl ? dl : 1)) || (st = reserve(c.buf[7], dc ? dc : 1)) || (st = reserve(c.buf[4], mbytes ? mbytes : 1))) return st;
+  uhdrb200_image dh = *hdr, ds = *sdr, dm;
+  memset(&dm, 0, sizeof dm);
+  dh.data = c.buf[2].p; dh.chroma_data = c.buf[3].p;
+  ds.data = c.buf[6].p; ds.chroma_data = c.buf[7].p;
+  dm.data = c.buf[4].p;
+  if ((st = api0_core(1, &dh, hdr_tf, &ds, md, &dm, c.stream))) return st;
+  if (dl) CU(cudaMemcpyAsync(sdr->data, c.buf[6].p, dl, cudaMemcpyDeviceToHost, c.stream));
+  if (dc) CU(cudaMemcpyAsync(sdr->chroma_data, c.buf[7].p, dc, cudaMemcpyDeviceToHost, c.stream));
+  if (mbytes) CU(cudaMemcpyAsync(map_buf, c.buf[4].p, mbytes, cudaMemcpyDeviceToHost, c.stream));
+  CU(cudaStreamSynchronize(c.stream));
+  sdr->colorGamut = hdr->colorGamut;
+  fill_map_desc(dest, mw, mh);
+  dest->data = map_buf;
+  return UHDRB200_NO_ERROR;
+}
+
 }  // namespace
 
 // ================================================================ extern "C"
@@ -752,6 +817,19 @@ int uhdrb200_tonemap_dev(const uhdrb200_image* src, uhdrb200_image* dest, void* 
 }
 int uhdrb200_tonemap_batch_dev(int n, const uhdrb200_image* src, uhdrb200_image* dest, void* stream) {
   return tonemap_core(n, src, dest, (cudaStream_t)stream);
+}
+int uhdrb200_tonemap_generate_gainmap_host_into(const uhdrb200_image* p010, int hdr_tf, uhdrb200_image* sdr_dest,
+                                                uhdrb200_metadata* metadata, uhdrb200_image* map_dest, void* map_buf,
+                                                size_t map_buf_bytes) {
+  return api0_host(p010, hdr_tf, sdr_dest, metadata, map_dest, map_buf, map_buf_bytes);
+}
+int uhdrb200_tonemap_generate_gainmap_dev(const uhdrb200_image* p010, int hdr_tf, uhdrb200_image* sdr_dest,
+                                          uhdrb200_metadata* metadata, uhdrb200_image* map_dest, void* stream) {
+  return api0_core(1, p010, hdr_tf, sdr_dest, metadata, map_dest, (cudaStream_t)stream);
+}
+int uhdrb200_tonemap_generate_gainmap_batch_dev(int n, const uhdrb200_image* p010, int hdr_tf, uhdrb200_image* sdr_dest,
+                                                uhdrb200_metadata* metadata, uhdrb200_image* map_dest, void* stream) {
+  return api0_core(n, p010, hdr_tf, sdr_dest, metadata, map_dest, (cudaStream_t)stream);
 }
 int uhdrb200_convert_yuv_host(uhdrb200_image* image, int src_encoding, int dest_encoding) {
   return convert_yuv_host(image, src_encoding, dest_encoding);

@@ -15,7 +15,12 @@
 namespace uhdr {
 namespace {
 
-template <bool VEC>
+// FUSED = API-0 (lib/src/jpegr.cpp:167-225): the SDR image is not an input but toneMap(HDR)
+// (ultrahdr.cpp:517-558: 8-bit sample = top 8 bits of the P010 word). The thread derives its
+// 4x4 SDR block from the P010 block it already holds, WRITES it to the SDR planes (with the
+// reference's zero-filled stride tails) and feeds it to the same gain computation: P010 is read
+// once and nothing is re-read (4.5625 B/px instead of 4.5 + 4.5625). Requires width, height % 4 == 0.
+template <bool VEC, bool FUSED>
 __global__ void __launch_bounds__(256) generate_kernel(GenerateParams p) {
   const Geometry& g = p.g;
   const int mx = blockIdx.x * 32 + threadIdx.x;
@@ -35,7 +40,38 @@ __global__ void __launch_bounds__(256) generate_kernel(GenerateParams p) {
     const uint8_t* v8 = (const uint8_t*)pl.sdr_v + (size_t)(y0 >> 1) * g.sdr_chroma_stride + (x0 >> 1);
     const uint16_t* y16 = (const uint16_t*)pl.hdr_y + (size_t)y0 * g.hdr_luma_stride + x0;
     const uint16_t* uv16 = (const uint16_t*)pl.hdr_uv + (size_t)(y0 >> 1) * g.hdr_chroma_stride + x0;
-    if (VEC) {
+    if (FUSED) {
+#pragma unroll
+      for (int r = 0; r < 4; r++) hy[r] = ldg8(y16 + (size_t)r * g.hdr_luma_stride);
+#pragma unroll
+      for (int r = 0; r < 2; r++) huv[r] = ldg8(uv16 + (size_t)r * g.hdr_chroma_stride);
+      uint8_t* oy = const_cast<uint8_t*>(y8);
+      uint8_t* ou = const_cast<uint8_t*>(u8);
+      uint8_t* ov = const_cast<uint8_t*>(v8);
+#pragma unroll
+      for (int r = 0; r < 4; r++) {
+        sy[r] = __byte_perm(hy[r].x, hy[r].y, 0x7531);  // high byte of each u16 == (v >> 6) >> 2, ultrahdr.cpp:530-531
+        *reinterpret_cast<uint32_t*>(oy + (size_t)r * g.sdr_luma_stride) = sy[r];
+      }
+#pragma unroll
+      for (int r = 0; r < 2; r++) {
+        su[r] = __byte_perm(huv[r].x, huv[r].y, 0x7751) & 0xFFFFu;  // U0 U1
+        sv[r] = __byte_perm(huv[r].x, huv[r].y, 0x7773) & 0xFFFFu;  // V0 V1
+        *reinterpret_cast<uint16_t*>(ou + (size_t)r * g.sdr_chroma_stride) = (uint16_t)su[r];
+        *reinterpret_cast<uint16_t*>(ov + (size_t)r * g.sdr_chroma_stride) = (uint16_t)sv[r];
+      }
+      if (mx == g.map_width - 1) {  // stride tails, ultrahdr.cpp:533-535, 551-554
+        for (int x = g.width; x < g.sdr_luma_stride; x++)
+#pragma unroll
+          for (int r = 0; r < 4; r++) oy[(size_t)r * g.sdr_luma_stride + (x - x0)] = 0;
+        for (int x = g.width / 2; x < g.sdr_chroma_stride; x++)
+#pragma unroll
+          for (int r = 0; r < 2; r++) {
+            ou[(size_t)r * g.sdr_chroma_stride + (x - (x0 >> 1))] = 0;
+            ov[(size_t)r * g.sdr_chroma_stride + (x - (x0 >> 1))] = 0;
+          }
+      }
+    } else if (VEC) {
 #pragma unroll
       for (int r = 0; r < 4; r++) hy[r] = ldg8(y16 + (size_t)r * g.hdr_luma_stride);
 #pragma unroll
@@ -136,8 +172,20 @@ cudaError_t launch_generate_impl(const GenerateParams& p, int n, bool vec, cudaS
   if (p.g.map_width == 0 || p.g.map_height == 0 || n == 0) return cudaSuccess;
   dim3 block(32, 8, 1);
   dim3 grid((p.g.map_width + 31) / 32, (p.g.map_height + 7) / 8, n);
-  if (vec) generate_kernel<true><<<grid, block, 0, s>>>(p);
-  else generate_kernel<false><<<grid, block, 0, s>>>(p);
+  if (vec) generate_kernel<true, false><<<grid, block, 0, s>>>(p);
+  else generate_kernel<false, false><<<grid, block, 0, s>>>(p);
+  return cudaGetLastError();
+}
+
+// API-0 fused toneMap + generateGainMap: the sdr_* planes of `Planes` are OUTPUTS here.
+bool api0_fused_ok(const Geometry& g, const Planes& pl) {
+  return g.width % 4 == 0 && g.height % 4 == 0 && g.width > 0 && g.height > 0 && generate_vec_ok(g, pl);
+}
+cudaError_t launch_api0_fused_impl(const GenerateParams& p, int n, cudaStream_t s) {
+  if (p.g.map_width == 0 || p.g.map_height == 0 || n == 0) return cudaSuccess;
+  dim3 block(32, 8, 1);
+  dim3 grid((p.g.map_width + 31) / 32, (p.g.map_height + 7) / 8, n);
+  generate_kernel<true, true><<<grid, block, 0, s>>>(p);
   return cudaGetLastError();
 }
 

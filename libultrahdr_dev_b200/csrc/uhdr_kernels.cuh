@@ -116,6 +116,8 @@ bool apply_vec_ok(const Geometry& g, const Planes& pl);
 bool tonemap_vec_ok(const Geometry& g, const Planes& pl);
 bool convert_yuv_vec_ok(const Geometry& g, const Planes& pl);
 cudaError_t launch_generate_impl(const GenerateParams& p, int n, bool vec, cudaStream_t s);
+bool api0_fused_ok(const Geometry& g, const Planes& pl);
+cudaError_t launch_api0_fused_impl(const GenerateParams& p, int n, cudaStream_t s);
 cudaError_t launch_apply_impl(const ApplyParams& p, int n, bool vec, cudaStream_t s);
 // fast path: scale 4, vector-aligned planes, gain factor bounded so that e + e0 < 2^kOHiExp
 bool apply_fast_ok(const Geometry& g, const Planes& pl);

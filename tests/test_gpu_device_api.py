@@ -277,3 +277,85 @@ def test_config5_image_sharded_batch_checksum(uh, orc, torch_cuda):
         d.data = o.ctypes.data
         assert uh.applyGainMap(hs, abi.host_map(single, w // 4, h // 4), md, abi.OUTPUT_HDR_HLG, FLT_MAX, d) == 0
         assert int(o.view(np.int32).astype(np.int64).sum()) == int(sums[i])
+
+
+# ------------------------------------------------------------------------- N2: fused API-0 (toneMap + generate)
+@pytest.mark.parametrize("w,h,ls,cs,dls", [
+    (256, 128, None, None, None),   # packed
+    (136, 72, 144, 152, 144),       # ALIGNM(w,16) destination stride with zero-filled tails (jpegr.cpp:185), padded source
+    (1280, 720, None, None, 1280),
+    (130, 66, None, None, 144),     # not multiples of 4 -> two-kernel fallback, same results
+    (8, 4, None, None, 16),
+])
+def test_api0_fused_equals_tonemap_then_generate(uh, orc, w, h, ls, cs, dls):
+    _, hdr_b = synth.natural_pair(w, h, 9, abi.TF_HLG, 2, 2, hdr_luma_stride=ls, hdr_chroma_stride=cs)
+    hdr = abi.host_p010(hdr_b, w, h, 2, ls, cs)
+    dls = dls or w
+    dcs = dls // 2
+    # reference flow, two calls
+    sdr_a = np.full(abi.yuv420_size(w, h, dls, dcs), 0x55, dtype=np.uint8)
+    sa = abi.host_yuv420(sdr_a, w, h, -1, dls, dcs)
+    assert uh.toneMap(hdr, sa) == 0
+    md_a, dest = abi.Metadata(), abi.Image()
+    assert uh.generateGainMap(sa, hdr, abi.TF_HLG, md_a, dest) == 0
+    map_a = take_map(dest)
+    # one call
+    sdr_b = np.full(abi.yuv420_size(w, h, dls, dcs), 0x55, dtype=np.uint8)
+    sb = abi.host_yuv420(sdr_b, w, h, -1, dls, dcs)
+    map_b = np.zeros((h // 4) * (w // 4), dtype=np.uint8)
+    md_b, mdesc = abi.Metadata(), abi.Image()
+    n0 = uh.lib.uhdrb200_launch_count()
+    assert uh.toneMapGenerateGainMapInto(hdr, abi.TF_HLG, sb, md_b, mdesc, map_b) == 0
+    launches = uh.lib.uhdrb200_launch_count() - n0
+    assert launches == (1 if (w % 4 == 0 and h % 4 == 0 and w >= 4) else 2)
+    assert sb.colorGamut == 2 and (mdesc.width, mdesc.height, mdesc.pixelFormat) == (w // 4, h // 4, abi.PIX_FMT_MONOCHROME)
+    assert np.array_equal(sdr_a, sdr_b), "fused SDR planes (incl. stride tails) differ from toneMap"
+    assert np.array_equal(map_a.ravel(), map_b) and md_a.as_dict() == md_b.as_dict()
+    # and against the oracle's two-step flow
+    sdr_o = np.full(abi.yuv420_size(w, h, dls, dcs), 0x55, dtype=np.uint8)
+    so = abi.host_yuv420(sdr_o, w, h, -1, dls, dcs)
+    assert orc.tonemap(hdr, so) == 0 and np.array_equal(sdr_o, sdr_b)
+    _, want, _, _ = orc.generate_gainmap(so, hdr, abi.TF_HLG)
+    parity.compare_bytes(map_b, want, "api0 fused map", min_exact=0.99)
+
+
+def test_api0_fused_error_codes(uh):
+    w, h = 32, 16
+    _, hdr_b = synth.uniform_pair(w, h, 1)
+    hdr = abi.host_p010(hdr_b, w, h, 2)
+    sdr_b = np.zeros(abi.yuv420_size(w, h), dtype=np.uint8)
+    mp = np.zeros(32, dtype=np.uint8)
+    md, d = abi.Metadata(), abi.Image()
+    assert uh.toneMapGenerateGainMapInto(None, abi.TF_HLG, abi.host_yuv420(sdr_b, w, h, -1), md, d, mp) == abi.ERROR_BAD_PTR
+    assert uh.toneMapGenerateGainMapInto(hdr, abi.TF_HLG, abi.host_yuv420(sdr_b, w, h - 2, -1), md, d, mp) == abi.ERROR_RESOLUTION_MISMATCH
+    assert uh.toneMapGenerateGainMapInto(abi.host_p010(hdr_b, w, h, -1), abi.TF_HLG, abi.host_yuv420(sdr_b, w, h, -1), md, d, mp) == abi.ERROR_INVALID_COLORGAMUT
+    assert uh.toneMapGenerateGainMapInto(hdr, abi.TF_SRGB, abi.host_yuv420(sdr_b, w, h, -1), md, d, mp) == abi.ERROR_INVALID_TRANS_FUNC
+
+
+def test_api0_fused_batch_device(uh, torch_cuda):
+    t = torch_cuda
+    w, h, n = 256, 128, 6
+    hdr_bufs = [synth.natural_pair(w, h, 20 + i, abi.TF_PQ, 2, 2)[1] for i in range(n)]
+    keep, hdrs, sdrs, maps = [], (abi.Image * n)(), (abi.Image * n)(), (abi.Image * n)()
+    mds = (abi.Metadata * n)()
+    d_sdr = t.zeros((n, abi.yuv420_size(w, h)), dtype=t.uint8, device="cuda")
+    d_map = t.zeros((n, w * h // 16), dtype=t.uint8, device="cuda")
+    for i in range(n):
+        a, himg = dev_p010(t, hdr_bufs[i], w, h, 2)
+        keep.append(a)
+        hdrs[i] = himg
+        sdrs[i] = abi.host_yuv420(np.zeros(1, np.uint8), w, h, -1)
+        sdrs[i].data, sdrs[i].chroma_data = d_sdr[i].data_ptr(), d_sdr[i].data_ptr() + w * h
+        maps[i].data = d_map[i].data_ptr()
+    n0 = uh.lib.uhdrb200_launch_count()
+    assert uh.toneMapGenerateGainMapBatch(n, hdrs, abi.TF_PQ, sdrs, mds, maps, t.cuda.current_stream().cuda_stream) == 0
+    t.cuda.synchronize()
+    assert uh.lib.uhdrb200_launch_count() - n0 == 1
+    for i in range(n):
+        hh = abi.host_p010(hdr_bufs[i], w, h, 2)
+        sb = np.zeros(abi.yuv420_size(w, h), dtype=np.uint8)
+        mb = np.zeros(w * h // 16, dtype=np.uint8)
+        md, md_desc = abi.Metadata(), abi.Image()
+        assert uh.toneMapGenerateGainMapInto(hh, abi.TF_PQ, abi.host_yuv420(sb, w, h, -1), md, md_desc, mb) == 0
+        assert np.array_equal(d_sdr[i].cpu().numpy(), sb) and np.array_equal(d_map[i].cpu().numpy(), mb)
+        assert sdrs[i].colorGamut == 2 and mds[i].as_dict() == md.as_dict()
