@@ -107,19 +107,53 @@ def cpu_arm(images_per_worker, workers=None):
 
 # ------------------------------------------------------------------------------------ clocks
 class ClockSampler:
+    """Samples SM clock, power and throttle reasons of one GPU every ~5 ms through NVML (falls back to
+    `nvidia-smi -lms`) while the timed region runs; window(t0, t1) summarises the samples inside it."""
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
     def __init__(self, index):
-        self.rows, self.proc = [], None
+        self.rows, self.proc, self.stop_flag, self.max_mhz = [], None, False, None
+        try:
+            import pynvml
+
+            pynvml.nvmlInit()
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            phys = int(vis.split(",")[index]) if vis and all(v.strip().isdigit() for v in vis.split(",")) else index
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(phys)
+            self.nv = pynvml
+            self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+            self.th = threading.Thread(target=self._poll, daemon=True)
+            self.th.start()
+            return
+        except Exception:
+            self.nv = None
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(index), "--query-gpu=" + self.Q,
-                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                          "--format=csv,noheader,nounits", "-lms", "20"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.th = threading.Thread(target=self._read, daemon=True)
             self.th.start()
         except OSError:
             self.proc = None
+
+    def _poll(self):
+        nv = self.nv
+        bits = {"hw_slowdown": nv.nvmlClocksEventReasonHwSlowdown if hasattr(nv, "nvmlClocksEventReasonHwSlowdown") else 0x8,
+                "hw_thermal_slowdown": 0x40, "sw_thermal_slowdown": 0x20, "sw_power_cap": 0x4}
+        while not self.stop_flag:
+            try:
+                mhz = nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)
+                try:
+                    r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                except Exception:
+                    r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                pw = nv.nvmlDeviceGetPowerUsage(self.h) / 1000.0
+                self.rows.append((time.perf_counter(), [str(mhz), str(self.max_mhz), str(pw)] +
+                                  ["Active" if r & bits[k] else "Not Active" for k in ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")]))
+            except Exception:
+                pass
+            time.sleep(0.005)
 
     def _read(self):
         for line in self.proc.stdout:
@@ -128,6 +162,7 @@ class ClockSampler:
     def window(self, t0, t1):
         rows = [r for t, r in self.rows if t0 <= t <= t1] or [r for _, r in self.rows[-3:]]
         sm = sorted(float(r[0]) for r in rows if r and r[0].replace(".", "").isdigit())
+        pw = sorted(float(r[2]) for r in rows if len(r) > 2 and r[2].replace(".", "").isdigit())
         reasons = set()
         for r in rows:
             for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[3:7]):
@@ -135,9 +170,10 @@ class ClockSampler:
                     reasons.add(name)
         mx = [float(r[1]) for r in rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx[0] if mx else None,
-                "reasons": sorted(reasons), "samples": len(rows)}
+                "power_w_median": pw[len(pw) // 2] if pw else None, "reasons": sorted(reasons), "samples": len(rows)}
 
     def stop(self):
+        self.stop_flag = True
         if self.proc:
             self.proc.terminate()
 
@@ -402,6 +438,19 @@ def main():
         peak, peak_src = float(peaks["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
     except (OSError, KeyError, ValueError):
         peak = 6650.0
+    # DRAM bytes per pixel of each kernel from the committed `ncu --set full` capture of this command
+    # (profiles/ncu_traffic.json, written by scripts/ncu_traffic.py from the .ncu-rep raw page).
+    traffic = {}
+    try:
+        with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
+            traffic = json.load(f)
+    except (OSError, ValueError):
+        pass
+
+    def traffic_of(kernel):
+        t = traffic.get(kernel)
+        return t["dram_bytes_per_pixel"] * B * PIX if t else None
+
     app_gbs = B * PIX * APPLY_BPP / (app_ms * 1e-3) / 1e9
     gen_gbs = B * PIX * GEN_BPP / (gen_ms * 1e-3) / 1e9
     value = world * B * PIX * a.steps / (total_ms * 1e-3) / 1e6
@@ -410,11 +459,11 @@ def main():
         "ms_per_step": total_ms / a.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32", "data": f"synthetic ({K} distinct seeded natural pairs per rank replicated into {B} device slots)",
         "config": config,
-        "roofline": {"bound": "hbm", "kernel": "apply_kernel (applyGainMap -> RGBA1010102 HLG)", "achieved": app_gbs,
-                     "peak": peak, "unit": "GB/s", "frac": app_gbs / peak, "traffic": None, "peak_source": peak_src,
+        "roofline": {"bound": "hbm", "kernel": "apply_fast_kernel<PACK_1010102> (applyGainMap -> RGBA1010102 HLG)", "achieved": app_gbs,
+                     "peak": peak, "unit": "GB/s", "frac": app_gbs / peak, "traffic": traffic_of("apply_fast_kernel"), "peak_source": peak_src,
                      "ms_per_launch": app_ms, "algorithmic_bytes_per_launch": B * PIX * APPLY_BPP},
         "roofline_generate": {"bound": "hbm", "kernel": "generate_kernel", "achieved": gen_gbs, "peak": peak,
-                              "unit": "GB/s", "frac": gen_gbs / peak, "ms_per_launch": gen_ms,
+                              "unit": "GB/s", "frac": gen_gbs / peak, "traffic": traffic_of("generate_kernel"), "ms_per_launch": gen_ms,
                               "algorithmic_bytes_per_launch": B * PIX * GEN_BPP},
         "stage_mpix_s": {"generate": B * PIX / gen_ms / 1e3, "apply": B * PIX / app_ms / 1e3},
         "e2e": {"value": world * E * PIX * e2e_steps / (e2e_ms * 1e-3) / 1e6, "unit": UNIT, "h2d_bytes_per_step": h2d,
