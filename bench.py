@@ -358,6 +358,19 @@ def main():
         other["apply_rgba_f16_linear"] = timed(lambda: uh.applyGainMapBatch(Bo, sdrs, maps, md, abi.OUTPUT_HDR_LINEAR, FLT_MAX, bigs, stream), 9.5625)
         other["apply_1010102_pq"] = timed(lambda: uh.applyGainMapBatch(Bo, sdrs, maps, md_pq, abi.OUTPUT_HDR_PQ, FLT_MAX, bigs, stream), APPLY_BPP)
         other["apply_planar_10bit"] = timed(lambda: uh.applyGainMapBatch(Bo, sdrs, maps, md, abi.OUTPUT_HDR_LINEAR_RGB_10BIT, FLT_MAX, bigs, stream), 7.5625)
+        assert lib.uhdrb200_set_apply_mode(abi.APPLY_TWO_TABLE) == 0
+        other["apply_1010102_hlg_two_table_kernel"] = timed(lambda: uh.applyGainMapBatch(Bo, sdrs, maps, md, abi.OUTPUT_HDR_HLG, FLT_MAX, bigs, stream), APPLY_BPP)
+        assert lib.uhdrb200_set_apply_mode(abi.APPLY_AUTO) == 0
+        # worst case for the q-domain kernel: i.i.d. uniform 8-bit samples (SURVEY 8d "uniform"), 19 % of the channels on
+        # srgbInvOetf's linear toe -> almost every quad-row takes the exact (MUFU) branch
+        d_rnd = torch.randint(0, 256, (Bo, sdr_len), dtype=torch.uint8, device=dev)
+        rnds = (abi.Image * Bo)()
+        for i in range(Bo):
+            C.memmove(C.byref(rnds[i]), C.byref(sdrs[i]), C.sizeof(abi.Image))
+            rb = d_rnd[i].data_ptr()
+            rnds[i].data, rnds[i].chroma_data = rb, rb + W * H
+        other["apply_1010102_hlg_uniform_random_input"] = timed(lambda: uh.applyGainMapBatch(Bo, rnds, maps, md, abi.OUTPUT_HDR_HLG, FLT_MAX, bigs, stream), APPLY_BPP)
+        del d_rnd
         assert lib.uhdrb200_set_apply_mode(abi.APPLY_GENERIC) == 0
         other["apply_1010102_hlg_generic_kernel"] = timed(lambda: uh.applyGainMapBatch(Bo, sdrs, maps, md, abi.OUTPUT_HDR_HLG, FLT_MAX, bigs, stream), APPLY_BPP, 2)
         assert lib.uhdrb200_set_apply_mode(abi.APPLY_AUTO) == 0
@@ -459,8 +472,8 @@ def main():
         "ms_per_step": total_ms / a.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32", "data": f"synthetic ({K} distinct seeded natural pairs per rank replicated into {B} device slots)",
         "config": config,
-        "roofline": {"bound": "hbm", "kernel": "apply_fast_kernel<PACK_1010102> (applyGainMap -> RGBA1010102 HLG)", "achieved": app_gbs,
-                     "peak": peak, "unit": "GB/s", "frac": app_gbs / peak, "traffic": traffic_of("apply_fast_kernel"), "peak_source": peak_src,
+        "roofline": {"bound": "hbm", "kernel": "apply_q_kernel (applyGainMap -> RGBA1010102 HLG)", "achieved": app_gbs,
+                     "peak": peak, "unit": "GB/s", "frac": app_gbs / peak, "traffic": traffic_of("apply_q_kernel"), "peak_source": peak_src,
                      "ms_per_launch": app_ms, "algorithmic_bytes_per_launch": B * PIX * APPLY_BPP},
         "roofline_generate": {"bound": "hbm", "kernel": "generate_kernel", "achieved": gen_gbs, "peak": peak,
                               "unit": "GB/s", "frac": gen_gbs / peak, "traffic": traffic_of("generate_kernel"), "ms_per_launch": gen_ms,

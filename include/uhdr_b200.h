@@ -138,10 +138,12 @@ void uhdrb200_free(void* p);
 /* number of kernel launches issued by this library in the calling process (monotonic). */
 uint64_t uhdrb200_launch_count(void);
 
-/* applyGainMap kernel selection (process-wide): AUTO uses the table-driven kernel whenever the
+/* applyGainMap kernel selection (process-wide): AUTO uses the table-driven kernels whenever the
  * layout allows it (map scale 4, 4-aligned planes) and the generic kernel otherwise; GENERIC forces
- * the generic kernel (any integer scale factor, MUFU-evaluated transfer functions). */
-enum { UHDRB200_APPLY_AUTO = 0, UHDRB200_APPLY_GENERIC = 1 };
+ * the generic kernel (any integer scale factor, MUFU-evaluated transfer functions); TWO_TABLE
+ * routes RGBA1010102 outputs through the srgbInvOetf-table + OETF-table kernel instead of the
+ * single-table q-domain kernel (kept for A/B measurements and as a cross-check in the tests). */
+enum { UHDRB200_APPLY_AUTO = 0, UHDRB200_APPLY_GENERIC = 1, UHDRB200_APPLY_TWO_TABLE = 2 };
 int uhdrb200_set_apply_mode(int mode);
 
 /* ---- A1: UltraHdr::generateGainMap (ultrahdr.cpp:185-358) ---- */

@@ -17,6 +17,8 @@
 //     blocks are persistent (grid = SMs x resident blocks, grid-stride over 128x32-pixel tiles).
 //   * the gain factor 2^(logBoost * displayBoost / maxContentBoost) / displayBoost
 //     (gainmapmath.cpp:550-555, ultrahdr.cpp:451) is one FFMA + one MUFU.EX2 per pixel.
+#include <type_traits>
+
 #include "uhdr_io.cuh"
 #include "uhdr_kernels.cuh"
 #include "uhdr_math.cuh"
@@ -69,6 +71,38 @@ __device__ __forceinline__ uint32_t floor_bits(float v) {
 __device__ __forceinline__ float srgb_inv_mufu(float c) {
   const float pw = mufu_ex2(2.4f * mufu_lg2(fmaf(c, (float)(1.0 / 1.055), (float)(0.055 / 1.055))));
   return c <= 0.04045f ? c * (float)(1.0 / 12.92) : pw;
+}
+
+// same, on a static shared array: the table's link-time offset and -BASE fold into the LDS immediate
+template <int SHIFT, int BASE, int N>
+__device__ __forceinline__ float seg_eval_static(const float2 (&tab)[N], float x) {
+  const float2 ab = tab[(int)(__float_as_uint(x) >> SHIFT) - BASE];
+  return fmaf(ab.y, x, ab.x);
+}
+
+// P table whose shared-memory ADDRESS is the float's bit-field: the table sits at a shared address
+// congruent to 8 * (kPBase mod 4096) modulo 32 KB, so entry address = ((bits >> 12) & 0x7ff8) | hi
+// with `hi` = the 32 KB-aligned part of the table address: SHF + LOP3, no base-register add.
+__device__ __forceinline__ float p_eval(uint32_t hi, float x) {
+  const uint32_t addr = ((__float_as_uint(x) >> (20 - kPBits)) & 0x7ff8u) | hi;
+  float a, b;
+  asm("ld.shared.v2.f32 {%0,%1}, [%2];" : "=f"(a), "=f"(b) : "r"(addr));
+  return fmaf(b, x, a);
+}
+constexpr uint32_t kPRing = 8u * (kPBase & 4095);  // 6144: offset of the first entry inside its 32 KB ring
+static_assert(kPBits == 8 && kPRing + kPEntries * 8 <= 32768, "P table must not wrap inside the 32 KB ring");
+
+// Dynamic shared memory the q kernel needs when its dynamic region starts at shared address dyn0
+// (= reserved shared memory per block + the kernel's static shared memory): header, padding up to
+// the ring position, table. The kernel recomputes the same layout and traps if it does not fit.
+__host__ __device__ constexpr uint32_t q_table_addr(uint32_t dyn0) {
+  return ((dyn0 + 16u + 1024u - kPRing + 32767u) & ~32767u) + kPRing;
+}
+
+__device__ __forceinline__ float add_rm(float a, float b) {
+  float r;
+  asm("add.rm.f32 %0, %1, %2;" : "=f"(r) : "f"(a), "f"(b));
+  return r;
 }
 
 __device__ __forceinline__ float ex2_fast(float x) {
@@ -290,6 +324,229 @@ __global__ void __launch_bounds__(kThreads, UHDR_APPLY_MIN_BLOCKS) apply_fast_ke
   }
 }
 
+// ---------------------------------------------------------------------------------------------
+// q-domain kernel for the RGBA1010102 outputs (HLG / PQ).
+//
+// Above its linear toe srgbInvOetf(c) = Phi^2.4 with Phi = (c + 0.055) / 1.055 (gainmapmath.cpp:153),
+// and Phi is LINEAR in the 8-bit luma: Phi = y * K + o, K = 1 / (255 * 1.055), o per channel and
+// per 2x2 chroma quad. With f' = f^(1/2.4) (the exponent's 1/2.4 is folded into the constant-bank
+// IDW weights) the reference chain  code = 1023 * OETF(f * srgbInvOetf(c))  is a function of
+// q = Phi * f' alone: code = P(q), P(q) = 1023 * OETF(q^2.4), ONE shared-memory table look-up per
+// channel instead of srgbInvOetf + OETF (2 look-ups or 1 look-up + 2 MUFU). Per channel:
+// FFMA.SAT (Phi), FFMA (q + q0), SHF + LOP3 (segment), LDS.64, FFMA (value), FADD.RM (floor).
+// The linear toe (c <= 0.04045, 8-bit code <= 10) has Phi = (c / 12.92)^(1/2.4): a quad-row of the
+// cell that contains such a channel (tested conservatively on min(y) and min(o)) takes a branch
+// that evaluates that power with MUFU lg2/ex2; everything downstream is shared.
+// two pixel rows (one row of 2x2 chroma quads) of a cell: Phi -> q -> P(q) -> floor -> pack -> 128-bit store per row
+template <bool MASK, bool kToe>
+__device__ __forceinline__ void q_rows(const uint32_t hiP, const float q0, const uint32_t uq, const uint32_t vq,
+                                       const float (&oR)[2], const float (&oG)[2], const float (&oB)[2], const float (&yf)[2][4],
+                                       const float* __restrict__ f8, uint8_t* orow, const size_t ostride) {
+  constexpr float KP = (float)(1.0 / (255.0 * 1.055));
+        float rv[2] = {0.f, 0.f}, gq[2] = {0.f, 0.f}, bu[2] = {0.f, 0.f};
+        if (kToe) {  // chroma terms in the reference's own order for the c <= 0.04045 test (ultrahdr.cpp:430-431)
+#pragma unroll
+          for (int c = 0; c < 2; c++) {
+            const float u = (float)((int)((uq >> (8 * c)) & 0xff) - 128) * (1 / 255.0f);
+            const float v = (float)((int)((vq >> (8 * c)) & 0xff) - 128) * (1 / 255.0f);
+            rv[c] = 1.402f * v;
+            gq[c] = -((0.114f * 1.772f / 0.587f) * u + (0.299f * 1.402f / 0.587f) * v);
+            bu[c] = 1.772f * u;
+          }
+        }
+#pragma unroll
+        for (int rr = 0; rr < 2; rr++) {
+          uint32_t w[4];
+#pragma unroll
+          for (int i = 0; i < 4; i++) {
+            const int c = i >> 1;
+            const float y = yf[rr][i], fi = f8[rr * 4 + i];
+            float phR = __saturatef(fmaf(y, KP, oR[c]));
+            float phG = __saturatef(fmaf(y, KP, oG[c]));
+            float phB = __saturatef(fmaf(y, KP, oB[c]));
+            if (kToe) {
+              const float cR = __saturatef(fmaf(y, 1 / 255.0f, rv[c]));
+              const float cG = __saturatef(fmaf(y, 1 / 255.0f, gq[c]));
+              const float cB = __saturatef(fmaf(y, 1 / 255.0f, bu[c]));
+              if (cR <= 0.04045f) phR = mufu_ex2((float)(1.0 / 2.4) * mufu_lg2(cR * (float)(1.0 / 12.92)));
+              if (cG <= 0.04045f) phG = mufu_ex2((float)(1.0 / 2.4) * mufu_lg2(cG * (float)(1.0 / 12.92)));
+              if (cB <= 0.04045f) phB = mufu_ex2((float)(1.0 / 2.4) * mufu_lg2(cB * (float)(1.0 / 12.92)));
+            }
+            // the P table is >= 0 everywhere (tables.cu), so floor == the reference's truncation
+            const float vR = p_eval(hiP, fmaf(phR, fi, q0));
+            const float vG = p_eval(hiP, fmaf(phG, fi, q0));
+            const float vB = p_eval(hiP, fmaf(phB, fi, q0));
+            if (MASK) {  // codes above 1023 wrap like the reference's `& 0x3ff` (gainmapmath.cpp:722-727)
+              w[i] = (floor_bits(vR) & 0x3ffu) | ((floor_bits(vG) & 0x3ffu) << 10) | ((floor_bits(vB) & 0x3ffu) << 20) | 0xC0000000u;
+            } else {
+              // floor + pack in 5 operations: G floored, moved up 10 bits inside the float (exact FFMA), R floored
+              // on top of it by one FADD.RM; B floored with a bias whose << 20 also supplies the alpha bits and
+              // cancels the 0x4B000000 of the R|G word.
+              const float Gm = add_rm(vG, 8388608.0f);
+              const float cGs = fmaf(Gm, 1024.0f, 8388608.0f - 8589934592.0f);  // 2^23 + 1024 * G
+              const float t = add_rm(vR, cGs);
+              const float Bm = add_rm(vB, 8388608.0f + 1872.0f);  // (0x750 << 20) == 0xC0000000 - 0x4B000000
+              w[i] = (__float_as_uint(Bm) << 20) + __float_as_uint(t);
+            }
+          }
+          stg16(orow + (size_t)rr * ostride, make_uint4(w[0], w[1], w[2], w[3]));
+        }
+}
+
+#ifndef UHDR_APPLYQ_MIN_BLOCKS
+#define UHDR_APPLYQ_MIN_BLOCKS 4
+#endif
+
+template <bool MASK>
+__global__ void __launch_bounds__(kThreads, UHDR_APPLYQ_MIN_BLOCKS) apply_q_kernel(const __grid_constant__ ApplyFastParams p) {
+  // dynamic shared memory: [mbarrier 16 B][e255 1 KB] ... [P table at shared address == kPRing (mod 32 KB)]
+  extern __shared__ __align__(16) uint8_t smem_dyn[];
+  uint64_t* bar = reinterpret_cast<uint64_t*>(smem_dyn);
+  float* sE = reinterpret_cast<float*>(smem_dyn + 16);
+  const uint32_t dyn0 = smem_u32(smem_dyn);
+  const uint32_t pAddr = q_table_addr(dyn0);
+  {
+    uint32_t dyn_size;
+    asm("mov.u32 %0, %%dynamic_smem_size;" : "=r"(dyn_size));
+    if (pAddr - dyn0 + kPEntries * (uint32_t)sizeof(float2) > dyn_size) __trap();
+  }
+  const uint32_t hiP = pAddr - kPRing;
+  float2* sP = reinterpret_cast<float2*>(smem_dyn + (pAddr - dyn0));
+  const int tid = threadIdx.x;
+  if (tid == 0) mbar_init(bar, 1);
+  __syncthreads();
+  if (tid == 0) {
+    constexpr uint32_t pb = kPEntries * sizeof(float2), eb = 256 * sizeof(float);
+    mbar_expect_tx(bar, pb + eb);
+    bulk_g2s(sP, p.output_format == 3 ? p.tab.p_hlg : p.tab.p_pq, pb, bar);
+    bulk_g2s(sE, p.tab.e255, eb, bar);
+  }
+  mbar_wait(bar, 0);
+
+  const Geometry& g = p.g;
+  const int mw = g.map_width, mh = g.map_height;
+  const int tiles_per_image = p.tiles_x * p.tiles_y;
+  // Phi-domain constants (double on the host side of the compiler): K = 1/(255*1.055), chroma gains of the
+  // BT.601 matrix (gainmapmath.cpp:177-196) times K, offsets = 0.055/1.055 - 128 * gain
+  constexpr double dK = 1.0 / (255.0 * 1.055);
+  constexpr double dCr = 1.402, dCb = 1.772;
+  constexpr double dGcb = 0.114 * 1.772 / 0.587, dGcr = 0.299 * 1.402 / 0.587;
+  constexpr float KP = (float)dK;
+  constexpr float kR = (float)(dCr * dK), kB = (float)(dCb * dK), kGu = (float)(-dGcb * dK), kGv = (float)(-dGcr * dK);
+  constexpr float oR0 = (float)(0.055 / 1.055 - 128.0 * dCr * dK), oB0 = (float)(0.055 / 1.055 - 128.0 * dCb * dK);
+  constexpr float oG0 = (float)(0.055 / 1.055 + 128.0 * (dGcb + dGcr) * dK);
+  constexpr float kPhiToe = 0.0905f;  // Phi(0.04045) = 0.090474; anything at or below 0.0905 takes the exact branch
+
+  const uint32_t tiles_x = p.tiles_x, tiles_y = p.tiles_y;
+  uint32_t tx, ty, z, dtx, dty, dz;
+  {
+    const uint32_t b0 = blockIdx.x, st = gridDim.x;
+    z = b0 / tiles_per_image;
+    uint32_t rem = b0 - z * tiles_per_image;
+    ty = rem / tiles_x;
+    tx = rem - ty * tiles_x;
+    dz = st / tiles_per_image;
+    rem = st - dz * tiles_per_image;
+    dty = rem / tiles_x;
+    dtx = rem - dty * tiles_x;
+  }
+  const uint32_t ls = g.sdr_luma_stride, cs = g.sdr_chroma_stride;
+
+  for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
+    const uint32_t cx = tx * kTileCellsX + (tid & 31), cy = ty * kTileCellsY + (tid >> 5);
+    const uint32_t zi = z;
+    tx += dtx;
+    if (tx >= tiles_x) { tx -= tiles_x; ty++; }
+    ty += dty;
+    if (ty >= tiles_y) { ty -= tiles_y; z++; }
+    z += dz;
+    if (cx >= (uint32_t)mw || cy >= (uint32_t)mh) continue;
+    const uint8_t *sdr_y, *sdr_u, *sdr_v, *map;
+    uint8_t* outp;
+    if (p.batch) {
+      const Planes* pl = p.batch + zi;
+      sdr_y = (const uint8_t*)__ldg((const unsigned long long*)&pl->sdr_y);
+      sdr_u = (const uint8_t*)__ldg((const unsigned long long*)&pl->sdr_u);
+      sdr_v = (const uint8_t*)__ldg((const unsigned long long*)&pl->sdr_v);
+      map = (const uint8_t*)__ldg((const unsigned long long*)&pl->map_in);
+      outp = (uint8_t*)__ldg((const unsigned long long*)&pl->out);
+    } else {
+      sdr_y = (const uint8_t*)p.single.sdr_y;
+      sdr_u = (const uint8_t*)p.single.sdr_u;
+      sdr_v = (const uint8_t*)p.single.sdr_v;
+      map = (const uint8_t*)p.single.map_in;
+      outp = (uint8_t*)p.single.out;
+    }
+    const uint8_t* yp = sdr_y + (4u * cy * ls + 4u * cx);
+    const uint32_t coff = 2u * cy * cs + 2u * cx;
+    const uint8_t* up = sdr_u + coff;
+    const uint8_t* vp = sdr_v + coff;
+
+    uint32_t yw[4], uw[2], vw[2];
+#pragma unroll
+    for (int r = 0; r < 4; r++) yw[r] = ldg4(yp + r * ls);
+#pragma unroll
+    for (int r = 0; r < 2; r++) {
+      uw[r] = ldg2(up + r * cs);
+      vw[r] = ldg2(vp + r * cs);
+    }
+    const uint32_t cxr = min(cx + 1, (uint32_t)mw - 1), cyb = min(cy + 1, (uint32_t)mh - 1);  // gainmapmath.cpp:690-697
+    const uint32_t b1 = __ldg(map + (cx + cy * mw)), b2 = __ldg(map + (cx + cyb * mw));
+    const uint32_t b3 = __ldg(map + (cxr + cy * mw)), b4 = __ldg(map + (cxr + cyb * mw));
+    const float e1 = sE[b1], e2 = sE[b2], e3 = sE[b3], e4 = sE[b4];
+
+    // ---- f' = f^(1/2.4) of the 16 pixels
+    float f[16];
+    if (cx + 1 < (uint32_t)mw && cy + 1 < (uint32_t)mh) {
+#pragma unroll
+      for (int i = 0; i < 16; i++) {
+        float ex = fmaf(e1, p.wq[i][0], p.Bq);
+        ex = fmaf(e2, p.wq[i][1], ex);
+        ex = fmaf(e3, p.wq[i][2], ex);
+        ex = fmaf(e4, p.wq[i][3], ex);
+        f[i] = ex2_fast(ex);
+      }
+    } else {  // map border: tables NR (1), NB (2), C (3)
+      const int t = (cx + 1 < (uint32_t)mw) ? 2 : ((cy + 1 < (uint32_t)mh) ? 1 : 3);
+      const float4* wt = reinterpret_cast<const float4*>(p.idw) + t * 16;
+#pragma unroll
+      for (int i = 0; i < 16; i++) {
+        const float4 w = __ldg(wt + i);
+        float gain = e1 * w.x;
+        gain = fmaf(e2, w.y, gain);
+        gain = fmaf(e3, w.z, gain);
+        gain = fmaf(e4, w.w, gain);
+        f[i] = ex2_fast(fmaf(gain, p.Aq, p.Bq));
+      }
+    }
+    uint8_t* orow = outp + (size_t)(4u * cy * (uint32_t)g.width + 4u * cx) * 4;
+    const size_t ostride = (size_t)g.width * 4;
+#pragma unroll
+    for (int qr = 0; qr < 2; qr++) {
+      // Phi-domain chroma offsets of the two 2x2 quads of this quad-row
+      float oR[2], oG[2], oB[2], yf[2][4];
+#pragma unroll
+      for (int c = 0; c < 2; c++) {
+        const float ub = (float)((uw[qr] >> (8 * c)) & 0xff), vb = (float)((vw[qr] >> (8 * c)) & 0xff);
+        oR[c] = fmaf(vb, kR, oR0);
+        oB[c] = fmaf(ub, kB, oB0);
+        oG[c] = fmaf(vb, kGv, fmaf(ub, kGu, oG0));
+      }
+#pragma unroll
+      for (int rr = 0; rr < 2; rr++)
+#pragma unroll
+        for (int i = 0; i < 4; i++) yf[rr][i] = (float)((yw[2 * qr + rr] >> (8 * i)) & 0xff);
+      const float ym0 = fminf(fminf(yf[0][0], yf[0][1]), fminf(yf[1][0], yf[1][1]));
+      const float ym1 = fminf(fminf(yf[0][2], yf[0][3]), fminf(yf[1][2], yf[1][3]));
+      const float om0 = fminf(oR[0], fminf(oG[0], oB[0])), om1 = fminf(oR[1], fminf(oG[1], oB[1]));
+      const bool toe = fminf(fmaf(ym0, KP, om0), fmaf(ym1, KP, om1)) <= kPhiToe;
+
+      if (toe) q_rows<MASK, true>(hiP, p.q0, uw[qr], vw[qr], oR, oG, oB, yf, &f[qr * 8], orow + (size_t)(2 * qr) * ostride, ostride);
+      else q_rows<MASK, false>(hiP, p.q0, uw[qr], vw[qr], oR, oG, oB, yf, &f[qr * 8], orow + (size_t)(2 * qr) * ostride, ostride);
+    }
+  }
+}
+
 bool aligned(const void* q, size_t a) { return (reinterpret_cast<uintptr_t>(q) & (a - 1)) == 0; }
 
 template <int PACK, bool MASK>
@@ -314,6 +571,34 @@ cudaError_t launch(const ApplyFastParams& p, cudaStream_t s) {
   return cudaGetLastError();
 }
 
+template <bool MASK>
+cudaError_t launch_q(const ApplyFastParams& p, cudaStream_t s) {
+  static int sms_of[64], per_sm_of[64], smem_of[64];
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  dev &= 63;
+  if (per_sm_of[dev] == 0) {
+    int n_sm = 0, n = 0, reserved = 0;
+    cudaFuncAttributes fa;
+    if ((e = cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev)) != cudaSuccess) return e;
+    if ((e = cudaDeviceGetAttribute(&reserved, cudaDevAttrReservedSharedMemoryPerBlock, dev)) != cudaSuccess) return e;
+    if ((e = cudaFuncGetAttributes(&fa, apply_q_kernel<MASK>)) != cudaSuccess) return e;
+    const uint32_t dyn0 = (uint32_t)reserved + (uint32_t)fa.sharedSizeBytes;
+    const int smem = (int)(q_table_addr(dyn0) - dyn0 + kPEntries * sizeof(float2)) + 64;  // + slack for the base alignment
+    if ((e = cudaFuncSetAttribute(apply_q_kernel<MASK>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)) != cudaSuccess) return e;
+    if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, apply_q_kernel<MASK>, kThreads, smem)) != cudaSuccess) return e;
+    sms_of[dev] = n_sm;
+    smem_of[dev] = smem;
+    per_sm_of[dev] = n > 0 ? n : 1;
+  }
+  const size_t kQSmem = (size_t)smem_of[dev];
+  const int cap = sms_of[dev] * per_sm_of[dev];
+  const int grid = p.n_tiles < cap ? p.n_tiles : cap;
+  apply_q_kernel<MASK><<<grid, kThreads, kQSmem, s>>>(p);
+  return cudaGetLastError();
+}
+
 }  // namespace
 
 bool apply_fast_ok(const Geometry& g, const Planes& pl) {
@@ -332,7 +617,9 @@ cudaError_t launch_apply_fast_impl(ApplyFastParams& p, int n, cudaStream_t s) {
   switch (p.output_format) {
     case 1: return launch<kPackF16, false>(p, s);
     case 4: return launch<kPackPlanar10, false>(p, s);
-    default: return p.need_mask ? launch<kPack1010102, true>(p, s) : launch<kPack1010102, false>(p, s);
+    default:
+      if (!p.two_table) return p.need_mask ? launch_q<true>(p, s) : launch_q<false>(p, s);
+      return p.need_mask ? launch<kPack1010102, true>(p, s) : launch<kPack1010102, false>(p, s);
   }
 }
 

@@ -155,14 +155,16 @@ int get_apply_tables(int device, ApplyTables* out) {
     *out = it->second;
     return 0;
   }
-  const size_t n2 = (size_t)kSEntries + (size_t)kSEntriesHi + 2 * (size_t)kOEntries;
+  const size_t n2 = (size_t)kSEntries + (size_t)kSEntriesHi + 2 * (size_t)kOEntries + 2 * (size_t)kPEntries;
   std::vector<float2> h2(n2);
   std::vector<float> e255(256);
   float2* hs = h2.data();
   float2* hs_hi = hs + kSEntries;
   float2* ho_hlg = hs_hi + kSEntriesHi;
   float2* ho_pq = ho_hlg + kOEntries;
-  build_apply_tables(hs, hs_hi, ho_hlg, ho_pq, e255.data());
+  float2* hp_hlg = ho_pq + kOEntries;
+  float2* hp_pq = hp_hlg + kPEntries;
+  build_apply_tables(hs, hs_hi, ho_hlg, ho_pq, hp_hlg, hp_pq, e255.data());
   char* d = nullptr;
   CU(cudaMalloc((void**)&d, n2 * sizeof(float2) + 256 * sizeof(float)));
   CU(cudaMemcpy(d, h2.data(), n2 * sizeof(float2), cudaMemcpyHostToDevice));
@@ -172,6 +174,8 @@ int get_apply_tables(int device, ApplyTables* out) {
   t.s_hi = t.s + kSEntries;
   t.o_hlg = t.s_hi + kSEntriesHi;
   t.o_pq = t.o_hlg + kOEntries;
+  t.p_hlg = t.o_pq + kOEntries;
+  t.p_pq = t.p_hlg + kPEntries;
   t.e255 = (const float*)(d + n2 * sizeof(float2));
   g_tables[device] = t;
   *out = t;
@@ -431,6 +435,12 @@ int apply_core(int n, const uhdrb200_image* sdr, const uhdrb200_image* map, cons
     idw_fill(&f.w[0][0], 4, 1, 1);  // ShepardsIDW::mWeights for scale 4 ...
     for (int i = 0; i < 16; i++)
       for (int c = 0; c < 4; c++) f.w[i][c] = (float)((double)f.w[i][c] * A);  // ... pre-multiplied by A
+    f.Aq = (float)(A / 2.4);
+    f.Bq = (float)(B / 2.4);
+    f.q0 = (float)ldexp(1.0, kPLoExp);
+    f.two_table = g_apply_mode == 2;
+    for (int i = 0; i < 16; i++)
+      for (int c = 0; c < 4; c++) f.wq[i][c] = (float)((double)f.w[i][c] / 2.4);
     f.idw = p.idw;
     if ((st = get_apply_tables(t_ctx.device, &f.tab))) return st;
     f.single = v[0];
@@ -773,7 +783,7 @@ void uhdrb200_host_free(void* p) { if (p) cudaFreeHost(p); }
 void uhdrb200_free(void* p) { free(p); }
 uint64_t uhdrb200_launch_count(void) { return g_launches.load(); }
 int uhdrb200_set_apply_mode(int mode) {
-  if (mode != UHDRB200_APPLY_AUTO && mode != UHDRB200_APPLY_GENERIC) return UHDRB200_ERROR_UNSUPPORTED_FEATURE;
+  if (mode != UHDRB200_APPLY_AUTO && mode != UHDRB200_APPLY_GENERIC && mode != UHDRB200_APPLY_TWO_TABLE) return UHDRB200_ERROR_UNSUPPORTED_FEATURE;
   g_apply_mode = mode;
   return UHDRB200_NO_ERROR;
 }

@@ -72,12 +72,21 @@ constexpr int kSEntriesHi = kSSegsHi + 2;
 constexpr int kOLoExp = -26, kOHiExp = 2, kOBits = 7;
 constexpr int kOEntries = (kOHiExp - kOLoExp) << kOBits;      // 3584 float2
 constexpr int kOBase = (kOLoExp + 127) << kOBits;
+//   P table (q-domain kernel, apply_fast.cu): srgbInvOetf above its linear toe is Phi(c)^2.4 with
+//            Phi = (c + 0.055) / 1.055 LINEAR in the 8-bit luma, so with f' = f^(1/2.4) the whole chain
+//            OETF(f * srgbInvOetf(c)) is a function of q = Phi * f' alone:
+//            P(q + 2^kPLoExp) = 1023 * OETF(q^2.4), log-spaced segments like the O table.
+constexpr int kPLoExp = -12, kPHiExp = 1, kPBits = 8;
+constexpr int kPEntries = (kPHiExp - kPLoExp) << kPBits;      // 3328 float2 = 26 KB
+constexpr int kPBase = (kPLoExp + 127) << kPBits;
 
 struct ApplyTables {       // device pointers, one set per device
   const float2* s;         // kSEntries
   const float2* s_hi;      // kSEntriesHi
   const float2* o_hlg;     // kOEntries
   const float2* o_pq;      // kOEntries
+  const float2* p_hlg;     // kPEntries
+  const float2* p_pq;      // kPEntries
   const float* e255;       // 256 floats: i / 255.0f, correctly rounded (gainmapmath.cpp:700-703)
 };
 
@@ -88,6 +97,9 @@ struct ApplyFastParams {
   float e0;                // 2^kOLoExp
   uint32_t s_bias;         // 0x4B000000 << 3 (see uni_eval in apply_fast.cu)
   int need_mask;           // 1 when 10-bit codes can exceed 1023 (displayBoost < maxContentBoost): `& 0x3ff` wraps like the reference
+  float Aq, Bq, q0;        // q-domain kernel: f' = 2^(gain * Aq + Bq) = f^(1/2.4); q0 = 2^kPLoExp
+  int two_table;           // 1: RGBA1010102 through the S+O table kernel instead of the q-domain kernel
+  float wq[16][4];         // Aq x interior IDW weights
   float w[16][4];          // A x interior IDW weights [oy * 4 + ox][k] (ShepardsIDW::mWeights, gainmapmath.h:184-228)
   const float* idw;        // all four tables (device), used by the cells on the right/bottom map border
   ApplyTables tab;
@@ -123,7 +135,7 @@ cudaError_t launch_apply_impl(const ApplyParams& p, int n, bool vec, cudaStream_
 bool apply_fast_ok(const Geometry& g, const Planes& pl);
 cudaError_t launch_apply_fast_impl(ApplyFastParams& p, int n, cudaStream_t s);
 // host: fills the double-precision-built tables (tables.cu)
-void build_apply_tables(float2* s, float2* s_hi, float2* o_hlg, float2* o_pq, float* e255);
+void build_apply_tables(float2* s, float2* s_hi, float2* o_hlg, float2* o_pq, float2* p_hlg, float2* p_pq, float* e255);
 cudaError_t launch_tonemap_impl(const ToneMapParams& p, int n, bool vec, cudaStream_t s);
 cudaError_t launch_convert_yuv_impl(const ConvertYuvParams& p, int n, bool vec, cudaStream_t s);
 

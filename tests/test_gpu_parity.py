@@ -106,14 +106,30 @@ def test_generate_strides(uh, orc, w, h, sls, scs, hls, hcs):
 
 
 # ------------------------------------------------------------------------------ applyGainMap
+MODES = [abi.APPLY_AUTO, abi.APPLY_TWO_TABLE, abi.APPLY_GENERIC]
+
+
+@pytest.fixture
+def apply_mode(uh, request):
+    """Selects the applyGainMap kernel family (uhdrb200_set_apply_mode) for one test."""
+    assert uh.lib.uhdrb200_set_apply_mode(request.param) == 0
+    yield request.param
+    assert uh.lib.uhdrb200_set_apply_mode(abi.APPLY_AUTO) == 0
+
+
+@pytest.mark.parametrize("apply_mode", MODES, indirect=True)
 @pytest.mark.parametrize("fmt", FORMATS)
-@pytest.mark.parametrize("kind", ["natural", "uniform"])
+@pytest.mark.parametrize("kind", ["natural", "uniform", "dark"])
 @pytest.mark.parametrize("max_boost", [1000.0 / 203.0, 10000.0 / 203.0])
-def test_apply_parity(uh, orc, fmt, kind, max_boost):
+def test_apply_parity(uh, orc, fmt, kind, max_boost, apply_mode):
     w, h = 512, 288
     if kind == "natural":
         sdr_b, _ = synth.natural_pair(w, h, 21)
         mp_b = synth.natural_map(w // 4, h // 4, 22)
+    elif kind == "dark":  # luma 0..24 with mild chroma: every pixel near srgbInvOetf's linear toe (c <= 0.04045)
+        rng = np.random.Generator(np.random.PCG64(25))
+        sdr_b = np.concatenate([rng.integers(0, 25, w * h, dtype=np.uint8), rng.integers(120, 137, w * h // 2, dtype=np.uint8)])
+        mp_b = synth.natural_map(w // 4, h // 4, 26)
     else:
         sdr_b, _ = synth.uniform_pair(w, h, 23)
         mp_b = np.random.Generator(np.random.PCG64(24)).integers(0, 256, (h // 4, w // 4), dtype=np.uint8)
@@ -123,7 +139,7 @@ def test_apply_parity(uh, orc, fmt, kind, max_boost):
     got, dest = gpu_apply(uh, sdr, mp, md, fmt, 3.4e38)
     assert st == 0 and (dest.width, dest.height, dest.colorGamut) == (w, h, 0)
     exact = parity.compare_output(fmt, got, want, w * h, f"apply fmt={fmt} {kind} boost={max_boost:.2f}", min_exact=0.97)
-    print(f"apply fmt={fmt} {kind} max_boost={max_boost:.2f}: exact {exact:.5f}")
+    print(f"apply mode={apply_mode} fmt={fmt} {kind} max_boost={max_boost:.2f}: exact {exact:.5f}")
 
 
 @pytest.mark.parametrize("scale", [1, 2, 4, 8, 16])
@@ -139,9 +155,10 @@ def test_apply_scale_factors(uh, orc, scale, fmt):
     parity.compare_output(fmt, got, want, w * h, f"apply scale={scale}", min_exact=0.97)
 
 
+@pytest.mark.parametrize("apply_mode", [abi.APPLY_AUTO, abi.APPLY_TWO_TABLE], indirect=True)
 @pytest.mark.parametrize("boost", [1.0, 2.0, 4.926108, 3.4e38])
 @pytest.mark.parametrize("min_boost", [1.0, 0.5])
-def test_apply_display_boost(uh, orc, boost, min_boost):
+def test_apply_display_boost(uh, orc, boost, min_boost, apply_mode):
     """max_display_boost below maxContentBoost: values can exceed 1.0 and the 10-bit pack wraps
     through `& 0x3ff` (gainmapmath.cpp:722-727) — compare modulo that wrap."""
     w, h = 256, 128
@@ -156,7 +173,7 @@ def test_apply_display_boost(uh, orc, boost, min_boost):
             g, wv = parity.unpack1010102(got, w * h)[:, :3], parity.unpack1010102(want, w * h)[:, :3]
             d = np.abs(g - wv)
             d = np.minimum(d, 1024 - d)  # +-1 LSB across the 10-bit wrap
-            assert d.max() <= 1
+            assert d.max() <= 1 and (d == 0).mean() >= 0.99
         else:
             parity.compare_output(fmt, got, want, w * h, f"apply boost={boost}")
 
@@ -175,6 +192,23 @@ def test_apply_strides(uh, orc, w, h, ls, cs):
         assert np.array_equal(a, b)
         _, want, _ = orc.apply_gainmap(abi.host_yuv420(sdr_s, w, h, 0, ls, cs), mp, md, fmt, 3.4e38)
         parity.compare_output(fmt, b, want, w * h, f"apply strided fmt={fmt}")
+
+
+@pytest.mark.parametrize("apply_mode", [abi.APPLY_AUTO, abi.APPLY_TWO_TABLE], indirect=True)
+@pytest.mark.parametrize("w,h,ls,cs", [(128, 64, 132, 70), (36, 20, 40, 24), (260, 12, 264, 132), (4, 4, None, None)])
+def test_apply_fast_path_strides(uh, orc, w, h, ls, cs, apply_mode):
+    """Map scale 4 (the table-driven kernels): strided input == packed input, ragged tiles, borders."""
+    sdr_p, _ = synth.uniform_pair(w, h, 53)
+    sdr_s, _ = synth.uniform_pair(w, h, 53, ls, cs)
+    mp_b = np.random.Generator(np.random.PCG64(54)).integers(0, 256, (h // 4, w // 4), dtype=np.uint8)
+    mp = abi.host_map(mp_b, w // 4, h // 4)
+    md = abi.default_metadata(4.926108)
+    for fmt in FORMATS:
+        a, _ = gpu_apply(uh, abi.host_yuv420(sdr_p, w, h, 0), mp, md, fmt, 3.4e38)
+        b, _ = gpu_apply(uh, abi.host_yuv420(sdr_s, w, h, 0, ls, cs), mp, md, fmt, 3.4e38)
+        assert np.array_equal(a, b)
+        _, want, _ = orc.apply_gainmap(abi.host_yuv420(sdr_s, w, h, 0, ls, cs), mp, md, fmt, 3.4e38)
+        parity.compare_output(fmt, b, want, w * h, f"apply scale-4 strided fmt={fmt}")
 
 
 # ------------------------------------------------------------------------------ convertYuv (N1)
