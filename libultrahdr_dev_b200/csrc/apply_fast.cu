@@ -80,23 +80,35 @@ __device__ __forceinline__ float seg_eval_static(const float2 (&tab)[N], float x
   return fmaf(ab.y, x, ab.x);
 }
 
-// P table whose shared-memory ADDRESS is the float's bit-field: the table sits at a shared address
-// congruent to 8 * (kPBase mod 4096) modulo 32 KB, so entry address = ((bits >> 12) & 0x7ff8) | hi
-// with `hi` = the 32 KB-aligned part of the table address: SHF + LOP3, no base-register add.
+// P table whose shared-memory ADDRESS is the float's bit-field. 16 octaves of segments form a ring of
+// kPRingBytes (32 KB at 8 bits per octave); the table (13 octaves) sits at a shared address congruent to
+// kPRing modulo the ring size, so entry address = ((bits >> (20 - kPBits)) & (kPRingBytes - 8)) | hi with
+// `hi` = the ring-aligned part of the table address: SHF + LOP3, no base-register add.
+constexpr uint32_t kPRingBytes = 128u << kPBits;
+constexpr uint32_t kPRing = 8u * (kPBase & ((16 << kPBits) - 1));  // offset of the first entry inside its ring
+static_assert(kPRing + kPEntries * 8 <= kPRingBytes, "P table must not wrap inside its ring");
 __device__ __forceinline__ float p_eval(uint32_t hi, float x) {
-  const uint32_t addr = ((__float_as_uint(x) >> (20 - kPBits)) & 0x7ff8u) | hi;
+#ifdef UHDR_P_IMAD  // shift on the FMA pipe (IMAD.HI) instead of the ALU pipe (SHF)
+  const uint32_t sh = __umulhi(__float_as_uint(x), 1u << (12 + kPBits));
+#else
+  const uint32_t sh = __float_as_uint(x) >> (20 - kPBits);
+#endif
+  const uint32_t addr = (sh & (kPRingBytes - 8u)) | hi;
   float a, b;
+#ifdef UHDR_DBG_NOLDS
+  a = __uint_as_float(addr);
+  b = 1.0f;
+#else
   asm("ld.shared.v2.f32 {%0,%1}, [%2];" : "=f"(a), "=f"(b) : "r"(addr));
+#endif
   return fmaf(b, x, a);
 }
-constexpr uint32_t kPRing = 8u * (kPBase & 4095);  // 6144: offset of the first entry inside its 32 KB ring
-static_assert(kPBits == 8 && kPRing + kPEntries * 8 <= 32768, "P table must not wrap inside the 32 KB ring");
 
 // Dynamic shared memory the q kernel needs when its dynamic region starts at shared address dyn0
 // (= reserved shared memory per block + the kernel's static shared memory): header, padding up to
 // the ring position, table. The kernel recomputes the same layout and traps if it does not fit.
 __host__ __device__ constexpr uint32_t q_table_addr(uint32_t dyn0) {
-  return ((dyn0 + 16u + 1024u - kPRing + 32767u) & ~32767u) + kPRing;
+  return ((dyn0 + 16u - kPRing + kPRingBytes - 1u) & ~(kPRingBytes - 1u)) + kPRing;
 }
 
 __device__ __forceinline__ float add_rm(float a, float b) {
@@ -339,10 +351,11 @@ __global__ void __launch_bounds__(kThreads, UHDR_APPLY_MIN_BLOCKS) apply_fast_ke
 // that evaluates that power with MUFU lg2/ex2; everything downstream is shared.
 // two pixel rows (one row of 2x2 chroma quads) of a cell: Phi -> q -> P(q) -> floor -> pack -> 128-bit store per row
 template <bool MASK, bool kToe>
-__device__ __forceinline__ void q_rows(const uint32_t hiP, const float q0, const uint32_t uq, const uint32_t vq,
+__device__ __forceinline__ void q_rows(const uint32_t hiP, const uint32_t uq, const uint32_t vq,
                                        const float (&oR)[2], const float (&oG)[2], const float (&oB)[2], const float (&yf)[2][4],
                                        const float* __restrict__ f8, uint8_t* orow, const size_t ostride) {
   constexpr float KP = (float)(1.0 / (255.0 * 1.055));
+  constexpr float q0 = 1.0f / (float)(1 << -kPLoExp);  // 2^kPLoExp as an FFMA immediate
         float rv[2] = {0.f, 0.f}, gq[2] = {0.f, 0.f}, bu[2] = {0.f, 0.f};
         if (kToe) {  // chroma terms in the reference's own order for the c <= 0.04045 test (ultrahdr.cpp:430-431)
 #pragma unroll
@@ -389,6 +402,9 @@ __device__ __forceinline__ void q_rows(const uint32_t hiP, const float q0, const
               w[i] = (__float_as_uint(Bm) << 20) + __float_as_uint(t);
             }
           }
+#ifdef UHDR_DBG_NOSTORE
+          if ((w[0] ^ w[1] ^ w[2] ^ w[3]) == 0x12345679u)
+#endif
           stg16(orow + (size_t)rr * ostride, make_uint4(w[0], w[1], w[2], w[3]));
         }
 }
@@ -397,12 +413,20 @@ __device__ __forceinline__ void q_rows(const uint32_t hiP, const float q0, const
 #define UHDR_APPLYQ_MIN_BLOCKS 4
 #endif
 
-template <bool MASK>
+#ifndef UHDR_APPLYQ_CELLS
+#define UHDR_APPLYQ_CELLS 4  // vertically adjacent map cells one thread walks per tile
+#endif
+constexpr int kQCells = UHDR_APPLYQ_CELLS;
+constexpr int kQTileRows = 8 * kQCells;  // cell rows per tile: 8 warps x kQCells
+
+// Tile = 32 x kQTileRows map cells (128 x 128 pixels for kQCells = 4). A lane owns one column of
+// cells; a warp walks kQCells cell rows downwards, so the lower pair of map samples of one cell is
+// the upper pair of the next (2 map loads per cell) and every plane pointer advances by a constant.
+template <bool MASK, bool BATCH>
 __global__ void __launch_bounds__(kThreads, UHDR_APPLYQ_MIN_BLOCKS) apply_q_kernel(const __grid_constant__ ApplyFastParams p) {
-  // dynamic shared memory: [mbarrier 16 B][e255 1 KB] ... [P table at shared address == kPRing (mod 32 KB)]
+  // dynamic shared memory: [mbarrier 16 B] ... [P table at shared address == kPRing (mod 32 KB)]
   extern __shared__ __align__(16) uint8_t smem_dyn[];
   uint64_t* bar = reinterpret_cast<uint64_t*>(smem_dyn);
-  float* sE = reinterpret_cast<float*>(smem_dyn + 16);
   const uint32_t dyn0 = smem_u32(smem_dyn);
   const uint32_t pAddr = q_table_addr(dyn0);
   {
@@ -411,21 +435,19 @@ __global__ void __launch_bounds__(kThreads, UHDR_APPLYQ_MIN_BLOCKS) apply_q_kern
     if (pAddr - dyn0 + kPEntries * (uint32_t)sizeof(float2) > dyn_size) __trap();
   }
   const uint32_t hiP = pAddr - kPRing;
-  float2* sP = reinterpret_cast<float2*>(smem_dyn + (pAddr - dyn0));
   const int tid = threadIdx.x;
   if (tid == 0) mbar_init(bar, 1);
   __syncthreads();
   if (tid == 0) {
-    constexpr uint32_t pb = kPEntries * sizeof(float2), eb = 256 * sizeof(float);
-    mbar_expect_tx(bar, pb + eb);
-    bulk_g2s(sP, p.output_format == 3 ? p.tab.p_hlg : p.tab.p_pq, pb, bar);
-    bulk_g2s(sE, p.tab.e255, eb, bar);
+    constexpr uint32_t pb = kPEntries * sizeof(float2);
+    mbar_expect_tx(bar, pb);
+    bulk_g2s(smem_dyn + (pAddr - dyn0), p.output_format == 3 ? p.tab.p_hlg : p.tab.p_pq, pb, bar);
   }
   mbar_wait(bar, 0);
 
   const Geometry& g = p.g;
-  const int mw = g.map_width, mh = g.map_height;
-  const int tiles_per_image = p.tiles_x * p.tiles_y;
+  const uint32_t mw = g.map_width, mh = g.map_height;
+  const uint32_t tiles_per_image = p.tiles_x * p.tiles_y;
   // Phi-domain constants (double on the host side of the compiler): K = 1/(255*1.055), chroma gains of the
   // BT.601 matrix (gainmapmath.cpp:177-196) times K, offsets = 0.055/1.055 - 128 * gain
   constexpr double dK = 1.0 / (255.0 * 1.055);
@@ -437,6 +459,7 @@ __global__ void __launch_bounds__(kThreads, UHDR_APPLYQ_MIN_BLOCKS) apply_q_kern
   constexpr float oG0 = (float)(0.055 / 1.055 + 128.0 * (dGcb + dGcr) * dK);
   constexpr float kPhiToe = 0.0905f;  // Phi(0.04045) = 0.090474; anything at or below 0.0905 takes the exact branch
 
+  // tile -> (image z, tile row ty, tile column tx), advanced incrementally: no division in the loop
   const uint32_t tiles_x = p.tiles_x, tiles_y = p.tiles_y;
   uint32_t tx, ty, z, dtx, dty, dz;
   {
@@ -451,19 +474,21 @@ __global__ void __launch_bounds__(kThreads, UHDR_APPLYQ_MIN_BLOCKS) apply_q_kern
     dtx = rem - dty * tiles_x;
   }
   const uint32_t ls = g.sdr_luma_stride, cs = g.sdr_chroma_stride;
+  const size_t ostride = (size_t)g.width * 4;
 
   for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
-    const uint32_t cx = tx * kTileCellsX + (tid & 31), cy = ty * kTileCellsY + (tid >> 5);
+    const uint32_t cx = tx * kTileCellsX + (tid & 31);
+    uint32_t cy = ty * kQTileRows + (tid >> 5) * kQCells;
     const uint32_t zi = z;
     tx += dtx;
     if (tx >= tiles_x) { tx -= tiles_x; ty++; }
     ty += dty;
     if (ty >= tiles_y) { ty -= tiles_y; z++; }
     z += dz;
-    if (cx >= (uint32_t)mw || cy >= (uint32_t)mh) continue;
+    if (cx >= mw || cy >= mh) continue;
     const uint8_t *sdr_y, *sdr_u, *sdr_v, *map;
     uint8_t* outp;
-    if (p.batch) {
+    if (BATCH) {
       const Planes* pl = p.batch + zi;
       sdr_y = (const uint8_t*)__ldg((const unsigned long long*)&pl->sdr_y);
       sdr_u = (const uint8_t*)__ldg((const unsigned long long*)&pl->sdr_u);
@@ -477,72 +502,144 @@ __global__ void __launch_bounds__(kThreads, UHDR_APPLYQ_MIN_BLOCKS) apply_q_kern
       map = (const uint8_t*)p.single.map_in;
       outp = (uint8_t*)p.single.out;
     }
+    // 32-bit offsets inside a plane (planes are < 2 GB after the capi checks)
     const uint8_t* yp = sdr_y + (4u * cy * ls + 4u * cx);
     const uint32_t coff = 2u * cy * cs + 2u * cx;
     const uint8_t* up = sdr_u + coff;
     const uint8_t* vp = sdr_v + coff;
+    const uint8_t* mp = map + (cy * mw + cx);
+    uint8_t* orow = outp + (size_t)(4u * cy * (uint32_t)g.width + 4u * cx) * 4;
+    const uint32_t dx = cx + 1 < mw ? 1u : 0u;  // xu = min(xl + 1, mw - 1), gainmapmath.cpp:690-697
+    // map samples as 0..255 floats: the 1/255 of gainmapmath.cpp:700-703 is folded into the weights
+    float e1 = (float)__ldg(mp), e3 = (float)__ldg(mp + dx);  // e1=(xl,yl) e3=(xu,yl)
+    const uint32_t kmax = min((uint32_t)kQCells, mh - cy);
 
-    uint32_t yw[4], uw[2], vw[2];
+#ifndef UHDR_APPLYQ_PREFETCH
+#define UHDR_APPLYQ_PREFETCH 0
+#endif
+#if UHDR_APPLYQ_PREFETCH
+    // software pipeline: the loads of cell k+1 are in flight while cell k is computed
+    uint32_t nyw[4], nuw[2], nvw[2], nb2, nb4;
+    const uint8_t* mp2 = (cy + 1 >= mh) ? mp : mp + mw;  // yu = min(yl + 1, mh - 1)
 #pragma unroll
-    for (int r = 0; r < 4; r++) yw[r] = ldg4(yp + r * ls);
+    for (int r = 0; r < 4; r++) nyw[r] = ldg4(yp + r * ls);
 #pragma unroll
     for (int r = 0; r < 2; r++) {
-      uw[r] = ldg2(up + r * cs);
-      vw[r] = ldg2(vp + r * cs);
+      nuw[r] = ldg2(up + r * cs);
+      nvw[r] = ldg2(vp + r * cs);
     }
-    const uint32_t cxr = min(cx + 1, (uint32_t)mw - 1), cyb = min(cy + 1, (uint32_t)mh - 1);  // gainmapmath.cpp:690-697
-    const uint32_t b1 = __ldg(map + (cx + cy * mw)), b2 = __ldg(map + (cx + cyb * mw));
-    const uint32_t b3 = __ldg(map + (cxr + cy * mw)), b4 = __ldg(map + (cxr + cyb * mw));
-    const float e1 = sE[b1], e2 = sE[b2], e3 = sE[b3], e4 = sE[b4];
+    nb2 = __ldg(mp2);
+    nb4 = __ldg(mp2 + dx);
 
-    // ---- f' = f^(1/2.4) of the 16 pixels
-    float f[16];
-    if (cx + 1 < (uint32_t)mw && cy + 1 < (uint32_t)mh) {
+#pragma unroll 1
+    for (uint32_t k = 0; k < kmax; k++, cy++) {
+      uint32_t yw[4], uw[2], vw[2];
 #pragma unroll
-      for (int i = 0; i < 16; i++) {
-        float ex = fmaf(e1, p.wq[i][0], p.Bq);
-        ex = fmaf(e2, p.wq[i][1], ex);
-        ex = fmaf(e3, p.wq[i][2], ex);
-        ex = fmaf(e4, p.wq[i][3], ex);
-        f[i] = ex2_fast(ex);
+      for (int r = 0; r < 4; r++) yw[r] = nyw[r];
+#pragma unroll
+      for (int r = 0; r < 2; r++) {
+        uw[r] = nuw[r];
+        vw[r] = nvw[r];
       }
-    } else {  // map border: tables NR (1), NB (2), C (3)
-      const int t = (cx + 1 < (uint32_t)mw) ? 2 : ((cy + 1 < (uint32_t)mh) ? 1 : 3);
-      const float4* wt = reinterpret_cast<const float4*>(p.idw) + t * 16;
+      const float e2 = (float)nb2, e4 = (float)nb4;  // e2=(xl,yu) e4=(xu,yu)
+      const bool last = cy + 1 >= mh;
+      yp += 4u * ls;
+      up += 2u * cs;
+      vp += 2u * cs;
+      mp = mp2;
+      if (k + 1 < kmax) {
+        mp2 = (cy + 2 >= mh) ? mp : mp + mw;
 #pragma unroll
-      for (int i = 0; i < 16; i++) {
-        const float4 w = __ldg(wt + i);
-        float gain = e1 * w.x;
-        gain = fmaf(e2, w.y, gain);
-        gain = fmaf(e3, w.z, gain);
-        gain = fmaf(e4, w.w, gain);
-        f[i] = ex2_fast(fmaf(gain, p.Aq, p.Bq));
+        for (int r = 0; r < 4; r++) nyw[r] = ldg4(yp + r * ls);
+#pragma unroll
+        for (int r = 0; r < 2; r++) {
+          nuw[r] = ldg2(up + r * cs);
+          nvw[r] = ldg2(vp + r * cs);
+        }
+        nb2 = __ldg(mp2);
+        nb4 = __ldg(mp2 + dx);
       }
-    }
-    uint8_t* orow = outp + (size_t)(4u * cy * (uint32_t)g.width + 4u * cx) * 4;
-    const size_t ostride = (size_t)g.width * 4;
-#pragma unroll
-    for (int qr = 0; qr < 2; qr++) {
-      // Phi-domain chroma offsets of the two 2x2 quads of this quad-row
-      float oR[2], oG[2], oB[2], yf[2][4];
-#pragma unroll
-      for (int c = 0; c < 2; c++) {
-        const float ub = (float)((uw[qr] >> (8 * c)) & 0xff), vb = (float)((vw[qr] >> (8 * c)) & 0xff);
-        oR[c] = fmaf(vb, kR, oR0);
-        oB[c] = fmaf(ub, kB, oB0);
-        oG[c] = fmaf(vb, kGv, fmaf(ub, kGu, oG0));
-      }
-#pragma unroll
-      for (int rr = 0; rr < 2; rr++)
-#pragma unroll
-        for (int i = 0; i < 4; i++) yf[rr][i] = (float)((yw[2 * qr + rr] >> (8 * i)) & 0xff);
-      const float ym0 = fminf(fminf(yf[0][0], yf[0][1]), fminf(yf[1][0], yf[1][1]));
-      const float ym1 = fminf(fminf(yf[0][2], yf[0][3]), fminf(yf[1][2], yf[1][3]));
-      const float om0 = fminf(oR[0], fminf(oG[0], oB[0])), om1 = fminf(oR[1], fminf(oG[1], oB[1]));
-      const bool toe = fminf(fmaf(ym0, KP, om0), fmaf(ym1, KP, om1)) <= kPhiToe;
 
-      if (toe) q_rows<MASK, true>(hiP, p.q0, uw[qr], vw[qr], oR, oG, oB, yf, &f[qr * 8], orow + (size_t)(2 * qr) * ostride, ostride);
-      else q_rows<MASK, false>(hiP, p.q0, uw[qr], vw[qr], oR, oG, oB, yf, &f[qr * 8], orow + (size_t)(2 * qr) * ostride, ostride);
+#else
+#pragma unroll 1
+    for (uint32_t k = 0; k < kmax; k++, cy++) {
+      uint32_t yw[4], uw[2], vw[2];
+#pragma unroll
+      for (int r = 0; r < 4; r++) yw[r] = ldg4(yp + r * ls);
+#pragma unroll
+      for (int r = 0; r < 2; r++) {
+        uw[r] = ldg2(up + r * cs);
+        vw[r] = ldg2(vp + r * cs);
+      }
+      const bool last = cy + 1 >= mh;  // yu = min(yl + 1, mh - 1)
+      const uint8_t* mp2 = last ? mp : mp + mw;
+      const float e2 = (float)__ldg(mp2), e4 = (float)__ldg(mp2 + dx);  // e2=(xl,yu) e4=(xu,yu)
+      yp += 4u * ls;
+      up += 2u * cs;
+      vp += 2u * cs;
+      mp = mp2;
+
+#endif
+      const float d2 = e2 - e1, d3 = e3 - e1, d4 = e4 - e1, exb = fmaf(e1, p.Aq, p.Bq);
+#ifdef UHDR_DBG_NOBORDER
+      const bool interior = true;
+#else
+      const bool interior = dx && !last;
+#endif
+
+#pragma unroll
+      for (int qr = 0; qr < 2; qr++) {
+        // ---- f' = f^(1/2.4) of the 8 pixels of this quad-row
+        float f[8];
+        if (interior) {
+#pragma unroll
+          for (int i = 0; i < 8; i++) {
+            // the four weights sum to 1: sum_k e_k w_k = e1 + sum_{k>1} (e_k - e1) w_k, three FFMAs per pixel
+            float ex = fmaf(d2, p.wq[qr * 8 + i][1], exb);
+            ex = fmaf(d3, p.wq[qr * 8 + i][2], ex);
+            ex = fmaf(d4, p.wq[qr * 8 + i][3], ex);
+            f[i] = ex2_fast(ex);
+          }
+        } else {  // map border: tables NR (1), NB (2), C (3), gainmapmath.cpp:710-716
+          const int t = dx ? 2 : (last ? 3 : 1);
+          const float4* wt = reinterpret_cast<const float4*>(p.idw) + t * 16 + qr * 8;
+#pragma unroll
+          for (int i = 0; i < 8; i++) {
+            const float4 w = __ldg(wt + i);
+            float gain = e1 * w.x;
+            gain = fmaf(e2, w.y, gain);
+            gain = fmaf(e3, w.z, gain);
+            gain = fmaf(e4, w.w, gain);
+            f[i] = ex2_fast(fmaf(gain, p.Aq, p.Bq));
+          }
+        }
+        // Phi-domain chroma offsets of the two 2x2 quads of this quad-row
+        float oR[2], oG[2], oB[2], yf[2][4];
+#pragma unroll
+        for (int c = 0; c < 2; c++) {
+          const float ub = (float)((uw[qr] >> (8 * c)) & 0xff), vb = (float)((vw[qr] >> (8 * c)) & 0xff);
+          oR[c] = fmaf(vb, kR, oR0);
+          oB[c] = fmaf(ub, kB, oB0);
+          oG[c] = fmaf(vb, kGv, fmaf(ub, kGu, oG0));
+        }
+#pragma unroll
+        for (int rr = 0; rr < 2; rr++)
+#pragma unroll
+          for (int i = 0; i < 4; i++) yf[rr][i] = (float)((yw[2 * qr + rr] >> (8 * i)) & 0xff);
+        const float ym0 = fminf(fminf(yf[0][0], yf[0][1]), fminf(yf[1][0], yf[1][1]));
+        const float ym1 = fminf(fminf(yf[0][2], yf[0][3]), fminf(yf[1][2], yf[1][3]));
+        const float om0 = fminf(oR[0], fminf(oG[0], oB[0])), om1 = fminf(oR[1], fminf(oG[1], oB[1]));
+#ifdef UHDR_DBG_NOTOE
+        const bool toe = false;
+#else
+        const bool toe = fminf(fmaf(ym0, KP, om0), fmaf(ym1, KP, om1)) <= kPhiToe;
+#endif
+        if (toe) q_rows<MASK, true>(hiP, uw[qr], vw[qr], oR, oG, oB, yf, f, orow + (size_t)(2 * qr) * ostride, ostride);
+        else q_rows<MASK, false>(hiP, uw[qr], vw[qr], oR, oG, oB, yf, f, orow + (size_t)(2 * qr) * ostride, ostride);
+      }
+      e1 = e2;
+      e3 = e4;
+      orow += 4 * ostride;
     }
   }
 }
@@ -571,8 +668,8 @@ cudaError_t launch(const ApplyFastParams& p, cudaStream_t s) {
   return cudaGetLastError();
 }
 
-template <bool MASK>
-cudaError_t launch_q(const ApplyFastParams& p, cudaStream_t s) {
+template <bool MASK, bool BATCH>
+cudaError_t launch_q(const ApplyFastParams& p0, cudaStream_t s) {
   static int sms_of[64], per_sm_of[64], smem_of[64];
   int dev = 0;
   cudaError_t e = cudaGetDevice(&dev);
@@ -583,20 +680,28 @@ cudaError_t launch_q(const ApplyFastParams& p, cudaStream_t s) {
     cudaFuncAttributes fa;
     if ((e = cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev)) != cudaSuccess) return e;
     if ((e = cudaDeviceGetAttribute(&reserved, cudaDevAttrReservedSharedMemoryPerBlock, dev)) != cudaSuccess) return e;
-    if ((e = cudaFuncGetAttributes(&fa, apply_q_kernel<MASK>)) != cudaSuccess) return e;
+    if ((e = cudaFuncGetAttributes(&fa, apply_q_kernel<MASK, BATCH>)) != cudaSuccess) return e;
     const uint32_t dyn0 = (uint32_t)reserved + (uint32_t)fa.sharedSizeBytes;
     const int smem = (int)(q_table_addr(dyn0) - dyn0 + kPEntries * sizeof(float2)) + 64;  // + slack for the base alignment
-    if ((e = cudaFuncSetAttribute(apply_q_kernel<MASK>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)) != cudaSuccess) return e;
-    if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, apply_q_kernel<MASK>, kThreads, smem)) != cudaSuccess) return e;
+    if ((e = cudaFuncSetAttribute(apply_q_kernel<MASK, BATCH>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)) != cudaSuccess) return e;
+    if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, apply_q_kernel<MASK, BATCH>, kThreads, smem)) != cudaSuccess) return e;
     sms_of[dev] = n_sm;
     smem_of[dev] = smem;
     per_sm_of[dev] = n > 0 ? n : 1;
   }
-  const size_t kQSmem = (size_t)smem_of[dev];
+  ApplyFastParams p = p0;
+  const int n_img = p.n_tiles / (p.tiles_x * p.tiles_y);
+  p.tiles_y = (p.g.map_height + kQTileRows - 1) / kQTileRows;  // this kernel's tiles are kQTileRows cell rows tall
+  p.n_tiles = p.tiles_x * p.tiles_y * n_img;
   const int cap = sms_of[dev] * per_sm_of[dev];
   const int grid = p.n_tiles < cap ? p.n_tiles : cap;
-  apply_q_kernel<MASK><<<grid, kThreads, kQSmem, s>>>(p);
+  apply_q_kernel<MASK, BATCH><<<grid, kThreads, (size_t)smem_of[dev], s>>>(p);
   return cudaGetLastError();
+}
+
+template <bool MASK>
+cudaError_t launch_q(const ApplyFastParams& p, cudaStream_t s) {
+  return p.batch ? launch_q<MASK, true>(p, s) : launch_q<MASK, false>(p, s);
 }
 
 }  // namespace

@@ -435,12 +435,12 @@ int apply_core(int n, const uhdrb200_image* sdr, const uhdrb200_image* map, cons
     idw_fill(&f.w[0][0], 4, 1, 1);  // ShepardsIDW::mWeights for scale 4 ...
     for (int i = 0; i < 16; i++)
       for (int c = 0; c < 4; c++) f.w[i][c] = (float)((double)f.w[i][c] * A);  // ... pre-multiplied by A
-    f.Aq = (float)(A / 2.4);
+    f.Aq = (float)(A / 2.4 / 255.0);  // the q kernel keeps the map samples as 0..255 floats
     f.Bq = (float)(B / 2.4);
     f.q0 = (float)ldexp(1.0, kPLoExp);
     f.two_table = g_apply_mode == 2;
     for (int i = 0; i < 16; i++)
-      for (int c = 0; c < 4; c++) f.wq[i][c] = (float)((double)f.w[i][c] / 2.4);
+      for (int c = 0; c < 4; c++) f.wq[i][c] = (float)((double)f.w[i][c] / 2.4 / 255.0);
     f.idw = p.idw;
     if ((st = get_apply_tables(t_ctx.device, &f.tab))) return st;
     f.single = v[0];

@@ -76,7 +76,10 @@ constexpr int kOBase = (kOLoExp + 127) << kOBits;
 //            Phi = (c + 0.055) / 1.055 LINEAR in the 8-bit luma, so with f' = f^(1/2.4) the whole chain
 //            OETF(f * srgbInvOetf(c)) is a function of q = Phi * f' alone:
 //            P(q + 2^kPLoExp) = 1023 * OETF(q^2.4), log-spaced segments like the O table.
-constexpr int kPLoExp = -12, kPHiExp = 1, kPBits = 8;
+#ifndef UHDR_P_BITS
+#define UHDR_P_BITS 8
+#endif
+constexpr int kPLoExp = -12, kPHiExp = 1, kPBits = UHDR_P_BITS;
 constexpr int kPEntries = (kPHiExp - kPLoExp) << kPBits;      // 3328 float2 = 26 KB
 constexpr int kPBase = (kPLoExp + 127) << kPBits;
 
@@ -97,9 +100,9 @@ struct ApplyFastParams {
   float e0;                // 2^kOLoExp
   uint32_t s_bias;         // 0x4B000000 << 3 (see uni_eval in apply_fast.cu)
   int need_mask;           // 1 when 10-bit codes can exceed 1023 (displayBoost < maxContentBoost): `& 0x3ff` wraps like the reference
-  float Aq, Bq, q0;        // q-domain kernel: f' = 2^(gain * Aq + Bq) = f^(1/2.4); q0 = 2^kPLoExp
+  float Aq, Bq, q0;        // q-domain kernel: f' = 2^(gain255 * Aq + Bq) = f^(1/2.4), gain255 = 255 * gain; q0 = 2^kPLoExp
   int two_table;           // 1: RGBA1010102 through the S+O table kernel instead of the q-domain kernel
-  float wq[16][4];         // Aq x interior IDW weights
+  float wq[16][4];         // Aq x interior IDW weights (so they include the 1/255 of the map samples)
   float w[16][4];          // A x interior IDW weights [oy * 4 + ox][k] (ShepardsIDW::mWeights, gainmapmath.h:184-228)
   const float* idw;        // all four tables (device), used by the cells on the right/bottom map border
   ApplyTables tab;
