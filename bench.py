@@ -358,6 +358,7 @@ def main():
         other["apply_rgba_f16_linear"] = timed(lambda: uh.applyGainMapBatch(Bo, sdrs, maps, md, abi.OUTPUT_HDR_LINEAR, FLT_MAX, bigs, stream), 9.5625)
         other["apply_1010102_pq"] = timed(lambda: uh.applyGainMapBatch(Bo, sdrs, maps, md_pq, abi.OUTPUT_HDR_PQ, FLT_MAX, bigs, stream), APPLY_BPP)
         other["apply_planar_10bit"] = timed(lambda: uh.applyGainMapBatch(Bo, sdrs, maps, md, abi.OUTPUT_HDR_LINEAR_RGB_10BIT, FLT_MAX, bigs, stream), 7.5625)
+        other["sdr_rgba8888_pack"] = timed(lambda: uh.yuv420ToRgba8888Batch(Bo, sdrs, bigs, stream), 5.5)
         assert lib.uhdrb200_set_apply_mode(abi.APPLY_TWO_TABLE) == 0
         other["apply_1010102_hlg_two_table_kernel"] = timed(lambda: uh.applyGainMapBatch(Bo, sdrs, maps, md, abi.OUTPUT_HDR_HLG, FLT_MAX, bigs, stream), APPLY_BPP)
         assert lib.uhdrb200_set_apply_mode(abi.APPLY_AUTO) == 0

@@ -208,6 +208,24 @@ int uhdrb200_convert_yuv_host(uhdrb200_image* image, int src_encoding, int dest_
 int uhdrb200_convert_yuv_dev(uhdrb200_image* image, int src_encoding, int dest_encoding,
                              void* stream);
 
+/* ---- N3: the SDR output pack and the copy-with-restride around the path ----
+ * yuv420_to_rgba8888: full-range BT.601 YUV420 -> RGBA8888 (R in bits 0-7, alpha 255), bit-exact
+ * with the reference's own routine UltraHdrAppInput::convertYuv420ToRGBImage
+ * (examples/ultrahdr_app.cpp:682-734); this is the device-side stand-in for what
+ * ULTRAHDR_OUTPUT_SDR obtains from libjpeg (jpegr.cpp:770-788; applyGainMap itself has no SDR
+ * case, ultrahdr.cpp:491-493). dest->data is caller-owned, width*height*4 bytes
+ * (dest->luma_stride >= width selects a row stride in pixels, 0 = width); the call sets
+ * dest->width/height/colorGamut. Even width and height.
+ * copy_yuv420: the luma/chroma copy into other strides of jpegr.cpp:315-359 and
+ * ultrahdr_api.cpp:437-479: dest->data/chroma_data/luma_stride/chroma_stride are pre-filled by the
+ * caller, rows are copied width (width/2) bytes at a time and the stride tails are zero-filled. */
+int uhdrb200_yuv420_to_rgba8888_host(const uhdrb200_image* yuv420, uhdrb200_image* dest);
+int uhdrb200_yuv420_to_rgba8888_dev(const uhdrb200_image* yuv420, uhdrb200_image* dest, void* stream);
+int uhdrb200_yuv420_to_rgba8888_batch_dev(int n, const uhdrb200_image* yuv420, uhdrb200_image* dest,
+                                          void* stream);
+int uhdrb200_copy_yuv420_host(const uhdrb200_image* src, uhdrb200_image* dest);
+int uhdrb200_copy_yuv420_dev(const uhdrb200_image* src, uhdrb200_image* dest, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

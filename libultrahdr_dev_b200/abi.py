@@ -19,7 +19,9 @@ PIX_FMT_UNSPECIFIED, PIX_FMT_P010, PIX_FMT_YUV420, PIX_FMT_MONOCHROME, PIX_FMT_R
 NO_ERROR = 0
 UNKNOWN_ERROR = -1
 ERROR_BAD_PTR = -10001
+ERROR_UNSUPPORTED_WIDTH_HEIGHT = -10002
 ERROR_INVALID_COLORGAMUT = -10003
+ERROR_INVALID_STRIDE = -10004
 ERROR_INVALID_TRANS_FUNC = -10005
 ERROR_RESOLUTION_MISMATCH = -10006
 ERROR_BAD_METADATA = -10010

@@ -47,6 +47,11 @@ SYMBOLS = {
     "uhdrb200_tonemap_generate_gainmap_batch_dev": (C.c_int, [C.c_int, P_IMG, C.c_int, P_IMG, P_MD, P_IMG, C.c_void_p]),
     "uhdrb200_convert_yuv_host": (C.c_int, [P_IMG, C.c_int, C.c_int]),
     "uhdrb200_convert_yuv_dev": (C.c_int, [P_IMG, C.c_int, C.c_int, C.c_void_p]),
+    "uhdrb200_yuv420_to_rgba8888_host": (C.c_int, [P_IMG, P_IMG]),
+    "uhdrb200_yuv420_to_rgba8888_dev": (C.c_int, [P_IMG, P_IMG, C.c_void_p]),
+    "uhdrb200_yuv420_to_rgba8888_batch_dev": (C.c_int, [C.c_int, P_IMG, P_IMG, C.c_void_p]),
+    "uhdrb200_copy_yuv420_host": (C.c_int, [P_IMG, P_IMG]),
+    "uhdrb200_copy_yuv420_dev": (C.c_int, [P_IMG, P_IMG, C.c_void_p]),
 }
 
 
@@ -163,6 +168,22 @@ class JpegR(UltraHdr):
 
     def convertYuvDevice(self, image, src_encoding, dest_encoding, stream=0):
         return _check(self.lib, self.lib.uhdrb200_convert_yuv_dev(_ref(image), src_encoding, dest_encoding, stream))
+
+    # -- row N3: SDR output pack (examples/ultrahdr_app.cpp:682-734) and copy-with-restride (jpegr.cpp:315-359)
+    def yuv420ToRgba8888(self, yuv420, dest):
+        return _check(self.lib, self.lib.uhdrb200_yuv420_to_rgba8888_host(_ref(yuv420), _ref(dest)))
+
+    def yuv420ToRgba8888Device(self, yuv420, dest, stream=0):
+        return _check(self.lib, self.lib.uhdrb200_yuv420_to_rgba8888_dev(_ref(yuv420), _ref(dest), stream))
+
+    def yuv420ToRgba8888Batch(self, n, yuv420s, dests, stream=0):
+        return _check(self.lib, self.lib.uhdrb200_yuv420_to_rgba8888_batch_dev(n, yuv420s, dests, stream))
+
+    def copyYuv420(self, src, dest):
+        return _check(self.lib, self.lib.uhdrb200_copy_yuv420_host(_ref(src), _ref(dest)))
+
+    def copyYuv420Device(self, src, dest, stream=0):
+        return _check(self.lib, self.lib.uhdrb200_copy_yuv420_dev(_ref(src), _ref(dest), stream))
 
 
 def take_map(dest):

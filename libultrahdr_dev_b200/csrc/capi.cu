@@ -353,6 +353,7 @@ int generate_core(int n, const uhdrb200_image* sdr, const uhdrb200_image* hdr, i
     const double den = (double)(p.log2_max - p.log2_min);
     p.code_at_min = (int)(uint8_t)((log2((double)p.min_boost) - (double)p.log2_min) / den * 255.0);
     p.code_at_max = (int)(uint8_t)((log2((double)p.max_boost) - (double)p.log2_min) / den * 255.0);
+    p.code_scale = (float)(255.0 / den);
   }
   BatchSlot* slot = nullptr;
   if (n == 1) p.single = v[0];
@@ -529,6 +530,73 @@ int convert_yuv_core(uhdrb200_image* im, int src_enc, int dst_enc, cudaStream_t 
   return UHDRB200_NO_ERROR;
 }
 
+// ---- row N3: SDR output pack (examples/ultrahdr_app.cpp:682-734) and copy-with-restride (jpegr.cpp:315-359)
+int sdr_pack_core(int n, const uhdrb200_image* sdr, uhdrb200_image* dest, cudaStream_t s) {
+  if (n <= 0) return UHDRB200_NO_ERROR;
+  if (!sdr || !dest) return UHDRB200_ERROR_BAD_PTR;
+  for (int i = 0; i < n; i++) {
+    if (!sdr[i].data || !sdr[i].chroma_data || !dest[i].data) return UHDRB200_ERROR_BAD_PTR;
+    if (sdr[i].width % 2 || sdr[i].height % 2) return UHDRB200_ERROR_UNSUPPORTED_WIDTH_HEIGHT;
+    if (sdr[i].luma_stride < sdr[i].width || sdr[i].chroma_stride < sdr[i].width / 2) return UHDRB200_ERROR_INVALID_STRIDE;
+    if (i && (!same_layout(sdr[i], sdr[0]) || dest[i].luma_stride != dest[0].luma_stride)) return UHDRB200_ERROR_RESOLUTION_MISMATCH;
+  }
+  if (!fits_int(sdr[0].width) || !fits_int(sdr[0].height) || !fits_int(sdr[0].luma_stride) || !fits_int(dest[0].luma_stride))
+    return UHDRB200_ERROR_UNSUPPORTED_WIDTH_HEIGHT;
+  int st = ensure_ctx();
+  if (st) return st;
+  SdrPackParams p;
+  memset(&p, 0, sizeof p);
+  p.g = geometry_of(&sdr[0], nullptr);
+  p.g.dst_luma_stride = (int)(dest[0].luma_stride >= sdr[0].width ? dest[0].luma_stride : sdr[0].width);  // in pixels
+  std::vector<Planes> v(n);
+  bool vec = true;
+  for (int i = 0; i < n; i++) {
+    memset(&v[i], 0, sizeof(Planes));
+    set_sdr_planes(v[i], sdr[i]);
+    v[i].out = dest[i].data;
+    vec = vec && sdr_pack_vec_ok(p.g, v[i]);
+    dest[i].width = sdr[i].width;
+    dest[i].height = sdr[i].height;
+    dest[i].colorGamut = sdr[i].colorGamut;
+  }
+  BatchSlot* slot = nullptr;
+  if (n == 1) p.single = v[0];
+  else if ((st = stage_batch(v, s, &p.batch, &slot))) return st;
+  cudaError_t e = launch_sdr_pack_impl(p, n, vec, s);
+  if (slot) cudaEventRecord(slot->done, s);
+  if (e != cudaSuccess) return fail(e, "yuv420_to_rgba8888 kernel launch");
+  g_launches++;
+  return UHDRB200_NO_ERROR;
+}
+
+int copy_yuv420_core(const uhdrb200_image* src, uhdrb200_image* dst, cudaStream_t s) {
+  if (!src || !dst || !src->data || !src->chroma_data || !dst->data || !dst->chroma_data) return UHDRB200_ERROR_BAD_PTR;
+  if (src->width % 2 || src->height % 2) return UHDRB200_ERROR_UNSUPPORTED_WIDTH_HEIGHT;
+  if (src->luma_stride < src->width || src->chroma_stride < src->width / 2 || dst->luma_stride < src->width ||
+      dst->chroma_stride < src->width / 2)
+    return UHDRB200_ERROR_INVALID_STRIDE;
+  if (!fits_int(src->width) || !fits_int(src->height) || !fits_int(src->luma_stride) || !fits_int(dst->luma_stride))
+    return UHDRB200_ERROR_UNSUPPORTED_WIDTH_HEIGHT;
+  int st = ensure_ctx();
+  if (st) return st;
+  SdrPackParams p;
+  memset(&p, 0, sizeof p);
+  p.g = geometry_of(src, nullptr);
+  p.g.dst_luma_stride = (int)dst->luma_stride;
+  p.g.dst_chroma_stride = (int)dst->chroma_stride;
+  set_sdr_planes(p.single, *src);
+  p.single.out = dst->data;
+  p.single.out_u = dst->chroma_data;
+  p.single.out_v = (uint8_t*)dst->chroma_data + dst->chroma_stride * (src->height / 2);
+  cudaError_t e = launch_copy_yuv420_impl(p, 1, s);
+  if (e != cudaSuccess) return fail(e, "copy_yuv420 kernel launch");
+  g_launches++;
+  dst->width = src->width;
+  dst->height = src->height;
+  dst->colorGamut = src->colorGamut;
+  return UHDRB200_NO_ERROR;
+}
+
 // API-0 (jpegr.cpp:167-225): toneMap(hdr -> sdr) then generateGainMap(sdr, hdr). One fused launch when the
 // layout allows it (width, height % 4 == 0, vector-aligned planes), else the two kernels back to back.
 int api0_core(int n, const uhdrb200_image* hdr, int hdr_tf, uhdrb200_image* sdr, uhdrb200_metadata* md,
@@ -701,6 +769,60 @@ int convert_yuv_host(uhdrb200_image* im, int src_enc, int dst_enc) {
   return UHDRB200_NO_ERROR;
 }
 
+int sdr_pack_host(const uhdrb200_image* sdr, uhdrb200_image* dest) {
+  if (!sdr || !dest || !sdr->data || !sdr->chroma_data || !dest->data) return UHDRB200_ERROR_BAD_PTR;
+  if (sdr->luma_stride < sdr->width || sdr->chroma_stride < sdr->width / 2) return UHDRB200_ERROR_INVALID_STRIDE;
+  int st = ensure_ctx();
+  if (st) return st;
+  Ctx& c = t_ctx;
+  const size_t lb = yuv420_luma_bytes(*sdr), cb = yuv420_chroma_bytes(*sdr);
+  const size_t os = dest->luma_stride >= sdr->width ? dest->luma_stride : sdr->width;
+  const size_t ob = sdr->height ? 4 * (os * (sdr->height - 1) + sdr->width) : 0;
+  if ((st = upload(c.buf[0], sdr->data, lb, c.stream))) return st;
+  if ((st = upload(c.buf[1], sdr->chroma_data, cb, c.stream))) return st;
+  if ((st = reserve(c.buf[6], ob ? ob : 1))) return st;
+  uhdrb200_image s2 = *sdr, d2 = *dest;
+  s2.data = c.buf[0].p; s2.chroma_data = c.buf[1].p;
+  d2.data = c.buf[6].p;
+  if ((st = sdr_pack_core(1, &s2, &d2, c.stream))) return st;
+  if (os == sdr->width) {
+    if (ob) CU(cudaMemcpyAsync(dest->data, c.buf[6].p, ob, cudaMemcpyDeviceToHost, c.stream));
+  } else if (ob) {  // only the pixels: bytes between width and the stride stay the caller's
+    CU(cudaMemcpy2DAsync(dest->data, os * 4, c.buf[6].p, os * 4, sdr->width * 4, sdr->height, cudaMemcpyDeviceToHost, c.stream));
+  }
+  CU(cudaStreamSynchronize(c.stream));
+  dest->width = sdr->width;
+  dest->height = sdr->height;
+  dest->colorGamut = sdr->colorGamut;
+  return UHDRB200_NO_ERROR;
+}
+
+int copy_yuv420_host(const uhdrb200_image* src, uhdrb200_image* dst) {
+  if (!src || !dst || !src->data || !src->chroma_data || !dst->data || !dst->chroma_data) return UHDRB200_ERROR_BAD_PTR;
+  if (src->luma_stride < src->width || src->chroma_stride < src->width / 2 || dst->luma_stride < src->width ||
+      dst->chroma_stride < src->width / 2)
+    return UHDRB200_ERROR_INVALID_STRIDE;
+  int st = ensure_ctx();
+  if (st) return st;
+  Ctx& c = t_ctx;
+  const size_t lb = yuv420_luma_bytes(*src), cb = yuv420_chroma_bytes(*src);
+  const size_t dl = dst->luma_stride * src->height, dc = 2 * (dst->chroma_stride * (src->height / 2));
+  if ((st = upload(c.buf[0], src->data, lb, c.stream))) return st;
+  if ((st = upload(c.buf[1], src->chroma_data, cb, c.stream))) return st;
+  if ((st = reserve(c.buf[6], dl ? dl : 1)) || (st = reserve(c.buf[7], dc ? dc : 1))) return st;
+  uhdrb200_image s2 = *src, d2 = *dst;
+  s2.data = c.buf[0].p; s2.chroma_data = c.buf[1].p;
+  d2.data = c.buf[6].p; d2.chroma_data = c.buf[7].p;
+  if ((st = copy_yuv420_core(&s2, &d2, c.stream))) return st;
+  if (dl) CU(cudaMemcpyAsync(dst->data, c.buf[6].p, dl, cudaMemcpyDeviceToHost, c.stream));
+  if (dc) CU(cudaMemcpyAsync(dst->chroma_data, c.buf[7].p, dc, cudaMemcpyDeviceToHost, c.stream));
+  CU(cudaStreamSynchronize(c.stream));
+  dst->width = src->width;
+  dst->height = src->height;
+  dst->colorGamut = src->colorGamut;
+  return UHDRB200_NO_ERROR;
+}
+
 int api0_host(const uhdrb200_image* hdr, int hdr_tf, uhdrb200_image* sdr, uhdrb200_metadata* md, uhdrb200_image* dest,
               void* map_buf, size_t map_buf_bytes) {
   int st = validate_tonemap(hdr, sdr);
@@ -846,6 +968,18 @@ int uhdrb200_convert_yuv_host(uhdrb200_image* image, int src_encoding, int dest_
 }
 int uhdrb200_convert_yuv_dev(uhdrb200_image* image, int src_encoding, int dest_encoding, void* stream) {
   return convert_yuv_core(image, src_encoding, dest_encoding, (cudaStream_t)stream);
+}
+
+int uhdrb200_yuv420_to_rgba8888_host(const uhdrb200_image* yuv420, uhdrb200_image* dest) { return sdr_pack_host(yuv420, dest); }
+int uhdrb200_yuv420_to_rgba8888_dev(const uhdrb200_image* yuv420, uhdrb200_image* dest, void* stream) {
+  return sdr_pack_core(1, yuv420, dest, (cudaStream_t)stream);
+}
+int uhdrb200_yuv420_to_rgba8888_batch_dev(int n, const uhdrb200_image* yuv420, uhdrb200_image* dest, void* stream) {
+  return sdr_pack_core(n, yuv420, dest, (cudaStream_t)stream);
+}
+int uhdrb200_copy_yuv420_host(const uhdrb200_image* src, uhdrb200_image* dest) { return copy_yuv420_host(src, dest); }
+int uhdrb200_copy_yuv420_dev(const uhdrb200_image* src, uhdrb200_image* dest, void* stream) {
+  return copy_yuv420_core(src, dest, (cudaStream_t)stream);
 }
 
 }  // extern "C"

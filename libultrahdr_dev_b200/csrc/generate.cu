@@ -51,14 +51,14 @@ __global__ void __launch_bounds__(256) generate_kernel(GenerateParams p) {
 #pragma unroll
       for (int r = 0; r < 4; r++) {
         sy[r] = __byte_perm(hy[r].x, hy[r].y, 0x7531);  // high byte of each u16 == (v >> 6) >> 2, ultrahdr.cpp:530-531
-        *reinterpret_cast<uint32_t*>(oy + (size_t)r * g.sdr_luma_stride) = sy[r];
+        stg4(oy + (size_t)r * g.sdr_luma_stride, sy[r]);
       }
 #pragma unroll
       for (int r = 0; r < 2; r++) {
         su[r] = __byte_perm(huv[r].x, huv[r].y, 0x7751) & 0xFFFFu;  // U0 U1
         sv[r] = __byte_perm(huv[r].x, huv[r].y, 0x7773) & 0xFFFFu;  // V0 V1
-        *reinterpret_cast<uint16_t*>(ou + (size_t)r * g.sdr_chroma_stride) = (uint16_t)su[r];
-        *reinterpret_cast<uint16_t*>(ov + (size_t)r * g.sdr_chroma_stride) = (uint16_t)sv[r];
+        stg2(ou + (size_t)r * g.sdr_chroma_stride, su[r]);
+        stg2(ov + (size_t)r * g.sdr_chroma_stride, sv[r]);
       }
       if (mx == g.map_width - 1) {  // stride tails, ultrahdr.cpp:533-535, 551-554
         for (int x = g.width; x < g.sdr_luma_stride; x++)
@@ -133,23 +133,23 @@ __global__ void __launch_bounds__(256) generate_kernel(GenerateParams p) {
 
   // ---- SDR: YUV->RGB, sRGB^-1, luminance * 203 (ultrahdr.cpp:316-324) ----
   const LumaCoefs lk = p.luma;
-  Color3 sg = yuv_to_rgb(p.sdr_k, s);
+  Color3 sg = yuv_to_rgb_fma(p.sdr_k, s);
   Color3 sl = {srgb_inv_oetf(sg.r), srgb_inv_oetf(sg.g), srgb_inv_oetf(sg.b)};
-  const float sdr_nits = luminance(lk, sl) * 203.0f;
+  const float sdr_nits = luminance_fma(lk, sl) * 203.0f;
 
   // ---- HDR: YUV->RGB, inverse OETF, gamut conversion into the SDR gamut, luminance (:326-330) ----
-  Color3 hg = yuv_to_rgb(p.hdr_k, h);
+  Color3 hg = yuv_to_rgb_fma(p.hdr_k, h);
   Color3 hl;
   if (p.hdr_tf == 1) hl = {hlg_inv_oetf(hg.r), hlg_inv_oetf(hg.g), hlg_inv_oetf(hg.b)};
   else if (p.hdr_tf == 2) hl = {pq_inv_oetf(hg.r), pq_inv_oetf(hg.g), pq_inv_oetf(hg.b)};
   else hl = hg;
-  if (p.use_gamut) hl = mat3_apply(p.gamut, hl);
-  const float hdr_nits = luminance(lk, hl) * p.hdr_white_nits;
+  if (p.use_gamut) hl = mat3_apply_fma(p.gamut, hl);
+  const float hdr_nits = luminance_fma(lk, hl) * p.hdr_white_nits;
 
   // ---- encodeGain (gainmapmath.cpp:529-541), truncating ----
   float gain = 1.0f;
-  if (sdr_nits > 0.0f) gain = __fdiv_rn(hdr_nits, sdr_nits);
-  float v = __fdiv_rn(mufu_lg2(gain) - p.log2_min, p.log2_max - p.log2_min) * 255.0f;
+  if (sdr_nits > 0.0f) gain = hdr_nits * mufu_rcp(sdr_nits);
+  float v = (mufu_lg2(gain) - p.log2_min) * p.code_scale;  // code_scale = 255 / (log2_max - log2_min), host double
   uint32_t code = __float2uint_rz(v);
   // A clamped gain is the common case (saturated map bytes); there the reference's double-precision
   // quotient against the float-rounded log2 bounds decides between e.g. 254 and 255, so those two

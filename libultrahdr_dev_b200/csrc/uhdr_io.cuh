@@ -35,6 +35,13 @@ __device__ __forceinline__ void stg8(void* p, uint2 v) {
   asm volatile("st.global.L1::no_allocate.v2.u32 [%0], {%1,%2};" ::"l"(p), "r"(v.x), "r"(v.y) : "memory");
 }
 
+__device__ __forceinline__ void stg2(void* p, uint32_t v) {
+  asm volatile("st.global.L1::no_allocate.u16 [%0], %1;" ::"l"(p), "h"((uint16_t)v) : "memory");
+}
+__device__ __forceinline__ void stg4(void* p, uint32_t v) {
+  asm volatile("st.global.L1::no_allocate.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
 // ---- mbarrier + 1-D TMA bulk copy (global -> shared), sm_90+ ----

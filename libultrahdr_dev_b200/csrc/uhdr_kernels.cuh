@@ -41,6 +41,7 @@ struct GenerateParams {
   float hdr_white_nits;
   float min_boost, max_boost, log2_min, log2_max;
   int code_at_min, code_at_max;  // encodeGain of a gain clamped to min/max, evaluated on the host in double
+  float code_scale;              // 255 / (log2_max - log2_min), the float difference like the reference, in double
   Planes single;
   const Planes* batch;  // device array, indexed by blockIdx.z; nullptr => `single`
 };
@@ -124,6 +125,12 @@ struct ConvertYuvParams {
   const Planes* batch;
 };
 
+struct SdrPackParams {   // row N3: yuv420 -> RGBA8888 (out = packed pixels, dst_luma_stride in pixels) and copy_yuv420
+  Geometry g;            // (out/out_u/out_v = destination planes, dst_luma_stride / dst_chroma_stride in bytes)
+  Planes single;
+  const Planes* batch;
+};
+
 // *_vec_ok: true when the planes/strides of an image allow the 128-bit vector path (the caller
 // ANDs it over a batch). launch_*_impl return the cudaError_t of the launch; `n` = images (grid.z).
 bool generate_vec_ok(const Geometry& g, const Planes& pl);
@@ -140,6 +147,9 @@ cudaError_t launch_apply_fast_impl(ApplyFastParams& p, int n, cudaStream_t s);
 // host: fills the double-precision-built tables (tables.cu)
 void build_apply_tables(float2* s, float2* s_hi, float2* o_hlg, float2* o_pq, float2* p_hlg, float2* p_pq, float* e255);
 cudaError_t launch_tonemap_impl(const ToneMapParams& p, int n, bool vec, cudaStream_t s);
+bool sdr_pack_vec_ok(const Geometry& g, const Planes& pl);
+cudaError_t launch_sdr_pack_impl(const SdrPackParams& p, int n, bool vec, cudaStream_t s);
+cudaError_t launch_copy_yuv420_impl(const SdrPackParams& p, int n, cudaStream_t s);
 cudaError_t launch_convert_yuv_impl(const ConvertYuvParams& p, int n, bool vec, cudaStream_t s);
 
 }  // namespace uhdr

@@ -54,12 +54,27 @@ __device__ __forceinline__ Color3 yuv_to_rgb(const YuvCoefs& k, Color3 e) {
 __device__ __forceinline__ float luminance(const LumaCoefs& k, Color3 e) {
   return k.r * e.r + k.g * e.g + k.b * e.b;
 }
+// Contracted variants for the generate kernel: its result is a truncated 8-bit code of a log2 whose
+// inputs already carry the MUFU error (2^-22), so the last-ulp difference of an FMA is immaterial
+// and each contraction saves an issue slot in an issue-bound kernel.
+__device__ __forceinline__ Color3 yuv_to_rgb_fma(const YuvCoefs& k, Color3 e) {
+  Color3 o;
+  o.r = clamp01(fmaf(k.cr, e.b, e.r));
+  o.g = clamp01(fmaf(-k.gcr, e.b, fmaf(-k.gcb, e.g, e.r)));
+  o.b = clamp01(fmaf(k.cb, e.g, e.r));
+  return o;
+}
+__device__ __forceinline__ float luminance_fma(const LumaCoefs& k, Color3 e) {
+  return fmaf(k.b, e.b, fmaf(k.g, e.g, k.r * e.r));
+}
 
 // ---- sRGB inverse OETF, gainmapmath.cpp:149-155 ----
+// The two divisions by constants are multiplications by the double-rounded reciprocals (1 ulp,
+// far below the MUFU error): a correctly rounded division costs ~10 instructions each.
 __device__ __forceinline__ float srgb_inv_oetf(float x) {
-  float t = __fdiv_rn(x + 0.055f, 1.055f);
+  float t = fmaf(x, (float)(1.0 / 1.055), (float)(0.055 / 1.055));
   float p = mufu_ex2(2.4f * mufu_lg2(t));
-  return x <= 0.04045f ? __fdiv_rn(x, 12.92f) : p;
+  return x <= 0.04045f ? x * (float)(1.0 / 12.92) : p;
 }
 
 // ---- HLG, gainmapmath.cpp:257-286 ----
@@ -136,6 +151,10 @@ __host__ __device__ inline Mat3 gamut_matrix(int to, int from) {
   Mat3 r;
   for (int i = 0; i < 9; i++) r.m[i] = t[to][from][i];
   return r;
+}
+__device__ __forceinline__ Color3 mat3_apply_fma(const Mat3& k, Color3 e) {
+  return {fmaf(k.m[2], e.b, fmaf(k.m[1], e.g, k.m[0] * e.r)), fmaf(k.m[5], e.b, fmaf(k.m[4], e.g, k.m[3] * e.r)),
+          fmaf(k.m[8], e.b, fmaf(k.m[7], e.g, k.m[6] * e.r))};
 }
 __device__ __forceinline__ Color3 mat3_apply(const Mat3& k, Color3 e) {
   return {k.m[0] * e.r + k.m[1] * e.g + k.m[2] * e.b, k.m[3] * e.r + k.m[4] * e.g + k.m[5] * e.b,

@@ -58,6 +58,10 @@ class CpuImpl:
         L("colorToRgba1010102", C.c_uint32, [C.c_float, C.c_float, C.c_float])
         L("colorToRgbaF16", C.c_uint64, [C.c_float, C.c_float, C.c_float])
         L("floatToHalf", C.c_uint16, [C.c_float])
+        # row N3 exists in the restatement only (the reference's routine lives in its example app: ref_app below)
+        if hasattr(self.lib, self.prefix + "yuv420_to_rgba8888"):
+            L("yuv420_to_rgba8888", C.c_int, [P_IMG, P_IMG])
+            L("copy_yuv420", C.c_int, [P_IMG, P_IMG])
 
     def _fn(self, name, restype, argtypes):
         f = getattr(self.lib, self.prefix + name)
@@ -118,6 +122,21 @@ class CpuImpl:
     def convert_yuv(self, img, src_enc, dst_enc):
         return self.c_convert_yuv(C.byref(img), src_enc, dst_enc)
 
+    def yuv420_to_rgba8888(self, sdr_img, out_stride=0):
+        """-> (status, uint32 array of height x stride)."""
+        import numpy as np
+
+        stride = max(int(out_stride), int(sdr_img.width))
+        out = np.zeros(max(int(sdr_img.height) * stride, 1), dtype=np.uint32)
+        dest = abi.Image()
+        dest.data = out.ctypes.data
+        dest.luma_stride = out_stride
+        st = self.c_yuv420_to_rgba8888(C.byref(sdr_img), C.byref(dest))
+        return st, out[: int(sdr_img.height) * stride].reshape(int(sdr_img.height), stride), dest
+
+    def copy_yuv420(self, src_img, dst_img):
+        return self.c_copy_yuv420(C.byref(src_img), C.byref(dst_img))
+
     # ---- L1 conveniences ------------------------------------------------------------------
     def vec3(self, fn, *lead):
         def call(v):
@@ -145,3 +164,27 @@ class CpuImpl:
         o = (C.c_float * (scale * scale * 4))()
         self.c_idwTable(scale, table, o)
         return np.array(list(o), dtype=np.float32)
+
+
+REF_APP_PATH = os.path.join(HERE, "_ref", "libuhdr_ref_app.so")
+
+
+def have_ref_app():
+    return os.path.exists(REF_APP_PATH)
+
+
+def ref_app_yuv420_to_rgba8888(y, u, v, w, h, y_stride, u_stride, v_stride):
+    """The reference's own UltraHdrAppInput::convertYuv420ToRGBImage (examples/ultrahdr_app.cpp:682-734),
+    compiled unmodified into oracle/_ref/libuhdr_ref_app.so. -> uint32 array (h, w)."""
+    import numpy as np
+
+    lib = C.CDLL(REF_APP_PATH)
+    fn = lib.ref_app_yuv420_to_rgba8888
+    fn.restype = C.c_int
+    fn.argtypes = [C.c_void_p] * 3 + [C.c_int] * 5 + [C.c_void_p]
+    out = np.zeros(w * h, dtype=np.uint32)
+    rc = fn(y.ctypes.data, u.ctypes.data, v.ctypes.data, w, h, y_stride, u_stride, v_stride, out.ctypes.data)
+    if rc != 0:
+        raise RuntimeError("reference app routine failed")
+    return out.reshape(h, w)
+

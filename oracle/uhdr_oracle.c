@@ -529,3 +529,62 @@ int orc_convert_yuv(uhdrb200_image* im, int src_enc, int dst_enc) {
     }
   return UHDRB200_NO_ERROR;
 }
+
+/* N3: SDR output pack, examples/ultrahdr_app.cpp:682-734 (convertYuv420ToRGBImage): full-range
+ * BT.601 YUV420 -> RGBA8888, nearest chroma sample (j/2, i/2), true divisions by 255.0f, the
+ * 3-term dot products summed left to right in float, *255 + 0.5, CLIP3 to [0,255], truncation,
+ * alpha 255. Matrix literals are the reference's double expressions narrowed to float (:34-35). */
+int orc_yuv420_to_rgba8888(const uhdrb200_image* im, uhdrb200_image* dest) {
+  if (!im || !dest || !im->data || !im->chroma_data || !dest->data) return UHDRB200_ERROR_BAD_PTR;
+  static const float c[9] = {1, 0, 1.402, 1, (-0.202008 / 0.587), (-0.419198 / 0.587), 1.0, 1.772, 0.0};
+  const uint8_t* y = (const uint8_t*)im->data;
+  const uint8_t* u = (const uint8_t*)im->chroma_data;
+  const uint8_t* v = u + im->chroma_stride * (im->height / 2);
+  uint32_t* out = (uint32_t*)dest->data;
+  const size_t os = dest->luma_stride >= im->width ? dest->luma_stride : im->width;
+  for (size_t i = 0; i < im->height; i++)
+    for (size_t j = 0; j < im->width; j++) {
+      float y0 = (float)y[im->luma_stride * i + j];
+      float u0 = (float)(u[im->chroma_stride * (i / 2) + (j / 2)] - 128);
+      float v0 = (float)(v[im->chroma_stride * (i / 2) + (j / 2)] - 128);
+      y0 /= 255.0f;
+      u0 /= 255.0f;
+      v0 /= 255.0f;
+      float r = c[0] * y0 + c[1] * u0 + c[2] * v0;
+      float g = c[3] * y0 + c[4] * u0 + c[5] * v0;
+      float b = c[6] * y0 + c[7] * u0 + c[8] * v0;
+      r = clip255(r * 255.0f + 0.5f);
+      g = clip255(g * 255.0f + 0.5f);
+      b = clip255(b * 255.0f + 0.5f);
+      out[i * os + j] = (uint32_t)(int32_t)r | ((uint32_t)(int32_t)g << 8) | ((uint32_t)(int32_t)b << 16) | (255u << 24);
+    }
+  dest->width = im->width;
+  dest->height = im->height;
+  dest->colorGamut = im->colorGamut;
+  return UHDRB200_NO_ERROR;
+}
+
+/* N3: copy-with-restride of a YUV420 image, jpegr.cpp:315-359 / ultrahdr_api.cpp:437-479: rows are
+ * copied `width` (`width/2`) bytes at a time and the destination stride tails are zero-filled. */
+int orc_copy_yuv420(const uhdrb200_image* src, uhdrb200_image* dst) {
+  if (!src || !dst || !src->data || !src->chroma_data || !dst->data || !dst->chroma_data) return UHDRB200_ERROR_BAD_PTR;
+  if (dst->luma_stride < src->width || dst->chroma_stride < src->width / 2) return UHDRB200_ERROR_INVALID_STRIDE;
+  const size_t w = src->width, h = src->height;
+  for (size_t i = 0; i < h; i++) {
+    uint8_t* d = (uint8_t*)dst->data + i * dst->luma_stride;
+    memcpy(d, (const uint8_t*)src->data + i * src->luma_stride, w);
+    memset(d + w, 0, dst->luma_stride - w);
+  }
+  for (int pl = 0; pl < 2; pl++) {
+    const uint8_t* s0 = (const uint8_t*)src->chroma_data + (size_t)pl * src->chroma_stride * (h / 2);
+    uint8_t* d0 = (uint8_t*)dst->chroma_data + (size_t)pl * dst->chroma_stride * (h / 2);
+    for (size_t i = 0; i < h / 2; i++) {
+      memcpy(d0 + i * dst->chroma_stride, s0 + i * src->chroma_stride, w / 2);
+      memset(d0 + i * dst->chroma_stride + w / 2, 0, dst->chroma_stride - w / 2);
+    }
+  }
+  dst->width = src->width;
+  dst->height = src->height;
+  dst->colorGamut = src->colorGamut;
+  return UHDRB200_NO_ERROR;
+}
