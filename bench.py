@@ -353,6 +353,7 @@ def main():
 
         other["tonemap"] = timed(lambda: uh.toneMapBatch(Bo, hdrs, tms, stream), 4.5)
         other["api0_fused_tonemap_generate"] = timed(lambda: uh.toneMapGenerateGainMapBatch(Bo, hdrs, abi.TF_HLG, tms, mds, maps, stream), 4.5625)
+        other["api0_fused_tonemap_generate_convert601"] = timed(lambda: uh.toneMapGenerateGainMapBatch(Bo, hdrs, abi.TF_HLG, tms, mds, maps, stream, sdr_to_601=True), 4.5625)
         other["generate_pq_p3"] = timed(lambda: uh.generateGainMapBatch(Bo, sdrs, hdrs, abi.TF_PQ, mds, maps, False, stream), GEN_BPP)
         assert uh.generateGainMapBatch(Bo, sdrs, hdrs, abi.TF_HLG, mds, maps, False, stream) == 0  # restore HLG maps
         other["apply_rgba_f16_linear"] = timed(lambda: uh.applyGainMapBatch(Bo, sdrs, maps, md, abi.OUTPUT_HDR_LINEAR, FLT_MAX, bigs, stream), 9.5625)

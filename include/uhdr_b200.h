@@ -187,18 +187,21 @@ int uhdrb200_apply_gainmap_batch_dev(int n, const uhdrb200_image* yuv420, const 
 int uhdrb200_tonemap_batch_dev(int n, const uhdrb200_image* src, uhdrb200_image* dest,
                                void* stream);
 
-/* ---- N2: API-0 front half, JpegR::encodeJPEGR(p010, ...) lib/src/jpegr.cpp:167-225: toneMap(p010 -> sdr_dest)
- * followed by generateGainMap(sdr_dest, p010, hdr_tf, metadata, map_dest). Same results, byte for byte, as
- * calling the two entry points above one after the other; when width and height are multiples of 4 and the
- * planes are vector-aligned it is ONE kernel that reads the P010 image once (4.5625 B/px instead of 9.06).
- * sdr_dest: caller-owned YUV420 descriptor (data, chroma_data, strides, dims set), colorGamut is written.
+/* ---- N2: API-0 front half, JpegR::encodeJPEGR(p010, ...) lib/src/jpegr.cpp:167-225: toneMap(p010 -> sdr_dest),
+ * generateGainMap(sdr_dest, p010, hdr_tf, metadata, map_dest) and, when sdr_to_601 != 0 and the gamut is not P3,
+ * convertYuv(sdr_dest, gamut -> BT.601) (jpegr.cpp:223-225; the gain map is computed from the un-converted
+ * image, as there). Same results, byte for byte, as calling the separate entry points one after the other;
+ * when width and height are multiples of 4 and the planes are vector-aligned it is ONE kernel that reads the
+ * P010 image once (4.5625 B/px instead of 9.06 + 3). sdr_dest: caller-owned YUV420 descriptor (data,
+ * chroma_data, strides, dims set), colorGamut is written (= the P010 gamut, convertYuv leaves it alone).
  * host_into: the map goes to map_buf (>= (w/4)*(h/4) bytes); dev: map_dest->data is a device buffer. ---- */
-int uhdrb200_tonemap_generate_gainmap_host_into(const uhdrb200_image* p010, int hdr_tf, uhdrb200_image* sdr_dest,
-                                                uhdrb200_metadata* metadata, uhdrb200_image* map_dest,
-                                                void* map_buf, size_t map_buf_bytes);
-int uhdrb200_tonemap_generate_gainmap_dev(const uhdrb200_image* p010, int hdr_tf, uhdrb200_image* sdr_dest,
-                                          uhdrb200_metadata* metadata, uhdrb200_image* map_dest, void* stream);
-int uhdrb200_tonemap_generate_gainmap_batch_dev(int n, const uhdrb200_image* p010, int hdr_tf,
+int uhdrb200_tonemap_generate_gainmap_host_into(const uhdrb200_image* p010, int hdr_tf, int sdr_to_601,
+                                                uhdrb200_image* sdr_dest, uhdrb200_metadata* metadata,
+                                                uhdrb200_image* map_dest, void* map_buf, size_t map_buf_bytes);
+int uhdrb200_tonemap_generate_gainmap_dev(const uhdrb200_image* p010, int hdr_tf, int sdr_to_601,
+                                          uhdrb200_image* sdr_dest, uhdrb200_metadata* metadata,
+                                          uhdrb200_image* map_dest, void* stream);
+int uhdrb200_tonemap_generate_gainmap_batch_dev(int n, const uhdrb200_image* p010, int hdr_tf, int sdr_to_601,
                                                 uhdrb200_image* sdr_dest, uhdrb200_metadata* metadata,
                                                 uhdrb200_image* map_dest, void* stream);
 

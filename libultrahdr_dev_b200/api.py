@@ -42,9 +42,9 @@ SYMBOLS = {
     "uhdrb200_tonemap_host": (C.c_int, [P_IMG, P_IMG]),
     "uhdrb200_tonemap_dev": (C.c_int, [P_IMG, P_IMG, C.c_void_p]),
     "uhdrb200_tonemap_batch_dev": (C.c_int, [C.c_int, P_IMG, P_IMG, C.c_void_p]),
-    "uhdrb200_tonemap_generate_gainmap_host_into": (C.c_int, [P_IMG, C.c_int, P_IMG, P_MD, P_IMG, C.c_void_p, C.c_size_t]),
-    "uhdrb200_tonemap_generate_gainmap_dev": (C.c_int, [P_IMG, C.c_int, P_IMG, P_MD, P_IMG, C.c_void_p]),
-    "uhdrb200_tonemap_generate_gainmap_batch_dev": (C.c_int, [C.c_int, P_IMG, C.c_int, P_IMG, P_MD, P_IMG, C.c_void_p]),
+    "uhdrb200_tonemap_generate_gainmap_host_into": (C.c_int, [P_IMG, C.c_int, C.c_int, P_IMG, P_MD, P_IMG, C.c_void_p, C.c_size_t]),
+    "uhdrb200_tonemap_generate_gainmap_dev": (C.c_int, [P_IMG, C.c_int, C.c_int, P_IMG, P_MD, P_IMG, C.c_void_p]),
+    "uhdrb200_tonemap_generate_gainmap_batch_dev": (C.c_int, [C.c_int, P_IMG, C.c_int, C.c_int, P_IMG, P_MD, P_IMG, C.c_void_p]),
     "uhdrb200_convert_yuv_host": (C.c_int, [P_IMG, C.c_int, C.c_int]),
     "uhdrb200_convert_yuv_dev": (C.c_int, [P_IMG, C.c_int, C.c_int, C.c_void_p]),
     "uhdrb200_yuv420_to_rgba8888_host": (C.c_int, [P_IMG, P_IMG]),
@@ -151,17 +151,18 @@ class JpegR(UltraHdr):
     """`JpegR : public UltraHdr` (jpegr.h:59) — the pixel steps on the path: convertYuv and the
     API-0 front half (toneMap + generateGainMap, jpegr.cpp:167-225) as one call."""
 
-    def toneMapGenerateGainMapInto(self, p010, hdr_tf, sdr_dest, metadata, map_dest, map_buf):
+    def toneMapGenerateGainMapInto(self, p010, hdr_tf, sdr_dest, metadata, map_dest, map_buf, sdr_to_601=False):
         return _check(self.lib, self.lib.uhdrb200_tonemap_generate_gainmap_host_into(
-            _ref(p010), hdr_tf, _ref(sdr_dest), _ref(metadata), _ref(map_dest), map_buf.ctypes.data, map_buf.nbytes))
+            _ref(p010), hdr_tf, 1 if sdr_to_601 else 0, _ref(sdr_dest), _ref(metadata), _ref(map_dest),
+            map_buf.ctypes.data, map_buf.nbytes))
 
-    def toneMapGenerateGainMapDevice(self, p010, hdr_tf, sdr_dest, metadata, map_dest, stream=0):
+    def toneMapGenerateGainMapDevice(self, p010, hdr_tf, sdr_dest, metadata, map_dest, stream=0, sdr_to_601=False):
         return _check(self.lib, self.lib.uhdrb200_tonemap_generate_gainmap_dev(
-            _ref(p010), hdr_tf, _ref(sdr_dest), _ref(metadata), _ref(map_dest), stream))
+            _ref(p010), hdr_tf, 1 if sdr_to_601 else 0, _ref(sdr_dest), _ref(metadata), _ref(map_dest), stream))
 
-    def toneMapGenerateGainMapBatch(self, n, p010s, hdr_tf, sdr_dests, metadatas, map_dests, stream=0):
+    def toneMapGenerateGainMapBatch(self, n, p010s, hdr_tf, sdr_dests, metadatas, map_dests, stream=0, sdr_to_601=False):
         return _check(self.lib, self.lib.uhdrb200_tonemap_generate_gainmap_batch_dev(
-            n, p010s, hdr_tf, sdr_dests, metadatas, map_dests, stream))
+            n, p010s, hdr_tf, 1 if sdr_to_601 else 0, sdr_dests, metadatas, map_dests, stream))
 
     def convertYuv(self, image, src_encoding, dest_encoding):
         return _check(self.lib, self.lib.uhdrb200_convert_yuv_host(_ref(image), src_encoding, dest_encoding))

@@ -307,7 +307,8 @@ void set_sdr_planes(Planes& pl, const uhdrb200_image& im) {
 
 // ================================================================ device-pointer cores
 int generate_core(int n, const uhdrb200_image* sdr, const uhdrb200_image* hdr, int hdr_tf,
-                  uhdrb200_metadata* md, uhdrb200_image* dest, int sdr_is_601, cudaStream_t s, bool fused = false) {
+                  uhdrb200_metadata* md, uhdrb200_image* dest, int sdr_is_601, cudaStream_t s, bool fused = false,
+                  const float* conv = nullptr) {
   if (n <= 0) return UHDRB200_NO_ERROR;
   if (!sdr || !hdr || !md || !dest) return UHDRB200_ERROR_BAD_PTR;
   for (int i = 0; i < n; i++) {
@@ -354,6 +355,10 @@ int generate_core(int n, const uhdrb200_image* sdr, const uhdrb200_image* hdr, i
     p.code_at_min = (int)(uint8_t)((log2((double)p.min_boost) - (double)p.log2_min) / den * 255.0);
     p.code_at_max = (int)(uint8_t)((log2((double)p.max_boost) - (double)p.log2_min) / den * 255.0);
     p.code_scale = (float)(255.0 / den);
+  }
+  if (conv) {
+    p.convert = 1;
+    memcpy(p.conv, conv, sizeof p.conv);
   }
   BatchSlot* slot = nullptr;
   if (n == 1) p.single = v[0];
@@ -501,6 +506,16 @@ int tonemap_core(int n, const uhdrb200_image* src, uhdrb200_image* dest, cudaStr
 }
 
 // jpegr.cpp:1134-1195: selector; identity conversions return NO_ERROR without touching the image
+// YUV->YUV matrices, gainmapmath.cpp:447-481; [src][dst]. All have the first column (1, 0, 0), which
+// transform_quad (uhdr_convert.cuh) relies on.
+const float kYuvToYuv[3][3][9] = {
+    {{0}, {1.0f, 0.101579f, 0.196076f, 0.0f, 0.989854f, -0.110653f, 0.0f, -0.072453f, 0.983398f},
+     {1.0f, -0.016969f, 0.096312f, 0.0f, 0.995306f, -0.051192f, 0.0f, 0.011507f, 1.002637f}},
+    {{1.0f, -0.118188f, -0.212685f, 0.0f, 1.018640f, 0.114618f, 0.0f, 0.075049f, 1.025327f}, {0},
+     {1.0f, -0.128245f, -0.115879f, 0.0f, 1.010016f, 0.061592f, 0.0f, 0.086969f, 1.029350f}},
+    {{1.0f, 0.018149f, -0.095132f, 0.0f, 1.004123f, 0.051267f, 0.0f, -0.011524f, 0.996782f},
+     {1.0f, 0.117887f, 0.105521f, 0.0f, 0.995211f, -0.059549f, 0.0f, -0.084085f, 0.976518f}, {0}}};
+
 int convert_yuv_core(uhdrb200_image* im, int src_enc, int dst_enc, cudaStream_t s) {
   if (!im) return UHDRB200_ERROR_BAD_PTR;
   if (src_enc == UHDRB200_COLORGAMUT_UNSPECIFIED || dst_enc == UHDRB200_COLORGAMUT_UNSPECIFIED)
@@ -508,20 +523,12 @@ int convert_yuv_core(uhdrb200_image* im, int src_enc, int dst_enc, cudaStream_t 
   if (src_enc < 0 || src_enc > 2 || dst_enc < 0 || dst_enc > 2) return UHDRB200_ERROR_INVALID_COLORGAMUT;
   if (src_enc == dst_enc) return UHDRB200_NO_ERROR;
   if (!im->data || !im->chroma_data) return UHDRB200_ERROR_BAD_PTR;
-  // gainmapmath.cpp:447-481; [src][dst]
-  static const float M[3][3][9] = {
-      {{0}, {1.0f, 0.101579f, 0.196076f, 0.0f, 0.989854f, -0.110653f, 0.0f, -0.072453f, 0.983398f},
-       {1.0f, -0.016969f, 0.096312f, 0.0f, 0.995306f, -0.051192f, 0.0f, 0.011507f, 1.002637f}},
-      {{1.0f, -0.118188f, -0.212685f, 0.0f, 1.018640f, 0.114618f, 0.0f, 0.075049f, 1.025327f}, {0},
-       {1.0f, -0.128245f, -0.115879f, 0.0f, 1.010016f, 0.061592f, 0.0f, 0.086969f, 1.029350f}},
-      {{1.0f, 0.018149f, -0.095132f, 0.0f, 1.004123f, 0.051267f, 0.0f, -0.011524f, 0.996782f},
-       {1.0f, 0.117887f, 0.105521f, 0.0f, 0.995211f, -0.059549f, 0.0f, -0.084085f, 0.976518f}, {0}}};
   int st = ensure_ctx();
   if (st) return st;
   ConvertYuvParams p;
   memset(&p, 0, sizeof p);
   p.g = geometry_of(im, nullptr);
-  memcpy(p.m, M[src_enc][dst_enc], sizeof p.m);
+  memcpy(p.m, kYuvToYuv[src_enc][dst_enc], sizeof p.m);
   set_sdr_planes(p.single, *im);
   p.single.sdr_v = (const uint8_t*)im->chroma_data + im->chroma_stride * im->height / 2;  // gainmapmath.cpp:507
   cudaError_t e = launch_convert_yuv_impl(p, 1, convert_yuv_vec_ok(p.g, p.single), s);
@@ -599,7 +606,7 @@ int copy_yuv420_core(const uhdrb200_image* src, uhdrb200_image* dst, cudaStream_
 
 // API-0 (jpegr.cpp:167-225): toneMap(hdr -> sdr) then generateGainMap(sdr, hdr). One fused launch when the
 // layout allows it (width, height % 4 == 0, vector-aligned planes), else the two kernels back to back.
-int api0_core(int n, const uhdrb200_image* hdr, int hdr_tf, uhdrb200_image* sdr, uhdrb200_metadata* md,
+int api0_core(int n, const uhdrb200_image* hdr, int hdr_tf, int sdr_to_601, uhdrb200_image* sdr, uhdrb200_metadata* md,
               uhdrb200_image* dest, cudaStream_t s) {
   if (n <= 0) return UHDRB200_NO_ERROR;
   if (!hdr || !sdr || !md || !dest) return UHDRB200_ERROR_BAD_PTR;
@@ -611,6 +618,9 @@ int api0_core(int n, const uhdrb200_image* hdr, int hdr_tf, uhdrb200_image* sdr,
     if ((st = validate_generate(&tmp, &hdr[i], hdr_tf, &md[i], &dest[i]))) return st;
     if (!dest[i].data) return UHDRB200_ERROR_BAD_PTR;
   }
+  // jpegr.cpp:223-225: the SDR image is re-encoded to BT.601 for the JPEG unless its gamut is P3 already
+  const int gamut = hdr[0].colorGamut;
+  const bool conv = sdr_to_601 && gamut != UHDRB200_COLORGAMUT_P3;
   bool fused = true;
   for (int i = 0; i < n && fused; i++) {
     Geometry g = geometry_of(&sdr[i], &hdr[i]);
@@ -624,10 +634,13 @@ int api0_core(int n, const uhdrb200_image* hdr, int hdr_tf, uhdrb200_image* sdr,
   if (!fused) {
     int st = tonemap_core(n, hdr, sdr, s);
     if (st) return st;
-    return generate_core(n, sdr, hdr, hdr_tf, md, dest, 0, s);
+    if ((st = generate_core(n, sdr, hdr, hdr_tf, md, dest, 0, s))) return st;
+    for (int i = 0; i < n && conv; i++)
+      if ((st = convert_yuv_core(&sdr[i], gamut, UHDRB200_COLORGAMUT_P3, s))) return st;
+    return UHDRB200_NO_ERROR;
   }
   for (int i = 0; i < n; i++) sdr[i].colorGamut = hdr[i].colorGamut;
-  return generate_core(n, sdr, hdr, hdr_tf, md, dest, 0, s, true);
+  return generate_core(n, sdr, hdr, hdr_tf, md, dest, 0, s, true, conv ? kYuvToYuv[gamut][UHDRB200_COLORGAMUT_P3] : nullptr);
 }
 
 }  // namespace
@@ -823,7 +836,7 @@ int copy_yuv420_host(const uhdrb200_image* src, uhdrb200_image* dst) {
   return UHDRB200_NO_ERROR;
 }
 
-int api0_host(const uhdrb200_image* hdr, int hdr_tf, uhdrb200_image* sdr, uhdrb200_metadata* md, uhdrb200_image* dest,
+int api0_host(const uhdrb200_image* hdr, int hdr_tf, int sdr_to_601, uhdrb200_image* sdr, uhdrb200_metadata* md, uhdrb200_image* dest,
               void* map_buf, size_t map_buf_bytes) {
   int st = validate_tonemap(hdr, sdr);
   if (st) return st;
@@ -844,7 +857,7 @@ int api0_host(const uhdrb200_image* hdr, int hdr_tf, uhdrb200_image* sdr, uhdrb2
   dh.data = c.buf[2].p; dh.chroma_data = c.buf[3].p;
   ds.data = c.buf[6].p; ds.chroma_data = c.buf[7].p;
   dm.data = c.buf[4].p;
-  if ((st = api0_core(1, &dh, hdr_tf, &ds, md, &dm, c.stream))) return st;
+  if ((st = api0_core(1, &dh, hdr_tf, sdr_to_601, &ds, md, &dm, c.stream))) return st;
   if (dl) CU(cudaMemcpyAsync(sdr->data, c.buf[6].p, dl, cudaMemcpyDeviceToHost, c.stream));
   if (dc) CU(cudaMemcpyAsync(sdr->chroma_data, c.buf[7].p, dc, cudaMemcpyDeviceToHost, c.stream));
   if (mbytes) CU(cudaMemcpyAsync(map_buf, c.buf[4].p, mbytes, cudaMemcpyDeviceToHost, c.stream));
@@ -950,18 +963,19 @@ int uhdrb200_tonemap_dev(const uhdrb200_image* src, uhdrb200_image* dest, void* 
 int uhdrb200_tonemap_batch_dev(int n, const uhdrb200_image* src, uhdrb200_image* dest, void* stream) {
   return tonemap_core(n, src, dest, (cudaStream_t)stream);
 }
-int uhdrb200_tonemap_generate_gainmap_host_into(const uhdrb200_image* p010, int hdr_tf, uhdrb200_image* sdr_dest,
+int uhdrb200_tonemap_generate_gainmap_host_into(const uhdrb200_image* p010, int hdr_tf, int sdr_to_601, uhdrb200_image* sdr_dest,
                                                 uhdrb200_metadata* metadata, uhdrb200_image* map_dest, void* map_buf,
                                                 size_t map_buf_bytes) {
-  return api0_host(p010, hdr_tf, sdr_dest, metadata, map_dest, map_buf, map_buf_bytes);
+  return api0_host(p010, hdr_tf, sdr_to_601, sdr_dest, metadata, map_dest, map_buf, map_buf_bytes);
 }
-int uhdrb200_tonemap_generate_gainmap_dev(const uhdrb200_image* p010, int hdr_tf, uhdrb200_image* sdr_dest,
+int uhdrb200_tonemap_generate_gainmap_dev(const uhdrb200_image* p010, int hdr_tf, int sdr_to_601, uhdrb200_image* sdr_dest,
                                           uhdrb200_metadata* metadata, uhdrb200_image* map_dest, void* stream) {
-  return api0_core(1, p010, hdr_tf, sdr_dest, metadata, map_dest, (cudaStream_t)stream);
+  return api0_core(1, p010, hdr_tf, sdr_to_601, sdr_dest, metadata, map_dest, (cudaStream_t)stream);
 }
-int uhdrb200_tonemap_generate_gainmap_batch_dev(int n, const uhdrb200_image* p010, int hdr_tf, uhdrb200_image* sdr_dest,
-                                                uhdrb200_metadata* metadata, uhdrb200_image* map_dest, void* stream) {
-  return api0_core(n, p010, hdr_tf, sdr_dest, metadata, map_dest, (cudaStream_t)stream);
+int uhdrb200_tonemap_generate_gainmap_batch_dev(int n, const uhdrb200_image* p010, int hdr_tf, int sdr_to_601,
+                                                uhdrb200_image* sdr_dest, uhdrb200_metadata* metadata, uhdrb200_image* map_dest,
+                                                void* stream) {
+  return api0_core(n, p010, hdr_tf, sdr_to_601, sdr_dest, metadata, map_dest, (cudaStream_t)stream);
 }
 int uhdrb200_convert_yuv_host(uhdrb200_image* image, int src_encoding, int dest_encoding) {
   return convert_yuv_host(image, src_encoding, dest_encoding);

@@ -7,37 +7,12 @@
 // One thread = two horizontally adjacent quads (4 px x 2 rows): 32-bit luma loads/stores, 16-bit
 // chroma loads/stores. In place, so plain (coherent) loads; every byte is read and written by the
 // same thread only. HBM-bound: 1.5 B/px read + 1.5 B/px written.
+#include "uhdr_convert.cuh"
 #include "uhdr_kernels.cuh"
 #include "uhdr_math.cuh"
 
 namespace uhdr {
 namespace {
-
-__device__ __forceinline__ uint32_t to_u8(float v) {  // static_cast<uint8_t>(CLIP3(v, 0, 255))
-  v = v < 0.0f ? 0.0f : (v > 255.0f ? 255.0f : v);
-  return __float2uint_rz(v);
-}
-
-struct Quad { uint32_t y[2][2]; uint32_t u, v; };
-
-__device__ __forceinline__ void transform_quad(const float* m, Quad& q) {
-  const float uf = (float)((int)q.u - 128) * (1 / 255.0f), vf = (float)((int)q.v - 128) * (1 / 255.0f);
-  float su = 0.f, sv = 0.f;
-  bool first = true;
-#pragma unroll
-  for (int r = 0; r < 2; r++)
-#pragma unroll
-    for (int c = 0; c < 2; c++) {  // order yuv1..yuv4 = (0,0),(1,0),(0,1),(1,1) in (x,y): gainmapmath.cpp:485-488
-      const float yf = (float)q.y[r][c] * (1 / 255.0f);
-      const float ny = m[0] * yf + m[1] * uf + m[2] * vf;
-      const float nu = m[3] * yf + m[4] * uf + m[5] * vf;
-      const float nv = m[6] * yf + m[7] * uf + m[8] * vf;
-      if (first) { su = nu; sv = nv; first = false; } else { su += nu; sv += nv; }
-      q.y[r][c] = to_u8(ny * 255.0f + 0.5f);
-    }
-  q.u = to_u8(su / 4.0f * 255.0f + 128.0f + 0.5f);
-  q.v = to_u8(sv / 4.0f * 255.0f + 128.0f + 0.5f);
-}
 
 template <bool VEC>
 __global__ void __launch_bounds__(256) convert_yuv_kernel(ConvertYuvParams p) {

@@ -8,6 +8,7 @@
 // The 4x4 box average (gainmapmath.cpp:605-615) is an exact integer sum (dp4a / dp2a) converted
 // once; with the fp32 transcendental chain (~1e-6 relative, uhdr_math.cuh) that is the only
 // deviation from the reference: map bytes +-1 LSB, >= 99.9 % exact.
+#include "uhdr_convert.cuh"
 #include "uhdr_io.cuh"
 #include "uhdr_kernels.cuh"
 #include "uhdr_math.cuh"
@@ -20,7 +21,9 @@ namespace {
 // 4x4 SDR block from the P010 block it already holds, WRITES it to the SDR planes (with the
 // reference's zero-filled stride tails) and feeds it to the same gain computation: P010 is read
 // once and nothing is re-read (4.5625 B/px instead of 4.5 + 4.5625). Requires width, height % 4 == 0.
-template <bool VEC, bool FUSED>
+// CONVERT (with FUSED): the SDR block is stored re-encoded by convertYuv (row N1, jpegr.cpp:223-225,
+// transformYuv420 gainmapmath.cpp:483-520) while the gain computation keeps the un-converted samples.
+template <bool VEC, bool FUSED, bool CONVERT = false>
 __global__ void __launch_bounds__(256) generate_kernel(GenerateParams p) {
   const Geometry& g = p.g;
   const int mx = blockIdx.x * 32 + threadIdx.x;
@@ -49,16 +52,44 @@ __global__ void __launch_bounds__(256) generate_kernel(GenerateParams p) {
       uint8_t* ou = const_cast<uint8_t*>(u8);
       uint8_t* ov = const_cast<uint8_t*>(v8);
 #pragma unroll
-      for (int r = 0; r < 4; r++) {
-        sy[r] = __byte_perm(hy[r].x, hy[r].y, 0x7531);  // high byte of each u16 == (v >> 6) >> 2, ultrahdr.cpp:530-531
-        stg4(oy + (size_t)r * g.sdr_luma_stride, sy[r]);
-      }
+      for (int r = 0; r < 4; r++) sy[r] = __byte_perm(hy[r].x, hy[r].y, 0x7531);  // high byte of each u16 == (v >> 6) >> 2, ultrahdr.cpp:530-531
 #pragma unroll
       for (int r = 0; r < 2; r++) {
         su[r] = __byte_perm(huv[r].x, huv[r].y, 0x7751) & 0xFFFFu;  // U0 U1
         sv[r] = __byte_perm(huv[r].x, huv[r].y, 0x7773) & 0xFFFFu;  // V0 V1
-        stg2(ou + (size_t)r * g.sdr_chroma_stride, su[r]);
-        stg2(ov + (size_t)r * g.sdr_chroma_stride, sv[r]);
+      }
+      uint32_t oy_w[4], ou_w[2], ov_w[2];  // what is stored: the tone-mapped block, re-encoded when CONVERT
+#pragma unroll
+      for (int r = 0; r < 4; r++) oy_w[r] = sy[r];
+#pragma unroll
+      for (int r = 0; r < 2; r++) { ou_w[r] = su[r]; ov_w[r] = sv[r]; }
+      if (CONVERT) {
+#pragma unroll
+        for (int qr = 0; qr < 2; qr++) {
+          uint32_t ya = 0, yb = 0, uu = 0, vv = 0;
+#pragma unroll
+          for (int qc = 0; qc < 2; qc++) {
+            Quad q;
+            q.y[0][0] = (sy[2 * qr] >> (16 * qc)) & 0xff;     q.y[0][1] = (sy[2 * qr] >> (16 * qc + 8)) & 0xff;
+            q.y[1][0] = (sy[2 * qr + 1] >> (16 * qc)) & 0xff; q.y[1][1] = (sy[2 * qr + 1] >> (16 * qc + 8)) & 0xff;
+            q.u = (su[qr] >> (8 * qc)) & 0xff;
+            q.v = (sv[qr] >> (8 * qc)) & 0xff;
+            transform_quad(p.conv, q);
+            ya |= (q.y[0][0] | (q.y[0][1] << 8)) << (16 * qc);
+            yb |= (q.y[1][0] | (q.y[1][1] << 8)) << (16 * qc);
+            uu |= q.u << (8 * qc);
+            vv |= q.v << (8 * qc);
+          }
+          oy_w[2 * qr] = ya; oy_w[2 * qr + 1] = yb;
+          ou_w[qr] = uu; ov_w[qr] = vv;
+        }
+      }
+#pragma unroll
+      for (int r = 0; r < 4; r++) stg4(oy + (size_t)r * g.sdr_luma_stride, oy_w[r]);
+#pragma unroll
+      for (int r = 0; r < 2; r++) {
+        stg2(ou + (size_t)r * g.sdr_chroma_stride, ou_w[r]);
+        stg2(ov + (size_t)r * g.sdr_chroma_stride, ov_w[r]);
       }
       if (mx == g.map_width - 1) {  // stride tails, ultrahdr.cpp:533-535, 551-554
         for (int x = g.width; x < g.sdr_luma_stride; x++)
@@ -185,7 +216,8 @@ cudaError_t launch_api0_fused_impl(const GenerateParams& p, int n, cudaStream_t 
   if (p.g.map_width == 0 || p.g.map_height == 0 || n == 0) return cudaSuccess;
   dim3 block(32, 8, 1);
   dim3 grid((p.g.map_width + 31) / 32, (p.g.map_height + 7) / 8, n);
-  generate_kernel<true, true><<<grid, block, 0, s>>>(p);
+  if (p.convert) generate_kernel<true, true, true><<<grid, block, 0, s>>>(p);
+  else generate_kernel<true, true, false><<<grid, block, 0, s>>>(p);
   return cudaGetLastError();
 }
 

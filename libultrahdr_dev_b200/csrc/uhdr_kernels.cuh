@@ -42,6 +42,8 @@ struct GenerateParams {
   float min_boost, max_boost, log2_min, log2_max;
   int code_at_min, code_at_max;  // encodeGain of a gain clamped to min/max, evaluated on the host in double
   float code_scale;              // 255 / (log2_max - log2_min), the float difference like the reference, in double
+  int convert;                   // fused API-0 only: 1 = the SDR planes are written re-encoded with `conv` (row N1, jpegr.cpp:223-225)
+  float conv[9];                 // YUV->YUV matrix, gainmapmath.cpp:447-481
   Planes single;
   const Planes* batch;  // device array, indexed by blockIdx.z; nullptr => `single`
 };

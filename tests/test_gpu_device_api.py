@@ -319,6 +319,34 @@ def test_api0_fused_equals_tonemap_then_generate(uh, orc, w, h, ls, cs, dls):
     parity.compare_bytes(map_b, want, "api0 fused map", min_exact=0.99)
 
 
+@pytest.mark.parametrize("gamut", [abi.COLORGAMUT_BT709, abi.COLORGAMUT_P3, abi.COLORGAMUT_BT2100])
+@pytest.mark.parametrize("w,h,dls", [(256, 128, 256), (136, 72, 144), (130, 66, 144), (8, 4, 16)])
+def test_api0_fused_with_convert_to_601(uh, orc, gamut, w, h, dls):
+    """The whole pixel part of API-0 (jpegr.cpp:167-225) in one call: toneMap, generateGainMap on the
+    un-converted image, convertYuv(gamut -> BT.601) of the SDR planes; byte-identical to the oracle's chain."""
+    _, hdr_b = synth.natural_pair(w, h, 12, abi.TF_HLG, gamut, gamut)
+    hdr = abi.host_p010(hdr_b, w, h, gamut)
+    dcs = dls // 2
+    sdr_o = np.full(abi.yuv420_size(w, h, dls, dcs), 0x55, dtype=np.uint8)
+    so = abi.host_yuv420(sdr_o, w, h, -1, dls, dcs)
+    assert orc.tonemap(hdr, so) == 0
+    _, want_map, _, _ = orc.generate_gainmap(so, hdr, abi.TF_HLG)
+    if gamut != abi.COLORGAMUT_P3:
+        assert orc.convert_yuv(so, gamut, abi.COLORGAMUT_P3) == 0
+    sdr_b = np.full(abi.yuv420_size(w, h, dls, dcs), 0x55, dtype=np.uint8)
+    sb = abi.host_yuv420(sdr_b, w, h, -1, dls, dcs)
+    map_b = np.zeros((h // 4) * (w // 4), dtype=np.uint8)
+    md, mdesc = abi.Metadata(), abi.Image()
+    n0 = uh.lib.uhdrb200_launch_count()
+    assert uh.toneMapGenerateGainMapInto(hdr, abi.TF_HLG, sb, md, mdesc, map_b, sdr_to_601=True) == 0
+    launches = uh.lib.uhdrb200_launch_count() - n0
+    fused = w % 4 == 0 and h % 4 == 0
+    assert launches == (1 if fused else (2 if gamut == abi.COLORGAMUT_P3 else 3))
+    assert sb.colorGamut == gamut
+    assert np.array_equal(sdr_b, sdr_o), "SDR planes after the fused convertYuv differ from the oracle chain"
+    parity.compare_bytes(map_b, want_map, "api0 fused+convert map", min_exact=0.99)
+
+
 def test_api0_fused_error_codes(uh):
     w, h = 32, 16
     _, hdr_b = synth.uniform_pair(w, h, 1)
