@@ -349,11 +349,31 @@ __global__ void __launch_bounds__(kThreads, UHDR_APPLY_MIN_BLOCKS) apply_fast_ke
 // The linear toe (c <= 0.04045, 8-bit code <= 10) has Phi = (c / 12.92)^(1/2.4): a quad-row of the
 // cell that contains such a channel (tested conservatively on min(y) and min(o)) takes a branch
 // that evaluates that power with MUFU lg2/ex2; everything downstream is shared.
+// (Phi * f')^2.4 for the linear outputs: two MUFU; q == 0 gives lg2 = -inf and ex2(-inf) = +0
+__device__ __forceinline__ float pow24(float q) { return mufu_ex2(2.4f * mufu_lg2(q)); }
+
+// {lo, hi} floats -> packed half2 with truncation (F2FP.PACK_AB.RZ): on the normal-half range this is exactly the
+// reference's floatToHalf (gainmapmath.h:136-147) once 0x1000 has been added to the float's bits
+__device__ __forceinline__ uint32_t pack_half2_rz(float lo, float hi) {
+  uint32_t d;
+  asm("cvt.rz.f16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(hi), "f"(lo));
+  return d;
+}
+
+// L table (q^2.4, 10 bits per octave): tL = shared address of the table - 8 * kLBase; SHF + LEA + LDS.64 + FFMA
+__device__ __forceinline__ float l_eval(uint32_t tL, float q) {
+  const uint32_t addr = ((__float_as_uint(q) >> (23 - kLBits)) << 3) + tL;
+  float a, b;
+  asm("ld.shared.v2.f32 {%0,%1}, [%2];" : "=f"(a), "=f"(b) : "r"(addr));
+  return fmaf(b, q, a);
+}
+
 // two pixel rows (one row of 2x2 chroma quads) of a cell: Phi -> q -> P(q) -> floor -> pack -> 128-bit store per row
-template <bool MASK, bool kToe>
+// (RGBA1010102), or Phi -> q -> q^2.4 -> half / 10-bit pack (linear outputs)
+template <int PACK, bool MASK, bool kToe, bool LTAB, bool NORM>
 __device__ __forceinline__ void q_rows(const uint32_t hiP, const uint32_t uq, const uint32_t vq,
                                        const float (&oR)[2], const float (&oG)[2], const float (&oB)[2], const float (&yf)[2][4],
-                                       const float* __restrict__ f8, uint8_t* orow, const size_t ostride) {
+                                       const float* __restrict__ f8, uint8_t* orow, const size_t ostride, const size_t plane_bytes) {
   constexpr float KP = (float)(1.0 / (255.0 * 1.055));
   constexpr float q0 = 1.0f / (float)(1 << -kPLoExp);  // 2^kPLoExp as an FFMA immediate
         float rv[2] = {0.f, 0.f}, gq[2] = {0.f, 0.f}, bu[2] = {0.f, 0.f};
@@ -369,7 +389,7 @@ __device__ __forceinline__ void q_rows(const uint32_t hiP, const uint32_t uq, co
         }
 #pragma unroll
         for (int rr = 0; rr < 2; rr++) {
-          uint32_t w[4];
+          uint32_t w[4][PACK == kPack1010102 ? 1 : (PACK == kPackF16 ? 2 : 3)];
 #pragma unroll
           for (int i = 0; i < 4; i++) {
             const int c = i >> 1;
@@ -377,35 +397,101 @@ __device__ __forceinline__ void q_rows(const uint32_t hiP, const uint32_t uq, co
             float phR = __saturatef(fmaf(y, KP, oR[c]));
             float phG = __saturatef(fmaf(y, KP, oG[c]));
             float phB = __saturatef(fmaf(y, KP, oB[c]));
+            float cR = 0.f, cG = 0.f, cB = 0.f;
+            bool tR = false, tG = false, tB = false;
             if (kToe) {
-              const float cR = __saturatef(fmaf(y, 1 / 255.0f, rv[c]));
-              const float cG = __saturatef(fmaf(y, 1 / 255.0f, gq[c]));
-              const float cB = __saturatef(fmaf(y, 1 / 255.0f, bu[c]));
-              if (cR <= 0.04045f) phR = mufu_ex2((float)(1.0 / 2.4) * mufu_lg2(cR * (float)(1.0 / 12.92)));
-              if (cG <= 0.04045f) phG = mufu_ex2((float)(1.0 / 2.4) * mufu_lg2(cG * (float)(1.0 / 12.92)));
-              if (cB <= 0.04045f) phB = mufu_ex2((float)(1.0 / 2.4) * mufu_lg2(cB * (float)(1.0 / 12.92)));
+              cR = __saturatef(fmaf(y, 1 / 255.0f, rv[c]));
+              cG = __saturatef(fmaf(y, 1 / 255.0f, gq[c]));
+              cB = __saturatef(fmaf(y, 1 / 255.0f, bu[c]));
+              tR = cR <= 0.04045f;
+              tG = cG <= 0.04045f;
+              tB = cB <= 0.04045f;
+              if (PACK == kPack1010102) {
+                if (tR) phR = mufu_ex2((float)(1.0 / 2.4) * mufu_lg2(cR * (float)(1.0 / 12.92)));
+                if (tG) phG = mufu_ex2((float)(1.0 / 2.4) * mufu_lg2(cG * (float)(1.0 / 12.92)));
+                if (tB) phB = mufu_ex2((float)(1.0 / 2.4) * mufu_lg2(cB * (float)(1.0 / 12.92)));
+              }
             }
-            // the P table is >= 0 everywhere (tables.cu), so floor == the reference's truncation
-            const float vR = p_eval(hiP, fmaf(phR, fi, q0));
-            const float vG = p_eval(hiP, fmaf(phG, fi, q0));
-            const float vB = p_eval(hiP, fmaf(phB, fi, q0));
-            if (MASK) {  // codes above 1023 wrap like the reference's `& 0x3ff` (gainmapmath.cpp:722-727)
-              w[i] = (floor_bits(vR) & 0x3ffu) | ((floor_bits(vG) & 0x3ffu) << 10) | ((floor_bits(vB) & 0x3ffu) << 20) | 0xC0000000u;
+            if (PACK == kPack1010102) {
+              // the P table is >= 0 everywhere (tables.cu), so floor == the reference's truncation
+              const float vR = p_eval(hiP, fmaf(phR, fi, q0));
+              const float vG = p_eval(hiP, fmaf(phG, fi, q0));
+              const float vB = p_eval(hiP, fmaf(phB, fi, q0));
+              if (MASK) {  // codes above 1023 wrap like the reference's `& 0x3ff` (gainmapmath.cpp:722-727)
+                w[i][0] = (floor_bits(vR) & 0x3ffu) | ((floor_bits(vG) & 0x3ffu) << 10) | ((floor_bits(vB) & 0x3ffu) << 20) | 0xC0000000u;
+              } else {
+                // floor + pack in 5 operations: G floored, moved up 10 bits inside the float (exact FFMA), R floored
+                // on top of it by one FADD.RM; B floored with a bias whose << 20 also supplies the alpha bits and
+                // cancels the 0x4B000000 of the R|G word.
+                const float Gm = add_rm(vG, 8388608.0f);
+                const float cGs = fmaf(Gm, 1024.0f, 8388608.0f - 8589934592.0f);  // 2^23 + 1024 * G
+                const float t = add_rm(vR, cGs);
+                const float Bm = add_rm(vB, 8388608.0f + 1872.0f);  // (0x750 << 20) == 0xC0000000 - 0x4B000000
+                w[i][0] = (__float_as_uint(Bm) << 20) + __float_as_uint(t);
+              }
             } else {
-              // floor + pack in 5 operations: G floored, moved up 10 bits inside the float (exact FFMA), R floored
-              // on top of it by one FADD.RM; B floored with a bias whose << 20 also supplies the alpha bits and
-              // cancels the 0x4B000000 of the R|G word.
-              const float Gm = add_rm(vG, 8388608.0f);
-              const float cGs = fmaf(Gm, 1024.0f, 8388608.0f - 8589934592.0f);  // 2^23 + 1024 * G
-              const float t = add_rm(vR, cGs);
-              const float Bm = add_rm(vB, 8388608.0f + 1872.0f);  // (0x750 << 20) == 0xC0000000 - 0x4B000000
-              w[i] = (__float_as_uint(Bm) << 20) + __float_as_uint(t);
+              // linear light: f * srgbInvOetf(c) = (Phi * f')^2.4 above the toe, f * c / 12.92 on it
+              float eR, eG, eB;
+              if (LTAB) {  // hiP carries the L table's biased shared address
+                // channels on the toe have Phi down to 0: keep their (discarded) look-up inside the table
+                constexpr float kQLo = 1.0f / (float)(1 << -kLLoExp);
+                const float qR = kToe ? fmaxf(phR * fi, kQLo) : phR * fi;
+                const float qG = kToe ? fmaxf(phG * fi, kQLo) : phG * fi;
+                const float qB = kToe ? fmaxf(phB * fi, kQLo) : phB * fi;
+                eR = l_eval(hiP, qR); eG = l_eval(hiP, qG); eB = l_eval(hiP, qB);
+              } else {
+                eR = pow24(phR * fi); eG = pow24(phG * fi); eB = pow24(phB * fi);
+              }
+              if (kToe) {
+                const float f24 = pow24(fi);
+                if (tR) eR = cR * (float)(1.0 / 12.92) * f24;
+                if (tG) eG = cG * (float)(1.0 / 12.92) * f24;
+                if (tB) eB = cB * (float)(1.0 / 12.92) * f24;
+              }
+              if (PACK == kPackF16) {
+                // floatToHalf (gainmapmath.h:136-147), see apply_fast_kernel: shift + re-bias on the normal-half range
+                const uint32_t bR = __float_as_uint(eR) + 0x1000u, bG = __float_as_uint(eG) + 0x1000u, bB = __float_as_uint(eB) + 0x1000u;
+                if (NORM && !kToe) {  // host guarantee: every value of a toe-free quad-row is a normal half
+                  w[i][0] = pack_half2_rz(__uint_as_float(bR), __uint_as_float(bG));
+                  w[i][1] = pack_half2_rz(__uint_as_float(bB), 1.0f);
+                } else {
+                  uint32_t hR, hG, hB;
+                  if (min(bR, min(bG, bB)) >= 0x38800000u) {
+                    hR = (bR >> 13) - 0x1C000u;
+                    hG = (bG >> 13) - 0x1C000u;
+                    hB = (bB >> 13) - 0x1C000u;
+                  } else {
+                    hR = bR >= 0x38800000u ? (bR >> 13) - 0x1C000u : 0u;
+                    hG = bG >= 0x38800000u ? (bG >> 13) - 0x1C000u : 0u;
+                    hB = bB >= 0x38800000u ? (bB >> 13) - 0x1C000u : 0u;
+                    if (bR - 0x33000000u < 0x05800000u) hR = float_to_half_ref(eR);
+                    if (bG - 0x33000000u < 0x05800000u) hG = float_to_half_ref(eG);
+                    if (bB - 0x33000000u < 0x05800000u) hB = float_to_half_ref(eB);
+                  }
+                  w[i][0] = hR | (hG << 16);
+                  w[i][1] = hB | (0x3C00u << 16);
+                }
+              } else {
+                // 0x3ff & uint(v * 1023) (ultrahdr.cpp:460-468): v >= 0, so truncation = floor = FADD.RM
+                w[i][0] = floor_bits(eR * 1023.0f) & 0x3ffu;
+                w[i][1] = floor_bits(eG * 1023.0f) & 0x3ffu;
+                w[i][2] = floor_bits(eB * 1023.0f) & 0x3ffu;
+              }
             }
           }
+          uint8_t* o = orow + (size_t)rr * ostride;
+          if (PACK == kPack1010102) {
 #ifdef UHDR_DBG_NOSTORE
-          if ((w[0] ^ w[1] ^ w[2] ^ w[3]) == 0x12345679u)
+            if ((w[0][0] ^ w[1][0] ^ w[2][0] ^ w[3][0]) == 0x12345679u)
 #endif
-          stg16(orow + (size_t)rr * ostride, make_uint4(w[0], w[1], w[2], w[3]));
+            stg16(o, make_uint4(w[0][0], w[1][0], w[2][0], w[3][0]));
+          } else if (PACK == kPackF16) {  // colorToRgbaF16, gainmapmath.cpp:729-732
+            stg32(o, make_uint4(w[0][0], w[0][1], w[1][0], w[1][1]), make_uint4(w[2][0], w[2][1], w[3][0], w[3][1]));
+          } else {  // three planar u16 planes, ultrahdr.cpp:460-468
+#pragma unroll
+            for (int ch = 0; ch < 3; ch++)
+              stg8(o + ch * plane_bytes, make_uint2(w[0][ch] | (w[1][ch] << 16), w[2][ch] | (w[3][ch] << 16)));
+          }
         }
 }
 
@@ -422,28 +508,44 @@ constexpr int kQTileRows = 8 * kQCells;  // cell rows per tile: 8 warps x kQCell
 // Tile = 32 x kQTileRows map cells (128 x 128 pixels for kQCells = 4). A lane owns one column of
 // cells; a warp walks kQCells cell rows downwards, so the lower pair of map samples of one cell is
 // the upper pair of the next (2 map loads per cell) and every plane pointer advances by a constant.
-template <bool MASK, bool BATCH>
-__global__ void __launch_bounds__(kThreads, UHDR_APPLYQ_MIN_BLOCKS) apply_q_kernel(const __grid_constant__ ApplyFastParams p) {
-  // dynamic shared memory: [mbarrier 16 B] ... [P table at shared address == kPRing (mod 32 KB)]
-  extern __shared__ __align__(16) uint8_t smem_dyn[];
-  uint64_t* bar = reinterpret_cast<uint64_t*>(smem_dyn);
-  const uint32_t dyn0 = smem_u32(smem_dyn);
-  const uint32_t pAddr = q_table_addr(dyn0);
-  {
-    uint32_t dyn_size;
-    asm("mov.u32 %0, %%dynamic_smem_size;" : "=r"(dyn_size));
-    if (pAddr - dyn0 + kPEntries * (uint32_t)sizeof(float2) > dyn_size) __trap();
-  }
-  const uint32_t hiP = pAddr - kPRing;
+template <int PACK, bool MASK, bool BATCH, bool LTAB, bool NORM>
+__global__ void __launch_bounds__(kThreads, LTAB ? 3 : UHDR_APPLYQ_MIN_BLOCKS) apply_q_kernel(const __grid_constant__ ApplyFastParams p) {
   const int tid = threadIdx.x;
-  if (tid == 0) mbar_init(bar, 1);
-  __syncthreads();
-  if (tid == 0) {
-    constexpr uint32_t pb = kPEntries * sizeof(float2);
-    mbar_expect_tx(bar, pb);
-    bulk_g2s(smem_dyn + (pAddr - dyn0), p.output_format == 3 ? p.tab.p_hlg : p.tab.p_pq, pb, bar);
+  uint32_t hiP = 0;
+  if (LTAB) {
+    // dynamic shared memory: [mbarrier 16 B][L table 56 KB]
+    extern __shared__ __align__(16) uint8_t smem_dyn[];
+    uint64_t* bar = reinterpret_cast<uint64_t*>(smem_dyn);
+    if (tid == 0) mbar_init(bar, 1);
+    __syncthreads();
+    if (tid == 0) {
+      constexpr uint32_t lb = kLEntries * sizeof(float2);
+      mbar_expect_tx(bar, lb);
+      bulk_g2s(smem_dyn + 16, p.tab.l_pow, lb, bar);
+    }
+    mbar_wait(bar, 0);
+    hiP = smem_u32(smem_dyn + 16) - 8u * (uint32_t)kLBase;
+  } else if (PACK == kPack1010102) {
+    // dynamic shared memory: [mbarrier 16 B] ... [P table at shared address == kPRing (mod the ring size)]
+    extern __shared__ __align__(16) uint8_t smem_dyn[];
+    uint64_t* bar = reinterpret_cast<uint64_t*>(smem_dyn);
+    const uint32_t dyn0 = smem_u32(smem_dyn);
+    const uint32_t pAddr = q_table_addr(dyn0);
+    {
+      uint32_t dyn_size;
+      asm("mov.u32 %0, %%dynamic_smem_size;" : "=r"(dyn_size));
+      if (pAddr - dyn0 + kPEntries * (uint32_t)sizeof(float2) > dyn_size) __trap();
+    }
+    hiP = pAddr - kPRing;
+    if (tid == 0) mbar_init(bar, 1);
+    __syncthreads();
+    if (tid == 0) {
+      constexpr uint32_t pb = kPEntries * sizeof(float2);
+      mbar_expect_tx(bar, pb);
+      bulk_g2s(smem_dyn + (pAddr - dyn0), p.output_format == 3 ? p.tab.p_hlg : p.tab.p_pq, pb, bar);
+    }
+    mbar_wait(bar, 0);
   }
-  mbar_wait(bar, 0);
 
   const Geometry& g = p.g;
   const uint32_t mw = g.map_width, mh = g.map_height;
@@ -474,7 +576,9 @@ __global__ void __launch_bounds__(kThreads, UHDR_APPLYQ_MIN_BLOCKS) apply_q_kern
     dtx = rem - dty * tiles_x;
   }
   const uint32_t ls = g.sdr_luma_stride, cs = g.sdr_chroma_stride;
-  const size_t ostride = (size_t)g.width * 4;
+  constexpr int kBpp = PACK == kPack1010102 ? 4 : (PACK == kPackF16 ? 8 : 2);  // bytes per pixel (per plane for planar)
+  const size_t ostride = (size_t)g.width * kBpp;
+  const size_t plane_bytes = (size_t)g.width * g.height * 2;
 
   for (int tile = blockIdx.x; tile < p.n_tiles; tile += gridDim.x) {
     const uint32_t cx = tx * kTileCellsX + (tid & 31);
@@ -508,7 +612,7 @@ __global__ void __launch_bounds__(kThreads, UHDR_APPLYQ_MIN_BLOCKS) apply_q_kern
     const uint8_t* up = sdr_u + coff;
     const uint8_t* vp = sdr_v + coff;
     const uint8_t* mp = map + (cy * mw + cx);
-    uint8_t* orow = outp + (size_t)(4u * cy * (uint32_t)g.width + 4u * cx) * 4;
+    uint8_t* orow = outp + (size_t)(4u * cy * (uint32_t)g.width + 4u * cx) * kBpp;
     const uint32_t dx = cx + 1 < mw ? 1u : 0u;  // xu = min(xl + 1, mw - 1), gainmapmath.cpp:690-697
     // map samples as 0..255 floats: the 1/255 of gainmapmath.cpp:700-703 is folded into the weights
     float e1 = (float)__ldg(mp), e3 = (float)__ldg(mp + dx);  // e1=(xl,yl) e3=(xu,yl)
@@ -634,8 +738,8 @@ __global__ void __launch_bounds__(kThreads, UHDR_APPLYQ_MIN_BLOCKS) apply_q_kern
 #else
         const bool toe = fminf(fmaf(ym0, KP, om0), fmaf(ym1, KP, om1)) <= kPhiToe;
 #endif
-        if (toe) q_rows<MASK, true>(hiP, uw[qr], vw[qr], oR, oG, oB, yf, f, orow + (size_t)(2 * qr) * ostride, ostride);
-        else q_rows<MASK, false>(hiP, uw[qr], vw[qr], oR, oG, oB, yf, f, orow + (size_t)(2 * qr) * ostride, ostride);
+        if (toe) q_rows<PACK, MASK, true, LTAB, NORM>(hiP, uw[qr], vw[qr], oR, oG, oB, yf, f, orow + (size_t)(2 * qr) * ostride, ostride, plane_bytes);
+        else q_rows<PACK, MASK, false, LTAB, NORM>(hiP, uw[qr], vw[qr], oR, oG, oB, yf, f, orow + (size_t)(2 * qr) * ostride, ostride, plane_bytes);
       }
       e1 = e2;
       e3 = e4;
@@ -668,7 +772,7 @@ cudaError_t launch(const ApplyFastParams& p, cudaStream_t s) {
   return cudaGetLastError();
 }
 
-template <bool MASK, bool BATCH>
+template <int PACK, bool MASK, bool BATCH, bool LTAB, bool NORM>
 cudaError_t launch_q(const ApplyFastParams& p0, cudaStream_t s) {
   static int sms_of[64], per_sm_of[64], smem_of[64];
   int dev = 0;
@@ -680,11 +784,12 @@ cudaError_t launch_q(const ApplyFastParams& p0, cudaStream_t s) {
     cudaFuncAttributes fa;
     if ((e = cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev)) != cudaSuccess) return e;
     if ((e = cudaDeviceGetAttribute(&reserved, cudaDevAttrReservedSharedMemoryPerBlock, dev)) != cudaSuccess) return e;
-    if ((e = cudaFuncGetAttributes(&fa, apply_q_kernel<MASK, BATCH>)) != cudaSuccess) return e;
+    if ((e = cudaFuncGetAttributes(&fa, apply_q_kernel<PACK, MASK, BATCH, LTAB, NORM>)) != cudaSuccess) return e;
     const uint32_t dyn0 = (uint32_t)reserved + (uint32_t)fa.sharedSizeBytes;
-    const int smem = (int)(q_table_addr(dyn0) - dyn0 + kPEntries * sizeof(float2)) + 64;  // + slack for the base alignment
-    if ((e = cudaFuncSetAttribute(apply_q_kernel<MASK, BATCH>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)) != cudaSuccess) return e;
-    if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, apply_q_kernel<MASK, BATCH>, kThreads, smem)) != cudaSuccess) return e;
+    const int smem = LTAB ? 16 + (int)(kLEntries * sizeof(float2))
+                          : (PACK == kPack1010102 ? (int)(q_table_addr(dyn0) - dyn0 + kPEntries * sizeof(float2)) + 64 : 0);  // + slack for the base alignment
+    if ((e = cudaFuncSetAttribute(apply_q_kernel<PACK, MASK, BATCH, LTAB, NORM>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)) != cudaSuccess) return e;
+    if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, apply_q_kernel<PACK, MASK, BATCH, LTAB, NORM>, kThreads, smem)) != cudaSuccess) return e;
     sms_of[dev] = n_sm;
     smem_of[dev] = smem;
     per_sm_of[dev] = n > 0 ? n : 1;
@@ -695,13 +800,18 @@ cudaError_t launch_q(const ApplyFastParams& p0, cudaStream_t s) {
   p.n_tiles = p.tiles_x * p.tiles_y * n_img;
   const int cap = sms_of[dev] * per_sm_of[dev];
   const int grid = p.n_tiles < cap ? p.n_tiles : cap;
-  apply_q_kernel<MASK, BATCH><<<grid, kThreads, (size_t)smem_of[dev], s>>>(p);
+  apply_q_kernel<PACK, MASK, BATCH, LTAB, NORM><<<grid, kThreads, (size_t)smem_of[dev], s>>>(p);
   return cudaGetLastError();
 }
 
-template <bool MASK>
+template <int PACK, bool MASK>
 cudaError_t launch_q(const ApplyFastParams& p, cudaStream_t s) {
-  return p.batch ? launch_q<MASK, true>(p, s) : launch_q<MASK, false>(p, s);
+  constexpr bool kLin = PACK != kPack1010102;
+  if (kLin && p.lin_table_ok) {  // lin_table_ok also implies normal halves (capi.cu)
+    constexpr bool kNorm = PACK == kPackF16;
+    return p.batch ? launch_q<PACK, MASK, true, kLin, kNorm>(p, s) : launch_q<PACK, MASK, false, kLin, kNorm>(p, s);
+  }
+  return p.batch ? launch_q<PACK, MASK, true, false, false>(p, s) : launch_q<PACK, MASK, false, false, false>(p, s);
 }
 
 }  // namespace
@@ -720,10 +830,10 @@ cudaError_t launch_apply_fast_impl(ApplyFastParams& p, int n, cudaStream_t s) {
   p.tiles_y = (p.g.map_height + kTileCellsY - 1) / kTileCellsY;
   p.n_tiles = p.tiles_x * p.tiles_y * n;
   switch (p.output_format) {
-    case 1: return launch<kPackF16, false>(p, s);
-    case 4: return launch<kPackPlanar10, false>(p, s);
+    case 1: return p.two_table ? launch<kPackF16, false>(p, s) : launch_q<kPackF16, false>(p, s);
+    case 4: return p.two_table ? launch<kPackPlanar10, false>(p, s) : launch_q<kPackPlanar10, false>(p, s);
     default:
-      if (!p.two_table) return p.need_mask ? launch_q<true>(p, s) : launch_q<false>(p, s);
+      if (!p.two_table) return p.need_mask ? launch_q<kPack1010102, true>(p, s) : launch_q<kPack1010102, false>(p, s);
       return p.need_mask ? launch<kPack1010102, true>(p, s) : launch<kPack1010102, false>(p, s);
   }
 }

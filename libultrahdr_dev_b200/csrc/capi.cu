@@ -155,7 +155,7 @@ int get_apply_tables(int device, ApplyTables* out) {
     *out = it->second;
     return 0;
   }
-  const size_t n2 = (size_t)kSEntries + (size_t)kSEntriesHi + 2 * (size_t)kOEntries + 2 * (size_t)kPEntries;
+  const size_t n2 = (size_t)kSEntries + (size_t)kSEntriesHi + 2 * (size_t)kOEntries + 2 * (size_t)kPEntries + (size_t)kLEntries;
   std::vector<float2> h2(n2);
   std::vector<float> e255(256);
   float2* hs = h2.data();
@@ -164,7 +164,8 @@ int get_apply_tables(int device, ApplyTables* out) {
   float2* ho_pq = ho_hlg + kOEntries;
   float2* hp_hlg = ho_pq + kOEntries;
   float2* hp_pq = hp_hlg + kPEntries;
-  build_apply_tables(hs, hs_hi, ho_hlg, ho_pq, hp_hlg, hp_pq, e255.data());
+  float2* hl_pow = hp_pq + kPEntries;
+  build_apply_tables(hs, hs_hi, ho_hlg, ho_pq, hp_hlg, hp_pq, hl_pow, e255.data());
   char* d = nullptr;
   CU(cudaMalloc((void**)&d, n2 * sizeof(float2) + 256 * sizeof(float)));
   CU(cudaMemcpy(d, h2.data(), n2 * sizeof(float2), cudaMemcpyHostToDevice));
@@ -176,6 +177,7 @@ int get_apply_tables(int device, ApplyTables* out) {
   t.o_pq = t.o_hlg + kOEntries;
   t.p_hlg = t.o_pq + kOEntries;
   t.p_pq = t.p_hlg + kPEntries;
+  t.l_pow = t.p_pq + kPEntries;
   t.e255 = (const float*)(d + n2 * sizeof(float2));
   g_tables[device] = t;
   *out = t;
@@ -445,6 +447,12 @@ int apply_core(int n, const uhdrb200_image* sdr, const uhdrb200_image* map, cons
     f.Bq = (float)(B / 2.4);
     f.q0 = (float)ldexp(1.0, kPLoExp);
     f.two_table = g_apply_mode == 2;
+    // linear outputs: every non-toe channel has Phi > 0.0904, so q >= 0.0904 * f'min must reach the L table's first
+    // octave, and q^2.4 must be a normal half with margin (the F16 kernel then skips the subnormal/flush checks)
+    {
+      const double qmin = 0.0904 * exp2((A > 0 ? B : A + B) / 2.4);
+      f.lin_table_ok = (qmin >= ldexp(1.0, kLLoExp) && pow(qmin, 2.4) >= ldexp(1.0, -14) * 1.01) ? 1 : 0;
+    }
     for (int i = 0; i < 16; i++)
       for (int c = 0; c < 4; c++) f.wq[i][c] = (float)((double)f.w[i][c] / 2.4 / 255.0);
     f.idw = p.idw;

@@ -84,7 +84,7 @@ void fill_s(float2* tab, int segs, int entries) {
 
 }  // namespace
 
-void build_apply_tables(float2* s, float2* s_hi, float2* o_hlg, float2* o_pq, float2* p_hlg, float2* p_pq, float* e255) {
+void build_apply_tables(float2* s, float2* s_hi, float2* o_hlg, float2* o_pq, float2* p_hlg, float2* p_pq, float2* l_pow, float* e255) {
   fill_s(s, kSSegs, kSEntries);
   fill_s(s_hi, kSSegsHi, kSEntriesHi);
   const double e0 = ldexp(1.0, kOLoExp);
@@ -95,6 +95,7 @@ void build_apply_tables(float2* s, float2* s_hi, float2* o_hlg, float2* o_pq, fl
   auto q24 = [q0](double x) { return x > q0 ? pow(x - q0, 2.4) : 0.0; };
   fill(p_hlg, kPLoExp, kPHiExp, kPBits, [q24](double x) { return 1023.0 * hlg_oetf_d(q24(x)); }, true);
   fill(p_pq, kPLoExp, kPHiExp, kPBits, [q24](double x) { return 1023.0 * pq_oetf_d(q24(x)); }, true);
+  fill(l_pow, kLLoExp, kLHiExp, kLBits, [](double x) { return pow(x, 2.4); });
   for (int i = 0; i < 256; i++) e255[i] = (float)i / 255.0f;  // gainmapmath.cpp:700-703
 }
 

@@ -35,6 +35,12 @@ __device__ __forceinline__ void stg8(void* p, uint2 v) {
   asm volatile("st.global.L1::no_allocate.v2.u32 [%0], {%1,%2};" ::"l"(p), "r"(v.x), "r"(v.y) : "memory");
 }
 
+// 256-bit store (sm_100+): one full 32-byte sector per lane
+__device__ __forceinline__ void stg32(void* p, uint4 a, uint4 b) {
+  asm volatile("st.global.L1::no_allocate.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "r"(a.x), "r"(a.y), "r"(a.z), "r"(a.w),
+               "r"(b.x), "r"(b.y), "r"(b.z), "r"(b.w)
+               : "memory");
+}
 __device__ __forceinline__ void stg2(void* p, uint32_t v) {
   asm volatile("st.global.L1::no_allocate.u16 [%0], %1;" ::"l"(p), "h"((uint16_t)v) : "memory");
 }

@@ -85,6 +85,11 @@ constexpr int kOBase = (kOLoExp + 127) << kOBits;
 constexpr int kPLoExp = -12, kPHiExp = 1, kPBits = UHDR_P_BITS;
 constexpr int kPEntries = (kPHiExp - kPLoExp) << kPBits;      // 3328 float2 = 26 KB
 constexpr int kPBase = (kPLoExp + 127) << kPBits;
+//   L table (q-domain kernel, linear outputs RGBA F16 / planar 10-bit): L(q) = q^2.4 = f * srgbInvOetf(c) above the
+//            toe, 10 bits per octave (relative error 2e-7, what bit-exact halves need) over q in [2^-6, 2): 56 KB.
+constexpr int kLLoExp = -6, kLHiExp = 1, kLBits = 10;
+constexpr int kLEntries = (kLHiExp - kLLoExp) << kLBits;      // 7168 float2
+constexpr int kLBase = (kLLoExp + 127) << kLBits;
 
 struct ApplyTables {       // device pointers, one set per device
   const float2* s;         // kSEntries
@@ -93,6 +98,7 @@ struct ApplyTables {       // device pointers, one set per device
   const float2* o_pq;      // kOEntries
   const float2* p_hlg;     // kPEntries
   const float2* p_pq;      // kPEntries
+  const float2* l_pow;     // kLEntries
   const float* e255;       // 256 floats: i / 255.0f, correctly rounded (gainmapmath.cpp:700-703)
 };
 
@@ -104,7 +110,8 @@ struct ApplyFastParams {
   uint32_t s_bias;         // 0x4B000000 << 3 (see uni_eval in apply_fast.cu)
   int need_mask;           // 1 when 10-bit codes can exceed 1023 (displayBoost < maxContentBoost): `& 0x3ff` wraps like the reference
   float Aq, Bq, q0;        // q-domain kernel: f' = 2^(gain255 * Aq + Bq) = f^(1/2.4), gain255 = 255 * gain; q0 = 2^kPLoExp
-  int two_table;           // 1: RGBA1010102 through the S+O table kernel instead of the q-domain kernel
+  int two_table;           // 1: the S+O table kernels (apply_fast_kernel) instead of the q-domain kernels
+  int lin_table_ok;        // 1: q = Phi * f' stays inside the L table for every non-toe channel (host check)
   float wq[16][4];         // Aq x interior IDW weights (so they include the 1/255 of the map samples)
   float w[16][4];          // A x interior IDW weights [oy * 4 + ox][k] (ShepardsIDW::mWeights, gainmapmath.h:184-228)
   const float* idw;        // all four tables (device), used by the cells on the right/bottom map border
@@ -147,7 +154,7 @@ cudaError_t launch_apply_impl(const ApplyParams& p, int n, bool vec, cudaStream_
 bool apply_fast_ok(const Geometry& g, const Planes& pl);
 cudaError_t launch_apply_fast_impl(ApplyFastParams& p, int n, cudaStream_t s);
 // host: fills the double-precision-built tables (tables.cu)
-void build_apply_tables(float2* s, float2* s_hi, float2* o_hlg, float2* o_pq, float2* p_hlg, float2* p_pq, float* e255);
+void build_apply_tables(float2* s, float2* s_hi, float2* o_hlg, float2* o_pq, float2* p_hlg, float2* p_pq, float2* l_pow, float* e255);
 cudaError_t launch_tonemap_impl(const ToneMapParams& p, int n, bool vec, cudaStream_t s);
 bool sdr_pack_vec_ok(const Geometry& g, const Planes& pl);
 cudaError_t launch_sdr_pack_impl(const SdrPackParams& p, int n, bool vec, cudaStream_t s);
