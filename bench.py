@@ -254,9 +254,15 @@ def main():
         v, cpu_info = cpu_arm(a.cpu_images)
         cpu_info.update(value=v, unit=UNIT)
 
-    # ---- synthetic inputs: K distinct natural pairs, replicated into B device slots
+    # ---- synthetic inputs. The job is world*B images; image i belongs to rank i mod world (shard.py).
+    # A rank materialises K distinct seeded pairs (seed = the global image index of its first K images) and
+    # replicates them into its B device slots.
+    from libultrahdr_dev_b200 import shard
+
     B, K = a.batch, 4
-    pairs = [synth.natural_pair(W, H, rank * K + i, abi.TF_HLG, abi.COLORGAMUT_BT709, abi.COLORGAMUT_BT2100) for i in range(K)]
+    mine = shard.shard_round_robin(world * B, rank, world)
+    assert len(mine.indices) == B
+    pairs = [synth.natural_pair(W, H, mine.indices[i], abi.TF_HLG, abi.COLORGAMUT_BT709, abi.COLORGAMUT_BT2100) for i in range(K)]
     sdr_len, hdr_len = abi.yuv420_size(W, H), abi.p010_size(W, H)
     d_sdr = torch.empty((B, sdr_len), dtype=torch.uint8, device=dev)
     d_hdr = torch.empty((B, hdr_len), dtype=torch.int16, device=dev)
@@ -472,7 +478,7 @@ def main():
     out = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3),
         "ms_per_step": total_ms / a.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "f32", "data": f"synthetic ({K} distinct seeded natural pairs per rank replicated into {B} device slots)",
+        "dtype": "f32", "data": f"synthetic ({K} distinct seeded natural pairs per rank replicated into {B} device slots; image i of the {world * B}-image job on rank i mod {world})",
         "config": config,
         "roofline": {"bound": "hbm", "kernel": "apply_q_kernel (applyGainMap -> RGBA1010102 HLG)", "achieved": app_gbs,
                      "peak": peak, "unit": "GB/s", "frac": app_gbs / peak, "traffic": traffic_of("apply_q_kernel"), "peak_source": peak_src,
