@@ -88,19 +88,10 @@ constexpr uint32_t kPRingBytes = 128u << kPBits;
 constexpr uint32_t kPRing = 8u * (kPBase & ((16 << kPBits) - 1));  // offset of the first entry inside its ring
 static_assert(kPRing + kPEntries * 8 <= kPRingBytes, "P table must not wrap inside its ring");
 __device__ __forceinline__ float p_eval(uint32_t hi, float x) {
-#ifdef UHDR_P_IMAD  // shift on the FMA pipe (IMAD.HI) instead of the ALU pipe (SHF)
-  const uint32_t sh = __umulhi(__float_as_uint(x), 1u << (12 + kPBits));
-#else
   const uint32_t sh = __float_as_uint(x) >> (20 - kPBits);
-#endif
   const uint32_t addr = (sh & (kPRingBytes - 8u)) | hi;
   float a, b;
-#ifdef UHDR_DBG_NOLDS
-  a = __uint_as_float(addr);
-  b = 1.0f;
-#else
   asm("ld.shared.v2.f32 {%0,%1}, [%2];" : "=f"(a), "=f"(b) : "r"(addr));
-#endif
   return fmaf(b, x, a);
 }
 
@@ -115,6 +106,30 @@ __device__ __forceinline__ float add_rm(float a, float b) {
   float r;
   asm("add.rm.f32 %0, %1, %2;" : "=f"(r) : "f"(a), "f"(b));
   return r;
+}
+
+// ---- packed fp32x2 arithmetic (sm_100a FFMA2 / FADD2): one issue slot for two lanes of work ----
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 pk2(float lo, float hi) {
+  f32x2 r;
+  asm("mov.b64 %0, {%1,%2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ void unpk2(f32x2 v, float& lo, float& hi) { asm("mov.b64 {%0,%1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
+__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) {
+  f32x2 d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+  return d;
+}
+__device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b) {
+  f32x2 d;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+__device__ __forceinline__ f32x2 add_rm2(f32x2 a, f32x2 b) {  // both lanes rounded towards -inf
+  f32x2 d;
+  asm("add.rm.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
 }
 
 __device__ __forceinline__ float ex2_fast(float x) {
@@ -368,6 +383,111 @@ __device__ __forceinline__ float l_eval(uint32_t tL, float q) {
   return fmaf(b, q, a);
 }
 
+#ifndef UHDR_APPLYQ_F32X2
+#define UHDR_APPLYQ_F32X2 1  // 0: scalar FFMA / FADD everywhere (the pre-FFMA2 kernel)
+#endif
+
+#if UHDR_APPLYQ_F32X2
+// q_rows for RGBA1010102 above the toe, without the `& 0x3ff` wrap, on packed fp32x2 arithmetic
+__device__ __forceinline__ void q_rows_paired(const uint32_t hiP, const float (&oR)[2], const float (&oG)[2], const float (&oB)[2],
+                                              const float (&yf)[2][4], const float* __restrict__ f8, uint8_t* orow, const size_t ostride) {
+  constexpr float KP = (float)(1.0 / (255.0 * 1.055));
+  constexpr float q0 = 1.0f / (float)(1 << -kPLoExp);
+  // the two pixels of a quad's row as one f32x2 lane pair: q, the three floors and the field move take one
+  // FFMA2 / FADD2 per pair instead of one FFMA / FADD per pixel (same arithmetic, half the issue slots)
+  const f32x2 q0q0 = pk2(q0, q0), two23 = pk2(8388608.0f, 8388608.0f), k1024 = pk2(1024.0f, 1024.0f);
+  const f32x2 gOff = pk2(8388608.0f - 8589934592.0f, 8388608.0f - 8589934592.0f);
+  const f32x2 bOff = pk2(8388608.0f + 1872.0f, 8388608.0f + 1872.0f);
+#pragma unroll
+  for (int rr = 0; rr < 2; rr++) {
+    uint32_t w[4];
+#pragma unroll
+    for (int c = 0; c < 2; c++) {
+      const float y0 = yf[rr][2 * c], y1 = yf[rr][2 * c + 1];
+      const f32x2 ff = pk2(f8[rr * 4 + 2 * c], f8[rr * 4 + 2 * c + 1]);
+      const f32x2 qR = fma2(pk2(__saturatef(fmaf(y0, KP, oR[c])), __saturatef(fmaf(y1, KP, oR[c]))), ff, q0q0);
+      const f32x2 qG = fma2(pk2(__saturatef(fmaf(y0, KP, oG[c])), __saturatef(fmaf(y1, KP, oG[c]))), ff, q0q0);
+      const f32x2 qB = fma2(pk2(__saturatef(fmaf(y0, KP, oB[c])), __saturatef(fmaf(y1, KP, oB[c]))), ff, q0q0);
+      float a0, a1;
+      unpk2(qR, a0, a1);
+      const f32x2 vR = pk2(p_eval(hiP, a0), p_eval(hiP, a1));
+      unpk2(qG, a0, a1);
+      const f32x2 vG = pk2(p_eval(hiP, a0), p_eval(hiP, a1));
+      unpk2(qB, a0, a1);
+      const f32x2 vB = pk2(p_eval(hiP, a0), p_eval(hiP, a1));
+      // floor + pack as in the scalar path below, two pixels per operation
+      const f32x2 t = add_rm2(vR, fma2(add_rm2(vG, two23), k1024, gOff));
+      const f32x2 Bm = add_rm2(vB, bOff);
+      float t0, t1, b0, b1;
+      unpk2(t, t0, t1);
+      unpk2(Bm, b0, b1);
+      w[2 * c] = (__float_as_uint(b0) << 20) + __float_as_uint(t0);
+      w[2 * c + 1] = (__float_as_uint(b1) << 20) + __float_as_uint(t1);
+    }
+    stg16(orow + (size_t)rr * ostride, make_uint4(w[0], w[1], w[2], w[3]));
+  }
+}
+
+// q_rows for the linear outputs above the toe (L table): q = Phi * f' and the 10-bit scale + floor on packed fp32x2
+template <int PACK, bool NORM>
+__device__ __forceinline__ void q_rows_paired_lin(const uint32_t tL, const float (&oR)[2], const float (&oG)[2], const float (&oB)[2],
+                                                  const float (&yf)[2][4], const float* __restrict__ f8, uint8_t* orow, const size_t ostride,
+                                                  const size_t plane_bytes) {
+  static_assert(PACK != kPackF16 || NORM, "the F16 L-table kernel relies on the host's normal-half guarantee");
+  constexpr float KP = (float)(1.0 / (255.0 * 1.055));
+#pragma unroll
+  for (int rr = 0; rr < 2; rr++) {
+    uint32_t w[4][PACK == kPackF16 ? 2 : 3];
+#pragma unroll
+    for (int c = 0; c < 2; c++) {
+      const float y0 = yf[rr][2 * c], y1 = yf[rr][2 * c + 1];
+      const f32x2 ff = pk2(f8[rr * 4 + 2 * c], f8[rr * 4 + 2 * c + 1]);
+      float e[3][2];
+      {
+        float a0, a1;
+        unpk2(mul2(pk2(__saturatef(fmaf(y0, KP, oR[c])), __saturatef(fmaf(y1, KP, oR[c]))), ff), a0, a1);
+        e[0][0] = l_eval(tL, a0);
+        e[0][1] = l_eval(tL, a1);
+        unpk2(mul2(pk2(__saturatef(fmaf(y0, KP, oG[c])), __saturatef(fmaf(y1, KP, oG[c]))), ff), a0, a1);
+        e[1][0] = l_eval(tL, a0);
+        e[1][1] = l_eval(tL, a1);
+        unpk2(mul2(pk2(__saturatef(fmaf(y0, KP, oB[c])), __saturatef(fmaf(y1, KP, oB[c]))), ff), a0, a1);
+        e[2][0] = l_eval(tL, a0);
+        e[2][1] = l_eval(tL, a1);
+      }
+      if (PACK == kPackF16) {
+#pragma unroll
+        for (int h = 0; h < 2; h++) {
+          const uint32_t bR = __float_as_uint(e[0][h]) + 0x1000u, bG = __float_as_uint(e[1][h]) + 0x1000u, bB = __float_as_uint(e[2][h]) + 0x1000u;
+          // floatToHalf (gainmapmath.h:136-147) on the normal-half range; the host only selects the L table when
+          // every value of a toe-free quad-row is a normal half (lin_table_ok)
+          w[2 * c + h][0] = pack_half2_rz(__uint_as_float(bR), __uint_as_float(bG));
+          w[2 * c + h][1] = pack_half2_rz(__uint_as_float(bB), 1.0f);
+        }
+      } else {
+        // 0x3ff & uint(v * 1023) (ultrahdr.cpp:460-468): v >= 0, so truncation = floor = FADD.RM
+        const f32x2 k1023 = pk2(1023.0f, 1023.0f), two23 = pk2(8388608.0f, 8388608.0f);
+#pragma unroll
+        for (int ch = 0; ch < 3; ch++) {
+          float m0, m1;
+          unpk2(add_rm2(mul2(pk2(e[ch][0], e[ch][1]), k1023), two23), m0, m1);
+          w[2 * c][ch] = __float_as_uint(m0) & 0x3ffu;
+          w[2 * c + 1][ch] = __float_as_uint(m1) & 0x3ffu;
+        }
+      }
+    }
+    uint8_t* o = orow + (size_t)rr * ostride;
+    if (PACK == kPackF16) {  // colorToRgbaF16, gainmapmath.cpp:729-732
+      stg32(o, make_uint4(w[0][0], w[0][1], w[1][0], w[1][1]), make_uint4(w[2][0], w[2][1], w[3][0], w[3][1]));
+    } else {  // three planar u16 planes, ultrahdr.cpp:460-468
+#pragma unroll
+      for (int ch = 0; ch < 3; ch++)
+        stg8(o + ch * plane_bytes, make_uint2(w[0][ch] | (w[1][ch] << 16), w[2][ch] | (w[3][ch] << 16)));
+    }
+  }
+}
+#endif
+
 // two pixel rows (one row of 2x2 chroma quads) of a cell: Phi -> q -> P(q) -> floor -> pack -> 128-bit store per row
 // (RGBA1010102), or Phi -> q -> q^2.4 -> half / 10-bit pack (linear outputs)
 template <int PACK, bool MASK, bool kToe, bool LTAB, bool NORM>
@@ -481,9 +601,6 @@ __device__ __forceinline__ void q_rows(const uint32_t hiP, const uint32_t uq, co
           }
           uint8_t* o = orow + (size_t)rr * ostride;
           if (PACK == kPack1010102) {
-#ifdef UHDR_DBG_NOSTORE
-            if ((w[0][0] ^ w[1][0] ^ w[2][0] ^ w[3][0]) == 0x12345679u)
-#endif
             stg16(o, make_uint4(w[0][0], w[1][0], w[2][0], w[3][0]));
           } else if (PACK == kPackF16) {  // colorToRgbaF16, gainmapmath.cpp:729-732
             stg32(o, make_uint4(w[0][0], w[0][1], w[1][0], w[1][1]), make_uint4(w[2][0], w[2][1], w[3][0], w[3][1]));
@@ -618,53 +735,6 @@ __global__ void __launch_bounds__(kThreads, LTAB ? 3 : UHDR_APPLYQ_MIN_BLOCKS) a
     float e1 = (float)__ldg(mp), e3 = (float)__ldg(mp + dx);  // e1=(xl,yl) e3=(xu,yl)
     const uint32_t kmax = min((uint32_t)kQCells, mh - cy);
 
-#ifndef UHDR_APPLYQ_PREFETCH
-#define UHDR_APPLYQ_PREFETCH 0
-#endif
-#if UHDR_APPLYQ_PREFETCH
-    // software pipeline: the loads of cell k+1 are in flight while cell k is computed
-    uint32_t nyw[4], nuw[2], nvw[2], nb2, nb4;
-    const uint8_t* mp2 = (cy + 1 >= mh) ? mp : mp + mw;  // yu = min(yl + 1, mh - 1)
-#pragma unroll
-    for (int r = 0; r < 4; r++) nyw[r] = ldg4(yp + r * ls);
-#pragma unroll
-    for (int r = 0; r < 2; r++) {
-      nuw[r] = ldg2(up + r * cs);
-      nvw[r] = ldg2(vp + r * cs);
-    }
-    nb2 = __ldg(mp2);
-    nb4 = __ldg(mp2 + dx);
-
-#pragma unroll 1
-    for (uint32_t k = 0; k < kmax; k++, cy++) {
-      uint32_t yw[4], uw[2], vw[2];
-#pragma unroll
-      for (int r = 0; r < 4; r++) yw[r] = nyw[r];
-#pragma unroll
-      for (int r = 0; r < 2; r++) {
-        uw[r] = nuw[r];
-        vw[r] = nvw[r];
-      }
-      const float e2 = (float)nb2, e4 = (float)nb4;  // e2=(xl,yu) e4=(xu,yu)
-      const bool last = cy + 1 >= mh;
-      yp += 4u * ls;
-      up += 2u * cs;
-      vp += 2u * cs;
-      mp = mp2;
-      if (k + 1 < kmax) {
-        mp2 = (cy + 2 >= mh) ? mp : mp + mw;
-#pragma unroll
-        for (int r = 0; r < 4; r++) nyw[r] = ldg4(yp + r * ls);
-#pragma unroll
-        for (int r = 0; r < 2; r++) {
-          nuw[r] = ldg2(up + r * cs);
-          nvw[r] = ldg2(vp + r * cs);
-        }
-        nb2 = __ldg(mp2);
-        nb4 = __ldg(mp2 + dx);
-      }
-
-#else
 #pragma unroll 1
     for (uint32_t k = 0; k < kmax; k++, cy++) {
       uint32_t yw[4], uw[2], vw[2];
@@ -683,27 +753,37 @@ __global__ void __launch_bounds__(kThreads, LTAB ? 3 : UHDR_APPLYQ_MIN_BLOCKS) a
       vp += 2u * cs;
       mp = mp2;
 
-#endif
       const float d2 = e2 - e1, d3 = e3 - e1, d4 = e4 - e1, exb = fmaf(e1, p.Aq, p.Bq);
-#ifdef UHDR_DBG_NOBORDER
-      const bool interior = true;
-#else
       const bool interior = dx && !last;
-#endif
 
 #pragma unroll
       for (int qr = 0; qr < 2; qr++) {
         // ---- f' = f^(1/2.4) of the 8 pixels of this quad-row
         float f[8];
         if (interior) {
+          // the four weights sum to 1: sum_k e_k w_k = e1 + sum_{k>1} (e_k - e1) w_k, three FFMAs per pixel
+#if UHDR_APPLYQ_F32X2
+          const f32x2 D2 = pk2(d2, d2), D3 = pk2(d3, d3), D4 = pk2(d4, d4), EXB = pk2(exb, exb);
+#pragma unroll
+          for (int j = 0; j < 4; j++) {  // ... issued as FFMA2 on horizontally adjacent pixel pairs
+            const int i = qr * 8 + 2 * j;
+            f32x2 ex = fma2(D2, *reinterpret_cast<const f32x2*>(&p.wq[0][i]), EXB);
+            ex = fma2(D3, *reinterpret_cast<const f32x2*>(&p.wq[1][i]), ex);
+            ex = fma2(D4, *reinterpret_cast<const f32x2*>(&p.wq[2][i]), ex);
+            float a, b;
+            unpk2(ex, a, b);
+            f[2 * j] = ex2_fast(a);
+            f[2 * j + 1] = ex2_fast(b);
+          }
+#else
 #pragma unroll
           for (int i = 0; i < 8; i++) {
-            // the four weights sum to 1: sum_k e_k w_k = e1 + sum_{k>1} (e_k - e1) w_k, three FFMAs per pixel
-            float ex = fmaf(d2, p.wq[qr * 8 + i][1], exb);
-            ex = fmaf(d3, p.wq[qr * 8 + i][2], ex);
-            ex = fmaf(d4, p.wq[qr * 8 + i][3], ex);
+            float ex = fmaf(d2, p.wq[0][qr * 8 + i], exb);
+            ex = fmaf(d3, p.wq[1][qr * 8 + i], ex);
+            ex = fmaf(d4, p.wq[2][qr * 8 + i], ex);
             f[i] = ex2_fast(ex);
           }
+#endif
         } else {  // map border: tables NR (1), NB (2), C (3), gainmapmath.cpp:710-716
           const int t = dx ? 2 : (last ? 3 : 1);
           const float4* wt = reinterpret_cast<const float4*>(p.idw) + t * 16 + qr * 8;
@@ -719,6 +799,15 @@ __global__ void __launch_bounds__(kThreads, LTAB ? 3 : UHDR_APPLYQ_MIN_BLOCKS) a
         }
         // Phi-domain chroma offsets of the two 2x2 quads of this quad-row
         float oR[2], oG[2], oB[2], yf[2][4];
+#if UHDR_APPLYQ_F32X2
+        {  // both quads per FFMA2
+          const f32x2 UB = pk2((float)(uw[qr] & 0xff), (float)((uw[qr] >> 8) & 0xff));
+          const f32x2 VB = pk2((float)(vw[qr] & 0xff), (float)((vw[qr] >> 8) & 0xff));
+          unpk2(fma2(VB, pk2(kR, kR), pk2(oR0, oR0)), oR[0], oR[1]);
+          unpk2(fma2(UB, pk2(kB, kB), pk2(oB0, oB0)), oB[0], oB[1]);
+          unpk2(fma2(VB, pk2(kGv, kGv), fma2(UB, pk2(kGu, kGu), pk2(oG0, oG0))), oG[0], oG[1]);
+        }
+#else
 #pragma unroll
         for (int c = 0; c < 2; c++) {
           const float ub = (float)((uw[qr] >> (8 * c)) & 0xff), vb = (float)((vw[qr] >> (8 * c)) & 0xff);
@@ -726,6 +815,7 @@ __global__ void __launch_bounds__(kThreads, LTAB ? 3 : UHDR_APPLYQ_MIN_BLOCKS) a
           oB[c] = fmaf(ub, kB, oB0);
           oG[c] = fmaf(vb, kGv, fmaf(ub, kGu, oG0));
         }
+#endif
 #pragma unroll
         for (int rr = 0; rr < 2; rr++)
 #pragma unroll
@@ -733,12 +823,18 @@ __global__ void __launch_bounds__(kThreads, LTAB ? 3 : UHDR_APPLYQ_MIN_BLOCKS) a
         const float ym0 = fminf(fminf(yf[0][0], yf[0][1]), fminf(yf[1][0], yf[1][1]));
         const float ym1 = fminf(fminf(yf[0][2], yf[0][3]), fminf(yf[1][2], yf[1][3]));
         const float om0 = fminf(oR[0], fminf(oG[0], oB[0])), om1 = fminf(oR[1], fminf(oG[1], oB[1]));
-#ifdef UHDR_DBG_NOTOE
-        const bool toe = false;
+#if UHDR_APPLYQ_F32X2
+        float ph0, ph1;
+        unpk2(fma2(pk2(ym0, ym1), pk2(KP, KP), pk2(om0, om1)), ph0, ph1);
+        const bool toe = fminf(ph0, ph1) <= kPhiToe;
 #else
         const bool toe = fminf(fmaf(ym0, KP, om0), fmaf(ym1, KP, om1)) <= kPhiToe;
 #endif
         if (toe) q_rows<PACK, MASK, true, LTAB, NORM>(hiP, uw[qr], vw[qr], oR, oG, oB, yf, f, orow + (size_t)(2 * qr) * ostride, ostride, plane_bytes);
+#if UHDR_APPLYQ_F32X2
+        else if constexpr (PACK == kPack1010102 && !MASK) q_rows_paired(hiP, oR, oG, oB, yf, f, orow + (size_t)(2 * qr) * ostride, ostride);
+        else if constexpr (LTAB) q_rows_paired_lin<PACK, NORM>(hiP, oR, oG, oB, yf, f, orow + (size_t)(2 * qr) * ostride, ostride, plane_bytes);
+#endif
         else q_rows<PACK, MASK, false, LTAB, NORM>(hiP, uw[qr], vw[qr], oR, oG, oB, yf, f, orow + (size_t)(2 * qr) * ostride, ostride, plane_bytes);
       }
       e1 = e2;

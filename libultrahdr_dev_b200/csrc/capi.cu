@@ -454,7 +454,7 @@ int apply_core(int n, const uhdrb200_image* sdr, const uhdrb200_image* map, cons
       f.lin_table_ok = (qmin >= ldexp(1.0, kLLoExp) && pow(qmin, 2.4) >= ldexp(1.0, -14) * 1.01) ? 1 : 0;
     }
     for (int i = 0; i < 16; i++)
-      for (int c = 0; c < 4; c++) f.wq[i][c] = (float)((double)f.w[i][c] / 2.4 / 255.0);
+      for (int c = 1; c < 4; c++) f.wq[c - 1][i] = (float)((double)f.w[i][c] / 2.4 / 255.0);
     f.idw = p.idw;
     if ((st = get_apply_tables(t_ctx.device, &f.tab))) return st;
     f.single = v[0];

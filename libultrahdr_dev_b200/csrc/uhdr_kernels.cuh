@@ -112,7 +112,9 @@ struct ApplyFastParams {
   float Aq, Bq, q0;        // q-domain kernel: f' = 2^(gain255 * Aq + Bq) = f^(1/2.4), gain255 = 255 * gain; q0 = 2^kPLoExp
   int two_table;           // 1: the S+O table kernels (apply_fast_kernel) instead of the q-domain kernels
   int lin_table_ok;        // 1: q = Phi * f' stays inside the L table for every non-toe channel (host check)
-  float wq[16][4];         // Aq x interior IDW weights (so they include the 1/255 of the map samples)
+  // Aq x interior IDW weights of corners 2..4 (they include the 1/255 of the map samples), [corner - 2][oy * 4 + ox]:
+  // horizontally adjacent pixels are one 8-byte pair for FFMA2
+  alignas(8) float wq[3][16];
   float w[16][4];          // A x interior IDW weights [oy * 4 + ox][k] (ShepardsIDW::mWeights, gainmapmath.h:184-228)
   const float* idw;        // all four tables (device), used by the cells on the right/bottom map border
   ApplyTables tab;
