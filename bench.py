@@ -191,6 +191,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-other-stages", action="store_true", help="skip the per-kernel rooflines of the other stages")
     ap.add_argument("--cpu-images", type=int, default=24, help="images per CPU worker process in the CPU arms")
+    ap.add_argument("--profile-once", action="store_true", help="one launch per other-stage kernel, no warm-up (for ncu captures; timings meaningless)")
     ap.add_argument("--cpu-worker", nargs=3, metavar=("N", "SEED", "TAG"))
     a = ap.parse_args()
     if a.cpu_worker:
@@ -344,7 +345,9 @@ def main():
         md_pq = abi.default_metadata(10000.0 / 203.0)
 
         def timed(fn, bpp, iters=5):
-            for _ in range(2):
+            if a.profile_once:
+                iters = 1
+            for _ in range(0 if a.profile_once else 2):
                 assert fn() == 0
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record()

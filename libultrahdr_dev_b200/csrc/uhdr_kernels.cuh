@@ -80,15 +80,18 @@ constexpr int kOBase = (kOLoExp + 127) << kOBits;
 //            OETF(f * srgbInvOetf(c)) is a function of q = Phi * f' alone:
 //            P(q + 2^kPLoExp) = 1023 * OETF(q^2.4), log-spaced segments like the O table.
 #ifndef UHDR_P_BITS
-#define UHDR_P_BITS 8
+#define UHDR_P_BITS 7  // 7 bits per octave: 99.93 % of the 10-bit codes exact (8 bits: 99.98 %), 5 % faster (fewer bank conflicts)
 #endif
 constexpr int kPLoExp = -12, kPHiExp = 1, kPBits = UHDR_P_BITS;
-constexpr int kPEntries = (kPHiExp - kPLoExp) << kPBits;      // 3328 float2 = 26 KB
+constexpr int kPEntries = (kPHiExp - kPLoExp) << kPBits;      // 1664 float2 = 13 KB
 constexpr int kPBase = (kPLoExp + 127) << kPBits;
 //   L table (q-domain kernel, linear outputs RGBA F16 / planar 10-bit): L(q) = q^2.4 = f * srgbInvOetf(c) above the
-//            toe, 10 bits per octave (relative error 2e-7, what bit-exact halves need) over q in [2^-6, 2): 56 KB.
-constexpr int kLLoExp = -6, kLHiExp = 1, kLBits = 10;
-constexpr int kLEntries = (kLHiExp - kLLoExp) << kLBits;      // 7168 float2
+//            toe, 9 bits per octave (relative error 8e-7) over q in [2^-6, 2).
+#ifndef UHDR_L_BITS
+#define UHDR_L_BITS 9  // 99.96 % of the halves bit-exact, same as 10 bits; 28 KB instead of 56 KB and 14 % faster. 8 bits: 99.89 %, +26 %
+#endif
+constexpr int kLLoExp = -6, kLHiExp = 1, kLBits = UHDR_L_BITS;
+constexpr int kLEntries = (kLHiExp - kLLoExp) << kLBits;      // 3584 float2 = 28 KB
 constexpr int kLBase = (kLLoExp + 127) << kLBits;
 
 struct ApplyTables {       // device pointers, one set per device
