@@ -191,6 +191,8 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-other-stages", action="store_true", help="skip the per-kernel rooflines of the other stages")
     ap.add_argument("--cpu-images", type=int, default=24, help="images per CPU worker process in the CPU arms")
+    ap.add_argument("--lib", default=None, help="experiments: path of a variant libuhdr_b200.so")
+    ap.add_argument("--no-e2e", action="store_true", help="experiments: skip the end-to-end leg (the line then has no valid e2e)")
     ap.add_argument("--profile-once", action="store_true", help="one launch per other-stage kernel, no warm-up (for ncu captures; timings meaningless)")
     ap.add_argument("--cpu-worker", nargs=3, metavar=("N", "SEED", "TAG"))
     a = ap.parse_args()
@@ -236,7 +238,7 @@ def main():
 
     from libultrahdr_dev_b200 import abi, api, synth
 
-    lib = api.load_library()  # raises when the CUDA library is missing: no CPU fallback
+    lib = api.load_library(a.lib)  # raises when the CUDA library is missing: no CPU fallback
     if not torch.cuda.is_available() or lib.uhdrb200_device_count() < 1:
         raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback")
     torch.cuda.set_device(local)
@@ -432,8 +434,9 @@ def main():
     def e2e_step():
         list(pool.map(e2e_one, range(E)))
 
-    e2e_steps = max(2, min(a.steps, 5))
-    e2e_step()
+    e2e_steps = 0 if a.no_e2e else max(2, min(a.steps, 5))
+    if not a.no_e2e:
+        e2e_step()
     barrier()
     te0 = time.perf_counter()
     for _ in range(e2e_steps):
@@ -490,7 +493,7 @@ def main():
                               "unit": "GB/s", "frac": gen_gbs / peak, "traffic": traffic_of("generate_kernel"), "ms_per_launch": gen_ms,
                               "algorithmic_bytes_per_launch": B * PIX * GEN_BPP},
         "stage_mpix_s": {"generate": B * PIX / gen_ms / 1e3, "apply": B * PIX / app_ms / 1e3},
-        "e2e": {"value": world * E * PIX * e2e_steps / (e2e_ms * 1e-3) / 1e6, "unit": UNIT, "h2d_bytes_per_step": h2d,
+        "e2e": {"value": world * E * PIX * e2e_steps / (e2e_ms * 1e-3) / 1e6 if e2e_steps else None, "unit": UNIT, "h2d_bytes_per_step": h2d,
                 "d2h_bytes_per_step": d2h, "images_per_step_per_gpu": E, "steps": e2e_steps,
                 "host_threads": T,
                 "api": "uhdrb200_generate_gainmap_host_into + uhdrb200_apply_gainmap_host (synchronous, reference-style), pinned host planes"},

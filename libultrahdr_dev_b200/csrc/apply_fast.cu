@@ -387,6 +387,11 @@ __device__ __forceinline__ float l_eval(uint32_t tL, float q) {
 #define UHDR_APPLYQ_F32X2 1  // 0: scalar FFMA / FADD everywhere (the pre-FFMA2 kernel)
 #endif
 
+#ifndef UHDR_L_MUFU_CHANNELS
+#define UHDR_L_MUFU_CHANNELS 1  // channels of the linear-output kernels evaluated as ex2(2.4 * lg2(q)) instead of the L table
+#endif
+constexpr int kLMufu = UHDR_L_MUFU_CHANNELS;
+
 #if UHDR_APPLYQ_F32X2
 // q_rows for RGBA1010102 above the toe, without the `& 0x3ff` wrap, on packed fp32x2 arithmetic
 __device__ __forceinline__ void q_rows_paired(const uint32_t hiP, const float (&oR)[2], const float (&oG)[2], const float (&oB)[2],
@@ -444,16 +449,18 @@ __device__ __forceinline__ void q_rows_paired_lin(const uint32_t tL, const float
       const f32x2 ff = pk2(f8[rr * 4 + 2 * c], f8[rr * 4 + 2 * c + 1]);
       float e[3][2];
       {
+        // q^2.4: table look-up (LSU) for the first channels, two MUFU for the last kLMufu ones, so that the shared-memory
+        // data pipe and the XU pipe share the work
         float a0, a1;
         unpk2(mul2(pk2(__saturatef(fmaf(y0, KP, oR[c])), __saturatef(fmaf(y1, KP, oR[c]))), ff), a0, a1);
-        e[0][0] = l_eval(tL, a0);
-        e[0][1] = l_eval(tL, a1);
+        e[0][0] = kLMufu >= 3 ? pow24(a0) : l_eval(tL, a0);
+        e[0][1] = kLMufu >= 3 ? pow24(a1) : l_eval(tL, a1);
         unpk2(mul2(pk2(__saturatef(fmaf(y0, KP, oG[c])), __saturatef(fmaf(y1, KP, oG[c]))), ff), a0, a1);
-        e[1][0] = l_eval(tL, a0);
-        e[1][1] = l_eval(tL, a1);
+        e[1][0] = kLMufu >= 2 ? pow24(a0) : l_eval(tL, a0);
+        e[1][1] = kLMufu >= 2 ? pow24(a1) : l_eval(tL, a1);
         unpk2(mul2(pk2(__saturatef(fmaf(y0, KP, oB[c])), __saturatef(fmaf(y1, KP, oB[c]))), ff), a0, a1);
-        e[2][0] = l_eval(tL, a0);
-        e[2][1] = l_eval(tL, a1);
+        e[2][0] = kLMufu >= 1 ? pow24(a0) : l_eval(tL, a0);
+        e[2][1] = kLMufu >= 1 ? pow24(a1) : l_eval(tL, a1);
       }
       if (PACK == kPackF16) {
 #pragma unroll
@@ -613,24 +620,24 @@ __device__ __forceinline__ void q_rows(const uint32_t hiP, const uint32_t uq, co
 }
 
 #ifndef UHDR_APPLYQ_MIN_BLOCKS
-#define UHDR_APPLYQ_MIN_BLOCKS 4
+#define UHDR_APPLYQ_MIN_BLOCKS 3  // 80 registers: room for the software prefetch without spills
 #endif
 
 #ifndef UHDR_APPLYQ_L_MIN_BLOCKS
 #define UHDR_APPLYQ_L_MIN_BLOCKS 3  // L-table kernels: 3 resident blocks measured faster than 4 (523 vs 509 Gpix/s planar)
 #endif
 
-#ifndef UHDR_APPLYQ_CELLS
-#define UHDR_APPLYQ_CELLS 4  // vertically adjacent map cells one thread walks per tile
+#ifndef UHDR_APPLYQ_PREFETCH
+#define UHDR_APPLYQ_PREFETCH 1  // loads of cell k + 1 issued before cell k is evaluated (needs the 80-register budget)
 #endif
-constexpr int kQCells = UHDR_APPLYQ_CELLS;
-constexpr int kQTileRows = 8 * kQCells;  // cell rows per tile: 8 warps x kQCells
 
-// Tile = 32 x kQTileRows map cells (128 x 128 pixels for kQCells = 4). A lane owns one column of
-// cells; a warp walks kQCells cell rows downwards, so the lower pair of map samples of one cell is
+// Tile = 32 x 8 * CELLS map cells (128 x 128 pixels for CELLS = 4). A lane owns one column of
+// cells; a warp walks CELLS cell rows downwards, so the lower pair of map samples of one cell is
 // the upper pair of the next (2 map loads per cell) and every plane pointer advances by a constant.
-template <int PACK, bool MASK, bool BATCH, bool LTAB, bool NORM>
+// CELLS = 8 for large batches (fewer tile prologues: 740 vs 728 Gpix/s), 4 otherwise (more tiles to balance).
+template <int PACK, bool MASK, bool BATCH, bool LTAB, bool NORM, int CELLS>
 __global__ void __launch_bounds__(kThreads, LTAB ? UHDR_APPLYQ_L_MIN_BLOCKS : UHDR_APPLYQ_MIN_BLOCKS) apply_q_kernel(const __grid_constant__ ApplyFastParams p) {
+  constexpr int kQCells = CELLS, kQTileRows = 8 * CELLS;  // cell rows per tile: 8 warps x CELLS
   const int tid = threadIdx.x;
   uint32_t hiP = 0;
   if (LTAB) {
@@ -739,9 +746,44 @@ __global__ void __launch_bounds__(kThreads, LTAB ? UHDR_APPLYQ_L_MIN_BLOCKS : UH
     float e1 = (float)__ldg(mp), e3 = (float)__ldg(mp + dx);  // e1=(xl,yl) e3=(xu,yl)
     const uint32_t kmax = min((uint32_t)kQCells, mh - cy);
 
+#if UHDR_APPLYQ_PREFETCH
+    // software pipeline: the 10 loads of cell k + 1 are in flight while cell k is evaluated
+    uint32_t nyw[4], nuw[2], nvw[2], ne2, ne4;
+    bool nlast;
+    auto fetch = [&](uint32_t cyy) {
+#pragma unroll
+      for (int r = 0; r < 4; r++) nyw[r] = ldg4(yp + r * ls);
+#pragma unroll
+      for (int r = 0; r < 2; r++) {
+        nuw[r] = ldg2(up + r * cs);
+        nvw[r] = ldg2(vp + r * cs);
+      }
+      nlast = cyy + 1 >= mh;  // yu = min(yl + 1, mh - 1)
+      const uint8_t* mp2 = nlast ? mp : mp + mw;
+      ne2 = __ldg(mp2);
+      ne4 = __ldg(mp2 + dx);
+      yp += 4u * ls;
+      up += 2u * cs;
+      vp += 2u * cs;
+      mp = mp2;
+    };
+    fetch(cy);
+#endif
 #pragma unroll 1
     for (uint32_t k = 0; k < kmax; k++, cy++) {
       uint32_t yw[4], uw[2], vw[2];
+#if UHDR_APPLYQ_PREFETCH
+#pragma unroll
+      for (int r = 0; r < 4; r++) yw[r] = nyw[r];
+#pragma unroll
+      for (int r = 0; r < 2; r++) {
+        uw[r] = nuw[r];
+        vw[r] = nvw[r];
+      }
+      const bool last = nlast;
+      const float e2 = (float)ne2, e4 = (float)ne4;  // e2=(xl,yu) e4=(xu,yu)
+      if (k + 1 < kmax) fetch(cy + 1);
+#else
 #pragma unroll
       for (int r = 0; r < 4; r++) yw[r] = ldg4(yp + r * ls);
 #pragma unroll
@@ -756,6 +798,7 @@ __global__ void __launch_bounds__(kThreads, LTAB ? UHDR_APPLYQ_L_MIN_BLOCKS : UH
       up += 2u * cs;
       vp += 2u * cs;
       mp = mp2;
+#endif
 
       const float d2 = e2 - e1, d3 = e3 - e1, d4 = e4 - e1, exb = fmaf(e1, p.Aq, p.Bq);
       const bool interior = dx && !last;
@@ -872,8 +915,9 @@ cudaError_t launch(const ApplyFastParams& p, cudaStream_t s) {
   return cudaGetLastError();
 }
 
-template <int PACK, bool MASK, bool BATCH, bool LTAB, bool NORM>
+template <int PACK, bool MASK, bool BATCH, bool LTAB, bool NORM, int CELLS>
 cudaError_t launch_q(const ApplyFastParams& p0, cudaStream_t s) {
+  constexpr int kQTileRows = 8 * CELLS;
   static int sms_of[64], per_sm_of[64], smem_of[64];
   int dev = 0;
   cudaError_t e = cudaGetDevice(&dev);
@@ -884,12 +928,12 @@ cudaError_t launch_q(const ApplyFastParams& p0, cudaStream_t s) {
     cudaFuncAttributes fa;
     if ((e = cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev)) != cudaSuccess) return e;
     if ((e = cudaDeviceGetAttribute(&reserved, cudaDevAttrReservedSharedMemoryPerBlock, dev)) != cudaSuccess) return e;
-    if ((e = cudaFuncGetAttributes(&fa, apply_q_kernel<PACK, MASK, BATCH, LTAB, NORM>)) != cudaSuccess) return e;
+    if ((e = cudaFuncGetAttributes(&fa, apply_q_kernel<PACK, MASK, BATCH, LTAB, NORM, CELLS>)) != cudaSuccess) return e;
     const uint32_t dyn0 = (uint32_t)reserved + (uint32_t)fa.sharedSizeBytes;
     const int smem = LTAB ? 16 + (int)(kLEntries * sizeof(float2))
                           : (PACK == kPack1010102 ? (int)(q_table_addr(dyn0) - dyn0 + kPEntries * sizeof(float2)) + 64 : 0);  // + slack for the base alignment
-    if ((e = cudaFuncSetAttribute(apply_q_kernel<PACK, MASK, BATCH, LTAB, NORM>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)) != cudaSuccess) return e;
-    if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, apply_q_kernel<PACK, MASK, BATCH, LTAB, NORM>, kThreads, smem)) != cudaSuccess) return e;
+    if ((e = cudaFuncSetAttribute(apply_q_kernel<PACK, MASK, BATCH, LTAB, NORM, CELLS>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)) != cudaSuccess) return e;
+    if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, apply_q_kernel<PACK, MASK, BATCH, LTAB, NORM, CELLS>, kThreads, smem)) != cudaSuccess) return e;
     sms_of[dev] = n_sm;
     smem_of[dev] = smem;
     per_sm_of[dev] = n > 0 ? n : 1;
@@ -900,18 +944,23 @@ cudaError_t launch_q(const ApplyFastParams& p0, cudaStream_t s) {
   p.n_tiles = p.tiles_x * p.tiles_y * n_img;
   const int cap = sms_of[dev] * per_sm_of[dev];
   const int grid = p.n_tiles < cap ? p.n_tiles : cap;
-  apply_q_kernel<PACK, MASK, BATCH, LTAB, NORM><<<grid, kThreads, (size_t)smem_of[dev], s>>>(p);
+  apply_q_kernel<PACK, MASK, BATCH, LTAB, NORM, CELLS><<<grid, kThreads, (size_t)smem_of[dev], s>>>(p);
   return cudaGetLastError();
 }
 
 template <int PACK, bool MASK>
 cudaError_t launch_q(const ApplyFastParams& p, cudaStream_t s) {
   constexpr bool kLin = PACK != kPack1010102;
+  // tall tiles (8 cells per lane) once the batch holds >= 2048 of them, i.e. several waves of the persistent grid
+  const int n_img = p.n_tiles / (p.tiles_x * p.tiles_y);
+  const bool tall = p.batch && (long long)p.tiles_x * ((p.g.map_height + 63) / 64) * n_img >= 2048;
   if (kLin && p.lin_table_ok) {  // lin_table_ok also implies normal halves (capi.cu)
     constexpr bool kNorm = PACK == kPackF16;
-    return p.batch ? launch_q<PACK, MASK, true, kLin, kNorm>(p, s) : launch_q<PACK, MASK, false, kLin, kNorm>(p, s);
+    if (tall) return launch_q<PACK, MASK, true, kLin, kNorm, 8>(p, s);
+    return p.batch ? launch_q<PACK, MASK, true, kLin, kNorm, 4>(p, s) : launch_q<PACK, MASK, false, kLin, kNorm, 4>(p, s);
   }
-  return p.batch ? launch_q<PACK, MASK, true, false, false>(p, s) : launch_q<PACK, MASK, false, false, false>(p, s);
+  if (tall) return launch_q<PACK, MASK, true, false, false, 8>(p, s);
+  return p.batch ? launch_q<PACK, MASK, true, false, false, 4>(p, s) : launch_q<PACK, MASK, false, false, false, 4>(p, s);
 }
 
 }  // namespace

@@ -26,6 +26,14 @@ namespace {
 template <bool VEC, bool FUSED, bool CONVERT = false>
 __global__ void __launch_bounds__(256) generate_kernel(GenerateParams p) {
   const Geometry& g = p.g;
+  uint32_t tY = 0, tC = 0;
+  if (CONVERT) {  // byte -> float tables of the quad transform (uhdr_convert.cuh), filled before any thread leaves
+    __shared__ float sYf[256], sCf[256];
+    fill_convert_tables(sYf, sCf, threadIdx.y * 32 + threadIdx.x);
+    __syncthreads();
+    tY = (uint32_t)__cvta_generic_to_shared(sYf);
+    tC = (uint32_t)__cvta_generic_to_shared(sCf);
+  }
   const int mx = blockIdx.x * 32 + threadIdx.x;
   const int my = blockIdx.y * 8 + threadIdx.y;
   if (mx >= g.map_width || my >= g.map_height) return;
@@ -65,24 +73,8 @@ __global__ void __launch_bounds__(256) generate_kernel(GenerateParams p) {
       for (int r = 0; r < 2; r++) { ou_w[r] = su[r]; ov_w[r] = sv[r]; }
       if (CONVERT) {
 #pragma unroll
-        for (int qr = 0; qr < 2; qr++) {
-          uint32_t ya = 0, yb = 0, uu = 0, vv = 0;
-#pragma unroll
-          for (int qc = 0; qc < 2; qc++) {
-            Quad q;
-            q.y[0][0] = (sy[2 * qr] >> (16 * qc)) & 0xff;     q.y[0][1] = (sy[2 * qr] >> (16 * qc + 8)) & 0xff;
-            q.y[1][0] = (sy[2 * qr + 1] >> (16 * qc)) & 0xff; q.y[1][1] = (sy[2 * qr + 1] >> (16 * qc + 8)) & 0xff;
-            q.u = (su[qr] >> (8 * qc)) & 0xff;
-            q.v = (sv[qr] >> (8 * qc)) & 0xff;
-            transform_quad(p.conv, q);
-            ya |= (q.y[0][0] | (q.y[0][1] << 8)) << (16 * qc);
-            yb |= (q.y[1][0] | (q.y[1][1] << 8)) << (16 * qc);
-            uu |= q.u << (8 * qc);
-            vv |= q.v << (8 * qc);
-          }
-          oy_w[2 * qr] = ya; oy_w[2 * qr + 1] = yb;
-          ou_w[qr] = uu; ov_w[qr] = vv;
-        }
+        for (int qr = 0; qr < 2; qr++)
+          transform_quad_pair(p.conv, tY, tC, oy_w[2 * qr], oy_w[2 * qr + 1], ou_w[qr], ov_w[qr]);
       }
 #pragma unroll
       for (int r = 0; r < 4; r++) stg4(oy + (size_t)r * g.sdr_luma_stride, oy_w[r]);

@@ -120,18 +120,33 @@ __global__ void __launch_bounds__(256) yuv420_to_rgba8888_vec_kernel(SdrPackPara
   const uint8_t* pu = (const uint8_t*)pl.sdr_u;
   const uint8_t* pv = (const uint8_t*)pl.sdr_v;
   uint32_t* out = (uint32_t*)pl.out;
+  // software pipeline: the 8 loads of cell k + 1 are in flight while cell k is converted and stored
+  const int cy0 = blockIdx.y * kPackCells * 8 + (threadIdx.x >> 5);  // a block covers 32 pixel rows per step
+  if (4 * cy0 >= g.height) return;
+  uint32_t nyw[4], nuw[2], nvw[2];
+  auto fetch = [&](int cy) {
+#pragma unroll
+    for (int r = 0; r < 4; r++) nyw[r] = ldg4(py + (size_t)(4 * cy + r) * g.sdr_luma_stride + 4 * cx);
+#pragma unroll
+    for (int r = 0; r < 2; r++) {
+      nuw[r] = ldg2(pu + (size_t)(2 * cy + r) * g.sdr_chroma_stride + 2 * cx);
+      nvw[r] = ldg2(pv + (size_t)(2 * cy + r) * g.sdr_chroma_stride + 2 * cx);
+    }
+  };
+  fetch(cy0);
 #pragma unroll 1
   for (int k = 0; k < kPackCells; k++) {
-    const int cy = (blockIdx.y * kPackCells + k) * 8 + (threadIdx.x >> 5);  // a block covers 32 pixel rows per step
+    const int cy = cy0 + 8 * k;
     if (4 * cy >= g.height) return;
     uint32_t yw[4], uw[2], vw[2];
 #pragma unroll
-    for (int r = 0; r < 4; r++) yw[r] = ldg4(py + (size_t)(4 * cy + r) * g.sdr_luma_stride + 4 * cx);
+    for (int r = 0; r < 4; r++) yw[r] = nyw[r];
 #pragma unroll
     for (int r = 0; r < 2; r++) {
-      uw[r] = ldg2(pu + (size_t)(2 * cy + r) * g.sdr_chroma_stride + 2 * cx);
-      vw[r] = ldg2(pv + (size_t)(2 * cy + r) * g.sdr_chroma_stride + 2 * cx);
+      uw[r] = nuw[r];
+      vw[r] = nvw[r];
     }
+    if (k + 1 < kPackCells && 4 * (cy + 8) < g.height) fetch(cy + 8);
 #pragma unroll
     for (int qr = 0; qr < 2; qr++) {
       f32x2 RV[2], GU[2], GV[2], BU[2];
