@@ -371,6 +371,32 @@ def main():
         other["apply_1010102_pq"] = timed(lambda: uh.applyGainMapBatch(Bo, sdrs, maps, md_pq, abi.OUTPUT_HDR_PQ, FLT_MAX, bigs, stream), APPLY_BPP)
         other["apply_planar_10bit"] = timed(lambda: uh.applyGainMapBatch(Bo, sdrs, maps, md, abi.OUTPUT_HDR_LINEAR_RGB_10BIT, FLT_MAX, bigs, stream), 7.5625)
         other["sdr_rgba8888_pack"] = timed(lambda: uh.yuv420ToRgba8888Batch(Bo, sdrs, bigs, stream), 5.5)
+        # N1 convertYuv in place (jpegr.cpp:1132-1206), one launch per image: four 8160x6144 images (75 MB each) in rotation
+        cw_, ch_ = 8160, 6144
+        d_cv = torch.empty((4, cw_ * ch_ * 3 // 2), dtype=torch.uint8, device=dev)
+        for i in range(4):  # the natural 4K SDR planes of image i, tiled 3 x 3 and cropped to 8160 x 6144
+            src = d_sdr[i % K]
+            for off_s, off_d, pw, ph_, tw, th in ((0, 0, W, H, cw_, ch_), (W * H, cw_ * ch_, W // 2, H // 2, cw_ // 2, ch_ // 2),
+                                                  (W * H * 5 // 4, cw_ * ch_ * 5 // 4, W // 2, H // 2, cw_ // 2, ch_ // 2)):
+                plane = src[off_s:off_s + pw * ph_].view(ph_, pw).repeat(3, 3)[:th, :tw]
+                d_cv[i, off_d:off_d + tw * th] = plane.reshape(-1)
+        cvs = (abi.Image * 4)()
+        for i in range(4):
+            cb = d_cv[i].data_ptr()
+            cvs[i].data, cvs[i].chroma_data = cb, cb + cw_ * ch_
+            cvs[i].width, cvs[i].height, cvs[i].colorGamut = cw_, ch_, abi.COLORGAMUT_BT709
+            cvs[i].luma_stride, cvs[i].chroma_stride, cvs[i].pixelFormat = cw_, cw_ // 2, abi.PIX_FMT_YUV420
+        cv_i = [0]
+
+        def cv_fn():
+            cv_i[0] += 1
+            return uh.convertYuvDevice(cvs[cv_i[0] % 4], abi.COLORGAMUT_BT709, abi.COLORGAMUT_P3, stream)
+
+        r = timed(cv_fn, 3.0, 8)
+        scale = (cw_ * ch_) / (Bo * PIX)  # timed() assumes Bo 4K images per launch
+        r.update(mpix_s=r["mpix_s"] * scale, achieved_gbs=r["achieved_gbs"] * scale, images_per_launch=1, image="8160x6144")
+        other["convert_yuv_709_to_601_50mp"] = r
+        del d_cv
         assert lib.uhdrb200_set_apply_mode(abi.APPLY_TWO_TABLE) == 0
         other["apply_1010102_hlg_two_table_kernel"] = timed(lambda: uh.applyGainMapBatch(Bo, sdrs, maps, md, abi.OUTPUT_HDR_HLG, FLT_MAX, bigs, stream), APPLY_BPP)
         assert lib.uhdrb200_set_apply_mode(abi.APPLY_AUTO) == 0

@@ -4,8 +4,8 @@
 // transformed with the quad's (U,V), luma is written back rounded (+0.5, clip), chroma gets the
 // average of the 4 transformed (U,V).
 //
-// One thread = two horizontally adjacent quads (4 px x 2 rows): 32-bit luma loads/stores, 16-bit
-// chroma loads/stores. In place, so plain (coherent) loads; every byte is read and written by the
+// One thread = 4 px x 4 rows (4-aligned planes; packed fp32x2 quad-pair transform) or two horizontally adjacent
+// quads (4 px x 2 rows, scalar fallback): 32-bit luma loads/stores, 16-bit chroma loads/stores. In place, so plain (coherent) loads; every byte is read and written by the
 // same thread only. HBM-bound: 1.5 B/px read + 1.5 B/px written.
 #include "uhdr_convert.cuh"
 #include "uhdr_kernels.cuh"
@@ -17,11 +17,49 @@ namespace {
 template <bool VEC>
 __global__ void __launch_bounds__(256) convert_yuv_kernel(ConvertYuvParams p) {
   const Geometry& g = p.g;
+  uint32_t tY = 0, tC = 0;
+  if (VEC) {  // byte -> float tables of the packed quad-pair transform, filled before any thread leaves
+    __shared__ float sYf[256], sCf[256];
+    fill_convert_tables(sYf, sCf, threadIdx.y * 32 + threadIdx.x);
+    __syncthreads();
+    tY = (uint32_t)__cvta_generic_to_shared(sYf);
+    tC = (uint32_t)__cvta_generic_to_shared(sCf);
+  }
   const int x0 = (blockIdx.x * 32 + threadIdx.x) * 4;
-  const int y0 = (blockIdx.y * 8 + threadIdx.y) * 2;
   const int cw = g.width / 2, ch = g.height / 2;
-  if ((x0 >> 1) >= cw || (y0 >> 1) >= ch) return;
   const Planes pl = p.batch ? p.batch[blockIdx.z] : p.single;
+  if (VEC) {
+    // thread = 4 px x 4 rows = two quad pairs on packed fp32x2 lanes (uhdr_convert.cuh), same roundings; all eight
+    // loads are issued before the first transform
+    const int y0 = (blockIdx.y * 8 + threadIdx.y) * 4;
+    if ((x0 >> 1) >= cw || (y0 >> 1) >= ch) return;
+    uint8_t* yp = (uint8_t*)pl.sdr_y + (size_t)y0 * g.sdr_luma_stride + x0;
+    uint8_t* up = (uint8_t*)pl.sdr_u + (size_t)(y0 >> 1) * g.sdr_chroma_stride + (x0 >> 1);
+    uint8_t* vp = (uint8_t*)pl.sdr_v + (size_t)(y0 >> 1) * g.sdr_chroma_stride + (x0 >> 1);
+    const bool two = (y0 >> 1) + 1 < ch;
+    uint32_t a[4] = {0, 0, 0, 0}, c[2] = {0, 0}, d[2] = {0, 0};
+#pragma unroll
+    for (int r = 0; r < 4; r++)
+      if (r < 2 || two) a[r] = *reinterpret_cast<uint32_t*>(yp + (size_t)r * g.sdr_luma_stride);
+#pragma unroll
+    for (int r = 0; r < 2; r++)
+      if (r < 1 || two) {
+        c[r] = *reinterpret_cast<uint16_t*>(up + (size_t)r * g.sdr_chroma_stride);
+        d[r] = *reinterpret_cast<uint16_t*>(vp + (size_t)r * g.sdr_chroma_stride);
+      }
+#pragma unroll
+    for (int r = 0; r < 2; r++) {
+      if (r == 1 && !two) break;
+      transform_quad_pair(p.m, tY, tC, a[2 * r], a[2 * r + 1], c[r], d[r]);
+      *reinterpret_cast<uint32_t*>(yp + (size_t)(2 * r) * g.sdr_luma_stride) = a[2 * r];
+      *reinterpret_cast<uint32_t*>(yp + (size_t)(2 * r + 1) * g.sdr_luma_stride) = a[2 * r + 1];
+      *reinterpret_cast<uint16_t*>(up + (size_t)r * g.sdr_chroma_stride) = (uint16_t)c[r];
+      *reinterpret_cast<uint16_t*>(vp + (size_t)r * g.sdr_chroma_stride) = (uint16_t)d[r];
+    }
+    return;
+  }
+  const int y0 = (blockIdx.y * 8 + threadIdx.y) * 2;
+  if ((x0 >> 1) >= cw || (y0 >> 1) >= ch) return;
   uint8_t* yp = (uint8_t*)pl.sdr_y + (size_t)y0 * g.sdr_luma_stride + x0;
   uint8_t* up = (uint8_t*)pl.sdr_u + (size_t)(y0 >> 1) * g.sdr_chroma_stride + (x0 >> 1);
   uint8_t* vp = (uint8_t*)pl.sdr_v + (size_t)(y0 >> 1) * g.sdr_chroma_stride + (x0 >> 1);
@@ -72,9 +110,13 @@ bool convert_yuv_vec_ok(const Geometry& g, const Planes& pl) {
 cudaError_t launch_convert_yuv_impl(const ConvertYuvParams& p, int n, bool vec, cudaStream_t s) {
   if (p.g.width < 2 || p.g.height < 2 || n == 0) return cudaSuccess;
   dim3 block(32, 8, 1);
-  dim3 grid((p.g.width + 127) / 128, (p.g.height + 15) / 16, n);
-  if (vec) convert_yuv_kernel<true><<<grid, block, 0, s>>>(p);
-  else convert_yuv_kernel<false><<<grid, block, 0, s>>>(p);
+  if (vec) {
+    dim3 grid((p.g.width + 127) / 128, (p.g.height + 31) / 32, n);  // thread = 4 x 4 pixels
+    convert_yuv_kernel<true><<<grid, block, 0, s>>>(p);
+  } else {
+    dim3 grid((p.g.width + 127) / 128, (p.g.height + 15) / 16, n);  // thread = 4 x 2 pixels
+    convert_yuv_kernel<false><<<grid, block, 0, s>>>(p);
+  }
   return cudaGetLastError();
 }
 

@@ -213,7 +213,7 @@ def test_apply_fast_path_strides(uh, orc, w, h, ls, cs, apply_mode):
 
 # ------------------------------------------------------------------------------ convertYuv (N1)
 @pytest.mark.parametrize("src,dst", [(0, 1), (0, 2), (1, 0), (1, 2), (2, 0), (2, 1)])
-@pytest.mark.parametrize("w,h,ls,cs", [(256, 128, None, None), (70, 38, 75, 39)])
+@pytest.mark.parametrize("w,h,ls,cs", [(256, 128, None, None), (70, 38, 75, 39), (64, 34, 68, 36), (132, 6, None, None)])
 def test_convert_yuv(uh, orc, src, dst, w, h, ls, cs):
     base, _ = synth.uniform_pair(w, h, 61, ls, cs)
     a, b = base.copy(), base.copy()
