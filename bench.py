@@ -410,6 +410,18 @@ def main():
             rnds[i].data, rnds[i].chroma_data = rb, rb + W * H
         other["apply_1010102_hlg_uniform_random_input"] = timed(lambda: uh.applyGainMapBatch(Bo, rnds, maps, md, abi.OUTPUT_HDR_HLG, FLT_MAX, bigs, stream), APPLY_BPP)
         del d_rnd
+        # dark natural scene: the natural SDR planes with luma / 8 and chroma pulled towards neutral -> every quad-row on the
+        # srgbInvOetf toe branch, with the spatial coherence of a real image (no table bank conflicts, no divergence)
+        d_drk = d_sdr[:Bo].clone()
+        d_drk[:, :W * H] //= 8
+        d_drk[:, W * H:] = (128 + (d_drk[:, W * H:].to(torch.int16) - 128) // 8).to(torch.uint8)
+        drks = (abi.Image * Bo)()
+        for i in range(Bo):
+            C.memmove(C.byref(drks[i]), C.byref(sdrs[i]), C.sizeof(abi.Image))
+            rb = d_drk[i].data_ptr()
+            drks[i].data, drks[i].chroma_data = rb, rb + W * H
+        other["apply_1010102_hlg_dark_natural_input"] = timed(lambda: uh.applyGainMapBatch(Bo, drks, maps, md, abi.OUTPUT_HDR_HLG, FLT_MAX, bigs, stream), APPLY_BPP)
+        del d_drk
         assert lib.uhdrb200_set_apply_mode(abi.APPLY_GENERIC) == 0
         other["apply_1010102_hlg_generic_kernel"] = timed(lambda: uh.applyGainMapBatch(Bo, sdrs, maps, md, abi.OUTPUT_HDR_HLG, FLT_MAX, bigs, stream), APPLY_BPP, 2)
         assert lib.uhdrb200_set_apply_mode(abi.APPLY_AUTO) == 0

@@ -534,9 +534,11 @@ __device__ __forceinline__ void q_rows(const uint32_t hiP, const uint32_t uq, co
               tG = cG <= 0.04045f;
               tB = cB <= 0.04045f;
               if (PACK == kPack1010102) {
-                if (tR) phR = mufu_ex2((float)(1.0 / 2.4) * mufu_lg2(cR * (float)(1.0 / 12.92)));
-                if (tG) phG = mufu_ex2((float)(1.0 / 2.4) * mufu_lg2(cG * (float)(1.0 / 12.92)));
-                if (tB) phB = mufu_ex2((float)(1.0 / 2.4) * mufu_lg2(cB * (float)(1.0 / 12.92)));
+                // (c / 12.92)^(1/2.4) = 2^(lg2(c) / 2.4 - lg2(12.92) / 2.4); c == 0 gives lg2 = -inf and ex2(-inf) = +0
+                constexpr float kToeA = (float)(1.0 / 2.4), kToeB = (float)(-3.6915341649192007 / 2.4);  // lg2(12.92) = 3.69153...
+                if (tR) phR = mufu_ex2(fmaf(mufu_lg2(cR), kToeA, kToeB));
+                if (tG) phG = mufu_ex2(fmaf(mufu_lg2(cG), kToeA, kToeB));
+                if (tB) phB = mufu_ex2(fmaf(mufu_lg2(cB), kToeA, kToeB));
               }
             }
             if (PACK == kPack1010102) {
