@@ -422,6 +422,15 @@ def main():
             drks[i].data, drks[i].chroma_data = rb, rb + W * H
         other["apply_1010102_hlg_dark_natural_input"] = timed(lambda: uh.applyGainMapBatch(Bo, drks, maps, md, abi.OUTPUT_HDR_HLG, FLT_MAX, bigs, stream), APPLY_BPP)
         del d_drk
+        # map scale factor 2 (half-resolution gain map, as other encoders write): the any-scale q-domain kernel
+        d_map2 = d_map[:Bo].view(Bo, MH, MW).repeat_interleave(2, 1).repeat_interleave(2, 2).contiguous()
+        maps2 = (abi.Image * Bo)()
+        for i in range(Bo):
+            maps2[i].data = d_map2[i].data_ptr()
+            maps2[i].width, maps2[i].height, maps2[i].luma_stride = 2 * MW, 2 * MH, 2 * MW
+            maps2[i].pixelFormat = abi.PIX_FMT_MONOCHROME
+        other["apply_1010102_hlg_map_scale_2"] = timed(lambda: uh.applyGainMapBatch(Bo, sdrs, maps2, md, abi.OUTPUT_HDR_HLG, FLT_MAX, bigs, stream), 1.5 + 0.25 + 4.0)
+        del d_map2
         assert lib.uhdrb200_set_apply_mode(abi.APPLY_GENERIC) == 0
         other["apply_1010102_hlg_generic_kernel"] = timed(lambda: uh.applyGainMapBatch(Bo, sdrs, maps, md, abi.OUTPUT_HDR_HLG, FLT_MAX, bigs, stream), APPLY_BPP, 2)
         assert lib.uhdrb200_set_apply_mode(abi.APPLY_AUTO) == 0

@@ -633,14 +633,10 @@ __device__ __forceinline__ void q_rows(const uint32_t hiP, const uint32_t uq, co
 #define UHDR_APPLYQ_PREFETCH 1  // loads of cell k + 1 issued before cell k is evaluated (needs the 80-register budget)
 #endif
 
-// Tile = 32 x 8 * CELLS map cells (128 x 128 pixels for CELLS = 4). A lane owns one column of
-// cells; a warp walks CELLS cell rows downwards, so the lower pair of map samples of one cell is
-// the upper pair of the next (2 map loads per cell) and every plane pointer advances by a constant.
-// CELLS = 8 for large batches (fewer tile prologues: 740 vs 728 Gpix/s), 4 otherwise (more tiles to balance).
-template <int PACK, bool MASK, bool BATCH, bool LTAB, bool NORM, int CELLS>
-__global__ void __launch_bounds__(kThreads, LTAB ? UHDR_APPLYQ_L_MIN_BLOCKS : UHDR_APPLYQ_MIN_BLOCKS) apply_q_kernel(const __grid_constant__ ApplyFastParams p) {
-  constexpr int kQCells = CELLS, kQTileRows = 8 * CELLS;  // cell rows per tile: 8 warps x CELLS
-  const int tid = threadIdx.x;
+// Stages the block's table (P for RGBA1010102, L for the linear outputs with LTAB) with one TMA bulk copy and returns
+// the biased shared address the look-ups use (0 when the instantiation uses no table).
+template <int PACK, bool LTAB>
+__device__ __forceinline__ uint32_t stage_q_table(const ApplyFastParams& p, const int tid) {
   uint32_t hiP = 0;
   if (LTAB) {
     // dynamic shared memory: [mbarrier 16 B][L table]
@@ -676,10 +672,15 @@ __global__ void __launch_bounds__(kThreads, LTAB ? UHDR_APPLYQ_L_MIN_BLOCKS : UH
     }
     mbar_wait(bar, 0);
   }
+  return hiP;
+}
 
-  const Geometry& g = p.g;
-  const uint32_t mw = g.map_width, mh = g.map_height;
-  const uint32_t tiles_per_image = p.tiles_x * p.tiles_y;
+// One quad-row of a 4x4 block (2 pixel rows x 4 columns = two 2x2 chroma quads) given its 8 gain factors f' = f^(1/2.4):
+// Phi-domain chroma offsets, int -> float luma, the conservative toe test and the look-up / pack / store of both rows.
+// yw0 / yw1 = the 4 luma bytes of the two rows, uq / vq = the two chroma bytes, orow = output address of the first row.
+template <int PACK, bool MASK, bool LTAB, bool NORM>
+__device__ __forceinline__ void quad_row_eval(const uint32_t hiP, const uint32_t yw0, const uint32_t yw1, const uint32_t uq, const uint32_t vq,
+                                              const float (&f)[8], uint8_t* orow, const size_t ostride, const size_t plane_bytes) {
   // Phi-domain constants (double on the host side of the compiler): K = 1/(255*1.055), chroma gains of the
   // BT.601 matrix (gainmapmath.cpp:177-196) times K, offsets = 0.055/1.055 - 128 * gain
   constexpr double dK = 1.0 / (255.0 * 1.055);
@@ -690,6 +691,60 @@ __global__ void __launch_bounds__(kThreads, LTAB ? UHDR_APPLYQ_L_MIN_BLOCKS : UH
   constexpr float oR0 = (float)(0.055 / 1.055 - 128.0 * dCr * dK), oB0 = (float)(0.055 / 1.055 - 128.0 * dCb * dK);
   constexpr float oG0 = (float)(0.055 / 1.055 + 128.0 * (dGcb + dGcr) * dK);
   constexpr float kPhiToe = 0.0905f;  // Phi(0.04045) = 0.090474; anything at or below 0.0905 takes the exact branch
+        // Phi-domain chroma offsets of the two 2x2 quads of this quad-row
+        float oR[2], oG[2], oB[2], yf[2][4];
+#if UHDR_APPLYQ_F32X2
+        {  // both quads per FFMA2
+          const f32x2 UB = pk2((float)(uq & 0xff), (float)((uq >> 8) & 0xff));
+          const f32x2 VB = pk2((float)(vq & 0xff), (float)((vq >> 8) & 0xff));
+          unpk2(fma2(VB, pk2(kR, kR), pk2(oR0, oR0)), oR[0], oR[1]);
+          unpk2(fma2(UB, pk2(kB, kB), pk2(oB0, oB0)), oB[0], oB[1]);
+          unpk2(fma2(VB, pk2(kGv, kGv), fma2(UB, pk2(kGu, kGu), pk2(oG0, oG0))), oG[0], oG[1]);
+        }
+#else
+#pragma unroll
+        for (int c = 0; c < 2; c++) {
+          const float ub = (float)((uq >> (8 * c)) & 0xff), vb = (float)((vq >> (8 * c)) & 0xff);
+          oR[c] = fmaf(vb, kR, oR0);
+          oB[c] = fmaf(ub, kB, oB0);
+          oG[c] = fmaf(vb, kGv, fmaf(ub, kGu, oG0));
+        }
+#endif
+#pragma unroll
+        for (int rr = 0; rr < 2; rr++)
+#pragma unroll
+          for (int i = 0; i < 4; i++) yf[rr][i] = (float)(((rr ? yw1 : yw0) >> (8 * i)) & 0xff);
+        const float ym0 = fminf(fminf(yf[0][0], yf[0][1]), fminf(yf[1][0], yf[1][1]));
+        const float ym1 = fminf(fminf(yf[0][2], yf[0][3]), fminf(yf[1][2], yf[1][3]));
+        const float om0 = fminf(oR[0], fminf(oG[0], oB[0])), om1 = fminf(oR[1], fminf(oG[1], oB[1]));
+#if UHDR_APPLYQ_F32X2
+        float ph0, ph1;
+        unpk2(fma2(pk2(ym0, ym1), pk2(KP, KP), pk2(om0, om1)), ph0, ph1);
+        const bool toe = fminf(ph0, ph1) <= kPhiToe;
+#else
+        const bool toe = fminf(fmaf(ym0, KP, om0), fmaf(ym1, KP, om1)) <= kPhiToe;
+#endif
+        if (toe) q_rows<PACK, MASK, true, LTAB, NORM>(hiP, uq, vq, oR, oG, oB, yf, f, orow, ostride, plane_bytes);
+#if UHDR_APPLYQ_F32X2
+        else if constexpr (PACK == kPack1010102 && !MASK) q_rows_paired(hiP, oR, oG, oB, yf, f, orow, ostride);
+        else if constexpr (LTAB) q_rows_paired_lin<PACK, NORM>(hiP, oR, oG, oB, yf, f, orow, ostride, plane_bytes);
+#endif
+        else q_rows<PACK, MASK, false, LTAB, NORM>(hiP, uq, vq, oR, oG, oB, yf, f, orow, ostride, plane_bytes);
+}
+
+// Tile = 32 x 8 * CELLS map cells (128 x 128 pixels for CELLS = 4). A lane owns one column of
+// cells; a warp walks CELLS cell rows downwards, so the lower pair of map samples of one cell is
+// the upper pair of the next (2 map loads per cell) and every plane pointer advances by a constant.
+// CELLS = 8 for large batches (fewer tile prologues: 740 vs 728 Gpix/s), 4 otherwise (more tiles to balance).
+template <int PACK, bool MASK, bool BATCH, bool LTAB, bool NORM, int CELLS>
+__global__ void __launch_bounds__(kThreads, LTAB ? UHDR_APPLYQ_L_MIN_BLOCKS : UHDR_APPLYQ_MIN_BLOCKS) apply_q_kernel(const __grid_constant__ ApplyFastParams p) {
+  constexpr int kQCells = CELLS, kQTileRows = 8 * CELLS;  // cell rows per tile: 8 warps x CELLS
+  const int tid = threadIdx.x;
+  const uint32_t hiP = stage_q_table<PACK, LTAB>(p, tid);
+
+  const Geometry& g = p.g;
+  const uint32_t mw = g.map_width, mh = g.map_height;
+  const uint32_t tiles_per_image = p.tiles_x * p.tiles_y;
 
   // tile -> (image z, tile row ty, tile column tx), advanced incrementally: no division in the loop
   const uint32_t tiles_x = p.tiles_x, tiles_y = p.tiles_y;
@@ -846,49 +901,105 @@ __global__ void __launch_bounds__(kThreads, LTAB ? UHDR_APPLYQ_L_MIN_BLOCKS : UH
             f[i] = ex2_fast(fmaf(gain, p.Aq, p.Bq));
           }
         }
-        // Phi-domain chroma offsets of the two 2x2 quads of this quad-row
-        float oR[2], oG[2], oB[2], yf[2][4];
-#if UHDR_APPLYQ_F32X2
-        {  // both quads per FFMA2
-          const f32x2 UB = pk2((float)(uw[qr] & 0xff), (float)((uw[qr] >> 8) & 0xff));
-          const f32x2 VB = pk2((float)(vw[qr] & 0xff), (float)((vw[qr] >> 8) & 0xff));
-          unpk2(fma2(VB, pk2(kR, kR), pk2(oR0, oR0)), oR[0], oR[1]);
-          unpk2(fma2(UB, pk2(kB, kB), pk2(oB0, oB0)), oB[0], oB[1]);
-          unpk2(fma2(VB, pk2(kGv, kGv), fma2(UB, pk2(kGu, kGu), pk2(oG0, oG0))), oG[0], oG[1]);
-        }
-#else
-#pragma unroll
-        for (int c = 0; c < 2; c++) {
-          const float ub = (float)((uw[qr] >> (8 * c)) & 0xff), vb = (float)((vw[qr] >> (8 * c)) & 0xff);
-          oR[c] = fmaf(vb, kR, oR0);
-          oB[c] = fmaf(ub, kB, oB0);
-          oG[c] = fmaf(vb, kGv, fmaf(ub, kGu, oG0));
-        }
-#endif
-#pragma unroll
-        for (int rr = 0; rr < 2; rr++)
-#pragma unroll
-          for (int i = 0; i < 4; i++) yf[rr][i] = (float)((yw[2 * qr + rr] >> (8 * i)) & 0xff);
-        const float ym0 = fminf(fminf(yf[0][0], yf[0][1]), fminf(yf[1][0], yf[1][1]));
-        const float ym1 = fminf(fminf(yf[0][2], yf[0][3]), fminf(yf[1][2], yf[1][3]));
-        const float om0 = fminf(oR[0], fminf(oG[0], oB[0])), om1 = fminf(oR[1], fminf(oG[1], oB[1]));
-#if UHDR_APPLYQ_F32X2
-        float ph0, ph1;
-        unpk2(fma2(pk2(ym0, ym1), pk2(KP, KP), pk2(om0, om1)), ph0, ph1);
-        const bool toe = fminf(ph0, ph1) <= kPhiToe;
-#else
-        const bool toe = fminf(fmaf(ym0, KP, om0), fmaf(ym1, KP, om1)) <= kPhiToe;
-#endif
-        if (toe) q_rows<PACK, MASK, true, LTAB, NORM>(hiP, uw[qr], vw[qr], oR, oG, oB, yf, f, orow + (size_t)(2 * qr) * ostride, ostride, plane_bytes);
-#if UHDR_APPLYQ_F32X2
-        else if constexpr (PACK == kPack1010102 && !MASK) q_rows_paired(hiP, oR, oG, oB, yf, f, orow + (size_t)(2 * qr) * ostride, ostride);
-        else if constexpr (LTAB) q_rows_paired_lin<PACK, NORM>(hiP, oR, oG, oB, yf, f, orow + (size_t)(2 * qr) * ostride, ostride, plane_bytes);
-#endif
-        else q_rows<PACK, MASK, false, LTAB, NORM>(hiP, uw[qr], vw[qr], oR, oG, oB, yf, f, orow + (size_t)(2 * qr) * ostride, ostride, plane_bytes);
+        quad_row_eval<PACK, MASK, LTAB, NORM>(hiP, yw[2 * qr], yw[2 * qr + 1], uw[qr], vw[qr], f, orow + (size_t)(2 * qr) * ostride, ostride, plane_bytes);
       }
       e1 = e2;
       e3 = e4;
       orow += 4 * ostride;
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Any integer map scale factor (sampleMap with a size_t scale, gainmapmath.cpp:686-720) on the same q-domain tables:
+// thread = one 4x4 PIXEL block; its 16 gain factors come from the general Shepard-IDW sampling (map samples and the
+// weight row of tables mWeights / NR / NB / C fetched per map cell the block touches), everything downstream
+// (quad_row_eval) is shared with the scale-4 kernel. x / scale uses a host-computed reciprocal (exact for x < 2^16).
+template <int PACK, bool MASK, bool BATCH, bool LTAB, bool NORM>
+__global__ void __launch_bounds__(kThreads, 3) apply_qs_kernel(const __grid_constant__ ApplyFastParams p) {
+  const int tid = threadIdx.x;
+  const uint32_t hiP = stage_q_table<PACK, LTAB>(p, tid);
+  const Geometry& g = p.g;
+  const uint32_t mw = g.map_width, mh = g.map_height, sc = (uint32_t)g.map_scale, magic = p.scale_magic;
+  const uint32_t bw = (uint32_t)g.width >> 2, bh = (uint32_t)g.height >> 2;  // 4x4 pixel blocks
+  const uint32_t tiles_x = p.tiles_x, tiles_per_image = p.tiles_x * p.tiles_y;  // tiles of 32 x 8 blocks
+  const uint32_t ls = g.sdr_luma_stride, cs = g.sdr_chroma_stride;
+  constexpr int kBpp = PACK == kPack1010102 ? 4 : (PACK == kPackF16 ? 8 : 2);  // bytes per pixel (per plane for planar)
+  const size_t ostride = (size_t)g.width * kBpp;
+  const size_t plane_bytes = (size_t)g.width * g.height * 2;
+  const float4* idw = reinterpret_cast<const float4*>(p.idw);  // [table][oy][ox] rows of 4 weights
+  const uint32_t ss = sc * sc;
+  auto div_s = [&](uint32_t x) { return magic ? __umulhi(x, magic) : x; };  // magic == 0 <=> scale 1
+
+  for (uint32_t tile = blockIdx.x; tile < (uint32_t)p.n_tiles; tile += gridDim.x) {
+    const uint32_t z = tile / tiles_per_image, rem = tile - z * tiles_per_image;
+    const uint32_t ty = rem / tiles_x, tx = rem - ty * tiles_x;
+    const uint32_t bx = tx * 32 + (tid & 31), by = ty * 8 + (tid >> 5);
+    if (bx >= bw || by >= bh) continue;
+    const uint8_t *sdr_y, *sdr_u, *sdr_v, *map;
+    uint8_t* outp;
+    if (BATCH) {
+      const Planes* pl = p.batch + z;
+      sdr_y = (const uint8_t*)__ldg((const unsigned long long*)&pl->sdr_y);
+      sdr_u = (const uint8_t*)__ldg((const unsigned long long*)&pl->sdr_u);
+      sdr_v = (const uint8_t*)__ldg((const unsigned long long*)&pl->sdr_v);
+      map = (const uint8_t*)__ldg((const unsigned long long*)&pl->map_in);
+      outp = (uint8_t*)__ldg((const unsigned long long*)&pl->out);
+    } else {
+      sdr_y = (const uint8_t*)p.single.sdr_y;
+      sdr_u = (const uint8_t*)p.single.sdr_u;
+      sdr_v = (const uint8_t*)p.single.sdr_v;
+      map = (const uint8_t*)p.single.map_in;
+      outp = (uint8_t*)p.single.out;
+    }
+    const uint8_t* yp = sdr_y + (4u * by * ls + 4u * bx);
+    const uint32_t coff = 2u * by * cs + 2u * bx;
+    uint8_t* orow = outp + (size_t)(4u * by * (uint32_t)g.width + 4u * bx) * kBpp;
+    uint32_t yw[4], uw[2], vw[2];
+#pragma unroll
+    for (int r = 0; r < 4; r++) yw[r] = ldg4(yp + r * ls);
+#pragma unroll
+    for (int r = 0; r < 2; r++) {
+      uw[r] = ldg2(sdr_u + coff + r * cs);
+      vw[r] = ldg2(sdr_v + coff + r * cs);
+    }
+    const uint32_t x0 = 4u * bx, xl0 = div_s(x0), ox0 = x0 - xl0 * sc;
+#pragma unroll
+    for (int qr = 0; qr < 2; qr++) {
+      float f[8];
+#pragma unroll
+      for (int rr = 0; rr < 2; rr++) {
+        const uint32_t y = 4u * by + 2u * qr + rr, yl = div_s(y), oy = y - yl * sc;
+        const bool ylast = yl + 1 >= mh;  // y_upper = min(y_lower + 1, height - 1)
+        const uint8_t* m0 = map + yl * mw;
+        const uint8_t* m1 = ylast ? m0 : m0 + mw;
+        const float4* wrow = idw + oy * sc;
+        uint32_t xl = xl0, ox = ox0, t = 0;
+        float e1 = 0.f, e2 = 0.f, e3 = 0.f, e4 = 0.f;
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+          if (i == 0 || ox == 0) {  // first pixel of the row segment or of a new map cell
+            const bool xlast = xl + 1 >= mw;
+            const uint32_t xu = xlast ? xl : xl + 1;
+            e1 = (float)__ldg(m0 + xl);
+            e2 = (float)__ldg(m1 + xl);
+            e3 = (float)__ldg(m0 + xu);
+            e4 = (float)__ldg(m1 + xu);
+            t = xlast ? (ylast ? 3u : 1u) : (ylast ? 2u : 0u);  // C / NR / NB / interior, gainmapmath.cpp:710-716
+          }
+          const float4 w = __ldg(wrow + t * ss + ox);
+          float gain = e1 * w.x;
+          gain = fmaf(e2, w.y, gain);
+          gain = fmaf(e3, w.z, gain);
+          gain = fmaf(e4, w.w, gain);
+          f[rr * 4 + i] = ex2_fast(fmaf(gain, p.Aq, p.Bq));
+          if (++ox == sc) {
+            ox = 0;
+            xl++;
+          }
+        }
+      }
+      quad_row_eval<PACK, MASK, LTAB, NORM>(hiP, yw[2 * qr], yw[2 * qr + 1], uw[qr], vw[qr], f, orow + (size_t)(2 * qr) * ostride, ostride, plane_bytes);
     }
   }
 }
@@ -965,6 +1076,44 @@ cudaError_t launch_q(const ApplyFastParams& p, cudaStream_t s) {
   return p.batch ? launch_q<PACK, MASK, true, false, false, 4>(p, s) : launch_q<PACK, MASK, false, false, false, 4>(p, s);
 }
 
+template <int PACK, bool MASK, bool BATCH, bool LTAB, bool NORM>
+cudaError_t launch_qs(const ApplyFastParams& p0, cudaStream_t s) {
+  static int sms_of[64], per_sm_of[64], smem_of[64];
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  dev &= 63;
+  if (per_sm_of[dev] == 0) {
+    int n_sm = 0, n = 0, reserved = 0;
+    cudaFuncAttributes fa;
+    if ((e = cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev)) != cudaSuccess) return e;
+    if ((e = cudaDeviceGetAttribute(&reserved, cudaDevAttrReservedSharedMemoryPerBlock, dev)) != cudaSuccess) return e;
+    if ((e = cudaFuncGetAttributes(&fa, apply_qs_kernel<PACK, MASK, BATCH, LTAB, NORM>)) != cudaSuccess) return e;
+    const uint32_t dyn0 = (uint32_t)reserved + (uint32_t)fa.sharedSizeBytes;
+    const int smem = LTAB ? 16 + (int)(kLEntries * sizeof(float2))
+                          : (PACK == kPack1010102 ? (int)(q_table_addr(dyn0) - dyn0 + kPEntries * sizeof(float2)) + 64 : 0);
+    if ((e = cudaFuncSetAttribute(apply_qs_kernel<PACK, MASK, BATCH, LTAB, NORM>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)) != cudaSuccess) return e;
+    if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, apply_qs_kernel<PACK, MASK, BATCH, LTAB, NORM>, kThreads, smem)) != cudaSuccess) return e;
+    sms_of[dev] = n_sm;
+    smem_of[dev] = smem;
+    per_sm_of[dev] = n > 0 ? n : 1;
+  }
+  const int cap = sms_of[dev] * per_sm_of[dev];
+  const int grid = p0.n_tiles < cap ? p0.n_tiles : cap;
+  apply_qs_kernel<PACK, MASK, BATCH, LTAB, NORM><<<grid, kThreads, (size_t)smem_of[dev], s>>>(p0);
+  return cudaGetLastError();
+}
+
+template <int PACK, bool MASK>
+cudaError_t launch_qs(const ApplyFastParams& p, cudaStream_t s) {
+  constexpr bool kLin = PACK != kPack1010102;
+  if (kLin && p.lin_table_ok) {
+    constexpr bool kNorm = PACK == kPackF16;
+    return p.batch ? launch_qs<PACK, MASK, true, kLin, kNorm>(p, s) : launch_qs<PACK, MASK, false, kLin, kNorm>(p, s);
+  }
+  return p.batch ? launch_qs<PACK, MASK, true, false, false>(p, s) : launch_qs<PACK, MASK, false, false, false>(p, s);
+}
+
 }  // namespace
 
 bool apply_fast_ok(const Geometry& g, const Planes& pl) {
@@ -975,8 +1124,29 @@ bool apply_fast_ok(const Geometry& g, const Planes& pl) {
          (uint64_t)g.height * (uint64_t)g.width < (1ull << 31);
 }
 
+// the any-scale q-domain kernel: 4-aligned planes, map = image / scale exactly, coordinates below 2^16 (reciprocal division)
+bool apply_qs_ok(const Geometry& g, const Planes& pl) {
+  return g.map_scale >= 1 && g.map_scale < 65536 && g.width % 4 == 0 && g.height % 4 == 0 && g.width < 65536 && g.height < 65536 &&
+         g.map_width * g.map_scale == g.width && g.map_height * g.map_scale == g.height && aligned(pl.sdr_y, 4) &&
+         aligned(pl.sdr_u, 2) && aligned(pl.sdr_v, 2) && aligned(pl.out, 16) && g.sdr_luma_stride % 4 == 0 &&
+         g.sdr_chroma_stride % 2 == 0 && ((size_t)g.width * g.height * 2) % 8 == 0 &&
+         (uint64_t)g.height * (uint64_t)g.sdr_luma_stride < (1ull << 31) && (uint64_t)g.height * (uint64_t)g.width < (1ull << 31);
+}
+
 cudaError_t launch_apply_fast_impl(ApplyFastParams& p, int n, cudaStream_t s) {
   if (p.g.width == 0 || p.g.height == 0 || n == 0) return cudaSuccess;
+  if (p.any_scale) {
+    p.tiles_x = (p.g.width / 4 + 31) / 32;
+    p.tiles_y = (p.g.height / 4 + 7) / 8;
+    p.n_tiles = p.tiles_x * p.tiles_y * n;
+    // x / scale == umulhi(x, ceil(2^32 / scale)) for x < 2^16 <= 2^32 / scale; scale 1 is the identity (magic 0)
+    p.scale_magic = p.g.map_scale == 1 ? 0u : (uint32_t)((0x100000000ull + (uint64_t)p.g.map_scale - 1) / (uint64_t)p.g.map_scale);
+    switch (p.output_format) {
+      case 1: return launch_qs<kPackF16, false>(p, s);
+      case 4: return launch_qs<kPackPlanar10, false>(p, s);
+      default: return p.need_mask ? launch_qs<kPack1010102, true>(p, s) : launch_qs<kPack1010102, false>(p, s);
+    }
+  }
   p.tiles_x = (p.g.map_width + kTileCellsX - 1) / kTileCellsX;
   p.tiles_y = (p.g.map_height + kTileCellsY - 1) / kTileCellsY;
   p.n_tiles = p.tiles_x * p.tiles_y * n;

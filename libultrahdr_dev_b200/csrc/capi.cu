@@ -421,6 +421,10 @@ int apply_core(int n, const uhdrb200_image* sdr, const uhdrb200_image* map, cons
   // f = 2^(gain*A + B) (gain in [0,1]) small enough for the OETF table range.
   bool fast = g_apply_mode != 1;
   for (int i = 0; i < n && fast; i++) fast = apply_fast_ok(p.g, v[i]);
+  // other integer scale factors (or scale 4 with a ragged map) keep the q-domain tables through apply_qs_kernel
+  bool any_scale = !fast && g_apply_mode == 0;
+  for (int i = 0; i < n && any_scale; i++) any_scale = apply_qs_ok(p.g, v[i]);
+  fast = fast || any_scale;
   const double k = (double)p.display_boost / (double)p.max_boost;
   const double A = ((double)p.log2_max - (double)p.log2_min) * k;
   const double B = (double)p.log2_min * k - log2((double)p.display_boost);
@@ -447,6 +451,7 @@ int apply_core(int n, const uhdrb200_image* sdr, const uhdrb200_image* map, cons
     f.Bq = (float)(B / 2.4);
     f.q0 = (float)ldexp(1.0, kPLoExp);
     f.two_table = g_apply_mode == 2;
+    f.any_scale = any_scale ? 1 : 0;
     // linear outputs: every non-toe channel has Phi > 0.0904, so q >= 0.0904 * f'min must reach the L table's first
     // octave, and q^2.4 must be a normal half with margin (the F16 kernel then skips the subnormal/flush checks)
     {

@@ -115,6 +115,8 @@ struct ApplyFastParams {
   float Aq, Bq, q0;        // q-domain kernel: f' = 2^(gain255 * Aq + Bq) = f^(1/2.4), gain255 = 255 * gain; q0 = 2^kPLoExp
   int two_table;           // 1: the S+O table kernels (apply_fast_kernel) instead of the q-domain kernels
   int lin_table_ok;        // 1: q = Phi * f' stays inside the L table for every non-toe channel (host check)
+  int any_scale;           // 1: apply_qs_kernel (any integer map scale factor, thread = 4x4 pixels) instead of the scale-4 kernels
+  uint32_t scale_magic;    // ceil(2^32 / map_scale), 0 for scale 1 (set by launch_apply_fast_impl)
   // Aq x interior IDW weights of corners 2..4 (they include the 1/255 of the map samples), [corner - 2][oy * 4 + ox]:
   // horizontally adjacent pixels are one 8-byte pair for FFMA2
   alignas(8) float wq[3][16];
@@ -157,6 +159,7 @@ cudaError_t launch_api0_fused_impl(const GenerateParams& p, int n, cudaStream_t 
 cudaError_t launch_apply_impl(const ApplyParams& p, int n, bool vec, cudaStream_t s);
 // fast path: scale 4, vector-aligned planes, gain factor bounded so that e + e0 < 2^kOHiExp
 bool apply_fast_ok(const Geometry& g, const Planes& pl);
+bool apply_qs_ok(const Geometry& g, const Planes& pl);
 cudaError_t launch_apply_fast_impl(ApplyFastParams& p, int n, cudaStream_t s);
 // host: fills the double-precision-built tables (tables.cu)
 void build_apply_tables(float2* s, float2* s_hi, float2* o_hlg, float2* o_pq, float2* p_hlg, float2* p_pq, float2* l_pow, float* e255);
