@@ -188,6 +188,7 @@ def main():
     ap.add_argument("--batch", type=int, default=256, help="4K pairs per step per GPU (device-resident)")
     ap.add_argument("--e2e-images", type=int, default=16, help="4K pairs per e2e step per GPU (host planes)")
     ap.add_argument("--e2e-threads", type=int, default=4, help="host threads calling the synchronous host-pointer API concurrently")
+    ap.add_argument("--e2e-join", default="auto", choices=["auto", "spin", "blocking"], help="how the host entry points wait (uhdrb200_set_sync_mode)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-other-stages", action="store_true", help="skip the per-kernel rooflines of the other stages")
     ap.add_argument("--cpu-images", type=int, default=24, help="images per CPU worker process in the CPU arms")
@@ -464,6 +465,9 @@ def main():
     import concurrent.futures as cf
 
     T = max(1, a.e2e_threads)
+    # more calling threads (all ranks) than cores: sleeping joins instead of spinning ones (include/uhdr_b200.h)
+    blocking = world * (T + 1) > host_cores() if a.e2e_join == "auto" else a.e2e_join == "blocking"
+    assert lib.uhdrb200_set_sync_mode(abi.SYNC_BLOCKING if blocking else abi.SYNC_SPIN) == 0
     pool = cf.ThreadPoolExecutor(T, initializer=lambda: lib.uhdrb200_init(local))
 
     def e2e_one(i):
@@ -542,7 +546,7 @@ def main():
         "stage_mpix_s": {"generate": B * PIX / gen_ms / 1e3, "apply": B * PIX / app_ms / 1e3},
         "e2e": {"value": world * E * PIX * e2e_steps / (e2e_ms * 1e-3) / 1e6 if e2e_steps else None, "unit": UNIT, "h2d_bytes_per_step": h2d,
                 "d2h_bytes_per_step": d2h, "images_per_step_per_gpu": E, "steps": e2e_steps,
-                "host_threads": T,
+                "host_threads": T, "join": "blocking" if blocking else "spin",
                 "api": "uhdrb200_generate_gainmap_host_into + uhdrb200_apply_gainmap_host (synchronous, reference-style), pinned host planes"},
         "other_stages": {k: dict(v, frac_of_hbm_peak=v["achieved_gbs"] / peak) for k, v in other.items()},
         "gpu_launches": int(launches),

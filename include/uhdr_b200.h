@@ -146,6 +146,14 @@ uint64_t uhdrb200_launch_count(void);
 enum { UHDRB200_APPLY_AUTO = 0, UHDRB200_APPLY_GENERIC = 1, UHDRB200_APPLY_TWO_TABLE = 2 };
 int uhdrb200_set_apply_mode(int mode);
 
+/* How the synchronous *_host entry points wait for their stream (process-wide). The reference joins its row-block
+ * worker threads before returning (ultrahdr.cpp:354, 513); here the join is a stream wait. SPIN (default,
+ * cudaStreamSynchronize) has the lowest latency; BLOCKING sleeps on a cudaEventBlockingSync event, which is what a
+ * host with more calling threads than cores wants (several processes x several threads per GPU). The environment
+ * variable UHDRB200_BLOCKING_SYNC=1 selects BLOCKING when this function has not been called. */
+enum { UHDRB200_SYNC_SPIN = 0, UHDRB200_SYNC_BLOCKING = 1 };
+int uhdrb200_set_sync_mode(int mode);
+
 /* ---- A1: UltraHdr::generateGainMap (ultrahdr.cpp:185-358) ---- */
 /* Host planes. On success dest->data is a malloc'ed map_w*map_h buffer owned by the caller
  * (release with uhdrb200_free); metadata is fully overwritten (ultrahdr.cpp:250-257). */

@@ -29,6 +29,7 @@ ERROR_UNSUPPORTED_MAP_SCALE_FACTOR = -20008
 ERROR_INSUFFICIENT_RESOURCE = -20009
 
 APPLY_AUTO, APPLY_GENERIC, APPLY_TWO_TABLE = 0, 1, 2  # uhdrb200_set_apply_mode
+SYNC_SPIN, SYNC_BLOCKING = 0, 1  # uhdrb200_set_sync_mode
 MAP_SCALE = 4  # kMapDimensionScaleFactor, ultrahdr.h:213
 SDR_WHITE_NITS, HLG_MAX_NITS, PQ_MAX_NITS = 203.0, 1000.0, 10000.0  # gainmapmath.h:34-36
 

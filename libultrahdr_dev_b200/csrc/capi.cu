@@ -23,6 +23,7 @@ namespace {
 using namespace uhdr;
 
 std::atomic<uint64_t> g_launches{0};
+std::atomic<int> g_sync_mode{-1};  // -1: from the environment (UHDRB200_BLOCKING_SYNC), 0 spin, 1 blocking
 std::atomic<int> g_apply_mode{0};  // 0 auto (table-driven fast path when eligible), 1 force the generic kernel
 
 // ---------------------------------------------------------------- per-thread context
@@ -41,6 +42,7 @@ struct Ctx {
   int device = -1;  // -1: not bound yet
   bool ready = false;
   cudaStream_t stream = nullptr;
+  cudaEvent_t sync_ev = nullptr;  // cudaEventBlockingSync: the joining host thread sleeps instead of spinning
   DevBuf buf[8];  // staging planes of the *_host entry points
   BatchSlot ring[kRing];
   int ring_next = 0;
@@ -81,8 +83,26 @@ int ensure_ctx() {
   }
   CU(cudaSetDevice(c.device));
   CU(cudaStreamCreateWithFlags(&c.stream, cudaStreamNonBlocking));
+  CU(cudaEventCreateWithFlags(&c.sync_ev, cudaEventBlockingSync | cudaEventDisableTiming));
   c.ready = true;
   return 0;
+}
+
+// The join of a synchronous *_host entry point (the reference joins its worker threads, ultrahdr.cpp:354, 513).
+// Spinning (cudaStreamSynchronize) has the lowest latency; when more host threads call into the library than there are
+// cores (several processes x several threads per GPU) the spinners steal the cores from each other, so the caller can
+// ask for a sleeping wait on a cudaEventBlockingSync event (uhdrb200_set_sync_mode, or UHDRB200_BLOCKING_SYNC=1).
+cudaError_t join_stream(Ctx& c) {
+  int mode = g_sync_mode.load();
+  if (mode < 0) {
+    const char* e = getenv("UHDRB200_BLOCKING_SYNC");
+    mode = (e && e[0] == '1') ? 1 : 0;
+    g_sync_mode = mode;
+  }
+  if (mode == 0) return cudaStreamSynchronize(c.stream);
+  cudaError_t e = cudaEventRecord(c.sync_ev, c.stream);
+  if (e != cudaSuccess) return e;
+  return cudaEventSynchronize(c.sync_ev);
 }
 
 int reserve(DevBuf& b, size_t bytes) {
@@ -702,7 +722,7 @@ int generate_host(const uhdrb200_image* sdr, const uhdrb200_image* hdr, int hdr_
   void* out = own_alloc ? malloc(mbytes ? mbytes : 1) : map_buf;
   if (!out) return UHDRB200_ERROR_INSUFFICIENT_RESOURCE;
   cudaError_t e = mbytes ? cudaMemcpyAsync(out, c.buf[4].p, mbytes, cudaMemcpyDeviceToHost, c.stream) : cudaSuccess;
-  if (e == cudaSuccess) e = cudaStreamSynchronize(c.stream);
+  if (e == cudaSuccess) e = join_stream(c);
   if (e != cudaSuccess) {
     if (own_alloc) free(out);
     return fail(e, "generateGainMap device->host");
@@ -744,7 +764,7 @@ int apply_host(const uhdrb200_image* sdr, const uhdrb200_image* map, const uhdrb
   ddst.data = c.buf[4].p;
   if ((st = apply_core(1, &dsdr, &dmap, md, fmt, max_display_boost, &ddst, c.stream))) return st;
   CU(cudaMemcpyAsync(dest->data, c.buf[4].p, obytes, cudaMemcpyDeviceToHost, c.stream));
-  CU(cudaStreamSynchronize(c.stream));
+  CU(join_stream(c));
   dest->width = sdr->width; dest->height = sdr->height; dest->colorGamut = sdr->colorGamut;
   return UHDRB200_NO_ERROR;
 }
@@ -768,7 +788,7 @@ int tonemap_host(const uhdrb200_image* src, uhdrb200_image* dest) {
   // stride tails of the last rows are part of the reference's writes (memset to the stride)
   if (dl) CU(cudaMemcpyAsync(dest->data, c.buf[6].p, dl, cudaMemcpyDeviceToHost, c.stream));
   if (dc) CU(cudaMemcpyAsync(dest->chroma_data, c.buf[7].p, dc, cudaMemcpyDeviceToHost, c.stream));
-  CU(cudaStreamSynchronize(c.stream));
+  CU(join_stream(c));
   dest->colorGamut = src->colorGamut;
   return UHDRB200_NO_ERROR;
 }
@@ -791,7 +811,7 @@ int convert_yuv_host(uhdrb200_image* im, int src_enc, int dst_enc) {
   if ((st = convert_yuv_core(&d, src_enc, dst_enc, c.stream))) return st;
   if (lb) CU(cudaMemcpyAsync(im->data, c.buf[0].p, lb, cudaMemcpyDeviceToHost, c.stream));
   if (cb) CU(cudaMemcpyAsync(im->chroma_data, c.buf[1].p, cb, cudaMemcpyDeviceToHost, c.stream));
-  CU(cudaStreamSynchronize(c.stream));
+  CU(join_stream(c));
   return UHDRB200_NO_ERROR;
 }
 
@@ -816,7 +836,7 @@ int sdr_pack_host(const uhdrb200_image* sdr, uhdrb200_image* dest) {
   } else if (ob) {  // only the pixels: bytes between width and the stride stay the caller's
     CU(cudaMemcpy2DAsync(dest->data, os * 4, c.buf[6].p, os * 4, sdr->width * 4, sdr->height, cudaMemcpyDeviceToHost, c.stream));
   }
-  CU(cudaStreamSynchronize(c.stream));
+  CU(join_stream(c));
   dest->width = sdr->width;
   dest->height = sdr->height;
   dest->colorGamut = sdr->colorGamut;
@@ -842,7 +862,7 @@ int copy_yuv420_host(const uhdrb200_image* src, uhdrb200_image* dst) {
   if ((st = copy_yuv420_core(&s2, &d2, c.stream))) return st;
   if (dl) CU(cudaMemcpyAsync(dst->data, c.buf[6].p, dl, cudaMemcpyDeviceToHost, c.stream));
   if (dc) CU(cudaMemcpyAsync(dst->chroma_data, c.buf[7].p, dc, cudaMemcpyDeviceToHost, c.stream));
-  CU(cudaStreamSynchronize(c.stream));
+  CU(join_stream(c));
   dst->width = src->width;
   dst->height = src->height;
   dst->colorGamut = src->colorGamut;
@@ -874,7 +894,7 @@ int api0_host(const uhdrb200_image* hdr, int hdr_tf, int sdr_to_601, uhdrb200_im
   if (dl) CU(cudaMemcpyAsync(sdr->data, c.buf[6].p, dl, cudaMemcpyDeviceToHost, c.stream));
   if (dc) CU(cudaMemcpyAsync(sdr->chroma_data, c.buf[7].p, dc, cudaMemcpyDeviceToHost, c.stream));
   if (mbytes) CU(cudaMemcpyAsync(map_buf, c.buf[4].p, mbytes, cudaMemcpyDeviceToHost, c.stream));
-  CU(cudaStreamSynchronize(c.stream));
+  CU(join_stream(c));
   sdr->colorGamut = hdr->colorGamut;
   fill_map_desc(dest, mw, mh);
   dest->data = map_buf;
@@ -917,6 +937,8 @@ void uhdrb200_shutdown(void) {
     s = BatchSlot();
   }
   cudaStreamDestroy(c.stream);
+  if (c.sync_ev) cudaEventDestroy(c.sync_ev);
+  c.sync_ev = nullptr;
   c.stream = nullptr;
   c.ready = false;
 }
@@ -933,6 +955,11 @@ uint64_t uhdrb200_launch_count(void) { return g_launches.load(); }
 int uhdrb200_set_apply_mode(int mode) {
   if (mode != UHDRB200_APPLY_AUTO && mode != UHDRB200_APPLY_GENERIC && mode != UHDRB200_APPLY_TWO_TABLE) return UHDRB200_ERROR_UNSUPPORTED_FEATURE;
   g_apply_mode = mode;
+  return UHDRB200_NO_ERROR;
+}
+int uhdrb200_set_sync_mode(int mode) {
+  if (mode != UHDRB200_SYNC_SPIN && mode != UHDRB200_SYNC_BLOCKING) return UHDRB200_ERROR_UNSUPPORTED_FEATURE;
+  g_sync_mode = mode;
   return UHDRB200_NO_ERROR;
 }
 

@@ -112,6 +112,8 @@ def test_argument_validation_precedes_cuda():
     keep = sdr_b.copy()
     assert uh.convertYuv(sdr, 1, 1) == abi.NO_ERROR and np.array_equal(keep, sdr_b)  # identity: untouched, no device
     assert lib.uhdrb200_set_apply_mode(7) != 0 and lib.uhdrb200_set_apply_mode(abi.APPLY_AUTO) == 0
+    assert lib.uhdrb200_set_sync_mode(7) != 0 and lib.uhdrb200_set_sync_mode(abi.SYNC_BLOCKING) == 0
+    assert lib.uhdrb200_set_sync_mode(abi.SYNC_SPIN) == 0
 
 
 def test_no_gpu_means_loud_failure_not_a_cpu_fallback():
