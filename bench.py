@@ -432,6 +432,14 @@ def main():
             maps2[i].pixelFormat = abi.PIX_FMT_MONOCHROME
         other["apply_1010102_hlg_map_scale_2"] = timed(lambda: uh.applyGainMapBatch(Bo, sdrs, maps2, md, abi.OUTPUT_HDR_HLG, FLT_MAX, bigs, stream), 1.5 + 0.25 + 4.0)
         del d_map2
+        d_map1 = d_map[:Bo].view(Bo, MH, MW).repeat_interleave(4, 1).repeat_interleave(4, 2).contiguous()  # full-resolution map
+        maps1 = (abi.Image * Bo)()
+        for i in range(Bo):
+            maps1[i].data = d_map1[i].data_ptr()
+            maps1[i].width, maps1[i].height, maps1[i].luma_stride = W, H, W
+            maps1[i].pixelFormat = abi.PIX_FMT_MONOCHROME
+        other["apply_1010102_hlg_map_scale_1"] = timed(lambda: uh.applyGainMapBatch(Bo, sdrs, maps1, md, abi.OUTPUT_HDR_HLG, FLT_MAX, bigs, stream), 1.5 + 1.0 + 4.0)
+        del d_map1
         assert lib.uhdrb200_set_apply_mode(abi.APPLY_GENERIC) == 0
         other["apply_1010102_hlg_generic_kernel"] = timed(lambda: uh.applyGainMapBatch(Bo, sdrs, maps, md, abi.OUTPUT_HDR_HLG, FLT_MAX, bigs, stream), APPLY_BPP, 2)
         assert lib.uhdrb200_set_apply_mode(abi.APPLY_AUTO) == 0

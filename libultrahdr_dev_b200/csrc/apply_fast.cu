@@ -915,7 +915,10 @@ __global__ void __launch_bounds__(kThreads, LTAB ? UHDR_APPLYQ_L_MIN_BLOCKS : UH
 // thread = one 4x4 PIXEL block; its 16 gain factors come from the general Shepard-IDW sampling (map samples and the
 // weight row of tables mWeights / NR / NB / C fetched per map cell the block touches), everything downstream
 // (quad_row_eval) is shared with the scale-4 kernel. x / scale uses a host-computed reciprocal (exact for x < 2^16).
-template <int PACK, bool MASK, bool BATCH, bool LTAB, bool NORM>
+// SCALE = 1 / 2 are compile-time specialisations (no interpolation at scale 1; one 3x3 map patch per block and the four
+// interior weight rows from the constant bank at scale 2, same operation order as the general code, so the results are
+// identical); SCALE = 0 is the general run-time scale.
+template <int PACK, bool MASK, bool BATCH, bool LTAB, bool NORM, int SCALE>
 __global__ void __launch_bounds__(kThreads, 3) apply_qs_kernel(const __grid_constant__ ApplyFastParams p) {
   const int tid = threadIdx.x;
   const uint32_t hiP = stage_q_table<PACK, LTAB>(p, tid);
@@ -964,38 +967,80 @@ __global__ void __launch_bounds__(kThreads, 3) apply_qs_kernel(const __grid_cons
       vw[r] = ldg2(sdr_v + coff + r * cs);
     }
     const uint32_t x0 = 4u * bx, xl0 = div_s(x0), ox0 = x0 - xl0 * sc;
+    // scale 2: the 3x3 map samples the block's four cells use (as 0..255 floats), interior blocks only
+    float P2[3][3];
+    bool patch = false;
+    if (SCALE == 2) {
+      patch = 2u * bx + 2u < mw && 2u * by + 2u < mh;  // no cell of the block on the right / bottom map border
+      if (patch) {
+#pragma unroll
+        for (int a = 0; a < 3; a++) {
+          const uint8_t* mr = map + (2u * by + a) * mw + 2u * bx;
+          const uint32_t two = ldg2(mr);
+          P2[a][0] = (float)(two & 0xff);
+          P2[a][1] = (float)(two >> 8);
+          P2[a][2] = (float)__ldg(mr + 2);
+        }
+      }
+    }
 #pragma unroll
     for (int qr = 0; qr < 2; qr++) {
       float f[8];
+      if (SCALE == 1) {  // offsets (0,0): weights [1,0,0,0] in all four tables, the gain is the pixel's own map sample
 #pragma unroll
-      for (int rr = 0; rr < 2; rr++) {
-        const uint32_t y = 4u * by + 2u * qr + rr, yl = div_s(y), oy = y - yl * sc;
-        const bool ylast = yl + 1 >= mh;  // y_upper = min(y_lower + 1, height - 1)
-        const uint8_t* m0 = map + yl * mw;
-        const uint8_t* m1 = ylast ? m0 : m0 + mw;
-        const float4* wrow = idw + oy * sc;
-        uint32_t xl = xl0, ox = ox0, t = 0;
-        float e1 = 0.f, e2 = 0.f, e3 = 0.f, e4 = 0.f;
+        for (int rr = 0; rr < 2; rr++) {
+          const uint32_t mwrd = ldg4(map + (4u * by + 2u * qr + rr) * mw + 4u * bx);
 #pragma unroll
-        for (int i = 0; i < 4; i++) {
-          if (i == 0 || ox == 0) {  // first pixel of the row segment or of a new map cell
-            const bool xlast = xl + 1 >= mw;
-            const uint32_t xu = xlast ? xl : xl + 1;
-            e1 = (float)__ldg(m0 + xl);
-            e2 = (float)__ldg(m1 + xl);
-            e3 = (float)__ldg(m0 + xu);
-            e4 = (float)__ldg(m1 + xu);
-            t = xlast ? (ylast ? 3u : 1u) : (ylast ? 2u : 0u);  // C / NR / NB / interior, gainmapmath.cpp:710-716
+          for (int i = 0; i < 4; i++) f[rr * 4 + i] = ex2_fast(fmaf((float)((mwrd >> (8 * i)) & 0xff), p.Aq, p.Bq));
+        }
+      } else if (SCALE == 2 && patch) {  // cell row qr of the block; pixel (rr, i): cell column i >> 1, offsets (rr, i & 1)
+#pragma unroll
+        for (int rr = 0; rr < 2; rr++)
+#pragma unroll
+          for (int i = 0; i < 4; i++) {
+            const int cxi = i >> 1, ox = i & 1;
+            const float e1 = P2[qr][cxi], e2 = P2[qr + 1][cxi], e3 = P2[qr][cxi + 1], e4 = P2[qr + 1][cxi + 1];
+            float gain = e1;  // offsets (0,0): e1 * 1 + e2 * 0 + e3 * 0 + e4 * 0
+            if (rr | ox) {
+              const float* w = p.w2[rr * 2 + ox];
+              gain = e1 * w[0];
+              gain = fmaf(e2, w[1], gain);
+              gain = fmaf(e3, w[2], gain);
+              gain = fmaf(e4, w[3], gain);
+            }
+            f[rr * 4 + i] = ex2_fast(fmaf(gain, p.Aq, p.Bq));
           }
-          const float4 w = __ldg(wrow + t * ss + ox);
-          float gain = e1 * w.x;
-          gain = fmaf(e2, w.y, gain);
-          gain = fmaf(e3, w.z, gain);
-          gain = fmaf(e4, w.w, gain);
-          f[rr * 4 + i] = ex2_fast(fmaf(gain, p.Aq, p.Bq));
-          if (++ox == sc) {
-            ox = 0;
-            xl++;
+      } else {
+#pragma unroll
+        for (int rr = 0; rr < 2; rr++) {
+          const uint32_t y = 4u * by + 2u * qr + rr, yl = div_s(y), oy = y - yl * sc;
+          const bool ylast = yl + 1 >= mh;  // y_upper = min(y_lower + 1, height - 1)
+          const uint8_t* m0 = map + yl * mw;
+          const uint8_t* m1 = ylast ? m0 : m0 + mw;
+          const float4* wrow = idw + oy * sc;
+          uint32_t xl = xl0, ox = ox0, t = 0;
+          float e1 = 0.f, e2 = 0.f, e3 = 0.f, e4 = 0.f;
+#pragma unroll
+          for (int i = 0; i < 4; i++) {
+            if (i == 0 || ox == 0) {  // first pixel of the row segment or of a new map cell
+              const bool xlast = xl + 1 >= mw;
+              const uint32_t xu = xlast ? xl : xl + 1;
+              e1 = (float)__ldg(m0 + xl);
+              e2 = (float)__ldg(m1 + xl);
+              e3 = (float)__ldg(m0 + xu);
+              e4 = (float)__ldg(m1 + xu);
+              t = xlast ? (ylast ? 3u : 1u) : (ylast ? 2u : 0u);  // C / NR / NB / interior, gainmapmath.cpp:710-716
+            }
+            const float4 w = __ldg(wrow + t * ss + ox);
+            float gain = e1 * w.x;
+            gain = fmaf(e2, w.y, gain);
+            gain = fmaf(e3, w.z, gain);
+            gain = fmaf(e4, w.w, gain);
+            f[rr * 4 + i] = ex2_fast(fmaf(gain, p.Aq, p.Bq));
+            if (++ox == sc) {
+              ox = 0;
+              xl++;
+            }
           }
         }
       }
@@ -1076,7 +1121,7 @@ cudaError_t launch_q(const ApplyFastParams& p, cudaStream_t s) {
   return p.batch ? launch_q<PACK, MASK, true, false, false, 4>(p, s) : launch_q<PACK, MASK, false, false, false, 4>(p, s);
 }
 
-template <int PACK, bool MASK, bool BATCH, bool LTAB, bool NORM>
+template <int PACK, bool MASK, bool BATCH, bool LTAB, bool NORM, int SCALE>
 cudaError_t launch_qs(const ApplyFastParams& p0, cudaStream_t s) {
   static int sms_of[64], per_sm_of[64], smem_of[64];
   int dev = 0;
@@ -1088,30 +1133,39 @@ cudaError_t launch_qs(const ApplyFastParams& p0, cudaStream_t s) {
     cudaFuncAttributes fa;
     if ((e = cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev)) != cudaSuccess) return e;
     if ((e = cudaDeviceGetAttribute(&reserved, cudaDevAttrReservedSharedMemoryPerBlock, dev)) != cudaSuccess) return e;
-    if ((e = cudaFuncGetAttributes(&fa, apply_qs_kernel<PACK, MASK, BATCH, LTAB, NORM>)) != cudaSuccess) return e;
+    if ((e = cudaFuncGetAttributes(&fa, apply_qs_kernel<PACK, MASK, BATCH, LTAB, NORM, SCALE>)) != cudaSuccess) return e;
     const uint32_t dyn0 = (uint32_t)reserved + (uint32_t)fa.sharedSizeBytes;
     const int smem = LTAB ? 16 + (int)(kLEntries * sizeof(float2))
                           : (PACK == kPack1010102 ? (int)(q_table_addr(dyn0) - dyn0 + kPEntries * sizeof(float2)) + 64 : 0);
-    if ((e = cudaFuncSetAttribute(apply_qs_kernel<PACK, MASK, BATCH, LTAB, NORM>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)) != cudaSuccess) return e;
-    if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, apply_qs_kernel<PACK, MASK, BATCH, LTAB, NORM>, kThreads, smem)) != cudaSuccess) return e;
+    if ((e = cudaFuncSetAttribute(apply_qs_kernel<PACK, MASK, BATCH, LTAB, NORM, SCALE>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)) != cudaSuccess) return e;
+    if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, apply_qs_kernel<PACK, MASK, BATCH, LTAB, NORM, SCALE>, kThreads, smem)) != cudaSuccess) return e;
     sms_of[dev] = n_sm;
     smem_of[dev] = smem;
     per_sm_of[dev] = n > 0 ? n : 1;
   }
   const int cap = sms_of[dev] * per_sm_of[dev];
   const int grid = p0.n_tiles < cap ? p0.n_tiles : cap;
-  apply_qs_kernel<PACK, MASK, BATCH, LTAB, NORM><<<grid, kThreads, (size_t)smem_of[dev], s>>>(p0);
+  apply_qs_kernel<PACK, MASK, BATCH, LTAB, NORM, SCALE><<<grid, kThreads, (size_t)smem_of[dev], s>>>(p0);
   return cudaGetLastError();
 }
 
-template <int PACK, bool MASK>
+template <int PACK, bool MASK, int SCALE>
 cudaError_t launch_qs(const ApplyFastParams& p, cudaStream_t s) {
   constexpr bool kLin = PACK != kPack1010102;
   if (kLin && p.lin_table_ok) {
     constexpr bool kNorm = PACK == kPackF16;
-    return p.batch ? launch_qs<PACK, MASK, true, kLin, kNorm>(p, s) : launch_qs<PACK, MASK, false, kLin, kNorm>(p, s);
+    return p.batch ? launch_qs<PACK, MASK, true, kLin, kNorm, SCALE>(p, s) : launch_qs<PACK, MASK, false, kLin, kNorm, SCALE>(p, s);
   }
-  return p.batch ? launch_qs<PACK, MASK, true, false, false>(p, s) : launch_qs<PACK, MASK, false, false, false>(p, s);
+  return p.batch ? launch_qs<PACK, MASK, true, false, false, SCALE>(p, s) : launch_qs<PACK, MASK, false, false, false, SCALE>(p, s);
+}
+
+template <int PACK, bool MASK>
+cudaError_t launch_qs(const ApplyFastParams& p, cudaStream_t s) {
+  switch (p.scale_special) {  // 1 / 2 when the map planes are aligned for the specialised loads (capi.cu)
+    case 1: return launch_qs<PACK, MASK, 1>(p, s);
+    case 2: return launch_qs<PACK, MASK, 2>(p, s);
+    default: return launch_qs<PACK, MASK, 0>(p, s);
+  }
 }
 
 }  // namespace

@@ -472,6 +472,12 @@ int apply_core(int n, const uhdrb200_image* sdr, const uhdrb200_image* map, cons
     f.q0 = (float)ldexp(1.0, kPLoExp);
     f.two_table = g_apply_mode == 2;
     f.any_scale = any_scale ? 1 : 0;
+    if (any_scale && (p.g.map_scale == 1 || p.g.map_scale == 2)) {
+      bool al = true;  // the specialised kernels read the map as 32-bit (scale 1) / 16-bit (scale 2) words
+      for (int i = 0; i < n; i++) al = al && (reinterpret_cast<uintptr_t>(v[i].map_in) % (p.g.map_scale == 1 ? 4 : 2)) == 0;
+      if (al) f.scale_special = p.g.map_scale;
+      idw_fill(&f.w2[0][0], 2, 1, 1);
+    }
     // linear outputs: every non-toe channel has Phi > 0.0904, so q >= 0.0904 * f'min must reach the L table's first
     // octave, and q^2.4 must be a normal half with margin (the F16 kernel then skips the subnormal/flush checks)
     {

@@ -117,6 +117,8 @@ struct ApplyFastParams {
   int lin_table_ok;        // 1: q = Phi * f' stays inside the L table for every non-toe channel (host check)
   int any_scale;           // 1: apply_qs_kernel (any integer map scale factor, thread = 4x4 pixels) instead of the scale-4 kernels
   uint32_t scale_magic;    // ceil(2^32 / map_scale), 0 for scale 1 (set by launch_apply_fast_impl)
+  int scale_special;       // 1 / 2: compile-time specialisation of apply_qs_kernel (map planes aligned to 4 / 2 bytes), else 0
+  float w2[4][4];          // ShepardsIDW::mWeights of scale 2, [oy * 2 + ox][k]
   // Aq x interior IDW weights of corners 2..4 (they include the 1/255 of the map samples), [corner - 2][oy * 4 + ox]:
   // horizontally adjacent pixels are one 8-byte pair for FFMA2
   alignas(8) float wq[3][16];
