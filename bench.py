@@ -505,6 +505,35 @@ def main():
     h2d = E * (sdr_len + hdr_len * 2 + sdr_len + MW * MH)  # generate: SDR+HDR planes; apply: SDR planes + map
     d2h = E * (MW * MH + PIX * 4)
 
+    # what the PCIe link of this box gives (rank 0, N = 1): pinned <-> device copies of 256 MB alone and in both directions
+    # at once, in the e2e traffic ratio. The e2e rate is judged against these, not against HBM.
+    pcie = None
+    if world == 1 and not a.no_e2e:
+        nb = 256 << 20
+        h_a = torch.empty(nb, dtype=torch.uint8).pin_memory()
+        h_b = torch.empty(nb, dtype=torch.uint8).pin_memory()
+        d_a = torch.empty(nb, dtype=torch.uint8, device=dev)
+        d_b = torch.empty(nb, dtype=torch.uint8, device=dev)
+        s1, s2 = torch.cuda.Stream(), torch.cuda.Stream()
+
+        def copy_rate(up, down, reps=4):
+            torch.cuda.synchronize()
+            t = time.perf_counter()
+            for _ in range(reps):
+                if up:
+                    with torch.cuda.stream(s1):
+                        d_a.copy_(h_a, non_blocking=True)
+                if down:
+                    with torch.cuda.stream(s2):
+                        h_b.copy_(d_b, non_blocking=True)
+            torch.cuda.synchronize()
+            return reps * nb / (time.perf_counter() - t) / 1e9
+
+        copy_rate(True, True, 1)
+        pcie = {"h2d_alone_gbs": copy_rate(True, False), "d2h_alone_gbs": copy_rate(False, True),
+                "each_direction_when_both_gbs": copy_rate(True, True)}
+        del h_a, h_b, d_a, d_b
+
     times = torch.tensor([total_ms, e2e_s * 1e3, gen_ms, app_ms], dtype=torch.float64, device=dev)
     if dist is not None:
         dist.all_reduce(times, op=dist.ReduceOp.MAX)
@@ -554,12 +583,16 @@ def main():
         "stage_mpix_s": {"generate": B * PIX / gen_ms / 1e3, "apply": B * PIX / app_ms / 1e3},
         "e2e": {"value": world * E * PIX * e2e_steps / (e2e_ms * 1e-3) / 1e6 if e2e_steps else None, "unit": UNIT, "h2d_bytes_per_step": h2d,
                 "d2h_bytes_per_step": d2h, "images_per_step_per_gpu": E, "steps": e2e_steps,
-                "host_threads": T, "join": "blocking" if blocking else "spin",
+                "host_threads": T, "join": "blocking" if blocking else "spin", "pcie_measured": pcie,
                 "api": "uhdrb200_generate_gainmap_host_into + uhdrb200_apply_gainmap_host (synchronous, reference-style), pinned host planes"},
         "other_stages": {k: dict(v, frac_of_hbm_peak=v["achieved_gbs"] / peak) for k, v in other.items()},
         "gpu_launches": int(launches),
         "clocks": clk,
     }
+    if out["e2e"]["value"]:
+        ips = out["e2e"]["value"] * 1e6 / PIX / world  # images per second per GPU
+        out["e2e"]["h2d_gbs_per_gpu"] = ips * h2d / E / 1e9
+        out["e2e"]["d2h_gbs_per_gpu"] = ips * d2h / E / 1e9
     if cpu_info:
         out["cpu_baseline"] = cpu_info
     print(json.dumps(out))
