@@ -186,7 +186,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--batch", type=int, default=256, help="4K pairs per step per GPU (device-resident)")
-    ap.add_argument("--e2e-images", type=int, default=16, help="4K pairs per e2e step per GPU (host planes)")
+    ap.add_argument("--e2e-images", type=int, default=64, help="4K pairs per e2e step per GPU (host planes)")
     ap.add_argument("--e2e-threads", type=int, default=4, help="host threads calling the synchronous host-pointer API concurrently")
     ap.add_argument("--e2e-join", default="auto", choices=["auto", "spin", "blocking"], help="how the host entry points wait (uhdrb200_set_sync_mode)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
