@@ -36,6 +36,10 @@ namespace {
 #define UHDR_APPLY_MIN_BLOCKS 3
 #endif
 constexpr int kThreads = 256;
+#ifndef UHDR_APPLYQ_THREADS
+#define UHDR_APPLYQ_THREADS 256
+#endif
+constexpr int kQThreads = UHDR_APPLYQ_THREADS;  // block size of apply_q_kernel (its tile is kQThreads / 32 warps x CELLS cell rows tall)
 constexpr int kTileCellsX = 32, kTileCellsY = 8;
 
 enum { kPack1010102 = 0, kPackF16 = 1, kPackPlanar10 = 2 };
@@ -737,8 +741,8 @@ __device__ __forceinline__ void quad_row_eval(const uint32_t hiP, const uint32_t
 // the upper pair of the next (2 map loads per cell) and every plane pointer advances by a constant.
 // CELLS = 8 for large batches (fewer tile prologues: 740 vs 728 Gpix/s), 4 otherwise (more tiles to balance).
 template <int PACK, bool MASK, bool BATCH, bool LTAB, bool NORM, int CELLS>
-__global__ void __launch_bounds__(kThreads, LTAB ? UHDR_APPLYQ_L_MIN_BLOCKS : UHDR_APPLYQ_MIN_BLOCKS) apply_q_kernel(const __grid_constant__ ApplyFastParams p) {
-  constexpr int kQCells = CELLS, kQTileRows = 8 * CELLS;  // cell rows per tile: 8 warps x CELLS
+__global__ void __launch_bounds__(kQThreads, LTAB ? UHDR_APPLYQ_L_MIN_BLOCKS : UHDR_APPLYQ_MIN_BLOCKS) apply_q_kernel(const __grid_constant__ ApplyFastParams p) {
+  constexpr int kQCells = CELLS, kQTileRows = (kQThreads / 32) * CELLS;  // cell rows per tile: warps x CELLS
   const int tid = threadIdx.x;
   const uint32_t hiP = stage_q_table<PACK, LTAB>(p, tid);
 
@@ -1075,7 +1079,7 @@ cudaError_t launch(const ApplyFastParams& p, cudaStream_t s) {
 
 template <int PACK, bool MASK, bool BATCH, bool LTAB, bool NORM, int CELLS>
 cudaError_t launch_q(const ApplyFastParams& p0, cudaStream_t s) {
-  constexpr int kQTileRows = 8 * CELLS;
+  constexpr int kQTileRows = (kQThreads / 32) * CELLS;
   static int sms_of[64], per_sm_of[64], smem_of[64];
   int dev = 0;
   cudaError_t e = cudaGetDevice(&dev);
@@ -1091,7 +1095,7 @@ cudaError_t launch_q(const ApplyFastParams& p0, cudaStream_t s) {
     const int smem = LTAB ? 16 + (int)(kLEntries * sizeof(float2))
                           : (PACK == kPack1010102 ? (int)(q_table_addr(dyn0) - dyn0 + kPEntries * sizeof(float2)) + 64 : 0);  // + slack for the base alignment
     if ((e = cudaFuncSetAttribute(apply_q_kernel<PACK, MASK, BATCH, LTAB, NORM, CELLS>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)) != cudaSuccess) return e;
-    if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, apply_q_kernel<PACK, MASK, BATCH, LTAB, NORM, CELLS>, kThreads, smem)) != cudaSuccess) return e;
+    if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, apply_q_kernel<PACK, MASK, BATCH, LTAB, NORM, CELLS>, kQThreads, smem)) != cudaSuccess) return e;
     sms_of[dev] = n_sm;
     smem_of[dev] = smem;
     per_sm_of[dev] = n > 0 ? n : 1;
@@ -1102,7 +1106,7 @@ cudaError_t launch_q(const ApplyFastParams& p0, cudaStream_t s) {
   p.n_tiles = p.tiles_x * p.tiles_y * n_img;
   const int cap = sms_of[dev] * per_sm_of[dev];
   const int grid = p.n_tiles < cap ? p.n_tiles : cap;
-  apply_q_kernel<PACK, MASK, BATCH, LTAB, NORM, CELLS><<<grid, kThreads, (size_t)smem_of[dev], s>>>(p);
+  apply_q_kernel<PACK, MASK, BATCH, LTAB, NORM, CELLS><<<grid, kQThreads, (size_t)smem_of[dev], s>>>(p);
   return cudaGetLastError();
 }
 
