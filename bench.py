@@ -333,7 +333,7 @@ def main():
     # ---- the other kernels of the path (not part of `value`): per-kernel roofline on the same batch, rank 0 only
     other = {}
     if rank == 0 and not a.no_other_stages:
-        Bo = min(B, 32)
+        Bo = min(B, 64)
         d_tm = torch.zeros((Bo, sdr_len), dtype=torch.uint8, device=dev)
         tms = (abi.Image * Bo)()
         for i in range(Bo):
@@ -347,7 +347,7 @@ def main():
             bigs[i].data = d_big[i].data_ptr()
         md_pq = abi.default_metadata(10000.0 / 203.0)
 
-        def timed(fn, bpp, iters=5):
+        def timed(fn, bpp, iters=8):
             if a.profile_once:
                 iters = 1
             for _ in range(0 if a.profile_once else 2):
