@@ -189,6 +189,8 @@ def main():
     ap.add_argument("--e2e-images", type=int, default=64, help="4K pairs per e2e step per GPU (host planes)")
     ap.add_argument("--e2e-threads", type=int, default=4, help="host threads calling the synchronous host-pointer API concurrently")
     ap.add_argument("--e2e-join", default="auto", choices=["auto", "spin", "blocking"], help="how the host entry points wait (uhdrb200_set_sync_mode)")
+    ap.add_argument("--e2e-host-memory", default="pinned", choices=["pinned", "pageable"],
+                    help="host planes of the e2e leg: uhdrb200_host_alloc (page-locked) or plain malloc'ed numpy buffers")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-other-stages", action="store_true", help="skip the per-kernel rooflines of the other stages")
     ap.add_argument("--cpu-images", type=int, default=24, help="images per CPU worker process in the CPU arms")
@@ -448,24 +450,37 @@ def main():
     # ---- e2e: host planes -> C ABI host entry points -> host results (copies inside the timing)
     E = a.e2e_images
     KH = max(4, a.e2e_threads)  # one private set of pinned buffers per in-flight image
-    host_bufs = []
-    for i in range(KH):
-        ps = lib.uhdrb200_host_alloc(sdr_len)
-        ph = lib.uhdrb200_host_alloc(hdr_len * 2)
-        po = lib.uhdrb200_host_alloc(PIX * 4)
-        pm = lib.uhdrb200_host_alloc(MW * MH)
-        assert ps and ph and po and pm, "pinned allocation failed"
-        C.memmove(ps, pairs[i % K][0].ctypes.data, sdr_len)
-        C.memmove(ph, pairs[i % K][1].ctypes.data, hdr_len * 2)
-        s_img, h_img, m_img, o_img = abi.Image(), abi.Image(), abi.Image(), abi.Image()
-        s_img.data, s_img.chroma_data = ps, ps + W * H
-        s_img.width, s_img.height, s_img.colorGamut = W, H, abi.COLORGAMUT_BT709
-        s_img.luma_stride, s_img.chroma_stride, s_img.pixelFormat = W, W // 2, abi.PIX_FMT_YUV420
-        h_img.data, h_img.chroma_data = ph, ph + 2 * W * H
-        h_img.width, h_img.height, h_img.colorGamut = W, H, abi.COLORGAMUT_BT2100
-        h_img.luma_stride, h_img.chroma_stride, h_img.pixelFormat = W, W, abi.PIX_FMT_P010
-        o_img.data = po
-        host_bufs.append((s_img, h_img, m_img, o_img, pm))
+    pageable_keep = []
+
+    def make_bufs(kind):
+        bufs = []
+        for i in range(KH):
+            if kind == "pinned":
+                ps = lib.uhdrb200_host_alloc(sdr_len)
+                ph = lib.uhdrb200_host_alloc(hdr_len * 2)
+                po = lib.uhdrb200_host_alloc(PIX * 4)
+                pm = lib.uhdrb200_host_alloc(MW * MH)
+                assert ps and ph and po and pm, "pinned allocation failed"
+            else:  # what an unmodified libultrahdr caller passes: pageable memory
+                keep = [np.empty(n, dtype=np.uint8) for n in (sdr_len, hdr_len * 2, PIX * 4, MW * MH)]
+                for k in keep:
+                    k[:] = 0  # touch the pages
+                pageable_keep.append(keep)
+                ps, ph, po, pm = (k.ctypes.data for k in keep)
+            C.memmove(ps, pairs[i % K][0].ctypes.data, sdr_len)
+            C.memmove(ph, pairs[i % K][1].ctypes.data, hdr_len * 2)
+            s_img, h_img, m_img, o_img = abi.Image(), abi.Image(), abi.Image(), abi.Image()
+            s_img.data, s_img.chroma_data = ps, ps + W * H
+            s_img.width, s_img.height, s_img.colorGamut = W, H, abi.COLORGAMUT_BT709
+            s_img.luma_stride, s_img.chroma_stride, s_img.pixelFormat = W, W // 2, abi.PIX_FMT_YUV420
+            h_img.data, h_img.chroma_data = ph, ph + 2 * W * H
+            h_img.width, h_img.height, h_img.colorGamut = W, H, abi.COLORGAMUT_BT2100
+            h_img.luma_stride, h_img.chroma_stride, h_img.pixelFormat = W, W, abi.PIX_FMT_P010
+            o_img.data = po
+            bufs.append((s_img, h_img, m_img, o_img, pm))
+        return bufs
+
+    host_bufs = make_bufs(a.e2e_host_memory)
 
     # Each host thread owns a CUDA stream + staging buffers inside the library (thread-local context), so T
     # threads calling the synchronous reference-style entry points overlap H2D, kernels and D2H of different
@@ -478,8 +493,10 @@ def main():
     assert lib.uhdrb200_set_sync_mode(abi.SYNC_BLOCKING if blocking else abi.SYNC_SPIN) == 0
     pool = cf.ThreadPoolExecutor(T, initializer=lambda: lib.uhdrb200_init(local))
 
+    cur_bufs = [host_bufs]
+
     def e2e_one(i):
-        s_img, h_img, m_img, o_img, pm = host_bufs[i % KH]
+        s_img, h_img, m_img, o_img, pm = cur_bufs[0][i % KH]
         mdh, m_loc = abi.Metadata(), abi.Image()
         st = lib.uhdrb200_generate_gainmap_host_into(C.byref(s_img), C.byref(h_img), abi.TF_HLG, C.byref(mdh),
                                                      C.byref(m_loc), 0, pm, MW * MH)
@@ -504,6 +521,17 @@ def main():
     e2e_s = time.perf_counter() - te0
     h2d = E * (sdr_len + hdr_len * 2 + sdr_len + MW * MH)  # generate: SDR+HDR planes; apply: SDR planes + map
     d2h = E * (MW * MH + PIX * 4)
+    # the same leg with pageable planes (what an unmodified libultrahdr caller passes): the library stages them through
+    # per-thread page-locked chunks (capi.cu copy_h2d / copy_d2h). Reported beside the pinned number, N = 1 only.
+    pageable_mpix = None
+    if world == 1 and not a.no_e2e and a.e2e_host_memory == "pinned":
+        cur_bufs[0] = make_bufs("pageable")
+        e2e_step()
+        tp0 = time.perf_counter()
+        for _ in range(2):
+            e2e_step()
+        pageable_mpix = 2 * E * PIX / (time.perf_counter() - tp0) / 1e6
+        cur_bufs[0] = host_bufs
 
     # what the PCIe link of this box gives (rank 0, N = 1): pinned <-> device copies of 256 MB alone and in both directions
     # at once, in the e2e traffic ratio. The e2e rate is judged against these, not against HBM.
@@ -583,7 +611,7 @@ def main():
         "stage_mpix_s": {"generate": B * PIX / gen_ms / 1e3, "apply": B * PIX / app_ms / 1e3},
         "e2e": {"value": world * E * PIX * e2e_steps / (e2e_ms * 1e-3) / 1e6 if e2e_steps else None, "unit": UNIT, "h2d_bytes_per_step": h2d,
                 "d2h_bytes_per_step": d2h, "images_per_step_per_gpu": E, "steps": e2e_steps,
-                "host_threads": T, "join": "blocking" if blocking else "spin", "pcie_measured": pcie,
+                "host_threads": T, "join": "blocking" if blocking else "spin", "pcie_measured": pcie, "host_memory": a.e2e_host_memory, "pageable_callers_mpix_s": pageable_mpix,
                 "api": "uhdrb200_generate_gainmap_host_into + uhdrb200_apply_gainmap_host (synchronous, reference-style), pinned host planes"},
         "other_stages": {k: dict(v, frac_of_hbm_peak=v["achieved_gbs"] / peak) for k, v in other.items()},
         "gpu_launches": int(launches),

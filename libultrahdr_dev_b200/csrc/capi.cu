@@ -43,6 +43,13 @@ struct Ctx {
   bool ready = false;
   cudaStream_t stream = nullptr;
   cudaEvent_t sync_ev = nullptr;  // cudaEventBlockingSync: the joining host thread sleeps instead of spinning
+  // page-locked staging chunks for callers that pass pageable planes (what an unmodified libultrahdr caller does)
+  static constexpr int kSlots = 4;
+  static constexpr size_t kChunk = size_t(4) << 20;
+  uint8_t* pin[kSlots] = {nullptr, nullptr, nullptr, nullptr};
+  cudaEvent_t pin_ev[kSlots] = {nullptr, nullptr, nullptr, nullptr};
+  bool pin_busy[kSlots] = {false, false, false, false};
+  int pin_next = 0;
   DevBuf buf[8];  // staging planes of the *_host entry points
   BatchSlot ring[kRing];
   int ring_next = 0;
@@ -103,6 +110,82 @@ cudaError_t join_stream(Ctx& c) {
   cudaError_t e = cudaEventRecord(c.sync_ev, c.stream);
   if (e != cudaSuccess) return e;
   return cudaEventSynchronize(c.sync_ev);
+}
+
+// ---- host <-> device copies of the *_host entry points -------------------------------------------------------------
+// Page-locked caller memory (uhdrb200_host_alloc, cudaHostRegister) is handed to the copy engine as it is. Pageable
+// memory (plain malloc / new, what JpegR passes) would make cudaMemcpyAsync stage through the driver's single bounce
+// buffer under a lock shared by all threads (measured 11 GB/s for 4 calling threads); instead every calling thread
+// owns kSlots page-locked chunks and overlaps its own memcpy into / out of them with the DMA of the previous chunk.
+bool is_pageable(const void* p) {
+  cudaPointerAttributes a;
+  if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+    cudaGetLastError();
+    return true;
+  }
+  return a.type == cudaMemoryTypeUnregistered;
+}
+int ensure_pins(Ctx& c) {
+  if (c.pin[0]) return 0;
+  for (int i = 0; i < Ctx::kSlots; i++) {
+    CU(cudaHostAlloc((void**)&c.pin[i], Ctx::kChunk, cudaHostAllocDefault));
+    CU(cudaEventCreateWithFlags(&c.pin_ev[i], cudaEventDisableTiming));
+    c.pin_busy[i] = false;
+  }
+  return 0;
+}
+int copy_h2d(Ctx& c, void* dst, const void* src, size_t bytes) {
+  if (!bytes) return 0;
+  if (!is_pageable(src)) {
+    CU(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, c.stream));
+    return 0;
+  }
+  int st = ensure_pins(c);
+  if (st) return st;
+  for (size_t off = 0; off < bytes; off += Ctx::kChunk) {
+    const size_t n = bytes - off < Ctx::kChunk ? bytes - off : Ctx::kChunk;
+    const int k = c.pin_next;
+    c.pin_next = (k + 1) % Ctx::kSlots;
+    if (c.pin_busy[k]) CU(cudaEventSynchronize(c.pin_ev[k]));  // the chunk's previous DMA has drained
+    memcpy(c.pin[k], (const uint8_t*)src + off, n);
+    CU(cudaMemcpyAsync((uint8_t*)dst + off, c.pin[k], n, cudaMemcpyHostToDevice, c.stream));
+    CU(cudaEventRecord(c.pin_ev[k], c.stream));
+    c.pin_busy[k] = true;
+  }
+  return 0;
+}
+// On return from the pageable path the bytes are in dst; the page-locked path only enqueues (the caller joins the stream).
+int copy_d2h(Ctx& c, void* dst, const void* src, size_t bytes) {
+  if (!bytes) return 0;
+  if (!is_pageable(dst)) {
+    CU(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, c.stream));
+    return 0;
+  }
+  int st = ensure_pins(c);
+  if (st) return st;
+  const size_t nchunks = (bytes + Ctx::kChunk - 1) / Ctx::kChunk;
+  size_t issued = 0, done = 0;
+  int slot_of[Ctx::kSlots];
+  while (done < nchunks) {
+    while (issued < nchunks && issued - done < (size_t)Ctx::kSlots) {
+      const int k = c.pin_next;
+      c.pin_next = (k + 1) % Ctx::kSlots;
+      if (c.pin_busy[k]) CU(cudaEventSynchronize(c.pin_ev[k]));
+      const size_t off = issued * Ctx::kChunk, n = bytes - off < Ctx::kChunk ? bytes - off : Ctx::kChunk;
+      CU(cudaMemcpyAsync(c.pin[k], (const uint8_t*)src + off, n, cudaMemcpyDeviceToHost, c.stream));
+      CU(cudaEventRecord(c.pin_ev[k], c.stream));
+      c.pin_busy[k] = true;
+      slot_of[issued % Ctx::kSlots] = k;
+      issued++;
+    }
+    const int k = slot_of[done % Ctx::kSlots];
+    const size_t off = done * Ctx::kChunk, n = bytes - off < Ctx::kChunk ? bytes - off : Ctx::kChunk;
+    CU(cudaEventSynchronize(c.pin_ev[k]));
+    memcpy((uint8_t*)dst + off, c.pin[k], n);
+    c.pin_busy[k] = false;
+    done++;
+  }
+  return 0;
 }
 
 int reserve(DevBuf& b, size_t bytes) {
@@ -702,8 +785,8 @@ size_t p010_chroma_bytes(const uhdrb200_image& im) {
 int upload(DevBuf& b, const void* host, size_t bytes, cudaStream_t s) {
   int st = reserve(b, bytes ? bytes : 1);
   if (st) return st;
-  if (bytes) CU(cudaMemcpyAsync(b.p, host, bytes, cudaMemcpyHostToDevice, s));
-  return 0;
+  (void)s;  // always the calling thread's stream
+  return copy_h2d(t_ctx, b.p, host, bytes);
 }
 
 int generate_host(const uhdrb200_image* sdr, const uhdrb200_image* hdr, int hdr_tf, uhdrb200_metadata* md,
@@ -727,11 +810,11 @@ int generate_host(const uhdrb200_image* sdr, const uhdrb200_image* hdr, int hdr_
   if ((st = generate_core(1, &dsdr, &dhdr, hdr_tf, md, &ddst, sdr_is_601, c.stream))) return st;
   void* out = own_alloc ? malloc(mbytes ? mbytes : 1) : map_buf;
   if (!out) return UHDRB200_ERROR_INSUFFICIENT_RESOURCE;
-  cudaError_t e = mbytes ? cudaMemcpyAsync(out, c.buf[4].p, mbytes, cudaMemcpyDeviceToHost, c.stream) : cudaSuccess;
-  if (e == cudaSuccess) e = join_stream(c);
+  st = copy_d2h(c, out, c.buf[4].p, mbytes);
+  cudaError_t e = st ? cudaErrorUnknown : join_stream(c);
   if (e != cudaSuccess) {
     if (own_alloc) free(out);
-    return fail(e, "generateGainMap device->host");
+    return st ? st : fail(e, "generateGainMap device->host");
   }
   fill_map_desc(dest, mw, mh);
   dest->data = out;
@@ -769,7 +852,7 @@ int apply_host(const uhdrb200_image* sdr, const uhdrb200_image* map, const uhdrb
   dmap.data = c.buf[5].p;
   ddst.data = c.buf[4].p;
   if ((st = apply_core(1, &dsdr, &dmap, md, fmt, max_display_boost, &ddst, c.stream))) return st;
-  CU(cudaMemcpyAsync(dest->data, c.buf[4].p, obytes, cudaMemcpyDeviceToHost, c.stream));
+  if ((st = copy_d2h(c, dest->data, c.buf[4].p, obytes))) return st;
   CU(join_stream(c));
   dest->width = sdr->width; dest->height = sdr->height; dest->colorGamut = sdr->colorGamut;
   return UHDRB200_NO_ERROR;
@@ -792,8 +875,8 @@ int tonemap_host(const uhdrb200_image* src, uhdrb200_image* dest) {
   dd.data = c.buf[6].p; dd.chroma_data = c.buf[7].p;
   if ((st = tonemap_core(1, &s2, &dd, c.stream))) return st;
   // stride tails of the last rows are part of the reference's writes (memset to the stride)
-  if (dl) CU(cudaMemcpyAsync(dest->data, c.buf[6].p, dl, cudaMemcpyDeviceToHost, c.stream));
-  if (dc) CU(cudaMemcpyAsync(dest->chroma_data, c.buf[7].p, dc, cudaMemcpyDeviceToHost, c.stream));
+  if ((st = copy_d2h(c, dest->data, c.buf[6].p, dl))) return st;
+  if ((st = copy_d2h(c, dest->chroma_data, c.buf[7].p, dc))) return st;
   CU(join_stream(c));
   dest->colorGamut = src->colorGamut;
   return UHDRB200_NO_ERROR;
@@ -815,8 +898,8 @@ int convert_yuv_host(uhdrb200_image* im, int src_enc, int dst_enc) {
   uhdrb200_image d = *im;
   d.data = c.buf[0].p; d.chroma_data = c.buf[1].p;
   if ((st = convert_yuv_core(&d, src_enc, dst_enc, c.stream))) return st;
-  if (lb) CU(cudaMemcpyAsync(im->data, c.buf[0].p, lb, cudaMemcpyDeviceToHost, c.stream));
-  if (cb) CU(cudaMemcpyAsync(im->chroma_data, c.buf[1].p, cb, cudaMemcpyDeviceToHost, c.stream));
+  if ((st = copy_d2h(c, im->data, c.buf[0].p, lb))) return st;
+  if ((st = copy_d2h(c, im->chroma_data, c.buf[1].p, cb))) return st;
   CU(join_stream(c));
   return UHDRB200_NO_ERROR;
 }
@@ -838,7 +921,7 @@ int sdr_pack_host(const uhdrb200_image* sdr, uhdrb200_image* dest) {
   d2.data = c.buf[6].p;
   if ((st = sdr_pack_core(1, &s2, &d2, c.stream))) return st;
   if (os == sdr->width) {
-    if (ob) CU(cudaMemcpyAsync(dest->data, c.buf[6].p, ob, cudaMemcpyDeviceToHost, c.stream));
+    if ((st = copy_d2h(c, dest->data, c.buf[6].p, ob))) return st;
   } else if (ob) {  // only the pixels: bytes between width and the stride stay the caller's
     CU(cudaMemcpy2DAsync(dest->data, os * 4, c.buf[6].p, os * 4, sdr->width * 4, sdr->height, cudaMemcpyDeviceToHost, c.stream));
   }
@@ -866,8 +949,8 @@ int copy_yuv420_host(const uhdrb200_image* src, uhdrb200_image* dst) {
   s2.data = c.buf[0].p; s2.chroma_data = c.buf[1].p;
   d2.data = c.buf[6].p; d2.chroma_data = c.buf[7].p;
   if ((st = copy_yuv420_core(&s2, &d2, c.stream))) return st;
-  if (dl) CU(cudaMemcpyAsync(dst->data, c.buf[6].p, dl, cudaMemcpyDeviceToHost, c.stream));
-  if (dc) CU(cudaMemcpyAsync(dst->chroma_data, c.buf[7].p, dc, cudaMemcpyDeviceToHost, c.stream));
+  if ((st = copy_d2h(c, dst->data, c.buf[6].p, dl))) return st;
+  if ((st = copy_d2h(c, dst->chroma_data, c.buf[7].p, dc))) return st;
   CU(join_stream(c));
   dst->width = src->width;
   dst->height = src->height;
@@ -897,9 +980,9 @@ int api0_host(const uhdrb200_image* hdr, int hdr_tf, int sdr_to_601, uhdrb200_im
   ds.data = c.buf[6].p; ds.chroma_data = c.buf[7].p;
   dm.data = c.buf[4].p;
   if ((st = api0_core(1, &dh, hdr_tf, sdr_to_601, &ds, md, &dm, c.stream))) return st;
-  if (dl) CU(cudaMemcpyAsync(sdr->data, c.buf[6].p, dl, cudaMemcpyDeviceToHost, c.stream));
-  if (dc) CU(cudaMemcpyAsync(sdr->chroma_data, c.buf[7].p, dc, cudaMemcpyDeviceToHost, c.stream));
-  if (mbytes) CU(cudaMemcpyAsync(map_buf, c.buf[4].p, mbytes, cudaMemcpyDeviceToHost, c.stream));
+  if ((st = copy_d2h(c, sdr->data, c.buf[6].p, dl))) return st;
+  if ((st = copy_d2h(c, sdr->chroma_data, c.buf[7].p, dc))) return st;
+  if ((st = copy_d2h(c, map_buf, c.buf[4].p, mbytes))) return st;
   CU(join_stream(c));
   sdr->colorGamut = hdr->colorGamut;
   fill_map_desc(dest, mw, mh);
@@ -941,6 +1024,13 @@ void uhdrb200_shutdown(void) {
     if (s.dev) cudaFree(s.dev);
     if (s.done) cudaEventDestroy(s.done);
     s = BatchSlot();
+  }
+  for (int i = 0; i < Ctx::kSlots; i++) {
+    if (c.pin[i]) cudaFreeHost(c.pin[i]);
+    if (c.pin_ev[i]) cudaEventDestroy(c.pin_ev[i]);
+    c.pin[i] = nullptr;
+    c.pin_ev[i] = nullptr;
+    c.pin_busy[i] = false;
   }
   cudaStreamDestroy(c.stream);
   if (c.sync_ev) cudaEventDestroy(c.sync_ev);
