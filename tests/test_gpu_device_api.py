@@ -387,3 +387,41 @@ def test_api0_fused_batch_device(uh, torch_cuda):
         assert uh.toneMapGenerateGainMapInto(hh, abi.TF_PQ, abi.host_yuv420(sb, w, h, -1), md, md_desc, mb) == 0
         assert np.array_equal(d_sdr[i].cpu().numpy(), sb) and np.array_equal(d_map[i].cpu().numpy(), mb)
         assert sdrs[i].colorGamut == 2 and mds[i].as_dict() == md.as_dict()
+
+
+# ---------------------------------------------------------------- pageable vs page-locked host planes
+def test_pinned_and_pageable_host_planes_agree(uh):
+    """The host entry points hand page-locked planes to the copy engine directly and stage pageable ones through
+    per-thread 4 MB chunks (capi.cu copy_h2d / copy_d2h): same bytes out, multi-chunk sizes (1080p and 4K planes),
+    including a size that is not a multiple of the chunk."""
+    lib = uh.lib
+    for w, h in ((1920, 1080), (3840, 2160)):
+        sdr_b, hdr_b = synth.uniform_pair(w, h, 77)
+        outs = []
+        for kind in ("pageable", "pinned"):
+            if kind == "pinned":
+                ps, ph = lib.uhdrb200_host_alloc(sdr_b.nbytes), lib.uhdrb200_host_alloc(hdr_b.nbytes)
+                po, pm = lib.uhdrb200_host_alloc(w * h * 4), lib.uhdrb200_host_alloc(w * h // 16)
+                assert ps and ph and po and pm
+                C.memmove(ps, sdr_b.ctypes.data, sdr_b.nbytes)
+                C.memmove(ph, hdr_b.ctypes.data, hdr_b.nbytes)
+            else:
+                keep = [sdr_b.copy(), hdr_b.copy(), np.zeros(w * h * 4, np.uint8), np.zeros(w * h // 16, np.uint8)]
+                ps, ph, po, pm = (k.ctypes.data for k in keep)
+            s_img = abi.host_yuv420(sdr_b, w, h, abi.COLORGAMUT_BT709)
+            h_img = abi.host_p010(hdr_b, w, h, abi.COLORGAMUT_BT2100)
+            s_img.data, s_img.chroma_data = ps, ps + w * h
+            h_img.data, h_img.chroma_data = ph, ph + 2 * w * h
+            md, m_img, o_img = abi.Metadata(), abi.Image(), abi.Image()
+            st = lib.uhdrb200_generate_gainmap_host_into(C.byref(s_img), C.byref(h_img), abi.TF_HLG, C.byref(md), C.byref(m_img), 0, pm, w * h // 16)
+            assert st == 0, lib.uhdrb200_last_error()
+            o_img.data = po
+            st = lib.uhdrb200_apply_gainmap_host(C.byref(s_img), C.byref(m_img), C.byref(md), abi.OUTPUT_HDR_HLG, FLT_MAX, C.byref(o_img))
+            assert st == 0, lib.uhdrb200_last_error()
+            outs.append((np.ctypeslib.as_array(C.cast(pm, C.POINTER(C.c_uint8)), (w * h // 16,)).copy(),
+                         np.ctypeslib.as_array(C.cast(po, C.POINTER(C.c_uint8)), (w * h * 4,)).copy()))
+            if kind == "pinned":
+                for q in (ps, ph, po, pm):
+                    lib.uhdrb200_host_free(q)
+        assert np.array_equal(outs[0][0], outs[1][0]) and np.array_equal(outs[0][1], outs[1][1])
+        assert outs[0][1].any()
