@@ -1,22 +1,27 @@
-// apply_fast.cu — A2 fast path: UltraHdr::applyGainMap (reference lib/src/ultrahdr.cpp:427-496) for
-// the layout every decode produces (map scale factor 4 = kMapDimensionScaleFactor, 4-aligned
-// planes), restructured so that it is bound by instruction issue / HBM instead of the SFU:
+// apply_fast.cu — A2: UltraHdr::applyGainMap (reference lib/src/ultrahdr.cpp:427-496) on table-driven kernels for
+// 4-aligned planes, restructured so that it is bound by instruction issue / HBM instead of the SFU. Three kernels:
 //
-//   * one thread = one gain-map cell = 4x4 pixels: the four surrounding map samples, the 2x2
-//     chroma samples and the cell's plane pointers are fetched once per 16 pixels; luma comes in
-//     as four 32-bit loads (a warp reads 128 contiguous bytes per row) and the packed output
-//     leaves as 128-bit stores (a warp writes 512 contiguous bytes per row).
-//   * the Shepard-IDW weights of the interior table (gainmapmath.h:184-228) sit in the kernel
-//     parameter block, i.e. in the constant bank: with the 4x4 loop fully unrolled every weight
-//     is an immediate constant-bank operand of an FFMA. Cells on the right/bottom map border
-//     (tables NR/NB/C, gainmapmath.cpp:710-716) read their weights from global memory.
-//   * srgbInvOetf (3 pow per pixel in the reference) and hlgOetf/pqOetf (sqrt/log or 9 pow per
-//     pixel) are piecewise-linear tables in shared memory on log-spaced segments: the float's
-//     exponent/mantissa bits are the index, one 64-bit LDS + one FFMA per evaluation. The tables
-//     (built in double on the host, tables.cu) are staged with one TMA bulk copy per block and the
-//     blocks are persistent (grid = SMs x resident blocks, grid-stride over 128x32-pixel tiles).
-//   * the gain factor 2^(logBoost * displayBoost / maxContentBoost) / displayBoost
-//     (gainmapmath.cpp:550-555, ultrahdr.cpp:451) is one FFMA + one MUFU.EX2 per pixel.
+//   apply_q_kernel   map scale factor 4 (kMapDimensionScaleFactor: what every libultrahdr encode writes). The kernel
+//                    the benchmark measures. One thread = one gain-map cell = 4x4 pixels, a lane walks CELLS cells
+//                    downwards with the next cell's loads in flight; ONE look-up per channel in the q domain (below).
+//   apply_qs_kernel  any integer scale factor (specialised for 1 and 2): thread = 4x4 pixel block, general Shepard-IDW
+//                    sampling, the same q-domain evaluation (stage_q_table, quad_row_eval are shared).
+//   apply_fast_kernel  the previous two-table design (srgbInvOetf table + OETF table), kept selectable for A/B runs and
+//                    for linear outputs whose values can leave the normal-half range.
+//
+// Common structure:
+//   * the four surrounding map samples, the 2x2 chroma samples and the plane pointers are fetched once per 16 pixels;
+//     luma comes in as four 32-bit loads (a warp reads 128 contiguous bytes per row) and the packed output leaves as
+//     128/256-bit stores (a warp writes 512/1024 contiguous bytes per row).
+//   * the Shepard-IDW weights of the interior table (gainmapmath.h:184-228) sit in the kernel parameter block, i.e. in
+//     the constant bank: with the 4x4 loop fully unrolled every weight is a constant-bank operand of an FFMA/FFMA2.
+//     Cells on the right/bottom map border (tables NR/NB/C, gainmapmath.cpp:710-716) read their weights from global memory.
+//   * transfer functions (3 pow per pixel + sqrt/log or 9 pow in the reference) are piecewise-linear tables in shared
+//     memory on log-spaced segments: the float's exponent/mantissa bits are the index, one 64-bit LDS + one FFMA per
+//     evaluation. The tables (built in double on the host, tables.cu) are staged with one TMA bulk copy per block and
+//     the blocks are persistent (grid = SMs x resident blocks, grid-stride over tiles).
+//   * the gain factor 2^(logBoost * displayBoost / maxContentBoost) / displayBoost (gainmapmath.cpp:550-555,
+//     ultrahdr.cpp:451) is three FFMA (FFMA2 on pixel pairs) + one MUFU.EX2 per pixel.
 #include <type_traits>
 
 #include "uhdr_io.cuh"
