@@ -374,6 +374,26 @@ def main():
         other["apply_1010102_pq"] = timed(lambda: uh.applyGainMapBatch(Bo, sdrs, maps, md_pq, abi.OUTPUT_HDR_PQ, FLT_MAX, bigs, stream), APPLY_BPP)
         other["apply_planar_10bit"] = timed(lambda: uh.applyGainMapBatch(Bo, sdrs, maps, md, abi.OUTPUT_HDR_LINEAR_RGB_10BIT, FLT_MAX, bigs, stream), 7.5625)
         other["sdr_rgba8888_pack"] = timed(lambda: uh.yuv420ToRgba8888Batch(Bo, sdrs, bigs, stream), 5.5)
+        # one image per call through the device-pointer entry points (the reference API's own granularity): kernel time of
+        # a single 4K image, images rotated so that L2 never holds the next one. Rates are per launch, not per batch.
+        def timed_single(fn, bpp, iters=64):
+            for i in range(4):
+                assert fn(i) == 0
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for i in range(iters):
+                fn(i % Bo)
+            e1.record()
+            torch.cuda.synchronize()
+            ms = e0.elapsed_time(e1) / iters
+            return {"mpix_s": PIX / ms / 1e3, "achieved_gbs": PIX * bpp / (ms * 1e-3) / 1e9, "algorithmic_bytes_per_px": bpp,
+                    "ms_per_launch": ms, "images_per_launch": 1}
+
+        md1 = abi.Metadata()
+        other["generate_single_image_call"] = timed_single(
+            lambda i: uh.generateGainMapDevice(sdrs[i], hdrs[i], abi.TF_HLG, md1, maps[i], False, stream), GEN_BPP)
+        other["apply_1010102_hlg_single_image_call"] = timed_single(
+            lambda i: uh.applyGainMapDevice(sdrs[i], maps[i], md, abi.OUTPUT_HDR_HLG, FLT_MAX, bigs[i], stream), APPLY_BPP)
         # N1 convertYuv in place (jpegr.cpp:1132-1206), one launch per image: four 8160x6144 images (75 MB each) in rotation
         cw_, ch_ = 8160, 6144
         d_cv = torch.empty((4, cw_ * ch_ * 3 // 2), dtype=torch.uint8, device=dev)

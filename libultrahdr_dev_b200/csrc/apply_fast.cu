@@ -744,10 +744,12 @@ __device__ __forceinline__ void quad_row_eval(const uint32_t hiP, const uint32_t
 // Tile = 32 x 8 * CELLS map cells (128 x 128 pixels for CELLS = 4). A lane owns one column of
 // cells; a warp walks CELLS cell rows downwards, so the lower pair of map samples of one cell is
 // the upper pair of the next (2 map loads per cell) and every plane pointer advances by a constant.
-// CELLS = 8 for large batches (fewer tile prologues: 740 vs 728 Gpix/s), 4 otherwise (more tiles to balance).
-template <int PACK, bool MASK, bool BATCH, bool LTAB, bool NORM, int CELLS>
+// CELLS = p.cells is chosen per launch (pick_cells): 8 for large batches (fewer tile prologues: 740 vs 728 Gpix/s at 4,
+// 711 at 16), and for a launch of only a few hundred tiles the height that fills the persistent grid in the fewest
+// rounds (a single 4K image: 5 cells -> 420 tiles in one round instead of 510 in two).
+template <int PACK, bool MASK, bool BATCH, bool LTAB, bool NORM>
 __global__ void __launch_bounds__(kQThreads, LTAB ? UHDR_APPLYQ_L_MIN_BLOCKS : UHDR_APPLYQ_MIN_BLOCKS) apply_q_kernel(const __grid_constant__ ApplyFastParams p) {
-  constexpr int kQCells = CELLS, kQTileRows = (kQThreads / 32) * CELLS;  // cell rows per tile: warps x CELLS
+  const uint32_t kQCells = (uint32_t)p.cells, kQTileRows = (kQThreads / 32) * kQCells;  // cell rows per tile: warps x CELLS
   const int tid = threadIdx.x;
   const uint32_t hiP = stage_q_table<PACK, LTAB>(p, tid);
 
@@ -810,7 +812,7 @@ __global__ void __launch_bounds__(kQThreads, LTAB ? UHDR_APPLYQ_L_MIN_BLOCKS : U
     const uint32_t dx = cx + 1 < mw ? 1u : 0u;  // xu = min(xl + 1, mw - 1), gainmapmath.cpp:690-697
     // map samples as 0..255 floats: the 1/255 of gainmapmath.cpp:700-703 is folded into the weights
     float e1 = (float)__ldg(mp), e3 = (float)__ldg(mp + dx);  // e1=(xl,yl) e3=(xu,yl)
-    const uint32_t kmax = min((uint32_t)kQCells, mh - cy);
+    const uint32_t kmax = min(kQCells, mh - cy);
 
 #if UHDR_APPLYQ_PREFETCH
     // software pipeline: the 10 loads of cell k + 1 are in flight while cell k is evaluated
@@ -1082,9 +1084,27 @@ cudaError_t launch(const ApplyFastParams& p, cudaStream_t s) {
   return cudaGetLastError();
 }
 
-template <int PACK, bool MASK, bool BATCH, bool LTAB, bool NORM, int CELLS>
+// Cells per lane and tile: the persistent grid runs ceil(tiles / cap) rounds of `cells` cell-times each. Large launches
+// take 8 (measured best); small ones the height with the cheapest rounds x (cells + per-tile overhead), ties to the taller.
+int pick_cells(int tiles_x, int map_height, int n_img, int cap) {
+  const int warps = kQThreads / 32;
+  if ((long long)tiles_x * ((map_height + warps * 8 - 1) / (warps * 8)) * n_img >= 8LL * cap) return 8;
+  int best = 1;
+  double best_cost = 1e30;
+  for (int c = 1; c <= 8; c++) {
+    const long long tiles = (long long)tiles_x * ((map_height + warps * c - 1) / (warps * c)) * n_img;
+    const long long rounds = (tiles + cap - 1) / cap;
+    const double cost = (double)rounds * (c + 0.25);
+    if (cost <= best_cost) {
+      best_cost = cost;
+      best = c;
+    }
+  }
+  return best;
+}
+
+template <int PACK, bool MASK, bool BATCH, bool LTAB, bool NORM>
 cudaError_t launch_q(const ApplyFastParams& p0, cudaStream_t s) {
-  constexpr int kQTileRows = (kQThreads / 32) * CELLS;
   static int sms_of[64], per_sm_of[64], smem_of[64];
   int dev = 0;
   cudaError_t e = cudaGetDevice(&dev);
@@ -1095,39 +1115,36 @@ cudaError_t launch_q(const ApplyFastParams& p0, cudaStream_t s) {
     cudaFuncAttributes fa;
     if ((e = cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev)) != cudaSuccess) return e;
     if ((e = cudaDeviceGetAttribute(&reserved, cudaDevAttrReservedSharedMemoryPerBlock, dev)) != cudaSuccess) return e;
-    if ((e = cudaFuncGetAttributes(&fa, apply_q_kernel<PACK, MASK, BATCH, LTAB, NORM, CELLS>)) != cudaSuccess) return e;
+    if ((e = cudaFuncGetAttributes(&fa, apply_q_kernel<PACK, MASK, BATCH, LTAB, NORM>)) != cudaSuccess) return e;
     const uint32_t dyn0 = (uint32_t)reserved + (uint32_t)fa.sharedSizeBytes;
     const int smem = LTAB ? 16 + (int)(kLEntries * sizeof(float2))
                           : (PACK == kPack1010102 ? (int)(q_table_addr(dyn0) - dyn0 + kPEntries * sizeof(float2)) + 64 : 0);  // + slack for the base alignment
-    if ((e = cudaFuncSetAttribute(apply_q_kernel<PACK, MASK, BATCH, LTAB, NORM, CELLS>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)) != cudaSuccess) return e;
-    if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, apply_q_kernel<PACK, MASK, BATCH, LTAB, NORM, CELLS>, kQThreads, smem)) != cudaSuccess) return e;
+    if ((e = cudaFuncSetAttribute(apply_q_kernel<PACK, MASK, BATCH, LTAB, NORM>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)) != cudaSuccess) return e;
+    if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, apply_q_kernel<PACK, MASK, BATCH, LTAB, NORM>, kQThreads, smem)) != cudaSuccess) return e;
     sms_of[dev] = n_sm;
     smem_of[dev] = smem;
     per_sm_of[dev] = n > 0 ? n : 1;
   }
   ApplyFastParams p = p0;
   const int n_img = p.n_tiles / (p.tiles_x * p.tiles_y);
+  const int cap = sms_of[dev] * per_sm_of[dev];
+  p.cells = pick_cells(p.tiles_x, p.g.map_height, n_img, cap);
+  const int kQTileRows = (kQThreads / 32) * p.cells;
   p.tiles_y = (p.g.map_height + kQTileRows - 1) / kQTileRows;  // this kernel's tiles are kQTileRows cell rows tall
   p.n_tiles = p.tiles_x * p.tiles_y * n_img;
-  const int cap = sms_of[dev] * per_sm_of[dev];
   const int grid = p.n_tiles < cap ? p.n_tiles : cap;
-  apply_q_kernel<PACK, MASK, BATCH, LTAB, NORM, CELLS><<<grid, kQThreads, (size_t)smem_of[dev], s>>>(p);
+  apply_q_kernel<PACK, MASK, BATCH, LTAB, NORM><<<grid, kQThreads, (size_t)smem_of[dev], s>>>(p);
   return cudaGetLastError();
 }
 
 template <int PACK, bool MASK>
 cudaError_t launch_q(const ApplyFastParams& p, cudaStream_t s) {
   constexpr bool kLin = PACK != kPack1010102;
-  // tall tiles (8 cells per lane) once the batch holds >= 2048 of them, i.e. several waves of the persistent grid
-  const int n_img = p.n_tiles / (p.tiles_x * p.tiles_y);
-  const bool tall = p.batch && (long long)p.tiles_x * ((p.g.map_height + 63) / 64) * n_img >= 2048;
   if (kLin && p.lin_table_ok) {  // lin_table_ok also implies normal halves (capi.cu)
     constexpr bool kNorm = PACK == kPackF16;
-    if (tall) return launch_q<PACK, MASK, true, kLin, kNorm, 8>(p, s);
-    return p.batch ? launch_q<PACK, MASK, true, kLin, kNorm, 4>(p, s) : launch_q<PACK, MASK, false, kLin, kNorm, 4>(p, s);
+    return p.batch ? launch_q<PACK, MASK, true, kLin, kNorm>(p, s) : launch_q<PACK, MASK, false, kLin, kNorm>(p, s);
   }
-  if (tall) return launch_q<PACK, MASK, true, false, false, 8>(p, s);
-  return p.batch ? launch_q<PACK, MASK, true, false, false, 4>(p, s) : launch_q<PACK, MASK, false, false, false, 4>(p, s);
+  return p.batch ? launch_q<PACK, MASK, true, false, false>(p, s) : launch_q<PACK, MASK, false, false, false>(p, s);
 }
 
 template <int PACK, bool MASK, bool BATCH, bool LTAB, bool NORM, int SCALE>

@@ -115,6 +115,7 @@ struct ApplyFastParams {
   float Aq, Bq, q0;        // q-domain kernel: f' = 2^(gain255 * Aq + Bq) = f^(1/2.4), gain255 = 255 * gain; q0 = 2^kPLoExp
   int two_table;           // 1: the S+O table kernels (apply_fast_kernel) instead of the q-domain kernels
   int lin_table_ok;        // 1: q = Phi * f' stays inside the L table for every non-toe channel (host check)
+  int cells;               // apply_q_kernel: map cells a lane walks per tile (set by launch_q / pick_cells)
   int any_scale;           // 1: apply_qs_kernel (any integer map scale factor, thread = 4x4 pixels) instead of the scale-4 kernels
   uint32_t scale_magic;    // ceil(2^32 / map_scale), 0 for scale 1 (set by launch_apply_fast_impl)
   int scale_special;       // 1 / 2: compile-time specialisation of apply_qs_kernel (map planes aligned to 4 / 2 bytes), else 0
