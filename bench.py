@@ -377,7 +377,9 @@ def main():
         # one image per call through the device-pointer entry points (the reference API's own granularity): kernel time of
         # a single 4K image, images rotated so that L2 never holds the next one. Rates are per launch, not per batch.
         def timed_single(fn, bpp, iters=64):
-            for i in range(4):
+            if a.profile_once:
+                iters = 1
+            for i in range(0 if a.profile_once else 4):
                 assert fn(i) == 0
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record()
