@@ -443,7 +443,7 @@ __device__ __forceinline__ void q_rows_paired(const uint32_t hiP, const float (&
 }
 
 // q_rows for the linear outputs above the toe (L table): q = Phi * f' and the 10-bit scale + floor on packed fp32x2
-template <int PACK, bool NORM>
+template <int PACK, bool NORM, bool MASK>
 __device__ __forceinline__ void q_rows_paired_lin(const uint32_t tL, const float (&oR)[2], const float (&oG)[2], const float (&oB)[2],
                                                   const float (&yf)[2][4], const float* __restrict__ f8, uint8_t* orow, const size_t ostride,
                                                   const size_t plane_bytes) {
@@ -451,7 +451,7 @@ __device__ __forceinline__ void q_rows_paired_lin(const uint32_t tL, const float
   constexpr float KP = (float)(1.0 / (255.0 * 1.055));
 #pragma unroll
   for (int rr = 0; rr < 2; rr++) {
-    uint32_t w[4][PACK == kPackF16 ? 2 : 3];
+    uint32_t w[4][PACK == kPackF16 ? 2 : 3];  // F16: two words per pixel; planar: [pixel pair][channel] u16 pairs
 #pragma unroll
     for (int c = 0; c < 2; c++) {
       const float y0 = yf[rr][2 * c], y1 = yf[rr][2 * c + 1];
@@ -487,8 +487,10 @@ __device__ __forceinline__ void q_rows_paired_lin(const uint32_t tL, const float
         for (int ch = 0; ch < 3; ch++) {
           float m0, m1;
           unpk2(add_rm2(mul2(pk2(e[ch][0], e[ch][1]), k1023), two23), m0, m1);
-          w[2 * c][ch] = __float_as_uint(m0) & 0x3ffu;
-          w[2 * c + 1][ch] = __float_as_uint(m1) & 0x3ffu;
+          // the integers sit in the low mantissa bits: one PRMT takes both low halves (dropping the 0x4B00 of the magic
+          // number) into the u16 pair; `& 0x3ff` only when a code can exceed 1023 (displayBoost < maxContentBoost)
+          const uint32_t pr = __byte_perm(__float_as_uint(m0), __float_as_uint(m1), 0x5410);
+          w[c][ch] = MASK ? (pr & 0x03ff03ffu) : pr;
         }
       }
     }
@@ -497,8 +499,7 @@ __device__ __forceinline__ void q_rows_paired_lin(const uint32_t tL, const float
       stg32(o, make_uint4(w[0][0], w[0][1], w[1][0], w[1][1]), make_uint4(w[2][0], w[2][1], w[3][0], w[3][1]));
     } else {  // three planar u16 planes, ultrahdr.cpp:460-468
 #pragma unroll
-      for (int ch = 0; ch < 3; ch++)
-        stg8(o + ch * plane_bytes, make_uint2(w[0][ch] | (w[1][ch] << 16), w[2][ch] | (w[3][ch] << 16)));
+      for (int ch = 0; ch < 3; ch++) stg8(o + ch * plane_bytes, make_uint2(w[0][ch], w[1][ch]));
     }
   }
 }
@@ -736,7 +737,7 @@ __device__ __forceinline__ void quad_row_eval(const uint32_t hiP, const uint32_t
         if (toe) q_rows<PACK, MASK, true, LTAB, NORM>(hiP, uq, vq, oR, oG, oB, yf, f, orow, ostride, plane_bytes);
 #if UHDR_APPLYQ_F32X2
         else if constexpr (PACK == kPack1010102 && !MASK) q_rows_paired(hiP, oR, oG, oB, yf, f, orow, ostride);
-        else if constexpr (LTAB) q_rows_paired_lin<PACK, NORM>(hiP, oR, oG, oB, yf, f, orow, ostride, plane_bytes);
+        else if constexpr (LTAB) q_rows_paired_lin<PACK, NORM, MASK>(hiP, oR, oG, oB, yf, f, orow, ostride, plane_bytes);
 #endif
         else q_rows<PACK, MASK, false, LTAB, NORM>(hiP, uq, vq, oR, oG, oB, yf, f, orow, ostride, plane_bytes);
 }
@@ -1223,7 +1224,7 @@ cudaError_t launch_apply_fast_impl(ApplyFastParams& p, int n, cudaStream_t s) {
     p.scale_magic = p.g.map_scale == 1 ? 0u : (uint32_t)((0x100000000ull + (uint64_t)p.g.map_scale - 1) / (uint64_t)p.g.map_scale);
     switch (p.output_format) {
       case 1: return launch_qs<kPackF16, false>(p, s);
-      case 4: return launch_qs<kPackPlanar10, false>(p, s);
+      case 4: return p.need_mask ? launch_qs<kPackPlanar10, true>(p, s) : launch_qs<kPackPlanar10, false>(p, s);
       default: return p.need_mask ? launch_qs<kPack1010102, true>(p, s) : launch_qs<kPack1010102, false>(p, s);
     }
   }
@@ -1232,7 +1233,9 @@ cudaError_t launch_apply_fast_impl(ApplyFastParams& p, int n, cudaStream_t s) {
   p.n_tiles = p.tiles_x * p.tiles_y * n;
   switch (p.output_format) {
     case 1: return p.two_table ? launch<kPackF16, false>(p, s) : launch_q<kPackF16, false>(p, s);
-    case 4: return p.two_table ? launch<kPackPlanar10, false>(p, s) : launch_q<kPackPlanar10, false>(p, s);
+    case 4:
+      if (p.two_table) return launch<kPackPlanar10, false>(p, s);
+      return p.need_mask ? launch_q<kPackPlanar10, true>(p, s) : launch_q<kPackPlanar10, false>(p, s);
     default:
       if (!p.two_table) return p.need_mask ? launch_q<kPack1010102, true>(p, s) : launch_q<kPack1010102, false>(p, s);
       return p.need_mask ? launch<kPack1010102, true>(p, s) : launch<kPack1010102, false>(p, s);
