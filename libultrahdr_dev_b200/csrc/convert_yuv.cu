@@ -17,14 +17,6 @@ namespace {
 template <bool VEC>
 __global__ void __launch_bounds__(256) convert_yuv_kernel(ConvertYuvParams p) {
   const Geometry& g = p.g;
-  uint32_t tY = 0, tC = 0;
-  if (VEC) {  // byte -> float tables of the packed quad-pair transform, filled before any thread leaves
-    __shared__ float sYf[256], sCf[256];
-    fill_convert_tables(sYf, sCf, threadIdx.y * 32 + threadIdx.x);
-    __syncthreads();
-    tY = (uint32_t)__cvta_generic_to_shared(sYf);
-    tC = (uint32_t)__cvta_generic_to_shared(sCf);
-  }
   const int x0 = (blockIdx.x * 32 + threadIdx.x) * 4;
   const int cw = g.width / 2, ch = g.height / 2;
   const Planes pl = p.batch ? p.batch[blockIdx.z] : p.single;
@@ -50,7 +42,7 @@ __global__ void __launch_bounds__(256) convert_yuv_kernel(ConvertYuvParams p) {
 #pragma unroll
     for (int r = 0; r < 2; r++) {
       if (r == 1 && !two) break;
-      transform_quad_pair(p.m, tY, tC, a[2 * r], a[2 * r + 1], c[r], d[r]);
+      transform_quad_pair(p.m, a[2 * r], a[2 * r + 1], c[r], d[r]);
       *reinterpret_cast<uint32_t*>(yp + (size_t)(2 * r) * g.sdr_luma_stride) = a[2 * r];
       *reinterpret_cast<uint32_t*>(yp + (size_t)(2 * r + 1) * g.sdr_luma_stride) = a[2 * r + 1];
       *reinterpret_cast<uint16_t*>(up + (size_t)r * g.sdr_chroma_stride) = (uint16_t)c[r];

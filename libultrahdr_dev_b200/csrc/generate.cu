@@ -26,14 +26,6 @@ namespace {
 template <bool VEC, bool FUSED, bool CONVERT = false>
 __global__ void __launch_bounds__(256) generate_kernel(GenerateParams p) {
   const Geometry& g = p.g;
-  uint32_t tY = 0, tC = 0;
-  if (CONVERT) {  // byte -> float tables of the quad transform (uhdr_convert.cuh), filled before any thread leaves
-    __shared__ float sYf[256], sCf[256];
-    fill_convert_tables(sYf, sCf, threadIdx.y * 32 + threadIdx.x);
-    __syncthreads();
-    tY = (uint32_t)__cvta_generic_to_shared(sYf);
-    tC = (uint32_t)__cvta_generic_to_shared(sCf);
-  }
   const int mx = blockIdx.x * 32 + threadIdx.x;
   const int my = blockIdx.y * 8 + threadIdx.y;
   if (mx >= g.map_width || my >= g.map_height) return;
@@ -74,7 +66,7 @@ __global__ void __launch_bounds__(256) generate_kernel(GenerateParams p) {
       if (CONVERT) {
 #pragma unroll
         for (int qr = 0; qr < 2; qr++)
-          transform_quad_pair(p.conv, tY, tC, oy_w[2 * qr], oy_w[2 * qr + 1], ou_w[qr], ov_w[qr]);
+          transform_quad_pair(p.conv, oy_w[2 * qr], oy_w[2 * qr + 1], ou_w[qr], ov_w[qr]);
       }
 #pragma unroll
       for (int r = 0; r < 4; r++) stg4(oy + (size_t)r * g.sdr_luma_stride, oy_w[r]);

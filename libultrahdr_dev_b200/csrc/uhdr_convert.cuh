@@ -38,8 +38,9 @@ __device__ __forceinline__ void transform_quad(const float* m, Quad& q) {
 }
 
 // ---- packed fp32x2 version for 4-aligned blocks (fused API-0 kernel, generate.cu) -------------------------------
-// Same arithmetic, same roundings: the int -> float * (1 / 255) conversions come from two byte-indexed shared-memory
-// tables filled with exactly those expressions, sums / products run on FADD2 / FMUL2 lanes (IEEE per lane), and
+// Same arithmetic, same roundings: the int -> float conversions are I2F.U8 with a byte selector (the XU pipe is idle in
+// these kernels; byte-indexed shared-memory tables cost 3 issue slots per sample and were 8-13 % slower), the * (1 / 255),
+// sums and products run on FADD2 / FMUL2 lanes (IEEE per lane), and
 // CLIP3 + truncation is one saturating float -> u8 conversion (F2IP.U8.F32.TRUNC). ptxas 12.9 contracts a
 // mul.rn.f32x2 feeding an add.rn.f32x2 into FFMA2 even under -fmad=false, so every "product + term" below adds
 // through fma(product, 1, term), which is the same two-rounding result.
@@ -71,28 +72,20 @@ __device__ __forceinline__ uint32_t cv_sat_u8(float v) {
   asm("cvt.rzi.u8.f32 %0, %1;" : "=r"(r) : "f"(v));
   return r;
 }
-__device__ __forceinline__ float cv_lds(uint32_t addr) {
-  float v;
-  asm("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr));
-  return v;
-}
-// entry t of the tables: (float)t * (1 / 255.0f) and (float)(t - 128) * (1 / 255.0f), as transform_quad computes them
-__device__ __forceinline__ void fill_convert_tables(float* sYf, float* sCf, int t) {
-  sYf[t] = (float)t * (1 / 255.0f);
-  sCf[t] = (float)(t - 128) * (1 / 255.0f);
-}
 // two pixel rows x four columns = two horizontally adjacent quads, in place on the packed words:
-// y0w / y1w = the 4 luma bytes of each row, uw / vw = U0 U1 / V0 V1 in the low 16 bits. tY / tC = shared addresses.
-__device__ __forceinline__ void transform_quad_pair(const float* m, uint32_t tY, uint32_t tC, uint32_t& y0w, uint32_t& y1w,
+// y0w / y1w = the 4 luma bytes of each row, uw / vw = U0 U1 / V0 V1 in the low 16 bits.
+__device__ __forceinline__ void transform_quad_pair(const float* m, uint32_t& y0w, uint32_t& y1w,
                                                     uint32_t& uw, uint32_t& vw) {
   const cv_f32x2 k255 = cv_pk2(255.0f, 255.0f), half = cv_pk2(0.5f, 0.5f), k128 = cv_pk2(128.0f, 128.0f), quarter = cv_pk2(0.25f, 0.25f);
-  const cv_f32x2 m47 = cv_pk2(m[4], m[7]), m58 = cv_pk2(m[5], m[8]);
+  const cv_f32x2 m47 = cv_pk2(m[4], m[7]), m58 = cv_pk2(m[5], m[8]), k255inv = cv_pk2(1 / 255.0f, 1 / 255.0f);
   uint32_t yo[2][4], uo[2], vo[2];
 #pragma unroll
   for (int qc = 0; qc < 2; qc++) {
-    const float uf = cv_lds(tC + (qc ? (uw >> 6) & 0x3fcu : (uw << 2) & 0x3fcu));
-    const float vf = cv_lds(tC + (qc ? (vw >> 6) & 0x3fcu : (vw << 2) & 0x3fcu));
-    const float yu = m[1] * uf, yv = m[2] * vf;
+    // (float)(c - 128) * (1 / 255.0f): the int -> float conversion of c - 128 equals (float)c - 128 exactly
+    float uf, vf, yu, yv;
+    const cv_f32x2 uv = cv_mul2(cv_add2(cv_pk2((float)((uw >> (8 * qc)) & 0xffu), (float)((vw >> (8 * qc)) & 0xffu)), cv_pk2(-128.0f, -128.0f)), k255inv);
+    cv_unpk2(uv, uf, vf);
+    cv_unpk2(cv_mul2(uv, cv_pk2(m[1], m[2])), yu, yv);
     const cv_f32x2 YU = cv_pk2(yu, yu), YV = cv_pk2(yv, yv);
     // lanes = (nu, nv) = (m4*u + m5*v, m7*u + m8*v); then the reference's running sum of four equal values, / 4
     const cv_f32x2 n = cv_sum2(cv_mul2(m58, cv_pk2(vf, vf)), cv_mul2(m47, cv_pk2(uf, uf)));
@@ -105,9 +98,9 @@ __device__ __forceinline__ void transform_quad_pair(const float* m, uint32_t tY,
 #pragma unroll
     for (int r = 0; r < 2; r++) {
       const uint32_t w = r ? y1w : y0w;
-      const uint32_t b0 = qc ? (w >> 14) & 0x3fcu : (w << 2) & 0x3fcu;
-      const uint32_t b1 = qc ? (w >> 22) & 0x3fcu : (w >> 6) & 0x3fcu;
-      const cv_f32x2 yf = cv_pk2(cv_lds(tY + b0), cv_lds(tY + b1));
+      // (float)y * (1 / 255.0f) as transform_quad computes it: the byte -> float conversions select their byte themselves
+      // (I2F.U8 .Bn on the otherwise idle XU pipe), the products share one FMUL2 per pixel pair
+      const cv_f32x2 yf = cv_mul2(cv_pk2((float)((w >> (16 * qc)) & 0xffu), (float)((w >> (16 * qc + 8)) & 0xffu)), k255inv);
       const cv_f32x2 ny = cv_add2(cv_add2(yf, YU), YV);  // m[0]*y + m[1]*u + m[2]*v, left to right
       float a0, a1;
       cv_unpk2(cv_sum2(cv_mul2(ny, k255), half), a0, a1);
