@@ -946,10 +946,27 @@ __global__ void __launch_bounds__(kThreads, 3) apply_qs_kernel(const __grid_cons
   const uint32_t ss = sc * sc;
   auto div_s = [&](uint32_t x) { return magic ? __umulhi(x, magic) : x; };  // magic == 0 <=> scale 1
 
+  // tile -> (image z, tile row ty, tile column tx), advanced incrementally: no division in the loop
+  const uint32_t tiles_y = p.tiles_y;
+  uint32_t tx, ty, zn, dtx, dty, dz;
+  {
+    const uint32_t b0 = blockIdx.x, st = gridDim.x;
+    zn = b0 / tiles_per_image;
+    uint32_t rem = b0 - zn * tiles_per_image;
+    ty = rem / tiles_x;
+    tx = rem - ty * tiles_x;
+    dz = st / tiles_per_image;
+    rem = st - dz * tiles_per_image;
+    dty = rem / tiles_x;
+    dtx = rem - dty * tiles_x;
+  }
   for (uint32_t tile = blockIdx.x; tile < (uint32_t)p.n_tiles; tile += gridDim.x) {
-    const uint32_t z = tile / tiles_per_image, rem = tile - z * tiles_per_image;
-    const uint32_t ty = rem / tiles_x, tx = rem - ty * tiles_x;
-    const uint32_t bx = tx * 32 + (tid & 31), by = ty * 8 + (tid >> 5);
+    const uint32_t bx = tx * 32 + (tid & 31), by = ty * 8 + (tid >> 5), z = zn;
+    tx += dtx;
+    if (tx >= tiles_x) { tx -= tiles_x; ty++; }
+    ty += dty;
+    if (ty >= tiles_y) { ty -= tiles_y; zn++; }
+    zn += dz;
     if (bx >= bw || by >= bh) continue;
     const uint8_t *sdr_y, *sdr_u, *sdr_v, *map;
     uint8_t* outp;
