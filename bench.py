@@ -372,6 +372,10 @@ def main():
         assert uh.generateGainMapBatch(Bo, sdrs, hdrs, abi.TF_HLG, mds, maps, False, stream) == 0  # restore HLG maps
         other["apply_rgba_f16_linear"] = timed(lambda: uh.applyGainMapBatch(Bo, sdrs, maps, md, abi.OUTPUT_HDR_LINEAR, FLT_MAX, bigs, stream), 9.5625)
         other["apply_1010102_pq"] = timed(lambda: uh.applyGainMapBatch(Bo, sdrs, maps, md_pq, abi.OUTPUT_HDR_PQ, FLT_MAX, bigs, stream), APPLY_BPP)
+        # an SDR-like display (max_display_boost = 1 < maxContentBoost): the gain factor maxContentBoost^(1/maxContentBoost)
+        # exceeds 1, codes can pass 1023 and wrap through the reference's `& 0x3ff` (gainmapmath.cpp:722-727): the masked
+        # packing path. From max_display_boost ~1.5 upwards the factor stays below 1 and the unmasked kernel runs.
+        other["apply_1010102_hlg_display_boost_1"] = timed(lambda: uh.applyGainMapBatch(Bo, sdrs, maps, md, abi.OUTPUT_HDR_HLG, 1.0, bigs, stream), APPLY_BPP)
         other["apply_planar_10bit"] = timed(lambda: uh.applyGainMapBatch(Bo, sdrs, maps, md, abi.OUTPUT_HDR_LINEAR_RGB_10BIT, FLT_MAX, bigs, stream), 7.5625)
         other["sdr_rgba8888_pack"] = timed(lambda: uh.yuv420ToRgba8888Batch(Bo, sdrs, bigs, stream), 5.5)
         # one image per call through the device-pointer entry points (the reference API's own granularity): kernel time of
