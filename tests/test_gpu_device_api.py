@@ -425,3 +425,41 @@ def test_pinned_and_pageable_host_planes_agree(uh):
                     lib.uhdrb200_host_free(q)
         assert np.array_equal(outs[0][0], outs[1][0]) and np.array_equal(outs[0][1], outs[1][1])
         assert outs[0][1].any()
+
+
+# ---------------------------------------------------------------- concurrent callers (thread-local contexts)
+def test_concurrent_host_callers_get_their_own_results(uh):
+    """The reference API is re-entrant (no shared mutable state); here every host thread owns a stream, device
+    staging buffers and page-locked chunks. Eight threads hammer generate + apply on different images and sizes
+    (pageable planes, multi-chunk at the larger sizes); every result must equal the one computed alone."""
+    import concurrent.futures as cf
+
+    lib = uh.lib
+    sizes = [(256, 128), (1920, 1080), (640, 360), (132, 68), (2048, 1024), (516, 36), (1280, 720), (64, 64)]
+    jobs = []
+    for i, (w, h) in enumerate(sizes):
+        sdr_b, hdr_b = synth.uniform_pair(w, h, 300 + i)
+        jobs.append((w, h, sdr_b, hdr_b))
+
+    def run(job):
+        w, h, sdr_b, hdr_b = job
+        s_img = abi.host_yuv420(sdr_b, w, h, abi.COLORGAMUT_BT709)
+        h_img = abi.host_p010(hdr_b, w, h, abi.COLORGAMUT_BT2100)
+        mp = np.zeros(w * h // 16, np.uint8)
+        out = np.zeros(w * h * 4, np.uint8)
+        md, m_img, o_img = abi.Metadata(), abi.Image(), abi.Image()
+        st = lib.uhdrb200_generate_gainmap_host_into(C.byref(s_img), C.byref(h_img), abi.TF_HLG, C.byref(md), C.byref(m_img), 0,
+                                                     mp.ctypes.data, mp.size)
+        assert st == 0, lib.uhdrb200_last_error()
+        o_img.data = out.ctypes.data
+        st = lib.uhdrb200_apply_gainmap_host(C.byref(s_img), C.byref(m_img), C.byref(md), abi.OUTPUT_HDR_HLG, FLT_MAX, C.byref(o_img))
+        assert st == 0, lib.uhdrb200_last_error()
+        return mp, out
+
+    alone = [run(j) for j in jobs]
+    with cf.ThreadPoolExecutor(8) as pool:
+        for _ in range(3):
+            order = list(range(len(jobs))) * 3
+            got = list(pool.map(lambda k: run(jobs[k]), order))
+            for k, (mp, out) in zip(order, got):
+                assert np.array_equal(mp, alone[k][0]) and np.array_equal(out, alone[k][1]), f"job {k} differs under concurrency"
