@@ -58,7 +58,7 @@ def cpu_worker(n_images, seed, tag):
     from oracle.pyoracle import CpuImpl
 
     impl = CpuImpl.reference() if tag == "reference" else CpuImpl.oracle()
-    sdr_b, hdr_b = synth.uniform_pair(W, H, seed)
+    sdr_b, hdr_b = make_pair(seed)  # the pixels of image `seed` of the GPU arm's job
     sdr = abi.host_yuv420(sdr_b, W, H, abi.COLORGAMUT_BT709)
     hdr = abi.host_p010(hdr_b, W, H, abi.COLORGAMUT_BT2100)
     sys.stdout.write("ready\n")
@@ -74,6 +74,23 @@ def cpu_worker(n_images, seed, tag):
     sys.stdout.flush()
 
 
+def make_pair(index):
+    """Image `index` of the job: seeded synthetic natural pair, identical in both bench arms."""
+    from libultrahdr_dev_b200 import abi, synth
+
+    return synth.natural_pair(W, H, int(index), abi.TF_HLG, abi.COLORGAMUT_BT709, abi.COLORGAMUT_BT2100)
+
+
+def make_pairs(indices, procs):
+    """Generates the pairs in parallel worker processes (numpy, ~3.5 s per 4K pair per core). Called before CUDA is up."""
+    if procs <= 1 or len(indices) <= 1:
+        return [make_pair(i) for i in indices]
+    import multiprocessing as mp
+
+    with mp.get_context("spawn").Pool(min(procs, len(indices))) as pool:
+        return pool.map(make_pair, list(indices))
+
+
 def cpu_arm(images_per_worker, workers=None):
     """Runs `workers` concurrent reference processes; returns (Mpix/s, info dict)."""
     from oracle.pyoracle import CpuImpl
@@ -84,8 +101,8 @@ def cpu_arm(images_per_worker, workers=None):
     if workers is None:
         workers = max(1, cores // threads_per)
     procs = [subprocess.Popen([sys.executable, os.path.abspath(__file__), "--cpu-worker", str(images_per_worker),
-                               str(0xB200 + i), tag], stdin=subprocess.PIPE, stdout=subprocess.PIPE, text=True, cwd=ROOT)
-             for i in range(workers)]
+                               str(i), tag], stdin=subprocess.PIPE, stdout=subprocess.PIPE, text=True, cwd=ROOT)
+             for i in range(workers)]  # worker i runs on image i of the job (the GPU arm's pair i)
     for p in procs:
         assert p.stdout.readline().strip() == "ready"
     t0 = time.perf_counter()
@@ -100,7 +117,7 @@ def cpu_arm(images_per_worker, workers=None):
     n = workers * images_per_worker
     return n * PIX / dt / 1e6, {
         "kind": tag, "cores": workers * threads_per, "host_cores": cores,
-        "sample": f"{n} synthetic 3840x2160 pairs (generate HLG 2100->709 + apply->RGBA1010102 HLG), "
+        "sample": f"{n} passes over the job's first {workers} synthetic natural 3840x2160 pairs (the GPU arm's pixels; generate HLG 2100->709 + apply->RGBA1010102 HLG), "
                   f"{workers} concurrent processes x {threads_per} threads (reference caps a call at 4 threads), {dt:.1f} s",
         "seconds": dt, "images": n}
 
@@ -185,7 +202,12 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--batch", type=int, default=256, help="4K pairs per step per GPU (device-resident)")
+    ap.add_argument("--batch", type=int, default=256, help="4K pairs per step per GPU (device-resident; weak scaling)")
+    ap.add_argument("--job-images", type=int, default=0,
+                    help="BASELINE config 5 as written: a FIXED job of this many 4K pairs (1024) image-sharded over the ranks "
+                         "(strong scaling: rank r owns images r, r+N, ...); 0 = the default weak-scaling batch per GPU")
+    ap.add_argument("--distinct", type=int, default=0, help="distinct seeded pairs materialised per rank (default 64 at N=1, 16 per rank at N>1); "
+                                                          "the other device slots hold cyclic shifts of them, so no two slots are byte-identical")
     ap.add_argument("--e2e-images", type=int, default=64, help="4K pairs per e2e step per GPU (host planes)")
     ap.add_argument("--e2e-threads", type=int, default=4, help="host threads calling the synchronous host-pointer API concurrently")
     ap.add_argument("--e2e-join", default="auto", choices=["auto", "spin", "blocking"], help="how the host entry points wait (uhdrb200_set_sync_mode)")
@@ -205,9 +227,12 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
-    config = {"workload": "BASELINE config 5 flavour: batch of synthetic 3840x2160 P010(HLG,BT.2100)+YUV420(BT.709) pairs, "
-                          "generateGainMap then applyGainMap->RGBA1010102 HLG (max_display_boost=FLT_MAX), image-sharded",
-              "width": W, "height": H, "map_scale": 4, "images_per_step_per_gpu": a.batch,
+    if a.job_images:
+        a.batch = len(range(rank, a.job_images, world))  # shard_round_robin
+    config = {"workload": (f"BASELINE config 5 as written: a fixed job of {a.job_images} synthetic 3840x2160 pairs, image i on rank i mod N (strong scaling), "
+                           if a.job_images else "BASELINE config 5 flavour: a batch of synthetic 3840x2160 pairs per GPU (weak scaling), ") +
+                          "P010(HLG,BT.2100)+YUV420(BT.709), generateGainMap then applyGainMap->RGBA1010102 HLG (max_display_boost=FLT_MAX), image-sharded",
+              "width": W, "height": H, "map_scale": 4, "images_per_step_per_gpu": a.batch, "job_images": a.job_images or None,
               "l2": "inputs+outputs per step >> 126 MB L2 (no flush needed)", "mode": "analytic (reference as built)"}
 
     if a.impl == "reference":
@@ -237,9 +262,16 @@ def main():
         return
 
     import numpy as np
+
+    # the distinct seeded pairs of this rank, generated in worker processes before CUDA is initialised
+    K = a.distinct or (64 if world == 1 else 16)
+    K = max(1, min(K, a.batch))
+    my_first = list(range(rank, (a.job_images or world * a.batch), world))[:K]
+    pairs = make_pairs(my_first, max(1, host_cores() // world))
+
     import torch
 
-    from libultrahdr_dev_b200 import abi, api, synth
+    from libultrahdr_dev_b200 import abi, api, refdata, synth
 
     lib = api.load_library(a.lib)  # raises when the CUDA library is missing: no CPU fallback
     if not torch.cuda.is_available() or lib.uhdrb200_device_count() < 1:
@@ -260,25 +292,37 @@ def main():
         v, cpu_info = cpu_arm(a.cpu_images)
         cpu_info.update(value=v, unit=UNIT)
 
-    # ---- synthetic inputs. The job is world*B images; image i belongs to rank i mod world (shard.py).
-    # A rank materialises K distinct seeded pairs (seed = the global image index of its first K images) and
-    # replicates them into its B device slots.
+    # ---- synthetic inputs. The job is J images (world*B, or --job-images); image i belongs to rank i mod world
+    # (shard.py). A rank materialises K distinct seeded pairs (seed = the global index of its first K images,
+    # generated BEFORE this point in worker processes) and fills its B device slots with cyclic shifts of them
+    # (slot j = pair j mod K rolled by 64 * (j div K) pixels in x and 36 * (j div K) in y, SDR and HDR alike), so that
+    # every slot holds different bytes.
     from libultrahdr_dev_b200 import shard
 
-    B, K = a.batch, 4
-    mine = shard.shard_round_robin(world * B, rank, world)
+    B = a.batch
+    mine = shard.shard_round_robin(a.job_images or world * B, rank, world)
     assert len(mine.indices) == B
-    pairs = [synth.natural_pair(W, H, mine.indices[i], abi.TF_HLG, abi.COLORGAMUT_BT709, abi.COLORGAMUT_BT2100) for i in range(K)]
+    K = len(pairs)
     sdr_len, hdr_len = abi.yuv420_size(W, H), abi.p010_size(W, H)
     d_sdr = torch.empty((B, sdr_len), dtype=torch.uint8, device=dev)
     d_hdr = torch.empty((B, hdr_len), dtype=torch.int16, device=dev)
     d_map = torch.zeros((B, MW * MH), dtype=torch.uint8, device=dev)
     d_out = torch.zeros((B, PIX), dtype=torch.int32, device=dev)
-    for i in range(K):
+
+    def roll420(dst, src, dy, dx):  # packed I420: Y | U | V
+        for off, pw, ph_, sc in ((0, W, H, 1), (W * H, W // 2, H // 2, 2), (W * H * 5 // 4, W // 2, H // 2, 2)):
+            dst[off:off + pw * ph_].view(ph_, pw).copy_(torch.roll(src[off:off + pw * ph_].view(ph_, pw), (dy // sc, dx // sc), (0, 1)))
+
+    def roll_p010(dst, src, dy, dx):  # Y plane | interleaved UV plane (dx even keeps the (u, v) pairing)
+        dst[:W * H].view(H, W).copy_(torch.roll(src[:W * H].view(H, W), (dy, dx), (0, 1)))
+        dst[W * H:].view(H // 2, W).copy_(torch.roll(src[W * H:].view(H // 2, W), (dy // 2, dx), (0, 1)))
+
+    for i in range(min(K, B)):
         s = torch.from_numpy(pairs[i][0]).to(dev)
         h = torch.from_numpy(pairs[i][1].view(np.int16)).to(dev)
-        d_sdr[i::K] = s
-        d_hdr[i::K] = h
+        for j in range(i, B, K):
+            roll420(d_sdr[j], s, 36 * (j // K), 64 * (j // K))
+            roll_p010(d_hdr[j], h, 36 * (j // K), 64 * (j // K))
     torch.cuda.synchronize()
 
     Img = abi.Image * B
@@ -471,6 +515,41 @@ def main():
         assert lib.uhdrb200_set_apply_mode(abi.APPLY_GENERIC) == 0
         other["apply_1010102_hlg_generic_kernel"] = timed(lambda: uh.applyGainMapBatch(Bo, sdrs, maps, md, abi.OUTPUT_HDR_HLG, FLT_MAX, bigs, stream), APPLY_BPP, 2)
         assert lib.uhdrb200_set_apply_mode(abi.APPLY_AUTO) == 0
+        # ---- real image content: the reference's own fixtures (tests/data, staged by build() into tests/_ref_data):
+        # the 1280x720 raw P010 + YUV420 pair of ProfileGainMapFuncs (tests/jpegr_test.cpp:2250-2304) tiled 3 x 3 to 4K,
+        # and the only photograph in the tree (minnie-320x240.yu12) tiled 12 x 9; every slot a different cyclic shift
+        if refdata.available():
+            fp, fw, fh = refdata.load("p010")
+            fy, _, _ = refdata.load("yuv420")
+            fm, mw0, mh0 = refdata.load("minnie")
+            base_s = torch.from_numpy(refdata.tile_yuv420(fy, fw, fh, W // fw, H // fh)[0]).to(dev)
+            base_h = torch.from_numpy(refdata.tile_p010(fp, fw, fh, W // fw, H // fh)[0].view(np.int16)).to(dev)
+            base_m = torch.from_numpy(refdata.tile_yuv420(fm, mw0, mh0, W // mw0, H // mh0)[0]).to(dev)
+            base_mm = torch.from_numpy(synth.natural_map(MW, MH, 71)).to(dev)
+            d_ps = torch.empty((Bo, sdr_len), dtype=torch.uint8, device=dev)
+            d_ph = torch.empty((Bo, hdr_len), dtype=torch.int16, device=dev)
+            d_pm = torch.empty((Bo, sdr_len), dtype=torch.uint8, device=dev)
+            pss, phs, pms = (abi.Image * Bo)(), (abi.Image * Bo)(), (abi.Image * Bo)()
+            for j in range(Bo):
+                dy, dx = 4 * ((5 * j) % MH), 4 * ((7 * j) % MW)
+                roll420(d_ps[j], base_s, dy, dx)
+                roll_p010(d_ph[j], base_h, dy, dx)
+                roll420(d_pm[j], base_m, dy, dx)
+                for arr, t in ((pss, d_ps), (pms, d_pm)):
+                    C.memmove(C.byref(arr[j]), C.byref(sdrs[j]), C.sizeof(abi.Image))
+                    arr[j].data, arr[j].chroma_data = t[j].data_ptr(), t[j].data_ptr() + W * H
+                C.memmove(C.byref(phs[j]), C.byref(hdrs[j]), C.sizeof(abi.Image))
+                phs[j].data, phs[j].chroma_data = d_ph[j].data_ptr(), d_ph[j].data_ptr() + 2 * W * H
+            other["generate_photo_content"] = timed(lambda: uh.generateGainMapBatch(Bo, pss, phs, abi.TF_HLG, mds, maps, False, stream), GEN_BPP)
+            other["generate_photo_content"]["content"] = "raw_p010_image.p010 + raw_yuv420_image.yuv420 (1280x720) tiled 3x3, 64 cyclic shifts"
+            other["apply_1010102_hlg_photo_content"] = timed(lambda: uh.applyGainMapBatch(Bo, pss, maps, md, abi.OUTPUT_HDR_HLG, FLT_MAX, bigs, stream), APPLY_BPP)
+            other["apply_1010102_hlg_photo_content"]["content"] = "raw_yuv420_image.yuv420 tiled 3x3 with its own generated gain map"
+            for j in range(Bo):
+                d_map[j].view(MH, MW).copy_(torch.roll(base_mm, ((5 * j) % MH, (7 * j) % MW), (0, 1)))
+            other["apply_1010102_hlg_photo_minnie"] = timed(lambda: uh.applyGainMapBatch(Bo, pms, maps, md, abi.OUTPUT_HDR_HLG, FLT_MAX, bigs, stream), APPLY_BPP)
+            other["apply_1010102_hlg_photo_minnie"]["content"] = "minnie-320x240.yu12 (photograph) tiled 12x9, smooth synthetic full-range gain map"
+            other["apply_rgba_f16_photo_minnie"] = timed(lambda: uh.applyGainMapBatch(Bo, pms, maps, md, abi.OUTPUT_HDR_LINEAR, FLT_MAX, bigs, stream), 9.5625)
+            del d_ps, d_ph, d_pm
         del d_tm, d_big
 
     # ---- e2e: host planes -> C ABI host entry points -> host results (copies inside the timing)
@@ -622,11 +701,12 @@ def main():
 
     app_gbs = B * PIX * APPLY_BPP / (app_ms * 1e-3) / 1e9
     gen_gbs = B * PIX * GEN_BPP / (gen_ms * 1e-3) / 1e9
-    value = world * B * PIX * a.steps / (total_ms * 1e-3) / 1e6
+    n_job = a.job_images or world * B  # images of the whole job per step
+    value = n_job * PIX * a.steps / (total_ms * 1e-3) / 1e6
     out = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3),
-        "ms_per_step": total_ms / a.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "f32", "data": f"synthetic ({K} distinct seeded natural pairs per rank replicated into {B} device slots; image i of the {world * B}-image job on rank i mod {world})",
+        "ms_per_step": total_ms / a.steps, "higher_is_better": True, "scaling": "strong" if a.job_images else "weak", "vs_baseline": None,
+        "dtype": "f32", "data": f"synthetic ({K} distinct seeded natural pairs per rank, cyclically shifted into {B} byte-distinct device slots; image i of the {a.job_images or world * B}-image job on rank i mod {world})",
         "config": config,
         "roofline": {"bound": "hbm", "kernel": "apply_q_kernel (applyGainMap -> RGBA1010102 HLG)", "achieved": app_gbs,
                      "peak": peak, "unit": "GB/s", "frac": app_gbs / peak, "traffic": traffic_of("apply_q_kernel"), "peak_source": peak_src,

@@ -279,6 +279,77 @@ def test_config5_image_sharded_batch_checksum(uh, orc, torch_cuda):
         assert int(o.view(np.int32).astype(np.int64).sum()) == int(sums[i])
 
 
+def test_config5_job_64_images_16_seeds_sharded(uh, torch_cuda):
+    """configs[4] as a FIXED job (strong scaling, bench.py --job-images): 64 4K pairs from 16 distinct seeds (each seed
+    in 4 cyclic shifts: 64 byte-distinct images), image i -> rank i mod G (shard.py). For G = 1, 2, 4 every rank's
+    batch launches run here one after the other; the merged per-image checksums must be identical for every G and
+    equal to single-image calls: sharding cannot change a byte."""
+    import concurrent.futures as cf
+    import multiprocessing as mp
+
+    from libultrahdr_dev_b200 import shard
+
+    t = torch_cuda
+    w, h, n, K = 3840, 2160, 64, 16
+    with cf.ProcessPoolExecutor(8, mp_context=mp.get_context("spawn")) as ex:
+        pairs = list(ex.map(synth.natural_pair, [w] * K, [h] * K, [500 + i for i in range(K)]))
+    sdr_len, hdr_len = abi.yuv420_size(w, h), abi.p010_size(w, h)
+    d_sdr = t.empty((n, sdr_len), dtype=t.uint8, device="cuda")
+    d_hdr = t.empty((n, hdr_len), dtype=t.int16, device="cuda")
+    d_map = t.zeros((n, w * h // 16), dtype=t.uint8, device="cuda")
+    d_out = t.zeros((n, w * h), dtype=t.int32, device="cuda")
+    for i in range(K):
+        s = t.from_numpy(pairs[i][0]).cuda()
+        hh = t.from_numpy(pairs[i][1].view(np.int16)).cuda()
+        for j in range(i, n, K):
+            dy, dx = 8 * (j // K), 16 * (j // K)
+            for off, pw, ph, sc in ((0, w, h, 1), (w * h, w // 2, h // 2, 2), (w * h * 5 // 4, w // 2, h // 2, 2)):
+                d_sdr[j, off:off + pw * ph].view(ph, pw).copy_(t.roll(s[off:off + pw * ph].view(ph, pw), (dy // sc, dx // sc), (0, 1)))
+            d_hdr[j, :w * h].view(h, w).copy_(t.roll(hh[:w * h].view(h, w), (dy, dx), (0, 1)))
+            d_hdr[j, w * h:].view(h // 2, w).copy_(t.roll(hh[w * h:].view(h // 2, w), (dy // 2, dx), (0, 1)))
+
+    def img_arrays(idx):
+        m = len(idx)
+        sd, hd, mp_, ou = (abi.Image * m)(), (abi.Image * m)(), (abi.Image * m)(), (abi.Image * m)()
+        for k, i in enumerate(idx):
+            sb, hb = d_sdr[i].data_ptr(), d_hdr[i].data_ptr()
+            sd[k].data, sd[k].chroma_data, sd[k].width, sd[k].height, sd[k].colorGamut = sb, sb + w * h, w, h, 0
+            sd[k].luma_stride, sd[k].chroma_stride, sd[k].pixelFormat = w, w // 2, abi.PIX_FMT_YUV420
+            hd[k].data, hd[k].chroma_data, hd[k].width, hd[k].height, hd[k].colorGamut = hb, hb + 2 * w * h, w, h, 2
+            hd[k].luma_stride, hd[k].chroma_stride, hd[k].pixelFormat = w, w, abi.PIX_FMT_P010
+            mp_[k].data, ou[k].data = d_map[i].data_ptr(), d_out[i].data_ptr()
+        return sd, hd, mp_, ou
+
+    st = t.cuda.current_stream().cuda_stream
+    merged = {}
+    for G in (1, 2, 4):
+        d_map.zero_()
+        d_out.zero_()
+        per_rank = []
+        for r in range(G):
+            idx = shard.shard_round_robin(n, r, G).indices
+            sd, hd, mp_, ou = img_arrays(idx)
+            mds = (abi.Metadata * len(idx))()
+            assert uh.generateGainMapBatch(len(idx), sd, hd, abi.TF_HLG, mds, mp_, False, st) == 0
+            assert uh.applyGainMapBatch(len(idx), sd, mp_, mds[0], abi.OUTPUT_HDR_HLG, FLT_MAX, ou, st) == 0
+            t.cuda.synchronize()
+            sums = d_out[idx].to(t.int64).sum(dim=1).cpu().numpy() * 1000003 + d_map[idx].to(t.int64).sum(dim=1).cpu().numpy()
+            per_rank.append([(i, int(c)) for i, c in zip(idx, sums)])
+        merged[G] = shard.merge_checksums(per_rank)
+    assert merged[1] == merged[2] == merged[4]
+    assert len(set(merged[1])) == n  # 64 byte-distinct images give 64 distinct checksums
+    for i in (0, 5, 37, 63):  # single-image device calls agree with the batch launches
+        sd, hd, mp_, ou = img_arrays([i])
+        d_map[i].zero_()
+        d_out[i].zero_()
+        md1 = abi.Metadata()
+        assert uh.generateGainMapDevice(sd[0], hd[0], abi.TF_HLG, md1, mp_[0], False, st) == 0
+        assert uh.applyGainMapDevice(sd[0], mp_[0], md1, abi.OUTPUT_HDR_HLG, FLT_MAX, ou[0], st) == 0
+        t.cuda.synchronize()
+        c = int(d_out[i].to(t.int64).sum()) * 1000003 + int(d_map[i].to(t.int64).sum())
+        assert c == merged[1][i]
+
+
 # ------------------------------------------------------------------------- N2: fused API-0 (toneMap + generate)
 @pytest.mark.parametrize("w,h,ls,cs,dls", [
     (256, 128, None, None, None),   # packed

@@ -72,7 +72,7 @@ def test_generate_parity(uh, orc, tf, sg, hg, kind):
     got, md_g, dest = gpu_generate(uh, sdr, hdr, tf)
     assert st == 0 and md_g.as_dict() == md_o.as_dict()
     assert (dest.width, dest.height, dest.luma_stride, dest.pixelFormat) == (w // 4, h // 4, w // 4, abi.PIX_FMT_MONOCHROME)
-    exact = parity.compare_bytes(got, want, f"map tf={tf} {sg}<-{hg} {kind}", min_exact=0.995)
+    exact = parity.compare_bytes(got, want, f"map tf={tf} {sg}<-{hg} {kind}", min_exact=0.999)
     print(f"generate tf={tf} sdr={sg} hdr={hg} {kind}: exact {exact:.5f}, map range {want.min()}..{want.max()}")
 
 
@@ -82,7 +82,7 @@ def test_generate_sdr_is_601(uh, orc):
     sdr, hdr = abi.host_yuv420(sdr_b, w, h, 0), abi.host_p010(hdr_b, w, h, 2)
     _, want, _, _ = orc.generate_gainmap(sdr, hdr, abi.TF_HLG, sdr_is_601=True)
     got, _, _ = gpu_generate(uh, sdr, hdr, abi.TF_HLG, sdr_is_601=True)
-    parity.compare_bytes(got, want, "map sdr_is_601", min_exact=0.995)
+    parity.compare_bytes(got, want, "map sdr_is_601", min_exact=0.999)
     _, other, _, _ = orc.generate_gainmap(sdr, hdr, abi.TF_HLG, sdr_is_601=False)
     assert not np.array_equal(want, other)  # the flag matters on this input
 
@@ -102,7 +102,7 @@ def test_generate_strides(uh, orc, w, h, sls, scs, hls, hcs):
     strided = gpu_generate(uh, abi.host_yuv420(sdr_s, w, h, 0, sls, scs), abi.host_p010(hdr_s, w, h, 2, hls, hcs), abi.TF_HLG)[0]
     assert np.array_equal(packed, strided)
     _, want, _, _ = orc.generate_gainmap(abi.host_yuv420(sdr_s, w, h, 0, sls, scs), abi.host_p010(hdr_s, w, h, 2, hls, hcs), abi.TF_HLG)
-    parity.compare_bytes(strided, want, "map strided", min_exact=0.99)
+    parity.compare_bytes(strided, want, "map strided", min_exact=0.995)
 
 
 # ------------------------------------------------------------------------------ applyGainMap
@@ -138,7 +138,9 @@ def test_apply_parity(uh, orc, fmt, kind, max_boost, apply_mode):
     st, want, _ = orc.apply_gainmap(sdr, mp, md, fmt, 3.4e38)  # FLT_MAX default, ultrahdr_api.cpp:1289
     got, dest = gpu_apply(uh, sdr, mp, md, fmt, 3.4e38)
     assert st == 0 and (dest.width, dest.height, dest.colorGamut) == (w, h, 0)
-    exact = parity.compare_output(fmt, got, want, w * h, f"apply fmt={fmt} {kind} boost={max_boost:.2f}", min_exact=0.97)
+    # floors: what DESIGN.md claims for the default (q-domain) kernels; the A/B and last-resort kernels a little lower
+    floor = 0.995 if apply_mode == abi.APPLY_AUTO else 0.99
+    exact = parity.compare_output(fmt, got, want, w * h, f"apply fmt={fmt} {kind} boost={max_boost:.2f}", min_exact=floor)
     print(f"apply mode={apply_mode} fmt={fmt} {kind} max_boost={max_boost:.2f}: exact {exact:.5f}")
 
 
@@ -152,7 +154,7 @@ def test_apply_scale_factors(uh, orc, scale, fmt):
     md = abi.default_metadata(4.926108)
     _, want, _ = orc.apply_gainmap(sdr, mp, md, fmt, 3.4e38)
     got, _ = gpu_apply(uh, sdr, mp, md, fmt, 3.4e38)
-    parity.compare_output(fmt, got, want, w * h, f"apply scale={scale}", min_exact=0.97)
+    parity.compare_output(fmt, got, want, w * h, f"apply scale={scale}", min_exact=0.995)
 
 
 @pytest.mark.parametrize("apply_mode", [abi.APPLY_AUTO, abi.APPLY_TWO_TABLE], indirect=True)
@@ -173,7 +175,7 @@ def test_apply_display_boost(uh, orc, boost, min_boost, apply_mode):
             g, wv = parity.unpack1010102(got, w * h)[:, :3], parity.unpack1010102(want, w * h)[:, :3]
             d = np.abs(g - wv)
             d = np.minimum(d, 1024 - d)  # +-1 LSB across the 10-bit wrap
-            assert d.max() <= 1 and (d == 0).mean() >= 0.99
+            assert d.max() <= 1 and (d == 0).mean() >= 0.995
         else:
             parity.compare_output(fmt, got, want, w * h, f"apply boost={boost}")
 
@@ -197,7 +199,7 @@ def test_apply_strides(uh, orc, w, h, ls, cs):
         if aligned(w, w // 2) == aligned(ls or w, cs or w // 2):
             assert np.array_equal(a, b)
         else:
-            parity.compare_output(fmt, a, b, w * h, f"apply packed vs strided fmt={fmt}", min_exact=0.97)
+            parity.compare_output(fmt, a, b, w * h, f"apply packed vs strided fmt={fmt}", min_exact=0.99)
         _, want, _ = orc.apply_gainmap(abi.host_yuv420(sdr_s, w, h, 0, ls, cs), mp, md, fmt, 3.4e38)
         parity.compare_output(fmt, b, want, w * h, f"apply strided fmt={fmt}")
 
@@ -222,7 +224,7 @@ def test_apply_fast_path_strides(uh, orc, w, h, ls, cs, apply_mode):
         if aligned(w, w // 2) == aligned(ls or w, cs or w // 2):
             assert np.array_equal(a, b)
         else:
-            parity.compare_output(fmt, a, b, w * h, f"apply packed vs strided fmt={fmt}", min_exact=0.97)
+            parity.compare_output(fmt, a, b, w * h, f"apply packed vs strided fmt={fmt}", min_exact=0.99)
         _, want, _ = orc.apply_gainmap(abi.host_yuv420(sdr_s, w, h, 0, ls, cs), mp, md, fmt, 3.4e38)
         parity.compare_output(fmt, b, want, w * h, f"apply scale-4 strided fmt={fmt}")
 

@@ -47,7 +47,7 @@ def test_sweep_generate(uh, orc, seed):
     got, md, dest = gpu_generate(uh, sdr, hdr, tf, is601)
     assert st == 0 and md.as_dict() == md_o.as_dict()
     assert (dest.width, dest.height) == (w // 4, h // 4)
-    parity.compare_bytes(got, want, f"sweep generate seed={seed} {w}x{h} tf={tf} {sg}->{hg} 601={is601} {kind}", min_exact=0.99)
+    parity.compare_bytes(got, want, f"sweep generate seed={seed} {w}x{h} tf={tf} {sg}->{hg} 601={is601} {kind}", min_exact=0.999 if w * h >= 4096 else 0.99)
 
 
 @pytest.mark.parametrize("seed", range(32))
@@ -85,11 +85,46 @@ def test_sweep_apply(uh, orc, seed):
         g, wv = parity.unpack1010102(got, w * h)[:, :3], parity.unpack1010102(want, w * h)[:, :3]
         d = np.abs(g - wv)
         d = np.minimum(d, 1024 - d)
-        assert d.max() <= 1 and (d == 0).mean() >= 0.97, what
+        assert d.max() <= 1 and (d == 0).mean() >= 0.99, what
     elif fmt == abi.OUTPUT_HDR_LINEAR_RGB_10BIT and disp < max_boost:
         g, wv = parity.unpack_planar10(got, w * h), parity.unpack_planar10(want, w * h)
         d = np.abs(g - wv)
         d = np.minimum(d, 1024 - d)
-        assert d.max() <= 1 and (d == 0).mean() >= 0.97, what
+        assert d.max() <= 1 and (d == 0).mean() >= 0.99, what
     else:
-        parity.compare_output(fmt, got, want, w * h, what, min_exact=0.97)
+        parity.compare_output(fmt, got, want, w * h, what, min_exact=0.995 if w * h >= 4096 else 0.98)
+
+
+# ------------------------------------------------------------------------------ the reference's size limits
+# kMaxWidth = kMaxHeight = 8192 (lib/include/ultrahdr/jpegr.h:31-32, fuzzer/ultrahdr_enc_fuzzer.cpp:116): extreme aspect
+# ratios and an almost-maximal image with padded strides, so that the 32-bit plane offsets of the kernels run near
+# their limits. Uniform-random planes; the oracle (4 threads) needs a few seconds for the large case.
+LIMITS = [(8192, 8, None, None, None, None), (8, 8192, None, None, None, None), (8190, 4094, 8200, 4104, 8198, 8204)]
+
+
+@pytest.mark.parametrize("w,h,sls,scs,hls,hcs", LIMITS)
+def test_limits_generate(uh, orc, w, h, sls, scs, hls, hcs):
+    sdr_b, hdr_b = synth.uniform_pair(w, h, 77, sls, scs, hls, hcs)
+    sdr = abi.host_yuv420(sdr_b, w, h, abi.COLORGAMUT_BT709, sls, scs)
+    hdr = abi.host_p010(hdr_b, w, h, abi.COLORGAMUT_BT2100, hls, hcs)
+    st, want, md_o, _ = orc.generate_gainmap(sdr, hdr, abi.TF_HLG)
+    got, md, dest = gpu_generate(uh, sdr, hdr, abi.TF_HLG)
+    assert st == 0 and md.as_dict() == md_o.as_dict() and (dest.width, dest.height) == (w // 4, h // 4)
+    exact = parity.compare_bytes(got, want, f"limits generate {w}x{h}", min_exact=0.999)
+    print(f"limits generate {w}x{h}: exact {exact:.6f}")
+
+
+@pytest.mark.parametrize("w,h,sls,scs,scale", [(8192, 8, None, None, 4), (8, 8192, None, None, 4), (8190, 4094, 8200, 4104, 2),
+                                                (8192, 4096, None, None, 4)])
+@pytest.mark.parametrize("fmt", [abi.OUTPUT_HDR_HLG, abi.OUTPUT_HDR_LINEAR])
+def test_limits_apply(uh, orc, w, h, sls, scs, scale, fmt):
+    sdr_b, _ = synth.uniform_pair(w, h, 78, sls, scs)
+    mp_b = _rng(79).integers(0, 256, (h // scale, w // scale), dtype=np.uint8)
+    sdr = abi.host_yuv420(sdr_b, w, h, abi.COLORGAMUT_BT709, sls, scs)
+    mp = abi.host_map(mp_b, w // scale, h // scale)
+    md = abi.default_metadata(1000.0 / 203.0)
+    st, want, _ = orc.apply_gainmap(sdr, mp, md, fmt, FLT_MAX)
+    got, dest = gpu_apply(uh, sdr, mp, md, fmt, FLT_MAX)
+    assert st == 0 and (dest.width, dest.height) == (w, h)
+    exact = parity.compare_output(fmt, got, want, w * h, f"limits apply {w}x{h} scale={scale} fmt={fmt}", min_exact=0.995)
+    print(f"limits apply {w}x{h} scale={scale} fmt={fmt}: exact {exact:.6f}")
