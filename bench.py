@@ -470,9 +470,9 @@ def main():
         r.update(mpix_s=r["mpix_s"] * scale, achieved_gbs=r["achieved_gbs"] * scale, images_per_launch=1, image="8160x6144")
         other["convert_yuv_709_to_601_50mp"] = r
         del d_cv
-        assert lib.uhdrb200_set_apply_mode(abi.APPLY_TWO_TABLE) == 0
+        assert lib.uhdrb200_test_set_apply_mode(abi.APPLY_TWO_TABLE) == 0
         other["apply_1010102_hlg_two_table_kernel"] = timed(lambda: uh.applyGainMapBatch(Bo, sdrs, maps, md, abi.OUTPUT_HDR_HLG, FLT_MAX, bigs, stream), APPLY_BPP)
-        assert lib.uhdrb200_set_apply_mode(abi.APPLY_AUTO) == 0
+        assert lib.uhdrb200_test_set_apply_mode(abi.APPLY_AUTO) == 0
         # worst case for the q-domain kernel: i.i.d. uniform 8-bit samples (SURVEY 8d "uniform"), 19 % of the channels on
         # srgbInvOetf's linear toe -> almost every quad-row takes the exact (MUFU) branch
         d_rnd = torch.randint(0, 256, (Bo, sdr_len), dtype=torch.uint8, device=dev)
@@ -512,9 +512,9 @@ def main():
             maps1[i].pixelFormat = abi.PIX_FMT_MONOCHROME
         other["apply_1010102_hlg_map_scale_1"] = timed(lambda: uh.applyGainMapBatch(Bo, sdrs, maps1, md, abi.OUTPUT_HDR_HLG, FLT_MAX, bigs, stream), 1.5 + 1.0 + 4.0)
         del d_map1
-        assert lib.uhdrb200_set_apply_mode(abi.APPLY_GENERIC) == 0
+        assert lib.uhdrb200_test_set_apply_mode(abi.APPLY_GENERIC) == 0
         other["apply_1010102_hlg_generic_kernel"] = timed(lambda: uh.applyGainMapBatch(Bo, sdrs, maps, md, abi.OUTPUT_HDR_HLG, FLT_MAX, bigs, stream), APPLY_BPP, 2)
-        assert lib.uhdrb200_set_apply_mode(abi.APPLY_AUTO) == 0
+        assert lib.uhdrb200_test_set_apply_mode(abi.APPLY_AUTO) == 0
         # ---- real image content: the reference's own fixtures (tests/data, staged by build() into tests/_ref_data):
         # the 1280x720 raw P010 + YUV420 pair of ProfileGainMapFuncs (tests/jpegr_test.cpp:2250-2304) tiled 3 x 3 to 4K,
         # and the only photograph in the tree (minnie-320x240.yu12) tiled 12 x 9; every slot a different cyclic shift

@@ -138,15 +138,6 @@ void uhdrb200_free(void* p);
 /* number of kernel launches issued by this library in the calling process (monotonic). */
 uint64_t uhdrb200_launch_count(void);
 
-/* applyGainMap kernel selection (process-wide): AUTO uses the table-driven q-domain kernels whenever the
- * layout allows it (4-aligned planes and strides, image a multiple of 4 and of the map scale factor: the scale-4
- * kernel, the scale-1 / scale-2 specialisations or the run-time-scale kernel) and the analytic kernel otherwise;
- * GENERIC forces the analytic kernel (any layout, MUFU-evaluated transfer functions); TWO_TABLE routes scale-4
- * inputs through the srgbInvOetf-table + OETF-table kernel instead of the single-table q-domain kernel (kept for
- * A/B measurements and as a cross-check in the tests). */
-enum { UHDRB200_APPLY_AUTO = 0, UHDRB200_APPLY_GENERIC = 1, UHDRB200_APPLY_TWO_TABLE = 2 };
-int uhdrb200_set_apply_mode(int mode);
-
 /* How the synchronous *_host entry points wait for their stream (process-wide). The reference joins its row-block
  * worker threads before returning (ultrahdr.cpp:354, 513); here the join is a stream wait. SPIN (default,
  * cudaStreamSynchronize) has the lowest latency; BLOCKING sleeps on a cudaEventBlockingSync event, which is what a

@@ -1,0 +1,48 @@
+/*
+ * uhdr_b200_test.h — TEST HOOKS of libuhdr_b200.so. Not part of the drop-in boundary (include/uhdr_b200.h): nothing a
+ * libultrahdr caller needs is declared here, and the shim never calls these. They exist so that tests/ and bench.py can
+ * (a) force a particular applyGainMap kernel family for A/B measurements and cross-checks, and (b) run the device-side
+ * pixel math (csrc/uhdr_math.cuh, the shared-memory table evaluators) over an array of arguments, which is how the
+ * known-answer tests of the reference's tests/gainmapmath_test.cpp are applied to the device functions one by one.
+ */
+#ifndef UHDR_B200_TEST_H
+#define UHDR_B200_TEST_H
+#include <stddef.h>
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* applyGainMap kernel selection FOR THE CALLING THREAD ONLY (thread-local; other threads keep AUTO):
+ * AUTO      what a caller gets: the TMA-fed q-domain pipeline (apply_pipe.cu) when the layout allows 16-byte bulk copies,
+ *           else the q-domain kernels fed by plain loads (scale 4, scale 1 / 2, any integer scale), else the analytic kernel;
+ * GENERIC   the analytic kernel (any layout, MUFU-evaluated transfer functions);
+ * TWO_TABLE scale-4 inputs through the srgbInvOetf-table + OETF-table kernel (previous design, kept as a cross-check);
+ * Q_LDG     the q-domain kernels fed by plain loads even where the pipeline would be eligible. */
+enum { UHDRB200_APPLY_AUTO = 0, UHDRB200_APPLY_GENERIC = 1, UHDRB200_APPLY_TWO_TABLE = 2, UHDRB200_APPLY_Q_LDG = 3 };
+int uhdrb200_test_set_apply_mode(int mode);
+
+/* Evaluates device function `fn` over n floats (device pointers, asynchronous on `stream`): out[i] = fn(in[i]).
+ * Integer-valued functions return their result as a float (exact below 2^24). For the two-argument functions
+ * `in` holds n pairs. Returns a status_t value. */
+enum {
+  UHDRB200_FN_SRGB_INV_OETF = 0, /* gainmapmath.cpp:149-155 */
+  UHDRB200_FN_HLG_OETF = 1,      /* :259-267 */
+  UHDRB200_FN_HLG_INV_OETF = 2,  /* :280-290 */
+  UHDRB200_FN_PQ_OETF = 3,       /* :309-314 */
+  UHDRB200_FN_PQ_INV_OETF = 4,   /* :330-342 */
+  UHDRB200_FN_FLOAT_TO_HALF = 5, /* gainmapmath.h:136-147 */
+  UHDRB200_FN_TO_10BIT = 6,      /* one channel of colorToRgba1010102, gainmapmath.cpp:722-727 */
+  UHDRB200_FN_P_HLG = 7,         /* shared-memory table: 1023 * hlgOetf(q^2.4), argument q */
+  UHDRB200_FN_P_PQ = 8,          /* shared-memory table: 1023 * pqOetf(q^2.4), argument q */
+  UHDRB200_FN_L_POW = 9,         /* shared-memory table: q^2.4 = f * srgbInvOetf(c) above the toe, argument q in [2^-6, 2) */
+  UHDRB200_FN_TOE_FIX = 10,      /* Phi -> srgbInvOetf(c)^(1/2.4) with c = 1.055 Phi - 0.055 (toe select, apply_q_common.cuh) */
+  UHDRB200_FN_ENCODE_GAIN = 11,  /* pairs (y_sdr, y_hdr) -> encodeGain byte for HLG metadata (min 1, max 1000/203), :524-541 */
+  UHDRB200_FN_COUNT = 12
+};
+int uhdrb200_test_eval(int fn, const float* in_dev, float* out_dev, size_t n, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* UHDR_B200_TEST_H */

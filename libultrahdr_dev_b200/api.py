@@ -31,7 +31,6 @@ SYMBOLS = {
     "uhdrb200_host_free": (None, [C.c_void_p]),
     "uhdrb200_free": (None, [C.c_void_p]),
     "uhdrb200_launch_count": (C.c_uint64, []),
-    "uhdrb200_set_apply_mode": (C.c_int, [C.c_int]),
     "uhdrb200_set_sync_mode": (C.c_int, [C.c_int]),
     "uhdrb200_generate_gainmap_host": (C.c_int, [P_IMG, P_IMG, C.c_int, P_MD, P_IMG, C.c_int]),
     "uhdrb200_generate_gainmap_host_into": (C.c_int, [P_IMG, P_IMG, C.c_int, P_MD, P_IMG, C.c_int, C.c_void_p, C.c_size_t]),
@@ -56,6 +55,13 @@ SYMBOLS = {
 }
 
 
+# test hooks (include/uhdr_b200_test.h): not part of the drop-in boundary
+TEST_SYMBOLS = {
+    "uhdrb200_test_set_apply_mode": (C.c_int, [C.c_int]),
+    "uhdrb200_test_eval": (C.c_int, [C.c_int, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
+}
+
+
 class UltraHdrCudaError(RuntimeError):
     pass
 
@@ -74,7 +80,7 @@ def load_library(path=None):
             f"{p} is missing: build it with `python -m libultrahdr_dev_b200.build` "
             "(or __graft_entry__.build()). There is no CPU fallback.")
     lib = C.CDLL(p)
-    for name, (res, args) in SYMBOLS.items():
+    for name, (res, args) in list(SYMBOLS.items()) + list(TEST_SYMBOLS.items()):
         f = getattr(lib, name)
         f.restype = res
         f.argtypes = args

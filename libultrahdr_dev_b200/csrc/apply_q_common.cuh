@@ -171,6 +171,19 @@ constexpr int kLMufu = UHDR_L_MUFU_CHANNELS;
 
 #if UHDR_APPLYQ_F32X2
 // q_rows for RGBA1010102 above the toe, without the `& 0x3ff` wrap, on packed fp32x2 arithmetic
+// srgbInvOetf's linear toe in the Phi domain: for c <= 0.04045 (Phi <= kPhiThr) the factor is (c / 12.92)^(1/2.4) with
+// c = 1.055 * Phi - 0.055 (clamped at 0: the reference clamps c, gainmapmath.cpp:142-146); 2 MUFU + 4 FMA/ALU-pipe
+// operations per channel. At the threshold both branches agree to 2e-6 relative, so deciding on Phi instead of on the
+// reference's own c changes no code.
+__device__ __forceinline__ float toe_fix(float phi) {
+  constexpr float kPhiThr = (float)((0.04045 + 0.055) / 1.055);
+  constexpr float kToeA = (float)(1.0 / 2.4), kToeB = (float)(-3.6915341649192007 / 2.4);  // lg2(12.92) = 3.69153...
+  const float c = __saturatef(fmaf(phi, 1.055f, -0.055f));
+  const float t = mufu_ex2(fmaf(mufu_lg2(c), kToeA, kToeB));  // c == 0: lg2 = -inf, ex2(-inf) = +0
+  return phi <= kPhiThr ? t : phi;
+}
+
+template <bool kToe = false>
 __device__ __forceinline__ void q_rows_paired(const uint32_t hiP, const float (&oR)[2], const float (&oG)[2], const float (&oB)[2],
                                               const float (&yf)[2][4], const float* __restrict__ f8, uint8_t* orow, const size_t ostride) {
   constexpr float KP = (float)(1.0 / (255.0 * 1.055));
@@ -187,9 +200,17 @@ __device__ __forceinline__ void q_rows_paired(const uint32_t hiP, const float (&
     for (int c = 0; c < 2; c++) {
       const float y0 = yf[rr][2 * c], y1 = yf[rr][2 * c + 1];
       const f32x2 ff = pk2(f8[rr * 4 + 2 * c], f8[rr * 4 + 2 * c + 1]);
-      const f32x2 qR = fma2(pk2(__saturatef(fmaf(y0, KP, oR[c])), __saturatef(fmaf(y1, KP, oR[c]))), ff, q0q0);
-      const f32x2 qG = fma2(pk2(__saturatef(fmaf(y0, KP, oG[c])), __saturatef(fmaf(y1, KP, oG[c]))), ff, q0q0);
-      const f32x2 qB = fma2(pk2(__saturatef(fmaf(y0, KP, oB[c])), __saturatef(fmaf(y1, KP, oB[c]))), ff, q0q0);
+      float pR0 = __saturatef(fmaf(y0, KP, oR[c])), pR1 = __saturatef(fmaf(y1, KP, oR[c]));
+      float pG0 = __saturatef(fmaf(y0, KP, oG[c])), pG1 = __saturatef(fmaf(y1, KP, oG[c]));
+      float pB0 = __saturatef(fmaf(y0, KP, oB[c])), pB1 = __saturatef(fmaf(y1, KP, oB[c]));
+      if (kToe) {  // a quad-row some lane of the warp has a toe channel in: every channel takes the exact select
+        pR0 = toe_fix(pR0); pR1 = toe_fix(pR1);
+        pG0 = toe_fix(pG0); pG1 = toe_fix(pG1);
+        pB0 = toe_fix(pB0); pB1 = toe_fix(pB1);
+      }
+      const f32x2 qR = fma2(pk2(pR0, pR1), ff, q0q0);
+      const f32x2 qG = fma2(pk2(pG0, pG1), ff, q0q0);
+      const f32x2 qB = fma2(pk2(pB0, pB1), ff, q0q0);
       float a0, a1;
       unpk2(qR, a0, a1);
       const f32x2 vR = pk2(p_eval(hiP, a0), p_eval(hiP, a1));
@@ -456,9 +477,12 @@ __device__ __forceinline__ uint32_t stage_q_table(const ApplyFastParams& p, cons
 // One quad-row of a 4x4 block (2 pixel rows x 4 columns = two 2x2 chroma quads) given its 8 gain factors f' = f^(1/2.4):
 // Phi-domain chroma offsets, int -> float luma, the conservative toe test and the look-up / pack / store of both rows.
 // yw0 / yw1 = the 4 luma bytes of the two rows, uq / vq = the two chroma bytes, orow = output address of the first row.
-template <int PACK, bool MASK, bool LTAB, bool NORM>
+// VOTE: `vote_mask` names the lanes executing this call together; when any of them has a toe channel the whole
+// group takes the toe-capable path (one pass through one path instead of both paths one after the other).
+template <int PACK, bool MASK, bool LTAB, bool NORM, bool VOTE = false>
 __device__ __forceinline__ void quad_row_eval(const uint32_t hiP, const uint32_t yw0, const uint32_t yw1, const uint32_t uq, const uint32_t vq,
-                                              const float (&f)[8], uint8_t* orow, const size_t ostride, const size_t plane_bytes) {
+                                              const float (&f)[8], uint8_t* orow, const size_t ostride, const size_t plane_bytes,
+                                              const unsigned vote_mask = 0xffffffffu) {
   // Phi-domain constants (double on the host side of the compiler): K = 1/(255*1.055), chroma gains of the
   // BT.601 matrix (gainmapmath.cpp:177-196) times K, offsets = 0.055/1.055 - 128 * gain
   constexpr double dK = 1.0 / (255.0 * 1.055);
@@ -502,7 +526,12 @@ __device__ __forceinline__ void quad_row_eval(const uint32_t hiP, const uint32_t
 #else
         const bool toe = fminf(fmaf(ym0, KP, om0), fmaf(ym1, KP, om1)) <= kPhiToe;
 #endif
-        if (toe) q_rows<PACK, MASK, true, LTAB, NORM>(hiP, uq, vq, oR, oG, oB, yf, f, orow, ostride, plane_bytes);
+        if constexpr (VOTE && PACK == kPack1010102 && !MASK && UHDR_APPLYQ_F32X2) {
+          if (__any_sync(vote_mask, toe)) q_rows_paired<true>(hiP, oR, oG, oB, yf, f, orow, ostride);
+          else q_rows_paired<false>(hiP, oR, oG, oB, yf, f, orow, ostride);
+          return;
+        }
+        if (VOTE ? __any_sync(vote_mask, toe) : toe) q_rows<PACK, MASK, true, LTAB, NORM>(hiP, uq, vq, oR, oG, oB, yf, f, orow, ostride, plane_bytes);
 #if UHDR_APPLYQ_F32X2
         else if constexpr (PACK == kPack1010102 && !MASK) q_rows_paired(hiP, oR, oG, oB, yf, f, orow, ostride);
         else if constexpr (LTAB) q_rows_paired_lin<PACK, NORM, MASK>(hiP, oR, oG, oB, yf, f, orow, ostride, plane_bytes);

@@ -19,6 +19,7 @@
 #include <vector>
 
 #include "../../include/uhdr_b200.h"
+#include "../../include/uhdr_b200_test.h"
 #include "uhdr_kernels.cuh"
 #include "uhdr_math.cuh"
 
@@ -27,7 +28,9 @@ using namespace uhdr;
 
 std::atomic<uint64_t> g_launches{0};
 std::atomic<int> g_sync_mode{-1};  // -1: from the environment (UHDRB200_BLOCKING_SYNC), 0 spin, 1 blocking
-std::atomic<int> g_apply_mode{0};  // 0 auto (table-driven fast path when eligible), 1 force the generic kernel
+// test hook (include/uhdr_b200_test.h), per calling thread: 0 auto, 1 analytic kernel, 2 two-table kernel, 3 q-domain kernels
+// fed by plain loads (no TMA pipeline)
+thread_local int t_apply_mode = 0;
 
 // ---------------------------------------------------------------- per-thread context
 struct DevBuf {
@@ -413,6 +416,21 @@ int validate_tonemap(const uhdrb200_image* src, const uhdrb200_image* dest) {
 
 bool fits_int(size_t v) { return v <= (size_t)0x7fffffff; }
 
+// encodeGain's constants (gainmapmath.cpp:524-541, ultrahdr.cpp:259-260): float-rounded log2 bounds, and the codes of a
+// gain clamped to min / max evaluated in double like the reference
+GainCode gain_code_of(float min_boost, float max_boost) {
+  GainCode k;
+  k.min_boost = min_boost;
+  k.max_boost = max_boost;
+  k.log2_min = (float)log2((double)min_boost);
+  const float log2_max = (float)log2((double)max_boost);
+  const double den = (double)(log2_max - k.log2_min);
+  k.code_at_min = (int)(uint8_t)((log2((double)min_boost) - (double)k.log2_min) / den * 255.0);
+  k.code_at_max = (int)(uint8_t)((log2((double)max_boost) - (double)k.log2_min) / den * 255.0);
+  k.code_scale = (float)(255.0 / den);
+  return k;
+}
+
 Geometry geometry_of(const uhdrb200_image* sdr, const uhdrb200_image* hdr) {
   Geometry g;
   memset(&g, 0, sizeof g);
@@ -476,16 +494,7 @@ int generate_core(int n, const uhdrb200_image* sdr, const uhdrb200_image* hdr, i
     v[i].out = dest[i].data;
     vec = vec && generate_vec_ok(p.g, v[i]);
   }
-  p.min_boost = md[0].minContentBoost;
-  p.max_boost = md[0].maxContentBoost;
-  p.log2_min = (float)log2((double)p.min_boost);  // ultrahdr.cpp:259-260
-  p.log2_max = (float)log2((double)p.max_boost);
-  {  // gainmapmath.cpp:539-540 for gain == min / max, in double like the reference
-    const double den = (double)(p.log2_max - p.log2_min);
-    p.code_at_min = (int)(uint8_t)((log2((double)p.min_boost) - (double)p.log2_min) / den * 255.0);
-    p.code_at_max = (int)(uint8_t)((log2((double)p.max_boost) - (double)p.log2_min) / den * 255.0);
-    p.code_scale = (float)(255.0 / den);
-  }
+  p.gc = gain_code_of(md[0].minContentBoost, md[0].maxContentBoost);
   if (conv) {
     p.convert = 1;
     memcpy(p.conv, conv, sizeof p.conv);
@@ -547,10 +556,10 @@ int apply_core(int n, const uhdrb200_image* sdr, const uhdrb200_image* map, cons
   }
   // Fast path (apply_fast.cu): map scale 4, 4-aligned planes, and a gain factor
   // f = 2^(gain*A + B) (gain in [0,1]) small enough for the OETF table range.
-  bool fast = g_apply_mode != 1;
+  bool fast = t_apply_mode != 1;
   for (int i = 0; i < n && fast; i++) fast = apply_fast_ok(p.g, v[i]);
   // other integer scale factors (or scale 4 with a ragged map) keep the q-domain tables through apply_qs_kernel
-  bool any_scale = !fast && g_apply_mode == 0;
+  bool any_scale = !fast && (t_apply_mode == 0 || t_apply_mode == 3);
   for (int i = 0; i < n && any_scale; i++) any_scale = apply_qs_ok(p.g, v[i]);
   fast = fast || any_scale;
   const double k = (double)p.display_boost / (double)p.max_boost;
@@ -578,7 +587,7 @@ int apply_core(int n, const uhdrb200_image* sdr, const uhdrb200_image* map, cons
     f.Aq = (float)(A / 2.4 / 255.0);  // the q kernel keeps the map samples as 0..255 floats
     f.Bq = (float)(B / 2.4);
     f.q0 = (float)ldexp(1.0, kPLoExp);
-    f.two_table = g_apply_mode == 2;
+    f.two_table = t_apply_mode == 2;
     f.any_scale = any_scale ? 1 : 0;
     if (any_scale && (p.g.map_scale == 1 || p.g.map_scale == 2)) {
       bool al = true;  // the specialised kernels read the map as 32-bit (scale 1) / 16-bit (scale 2) words
@@ -1073,9 +1082,21 @@ void* uhdrb200_host_alloc(size_t bytes) {
 void uhdrb200_host_free(void* p) { if (p) cudaFreeHost(p); }
 void uhdrb200_free(void* p) { free(p); }
 uint64_t uhdrb200_launch_count(void) { return g_launches.load(); }
-int uhdrb200_set_apply_mode(int mode) {
-  if (mode != UHDRB200_APPLY_AUTO && mode != UHDRB200_APPLY_GENERIC && mode != UHDRB200_APPLY_TWO_TABLE) return UHDRB200_ERROR_UNSUPPORTED_FEATURE;
-  g_apply_mode = mode;
+int uhdrb200_test_set_apply_mode(int mode) {
+  if (mode < UHDRB200_APPLY_AUTO || mode > UHDRB200_APPLY_Q_LDG) return UHDRB200_ERROR_UNSUPPORTED_FEATURE;
+  t_apply_mode = mode;
+  return UHDRB200_NO_ERROR;
+}
+int uhdrb200_test_eval(int fn, const float* in_dev, float* out_dev, size_t n, void* stream) {
+  if (fn < 0 || fn >= UHDRB200_FN_COUNT) return UHDRB200_ERROR_UNSUPPORTED_FEATURE;
+  if (n && (!in_dev || !out_dev)) return UHDRB200_ERROR_BAD_PTR;
+  int st = ensure_ctx();
+  if (st) return st;
+  ApplyTables tab;
+  if ((st = get_apply_tables(t_ctx.device, &tab))) return st;
+  const GainCode gc = gain_code_of(1.0f, 1000.0f / 203.0f);  // what generateGainMap writes for HLG (ultrahdr.cpp:250-257)
+  cudaError_t e = launch_kat_impl(fn, in_dev, out_dev, n, tab, gc, (cudaStream_t)stream);
+  if (e != cudaSuccess) return fail(e, "test_eval kernel launch");
   return UHDRB200_NO_ERROR;
 }
 int uhdrb200_set_sync_mode(int mode) {

@@ -161,16 +161,8 @@ __global__ void __launch_bounds__(256) generate_kernel(GenerateParams p) {
   if (p.use_gamut) hl = mat3_apply_fma(p.gamut, hl);
   const float hdr_nits = luminance_fma(lk, hl) * p.hdr_white_nits;
 
-  // ---- encodeGain (gainmapmath.cpp:529-541), truncating ----
-  float gain = 1.0f;
-  if (sdr_nits > 0.0f) gain = hdr_nits * mufu_rcp(sdr_nits);
-  float v = (mufu_lg2(gain) - p.log2_min) * p.code_scale;  // code_scale = 255 / (log2_max - log2_min), host double
-  uint32_t code = __float2uint_rz(v);
-  // A clamped gain is the common case (saturated map bytes); there the reference's double-precision
-  // quotient against the float-rounded log2 bounds decides between e.g. 254 and 255, so those two
-  // codes come from the host, computed exactly as the reference does.
-  if (gain <= p.min_boost) code = p.code_at_min;
-  if (gain >= p.max_boost) code = p.code_at_max;
+  // ---- encodeGain (gainmapmath.cpp:529-541), truncating; clamped gains take the host-computed codes ----
+  const uint32_t code = encode_gain(sdr_nits, hdr_nits, p.gc);
   ((uint8_t*)pl.out)[(size_t)my * g.map_width + mx] = (uint8_t)code;
 }
 

@@ -39,9 +39,7 @@ struct GenerateParams {
   int use_gamut;    // 0 when both gamuts are equal (identityConversion)
   int hdr_tf;       // 0 linear, 1 HLG, 2 PQ
   float hdr_white_nits;
-  float min_boost, max_boost, log2_min, log2_max;
-  int code_at_min, code_at_max;  // encodeGain of a gain clamped to min/max, evaluated on the host in double
-  float code_scale;              // 255 / (log2_max - log2_min), the float difference like the reference, in double
+  GainCode gc;      // encodeGain constants (uhdr_math.cuh), filled by the host
   int convert;                   // fused API-0 only: 1 = the SDR planes are written re-encoded with `conv` (row N1, jpegr.cpp:223-225)
   float conv[9];                 // YUV->YUV matrix, gainmapmath.cpp:447-481
   Planes single;
@@ -167,6 +165,8 @@ cudaError_t launch_apply_fast_impl(ApplyFastParams& p, int n, cudaStream_t s);
 // host: fills the double-precision-built tables (tables.cu)
 void build_apply_tables(float2* s, float2* s_hi, float2* o_hlg, float2* o_pq, float2* p_hlg, float2* p_pq, float2* l_pow, float* e255);
 cudaError_t launch_tonemap_impl(const ToneMapParams& p, int n, bool vec, cudaStream_t s);
+// test hook (include/uhdr_b200_test.h): out[i] = fn(in[i]) with the device functions of uhdr_math.cuh / apply_q_common.cuh
+cudaError_t launch_kat_impl(int fn, const float* in, float* out, size_t n, const ApplyTables& tab, const GainCode& gc, cudaStream_t s);
 bool sdr_pack_vec_ok(const Geometry& g, const Planes& pl);
 cudaError_t launch_sdr_pack_impl(const SdrPackParams& p, int n, bool vec, cudaStream_t s);
 cudaError_t launch_copy_yuv420_impl(const SdrPackParams& p, int n, cudaStream_t s);

@@ -161,6 +161,24 @@ __device__ __forceinline__ Color3 mat3_apply(const Mat3& k, Color3 e) {
           k.m[6] * e.r + k.m[7] * e.g + k.m[8] * e.b};
 }
 
+// ---- encodeGain, gainmapmath.cpp:524-541 (truncating). The reference evaluates log2 in double against float-rounded
+// log2 bounds; a gain clamped to min / max (the common case: saturated map bytes) takes its code from the host, which
+// computes it exactly as the reference does (capi.cu: gain_code_of).
+struct GainCode {
+  float min_boost, max_boost, log2_min;
+  float code_scale;              // 255 / (log2_max - log2_min), the float difference like the reference, in double
+  int code_at_min, code_at_max;  // encodeGain of a gain clamped to min / max
+};
+__device__ __forceinline__ uint32_t encode_gain(float sdr_nits, float hdr_nits, const GainCode& k) {
+  float gain = 1.0f;
+  if (sdr_nits > 0.0f) gain = hdr_nits * mufu_rcp(sdr_nits);
+  const float v = (mufu_lg2(gain) - k.log2_min) * k.code_scale;
+  uint32_t code = __float2uint_rz(v);
+  if (gain <= k.min_boost) code = (uint32_t)k.code_at_min;
+  if (gain >= k.max_boost) code = (uint32_t)k.code_at_max;
+  return code;
+}
+
 // ---- packers ----
 // floatToHalf, gainmapmath.h:136-147: bit-exact integer routine (+0x1000 rounding, saturate to
 // 0x7FFF, flush e<=101 to zero).

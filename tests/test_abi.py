@@ -14,8 +14,8 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 HEADER = os.path.join(ROOT, "include", "uhdr_b200.h")
 
 
-def declared_symbols():
-    text = open(HEADER).read()
+def declared_symbols(header=HEADER):
+    text = open(header).read()
     text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
     return sorted(set(re.findall(r"\b(uhdrb200_[a-z0-9_]+)\s*\(", text)))
 
@@ -27,6 +27,9 @@ def test_library_exports_every_declared_symbol():
     for s in syms:
         assert hasattr(lib, s), f"{s} declared in include/uhdr_b200.h but not exported"
     assert set(syms) == set(api.SYMBOLS), "python mirror and header disagree"
+    test_syms = declared_symbols(os.path.join(ROOT, "include", "uhdr_b200_test.h"))
+    assert set(test_syms) == set(api.TEST_SYMBOLS) and all(hasattr(lib, s) for s in test_syms)
+    assert not set(test_syms) & set(syms), "test hooks must stay out of the drop-in header"
     out = subprocess.run(["nm", "-D", "--defined-only", api.LIB_PATH], capture_output=True, text=True).stdout
     exported = set(re.findall(r" T (uhdrb200_\w+)", out))
     assert set(syms) <= exported
@@ -111,7 +114,7 @@ def test_argument_validation_precedes_cuda():
     assert uh.convertYuv(sdr, 0, -1) == abi.ERROR_INVALID_COLORGAMUT
     keep = sdr_b.copy()
     assert uh.convertYuv(sdr, 1, 1) == abi.NO_ERROR and np.array_equal(keep, sdr_b)  # identity: untouched, no device
-    assert lib.uhdrb200_set_apply_mode(7) != 0 and lib.uhdrb200_set_apply_mode(abi.APPLY_AUTO) == 0
+    assert lib.uhdrb200_test_set_apply_mode(7) != 0 and lib.uhdrb200_test_set_apply_mode(abi.APPLY_AUTO) == 0
     assert lib.uhdrb200_set_sync_mode(7) != 0 and lib.uhdrb200_set_sync_mode(abi.SYNC_BLOCKING) == 0
     assert lib.uhdrb200_set_sync_mode(abi.SYNC_SPIN) == 0
 

@@ -333,8 +333,9 @@ def test_config5_job_64_images_16_seeds_sharded(uh, torch_cuda):
             assert uh.generateGainMapBatch(len(idx), sd, hd, abi.TF_HLG, mds, mp_, False, st) == 0
             assert uh.applyGainMapBatch(len(idx), sd, mp_, mds[0], abi.OUTPUT_HDR_HLG, FLT_MAX, ou, st) == 0
             t.cuda.synchronize()
-            sums = d_out[idx].to(t.int64).sum(dim=1).cpu().numpy() * 1000003 + d_map[idx].to(t.int64).sum(dim=1).cpu().numpy()
-            per_rank.append([(i, int(c)) for i, c in zip(idx, sums)])
+            osum = d_out[idx].to(t.int64).sum(dim=1).cpu().tolist()  # Python ints: no wrap-around in the combination
+            msum = d_map[idx].to(t.int64).sum(dim=1).cpu().tolist()
+            per_rank.append([(i, o * 1000003 + m) for i, o, m in zip(idx, osum, msum)])
         merged[G] = shard.merge_checksums(per_rank)
     assert merged[1] == merged[2] == merged[4]
     assert len(set(merged[1])) == n  # 64 byte-distinct images give 64 distinct checksums

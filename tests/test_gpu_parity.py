@@ -111,10 +111,10 @@ MODES = [abi.APPLY_AUTO, abi.APPLY_TWO_TABLE, abi.APPLY_GENERIC]
 
 @pytest.fixture
 def apply_mode(uh, request):
-    """Selects the applyGainMap kernel family (uhdrb200_set_apply_mode) for one test."""
-    assert uh.lib.uhdrb200_set_apply_mode(request.param) == 0
+    """Selects the applyGainMap kernel family (uhdrb200_test_set_apply_mode) for one test."""
+    assert uh.lib.uhdrb200_test_set_apply_mode(request.param) == 0
     yield request.param
-    assert uh.lib.uhdrb200_set_apply_mode(abi.APPLY_AUTO) == 0
+    assert uh.lib.uhdrb200_test_set_apply_mode(abi.APPLY_AUTO) == 0
 
 
 @pytest.mark.parametrize("apply_mode", MODES, indirect=True)
