@@ -14,12 +14,13 @@ extern "C" {
 #endif
 
 /* applyGainMap kernel selection FOR THE CALLING THREAD ONLY (thread-local; other threads keep AUTO):
- * AUTO      what a caller gets: the TMA-fed q-domain pipeline (apply_pipe.cu) when the layout allows 16-byte bulk copies,
- *           else the q-domain kernels fed by plain loads (scale 4, scale 1 / 2, any integer scale), else the analytic kernel;
+ * AUTO      what a caller gets: the q-domain kernels (scale 4, scale 1 / 2, any integer scale) when the layout allows
+ *           them, else the analytic kernel;
  * GENERIC   the analytic kernel (any layout, MUFU-evaluated transfer functions);
  * TWO_TABLE scale-4 inputs through the srgbInvOetf-table + OETF-table kernel (previous design, kept as a cross-check);
- * Q_LDG     the q-domain kernels fed by plain loads even where the pipeline would be eligible. */
-enum { UHDRB200_APPLY_AUTO = 0, UHDRB200_APPLY_GENERIC = 1, UHDRB200_APPLY_TWO_TABLE = 2, UHDRB200_APPLY_Q_LDG = 3 };
+ * Q_PIPE    scale-4 inputs through the TMA-fed per-warp pipeline (apply_pipe.cu) where the layout allows 16-byte bulk
+ *           copies: same arithmetic as AUTO's kernel, measured slower on coherent images, kept for A/B runs. */
+enum { UHDRB200_APPLY_AUTO = 0, UHDRB200_APPLY_GENERIC = 1, UHDRB200_APPLY_TWO_TABLE = 2, UHDRB200_APPLY_Q_PIPE = 3 };
 int uhdrb200_test_set_apply_mode(int mode);
 
 /* Evaluates device function `fn` over n floats (device pointers, asynchronous on `stream`): out[i] = fn(in[i]).

@@ -27,8 +27,9 @@ ERROR_RESOLUTION_MISMATCH = -10006
 ERROR_BAD_METADATA = -10010
 ERROR_UNSUPPORTED_MAP_SCALE_FACTOR = -20008
 ERROR_INSUFFICIENT_RESOURCE = -20009
+ERROR_UNSUPPORTED_FEATURE = -30000
 
-APPLY_AUTO, APPLY_GENERIC, APPLY_TWO_TABLE, APPLY_Q_LDG = 0, 1, 2, 3  # uhdrb200_test_set_apply_mode (include/uhdr_b200_test.h)
+APPLY_AUTO, APPLY_GENERIC, APPLY_TWO_TABLE, APPLY_Q_PIPE = 0, 1, 2, 3  # uhdrb200_test_set_apply_mode (include/uhdr_b200_test.h)
 # uhdrb200_test_eval function selectors (include/uhdr_b200_test.h)
 (FN_SRGB_INV_OETF, FN_HLG_OETF, FN_HLG_INV_OETF, FN_PQ_OETF, FN_PQ_INV_OETF, FN_FLOAT_TO_HALF, FN_TO_10BIT, FN_P_HLG, FN_P_PQ,
  FN_L_POW, FN_TOE_FIX, FN_ENCODE_GAIN) = range(12)

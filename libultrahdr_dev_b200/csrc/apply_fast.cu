@@ -370,6 +370,7 @@ __global__ void __launch_bounds__(kQThreads, LTAB ? UHDR_APPLYQ_L_MIN_BLOCKS : U
 
       const float d2 = e2 - e1, d3 = e3 - e1, d4 = e4 - e1, exb = fmaf(e1, p.Aq, p.Bq);
       const bool interior = dx && !last;
+      const bool satcell = interior && e1 == 255.0f && d2 == 0.0f && d3 == 0.0f && d4 == 0.0f;  // ApplyFastParams::vsat
 
 #pragma unroll
       for (int qr = 0; qr < 2; qr++) {
@@ -412,7 +413,8 @@ __global__ void __launch_bounds__(kQThreads, LTAB ? UHDR_APPLYQ_L_MIN_BLOCKS : U
             f[i] = ex2_fast(fmaf(gain, p.Aq, p.Bq));
           }
         }
-        quad_row_eval<PACK, MASK, LTAB, NORM>(hiP, yw[2 * qr], yw[2 * qr + 1], uw[qr], vw[qr], f, orow + (size_t)(2 * qr) * ostride, ostride, plane_bytes);
+        quad_row_eval<PACK, MASK, LTAB, NORM>(hiP, yw[2 * qr], yw[2 * qr + 1], uw[qr], vw[qr], f, orow + (size_t)(2 * qr) * ostride, ostride, plane_bytes,
+                                              0xffffffffu, satcell, p.vsat + qr * 8, p.rsat + qr * 8);
       }
       e1 = e2;
       e3 = e4;
@@ -744,6 +746,7 @@ cudaError_t launch_apply_fast_impl(ApplyFastParams& p, int n, cudaStream_t s) {
       default: return p.need_mask ? launch_qs<kPack1010102, true>(p, s) : launch_qs<kPack1010102, false>(p, s);
     }
   }
+  if (p.pipe && !p.two_table) return launch_apply_pipe_impl(p, n, s);
   p.tiles_x = (p.g.map_width + kTileCellsX - 1) / kTileCellsX;
   p.tiles_y = (p.g.map_height + kTileCellsY - 1) / kTileCellsY;
   p.n_tiles = p.tiles_x * p.tiles_y * n;

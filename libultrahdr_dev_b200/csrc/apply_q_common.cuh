@@ -183,9 +183,12 @@ __device__ __forceinline__ float toe_fix(float phi) {
   return phi <= kPhiThr ? t : phi;
 }
 
-template <bool kToe = false>
+// kSat: lanes with `satcell` (interior cell, four map samples 255) take the host-computed exact code vs8[.] (+ 0.5, so
+// that the shared floor returns it) for every channel clamped to Phi == 1; see ApplyFastParams::vsat.
+template <bool kToe = false, bool kSat = false>
 __device__ __forceinline__ void q_rows_paired(const uint32_t hiP, const float (&oR)[2], const float (&oG)[2], const float (&oB)[2],
-                                              const float (&yf)[2][4], const float* __restrict__ f8, uint8_t* orow, const size_t ostride) {
+                                              const float (&yf)[2][4], const float* __restrict__ f8, uint8_t* orow, const size_t ostride,
+                                              const bool satcell = false, const float* __restrict__ vs8 = nullptr) {
   constexpr float KP = (float)(1.0 / (255.0 * 1.055));
   constexpr float q0 = 1.0f / (float)(1 << -kPLoExp);
   // the two pixels of a quad's row as one f32x2 lane pair: q, the three floors and the field move take one
@@ -213,11 +216,18 @@ __device__ __forceinline__ void q_rows_paired(const uint32_t hiP, const float (&
       const f32x2 qB = fma2(pk2(pB0, pB1), ff, q0q0);
       float a0, a1;
       unpk2(qR, a0, a1);
-      const f32x2 vR = pk2(p_eval(hiP, a0), p_eval(hiP, a1));
+      float r0 = p_eval(hiP, a0), r1 = p_eval(hiP, a1);
       unpk2(qG, a0, a1);
-      const f32x2 vG = pk2(p_eval(hiP, a0), p_eval(hiP, a1));
+      float g0 = p_eval(hiP, a0), g1 = p_eval(hiP, a1);
       unpk2(qB, a0, a1);
-      const f32x2 vB = pk2(p_eval(hiP, a0), p_eval(hiP, a1));
+      float b0v = p_eval(hiP, a0), b1v = p_eval(hiP, a1);
+      if (kSat) {
+        const float s0 = vs8[rr * 4 + 2 * c], s1 = vs8[rr * 4 + 2 * c + 1];
+        r0 = satcell && pR0 >= 1.0f ? s0 : r0; r1 = satcell && pR1 >= 1.0f ? s1 : r1;
+        g0 = satcell && pG0 >= 1.0f ? s0 : g0; g1 = satcell && pG1 >= 1.0f ? s1 : g1;
+        b0v = satcell && pB0 >= 1.0f ? s0 : b0v; b1v = satcell && pB1 >= 1.0f ? s1 : b1v;
+      }
+      const f32x2 vR = pk2(r0, r1), vG = pk2(g0, g1), vB = pk2(b0v, b1v);
       // floor + pack as in the scalar path below, two pixels per operation
       const f32x2 t = add_rm2(vR, fma2(add_rm2(vG, two23), k1024, gOff));
       const f32x2 Bm = add_rm2(vB, bOff);
@@ -299,7 +309,8 @@ __device__ __forceinline__ void q_rows_paired_lin(const uint32_t tL, const float
 template <int PACK, bool MASK, bool kToe, bool LTAB, bool NORM>
 __device__ __forceinline__ void q_rows(const uint32_t hiP, const uint32_t uq, const uint32_t vq,
                                        const float (&oR)[2], const float (&oG)[2], const float (&oB)[2], const float (&yf)[2][4],
-                                       const float* __restrict__ f8, uint8_t* orow, const size_t ostride, const size_t plane_bytes) {
+                                       const float* __restrict__ f8, uint8_t* orow, const size_t ostride, const size_t plane_bytes,
+                                       const bool satcell = false, const float* __restrict__ vs8 = nullptr, const float* __restrict__ rs8 = nullptr) {
   constexpr float KP = (float)(1.0 / (255.0 * 1.055));
   constexpr float q0 = 1.0f / (float)(1 << -kPLoExp);  // 2^kPLoExp as an FFMA immediate
         float rv[2] = {0.f, 0.f}, gq[2] = {0.f, 0.f}, bu[2] = {0.f, 0.f};
@@ -342,9 +353,15 @@ __device__ __forceinline__ void q_rows(const uint32_t hiP, const uint32_t uq, co
             }
             if (PACK == kPack1010102) {
               // the P table is >= 0 everywhere (tables.cu), so floor == the reference's truncation
-              const float vR = p_eval(hiP, fmaf(phR, fi, q0));
-              const float vG = p_eval(hiP, fmaf(phG, fi, q0));
-              const float vB = p_eval(hiP, fmaf(phB, fi, q0));
+              float vR = p_eval(hiP, fmaf(phR, fi, q0));
+              float vG = p_eval(hiP, fmaf(phG, fi, q0));
+              float vB = p_eval(hiP, fmaf(phB, fi, q0));
+              if (kToe && satcell) {  // the special path also serves saturated cells (ApplyFastParams::vsat)
+                const float vs = vs8[rr * 4 + i];
+                vR = phR >= 1.0f ? vs : vR;
+                vG = phG >= 1.0f ? vs : vG;
+                vB = phB >= 1.0f ? vs : vB;
+              }
               if (MASK) {  // codes above 1023 wrap like the reference's `& 0x3ff` (gainmapmath.cpp:722-727)
                 w[i][0] = (floor_bits(vR) & 0x3ffu) | ((floor_bits(vG) & 0x3ffu) << 10) | ((floor_bits(vB) & 0x3ffu) << 20) | 0xC0000000u;
               } else {
@@ -369,6 +386,12 @@ __device__ __forceinline__ void q_rows(const uint32_t hiP, const uint32_t uq, co
                 eR = l_eval(hiP, qR); eG = l_eval(hiP, qG); eB = l_eval(hiP, qB);
               } else {
                 eR = pow24(phR * fi); eG = pow24(phG * fi); eB = pow24(phB * fi);
+              }
+              if (kToe && satcell) {  // ApplyFastParams::rsat
+                const float rs = rs8[rr * 4 + i];
+                eR = phR >= 1.0f ? rs : eR;
+                eG = phG >= 1.0f ? rs : eG;
+                eB = phB >= 1.0f ? rs : eB;
               }
               if (kToe) {
                 const float f24 = pow24(fi);
@@ -482,7 +505,8 @@ __device__ __forceinline__ uint32_t stage_q_table(const ApplyFastParams& p, cons
 template <int PACK, bool MASK, bool LTAB, bool NORM, bool VOTE = false>
 __device__ __forceinline__ void quad_row_eval(const uint32_t hiP, const uint32_t yw0, const uint32_t yw1, const uint32_t uq, const uint32_t vq,
                                               const float (&f)[8], uint8_t* orow, const size_t ostride, const size_t plane_bytes,
-                                              const unsigned vote_mask = 0xffffffffu) {
+                                              const unsigned vote_mask = 0xffffffffu, const bool satcell = false,
+                                              const float* __restrict__ vs8 = nullptr, const float* __restrict__ rs8 = nullptr) {
   // Phi-domain constants (double on the host side of the compiler): K = 1/(255*1.055), chroma gains of the
   // BT.601 matrix (gainmapmath.cpp:177-196) times K, offsets = 0.055/1.055 - 128 * gain
   constexpr double dK = 1.0 / (255.0 * 1.055);
@@ -526,14 +550,23 @@ __device__ __forceinline__ void quad_row_eval(const uint32_t hiP, const uint32_t
 #else
         const bool toe = fminf(fmaf(ym0, KP, om0), fmaf(ym1, KP, om1)) <= kPhiToe;
 #endif
-        if constexpr (VOTE && PACK == kPack1010102 && !MASK && UHDR_APPLYQ_F32X2) {
-          if (__any_sync(vote_mask, toe)) q_rows_paired<true>(hiP, oR, oG, oB, yf, f, orow, ostride);
-          else q_rows_paired<false>(hiP, oR, oG, oB, yf, f, orow, ostride);
+        if constexpr (PACK == kPack1010102 && !MASK && UHDR_APPLYQ_F32X2) {
+          // three instantiations of the packed path: plain, + exact codes of saturated cells, + toe select as well
+          const bool t = VOTE ? __any_sync(vote_mask, toe) : toe;
+          const bool sc = VOTE ? __any_sync(vote_mask, satcell) : satcell;
+          if (t) {
+            if constexpr (VOTE) q_rows_paired<true, true>(hiP, oR, oG, oB, yf, f, orow, ostride, satcell, vs8);
+            else q_rows<PACK, MASK, true, LTAB, NORM>(hiP, uq, vq, oR, oG, oB, yf, f, orow, ostride, plane_bytes, satcell, vs8, rs8);
+          } else if (sc) {
+            q_rows_paired<false, true>(hiP, oR, oG, oB, yf, f, orow, ostride, satcell, vs8);
+          } else {
+            q_rows_paired<false, false>(hiP, oR, oG, oB, yf, f, orow, ostride);
+          }
           return;
         }
-        if (VOTE ? __any_sync(vote_mask, toe) : toe) q_rows<PACK, MASK, true, LTAB, NORM>(hiP, uq, vq, oR, oG, oB, yf, f, orow, ostride, plane_bytes);
+        const bool special = VOTE ? __any_sync(vote_mask, toe || satcell) : (toe || satcell);
+        if (special) q_rows<PACK, MASK, true, LTAB, NORM>(hiP, uq, vq, oR, oG, oB, yf, f, orow, ostride, plane_bytes, satcell, vs8, rs8);
 #if UHDR_APPLYQ_F32X2
-        else if constexpr (PACK == kPack1010102 && !MASK) q_rows_paired(hiP, oR, oG, oB, yf, f, orow, ostride);
         else if constexpr (LTAB) q_rows_paired_lin<PACK, NORM, MASK>(hiP, oR, oG, oB, yf, f, orow, ostride, plane_bytes);
 #endif
         else q_rows<PACK, MASK, false, LTAB, NORM>(hiP, uq, vq, oR, oG, oB, yf, f, orow, ostride, plane_bytes);

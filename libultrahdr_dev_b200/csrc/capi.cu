@@ -28,8 +28,8 @@ using namespace uhdr;
 
 std::atomic<uint64_t> g_launches{0};
 std::atomic<int> g_sync_mode{-1};  // -1: from the environment (UHDRB200_BLOCKING_SYNC), 0 spin, 1 blocking
-// test hook (include/uhdr_b200_test.h), per calling thread: 0 auto, 1 analytic kernel, 2 two-table kernel, 3 q-domain kernels
-// fed by plain loads (no TMA pipeline)
+// test hook (include/uhdr_b200_test.h), per calling thread: 0 auto, 1 analytic kernel, 2 two-table kernel, 3 the TMA-fed
+// pipeline variant of the q-domain kernel
 thread_local int t_apply_mode = 0;
 
 // ---------------------------------------------------------------- per-thread context
@@ -315,6 +315,34 @@ int get_apply_tables(int device, ApplyTables* out) {
   return 0;
 }
 
+// ---------------------------------------------------------------- saturated-white pixels under a saturated map
+// The reference's own float / double chain for a channel with c == 1 in an interior scale-4 cell whose four map samples
+// are 255: sampleMap (gainmapmath.cpp:700-719, e = 255 / 255.0f = 1, left-to-right float sum of the four weights),
+// applyGain (:550-555, double log2 / exp2 narrowed to float), `/ display_boost` (ultrahdr.cpp:451), srgbInvOetf(1)
+// (:149-155), hlgOetf / pqOetf (:259-267, 309-314, double) and the truncating `* 1023.0f` (:722-727).
+void fill_sat_cell(ApplyFastParams& f, const float w[16][4], float mn, float mx, float db, int fmt) {
+  const float lin1 = (float)pow((double)((1.0f + 0.055f) / 1.055f), 2.4);
+  for (int i = 0; i < 16; i++) {
+    const float e = 255.0f / 255.0f;
+    const float gain = e * w[i][0] + e * w[i][1] + e * w[i][2] + e * w[i][3];
+    const float log_boost = (float)(log2((double)mn) * (double)(1.0f - gain) + log2((double)mx) * (double)gain);
+    const float gf = (float)exp2((double)(log_boost * db / mx));
+    const float r = (lin1 * gf) / db;
+    f.rsat[i] = r;
+    float o = r;
+    if (fmt == UHDRB200_OUTPUT_HDR_HLG) {
+      const float A = 0.17883277f, B = 0.28466892f, C = (float)0.55991073;
+      o = r <= 1.0f / 12.0f ? sqrtf(3.0f * r) : (float)((double)A * log((double)(12.0f * r - B)) + (double)C);
+    } else if (fmt == UHDRB200_OUTPUT_HDR_PQ) {
+      const float m1 = 2610.0f / 16384.0f, m2 = 2523.0f / 4096.0f * 128.0f;
+      const float c1 = 3424.0f / 4096.0f, c2 = 2413.0f / 4096.0f * 32.0f, c3 = 2392.0f / 4096.0f * 32.0f;
+      const double pw = pow((double)r, (double)m1);
+      o = r <= 0.0f ? 0.0f : (float)pow(((double)c1 + (double)c2 * pw) / (1 + (double)c3 * pw), (double)m2);
+    }
+    f.vsat[i] = (float)(uint32_t)(o * 1023.0f) + 0.5f;
+  }
+}
+
 // ---------------------------------------------------------------- batch descriptor staging
 // A launch over n>1 images reads its per-image plane pointers from a small device array. Slots
 // come from a ring guarded by events so an async caller can have kRing launches in flight.
@@ -582,12 +610,16 @@ int apply_core(int n, const uhdrb200_image* sdr, const uhdrb200_image* map, cons
     f.s_bias = 0x4B000000u << 3;
     f.need_mask = fmax > 1.0005 ? 1 : 0;  // at f <= 1.0005 no 10-bit code can reach 1024
     idw_fill(&f.w[0][0], 4, 1, 1);  // ShepardsIDW::mWeights for scale 4 ...
+    fill_sat_cell(f, f.w, md->minContentBoost, md->maxContentBoost, p.display_boost, fmt);
     for (int i = 0; i < 16; i++)
       for (int c = 0; c < 4; c++) f.w[i][c] = (float)((double)f.w[i][c] * A);  // ... pre-multiplied by A
     f.Aq = (float)(A / 2.4 / 255.0);  // the q kernel keeps the map samples as 0..255 floats
     f.Bq = (float)(B / 2.4);
     f.q0 = (float)ldexp(1.0, kPLoExp);
     f.two_table = t_apply_mode == 2;
+    f.pipe = (t_apply_mode == 3 && !any_scale) ? 1 : 0;
+    for (int i = 0; i < n && f.pipe; i++) f.pipe = apply_pipe_ok(p.g, v[i]) ? 1 : 0;
+    f.pdl = 1;
     f.any_scale = any_scale ? 1 : 0;
     if (any_scale && (p.g.map_scale == 1 || p.g.map_scale == 2)) {
       bool al = true;  // the specialised kernels read the map as 32-bit (scale 1) / 16-bit (scale 2) words
@@ -1083,7 +1115,7 @@ void uhdrb200_host_free(void* p) { if (p) cudaFreeHost(p); }
 void uhdrb200_free(void* p) { free(p); }
 uint64_t uhdrb200_launch_count(void) { return g_launches.load(); }
 int uhdrb200_test_set_apply_mode(int mode) {
-  if (mode < UHDRB200_APPLY_AUTO || mode > UHDRB200_APPLY_Q_LDG) return UHDRB200_ERROR_UNSUPPORTED_FEATURE;
+  if (mode < UHDRB200_APPLY_AUTO || mode > UHDRB200_APPLY_Q_PIPE) return UHDRB200_ERROR_UNSUPPORTED_FEATURE;
   t_apply_mode = mode;
   return UHDRB200_NO_ERROR;
 }

@@ -117,6 +117,14 @@ struct ApplyFastParams {
   int any_scale;           // 1: apply_qs_kernel (any integer map scale factor, thread = 4x4 pixels) instead of the scale-4 kernels
   uint32_t scale_magic;    // ceil(2^32 / map_scale), 0 for scale 1 (set by launch_apply_fast_impl)
   int scale_special;       // 1 / 2: compile-time specialisation of apply_qs_kernel (map planes aligned to 4 / 2 bytes), else 0
+  int pipe;                // 1: apply_pipe_kernel (TMA-fed per-warp pipeline, apply_pipe.cu) instead of apply_q_kernel
+  int pdl;                 // 1: launch with programmatic stream serialization (the kernels call griddepcontrol.*)
+  // A channel clamped to c = 1 (ultrahdr.cpp:430-431 -> clampPixelFloat) inside an interior cell whose four map samples
+  // are all 255 (blown highlight under a saturated map: gain = the weight sum, 1 or 1 - 1..2 ulp) lands exactly on a code
+  // boundary of the reference's float chain, finer than the q domain resolves; the host evaluates that chain exactly
+  // (capi.cu: fill_sat_cell) per pixel position [oy * 4 + ox]:
+  float vsat[16];          // RGBA1010102: the reference's 10-bit code (before `& 0x3ff`) + 0.5
+  float rsat[16];          // linear outputs: the reference's value f * srgbInvOetf(1) / displayBoost
   float w2[4][4];          // ShepardsIDW::mWeights of scale 2, [oy * 2 + ox][k]
   // Aq x interior IDW weights of corners 2..4 (they include the 1/255 of the map samples), [corner - 2][oy * 4 + ox]:
   // horizontally adjacent pixels are one 8-byte pair for FFMA2
@@ -162,6 +170,9 @@ cudaError_t launch_apply_impl(const ApplyParams& p, int n, bool vec, cudaStream_
 bool apply_fast_ok(const Geometry& g, const Planes& pl);
 bool apply_qs_ok(const Geometry& g, const Planes& pl);
 cudaError_t launch_apply_fast_impl(ApplyFastParams& p, int n, cudaStream_t s);
+// scale 4 on the TMA-fed pipeline: additionally 16-byte aligned planes / strides and a map width % 16 == 0
+bool apply_pipe_ok(const Geometry& g, const Planes& pl);
+cudaError_t launch_apply_pipe_impl(const ApplyFastParams& p, int n, cudaStream_t s);
 // host: fills the double-precision-built tables (tables.cu)
 void build_apply_tables(float2* s, float2* s_hi, float2* o_hlg, float2* o_pq, float2* p_hlg, float2* p_pq, float2* l_pow, float* e255);
 cudaError_t launch_tonemap_impl(const ToneMapParams& p, int n, bool vec, cudaStream_t s);

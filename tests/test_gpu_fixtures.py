@@ -46,9 +46,17 @@ def test_fixture_generate(uh, checker, raw_pair, tf):
           f"saturated {(want == 255).mean():.3f}")
 
 
+@pytest.fixture(params=[abi.APPLY_AUTO, abi.APPLY_Q_PIPE], ids=["q", "pipe"])
+def q_family(uh, request):
+    """Both q-domain kernel families: the default plain-load kernels and the TMA pipeline variant."""
+    assert uh.lib.uhdrb200_test_set_apply_mode(request.param) == 0
+    yield request.param
+    assert uh.lib.uhdrb200_test_set_apply_mode(abi.APPLY_AUTO) == 0
+
+
 @pytest.mark.parametrize("fmt", FORMATS)
 @pytest.mark.parametrize("tf", [abi.TF_HLG, abi.TF_PQ])
-def test_fixture_apply(uh, checker, raw_pair, fmt, tf):
+def test_fixture_apply(uh, checker, raw_pair, fmt, tf, q_family):
     """applyGainMap on the fixture SDR image with the reference's own map of the pair, all four output formats."""
     yuv, p010, w, h = raw_pair
     sdr = abi.host_yuv420(yuv, w, h, abi.COLORGAMUT_BT709)
@@ -63,7 +71,7 @@ def test_fixture_apply(uh, checker, raw_pair, fmt, tf):
 
 
 @pytest.mark.parametrize("fmt", FORMATS)
-def test_minnie_apply(uh, checker, fmt):
+def test_minnie_apply(uh, checker, fmt, q_family):
     """The photograph (mean |dx| of the luma 6.2 codes, 3.7 % of the pixels on srgbInvOetf's toe), tiled 4 x 4 to
     1280x960, with a smooth full-range map; HLG-sized and PQ-sized boosts."""
     buf, w0, h0 = refdata.load("minnie")

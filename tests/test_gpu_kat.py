@@ -131,8 +131,8 @@ def test_grid_float_to_half_bit_exact(ev, orc):
     assert np.array_equal(got[sel], want)
 
 
-def _q_grid():
-    return np.exp(np.linspace(np.log(2.0 ** -11), np.log(1.999), N_GRID)).astype(np.float32)
+def _q_grid():  # the kernels keep f < 3.9 (capi.cu), i.e. q < 3.9^(1/2.4) = 1.763
+    return np.exp(np.linspace(np.log(2.0 ** -11), np.log(1.76), N_GRID)).astype(np.float32)
 
 
 @pytest.mark.parametrize("fn,oetf", [(abi.FN_P_HLG, "hlgOetf"), (abi.FN_P_PQ, "pqOetf")])
@@ -141,7 +141,7 @@ def test_grid_p_table(ev, orc, fn, oetf):
     q = _q_grid()
     got = ev(fn, q).astype(np.float64)
     sel = np.random.Generator(np.random.PCG64(fn)).choice(N_GRID, 20000, replace=False)
-    lin = np.minimum(q[sel].astype(np.float64) ** 2.4, 4.0)
+    lin = q[sel].astype(np.float64) ** 2.4
     want = 1023.0 * np.array([getattr(orc, "c_" + oetf)(float(v)) for v in lin.astype(np.float32)], dtype=np.float64)
     err = np.abs(got[sel] - want)
     print(f"P table ({oetf}): max abs error {err.max():.4f} codes, mean {err.mean():.5f}")

@@ -106,7 +106,7 @@ def test_generate_strides(uh, orc, w, h, sls, scs, hls, hcs):
 
 
 # ------------------------------------------------------------------------------ applyGainMap
-MODES = [abi.APPLY_AUTO, abi.APPLY_TWO_TABLE, abi.APPLY_GENERIC]
+MODES = [abi.APPLY_AUTO, abi.APPLY_Q_PIPE, abi.APPLY_TWO_TABLE, abi.APPLY_GENERIC]
 
 
 @pytest.fixture
@@ -139,7 +139,7 @@ def test_apply_parity(uh, orc, fmt, kind, max_boost, apply_mode):
     got, dest = gpu_apply(uh, sdr, mp, md, fmt, 3.4e38)
     assert st == 0 and (dest.width, dest.height, dest.colorGamut) == (w, h, 0)
     # floors: what DESIGN.md claims for the default (q-domain) kernels; the A/B and last-resort kernels a little lower
-    floor = 0.995 if apply_mode == abi.APPLY_AUTO else 0.99
+    floor = 0.995 if apply_mode in (abi.APPLY_AUTO, abi.APPLY_Q_PIPE) else 0.99
     exact = parity.compare_output(fmt, got, want, w * h, f"apply fmt={fmt} {kind} boost={max_boost:.2f}", min_exact=floor)
     print(f"apply mode={apply_mode} fmt={fmt} {kind} max_boost={max_boost:.2f}: exact {exact:.5f}")
 
@@ -157,7 +157,7 @@ def test_apply_scale_factors(uh, orc, scale, fmt):
     parity.compare_output(fmt, got, want, w * h, f"apply scale={scale}", min_exact=0.995)
 
 
-@pytest.mark.parametrize("apply_mode", [abi.APPLY_AUTO, abi.APPLY_TWO_TABLE], indirect=True)
+@pytest.mark.parametrize("apply_mode", [abi.APPLY_AUTO, abi.APPLY_Q_PIPE, abi.APPLY_TWO_TABLE], indirect=True)
 @pytest.mark.parametrize("boost", [1.0, 2.0, 4.926108, 3.4e38])
 @pytest.mark.parametrize("min_boost", [1.0, 0.5])
 def test_apply_display_boost(uh, orc, boost, min_boost, apply_mode):
@@ -204,7 +204,7 @@ def test_apply_strides(uh, orc, w, h, ls, cs):
         parity.compare_output(fmt, b, want, w * h, f"apply strided fmt={fmt}")
 
 
-@pytest.mark.parametrize("apply_mode", [abi.APPLY_AUTO, abi.APPLY_TWO_TABLE], indirect=True)
+@pytest.mark.parametrize("apply_mode", [abi.APPLY_AUTO, abi.APPLY_Q_PIPE, abi.APPLY_TWO_TABLE], indirect=True)
 @pytest.mark.parametrize("w,h,ls,cs", [(128, 64, 132, 70), (36, 20, 40, 24), (260, 12, 264, 132), (4, 4, None, None)])
 def test_apply_fast_path_strides(uh, orc, w, h, ls, cs, apply_mode):
     """Map scale 4 (the table-driven kernels): strided input == packed input, ragged tiles, borders."""
