@@ -181,6 +181,20 @@ int uhdrb200_tonemap_dev(const uhdrb200_image* src, uhdrb200_image* dest, void* 
 int uhdrb200_generate_gainmap_batch_dev(int n, const uhdrb200_image* yuv420, const uhdrb200_image* p010,
                                         int hdr_tf, uhdrb200_metadata* metadata,
                                         uhdrb200_image* dest, int sdr_is_601, void* stream);
+/* No counterpart in the reference: added for callers that must not allocate
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc). Same arguments, results and
+ * status codes as uhdrb200_generate_gainmap_batch_dev, but the call allocates NOTHING: no cudaMalloc / cudaFree, no
+ * stream or event creation, no heap. The per-image plane-pointer array the kernel reads lives in a file-scope
+ * `static __device__` array of UHDRB200_NOALLOC_MAX_IMAGES entries (18 KB, held by every GPU that loads the library until
+ * exit) whose device address is taken once per device with cudaGetSymbolAddress. It runs on the CALLER's current device
+ * and `stream` (the thread's uhdrb200_init binding is not used). n > UHDRB200_NOALLOC_MAX_IMAGES returns
+ * UHDRB200_ERROR_UNSUPPORTED_FEATURE with the reason in uhdrb200_last_error(). All calls share the one array: calls on
+ * the same stream are ordered, calls that overlap on the GPU (different streams, different host threads) RACE on it and
+ * must be serialised by the caller. The array keeps the last call's entries; each call overwrites the n it uses. */
+#define UHDRB200_NOALLOC_MAX_IMAGES 256
+int uhdrb200_generate_gainmap_batch_dev_noalloc(int n, const uhdrb200_image* yuv420, const uhdrb200_image* p010,
+                                                int hdr_tf, uhdrb200_metadata* metadata, uhdrb200_image* dest,
+                                                int sdr_is_601, void* stream);
 int uhdrb200_apply_gainmap_batch_dev(int n, const uhdrb200_image* yuv420, const uhdrb200_image* gainmap,
                                      const uhdrb200_metadata* metadata, int output_format,
                                      float max_display_boost, uhdrb200_image* dest, void* stream);

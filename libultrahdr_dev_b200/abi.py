@@ -28,6 +28,7 @@ ERROR_BAD_METADATA = -10010
 ERROR_UNSUPPORTED_MAP_SCALE_FACTOR = -20008
 ERROR_INSUFFICIENT_RESOURCE = -20009
 ERROR_UNSUPPORTED_FEATURE = -30000
+NOALLOC_MAX_IMAGES = 256  # UHDRB200_NOALLOC_MAX_IMAGES
 
 APPLY_AUTO, APPLY_GENERIC, APPLY_TWO_TABLE, APPLY_Q_PIPE = 0, 1, 2, 3  # uhdrb200_test_set_apply_mode (include/uhdr_b200_test.h)
 # uhdrb200_test_eval function selectors (include/uhdr_b200_test.h)

@@ -36,6 +36,7 @@ SYMBOLS = {
     "uhdrb200_generate_gainmap_host_into": (C.c_int, [P_IMG, P_IMG, C.c_int, P_MD, P_IMG, C.c_int, C.c_void_p, C.c_size_t]),
     "uhdrb200_generate_gainmap_dev": (C.c_int, [P_IMG, P_IMG, C.c_int, P_MD, P_IMG, C.c_int, C.c_void_p]),
     "uhdrb200_generate_gainmap_batch_dev": (C.c_int, [C.c_int, P_IMG, P_IMG, C.c_int, P_MD, P_IMG, C.c_int, C.c_void_p]),
+    "uhdrb200_generate_gainmap_batch_dev_noalloc": (C.c_int, [C.c_int, P_IMG, P_IMG, C.c_int, P_MD, P_IMG, C.c_int, C.c_void_p]),
     "uhdrb200_apply_gainmap_host": (C.c_int, [P_IMG, P_IMG, P_MD, C.c_int, C.c_float, P_IMG]),
     "uhdrb200_apply_gainmap_dev": (C.c_int, [P_IMG, P_IMG, P_MD, C.c_int, C.c_float, P_IMG, C.c_void_p]),
     "uhdrb200_apply_gainmap_batch_dev": (C.c_int, [C.c_int, P_IMG, P_IMG, P_MD, C.c_int, C.c_float, P_IMG, C.c_void_p]),

@@ -833,6 +833,97 @@ int api0_core(int n, const uhdrb200_image* hdr, int hdr_tf, int sdr_to_601, uhdr
 
 }  // namespace
 
+// ================================================================ no-allocation batched generateGainMap
+// (no counterpart in the reference, see include/uhdr_b200.h)
+// The batched launches read their per-image plane pointers from a small device array. The regular entry point takes that
+// array from a cudaMalloc'ed ring (stage_batch); this variant keeps it in a file-scope __device__ array instead, so
+// that it never allocates. Every GPU that loads the library holds the array (18 KB) until exit; all calls share it.
+static __device__ __align__(256) unsigned char g_noalloc_batch[UHDRB200_NOALLOC_MAX_IMAGES * sizeof(uhdr::Planes)];
+
+namespace {
+
+std::mutex g_noalloc_mu;
+Planes* g_noalloc_dev[64];  // per device: the DEVICE address of g_noalloc_batch (in host code the symbol is only a stand-in)
+
+// once per device, with that device current
+int noalloc_scratch(Planes** out) {
+  int dev = 0;
+  CU(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64) {
+    t_ctx.err = "no-alloc entry point: device index beyond 63";
+    return UHDRB200_ERROR_UNSUPPORTED_FEATURE;
+  }
+  std::lock_guard<std::mutex> lk(g_noalloc_mu);
+  if (!g_noalloc_dev[dev]) {
+    void* ptr = nullptr;
+    CU(cudaGetSymbolAddress((void**)&ptr, g_noalloc_batch));
+    g_noalloc_dev[dev] = static_cast<Planes*>(ptr);
+  }
+  *out = g_noalloc_dev[dev];
+  return 0;
+}
+
+int generate_noalloc(int n, const uhdrb200_image* sdr, const uhdrb200_image* hdr, int hdr_tf, uhdrb200_metadata* md,
+                     uhdrb200_image* dest, int sdr_is_601, cudaStream_t s) {
+  if (n <= 0) return UHDRB200_NO_ERROR;
+  if (n > UHDRB200_NOALLOC_MAX_IMAGES) {
+    char msg[160];
+    snprintf(msg, sizeof msg, "uhdrb200_generate_gainmap_batch_dev_noalloc: n = %d exceeds UHDRB200_NOALLOC_MAX_IMAGES (%d)", n,
+             UHDRB200_NOALLOC_MAX_IMAGES);
+    t_ctx.err = msg;
+    return UHDRB200_ERROR_UNSUPPORTED_FEATURE;
+  }
+  if (!sdr || !hdr || !md || !dest) return UHDRB200_ERROR_BAD_PTR;
+  for (int i = 0; i < n; i++) {  // the checks of generate_core, in the reference's order (ultrahdr.cpp:189-202, 245-247)
+    int st = validate_generate(&sdr[i], &hdr[i], hdr_tf, &md[i], &dest[i]);
+    if (st) return st;
+    if (!dest[i].data) return UHDRB200_ERROR_BAD_PTR;
+    if (i && (!same_layout(sdr[i], sdr[0]) || !same_layout(hdr[i], hdr[0]))) return UHDRB200_ERROR_RESOLUTION_MISMATCH;
+  }
+  if (!fits_int(sdr[0].width) || !fits_int(sdr[0].height) || !fits_int(sdr[0].luma_stride) || !fits_int(hdr[0].luma_stride))
+    return UHDRB200_ERROR_UNSUPPORTED_WIDTH_HEIGHT;
+  Planes* scratch = nullptr;
+  int st = noalloc_scratch(&scratch);  // runs on the caller's current device and stream: no per-thread context, no stream creation
+  if (st) return st;
+  GenerateParams p;
+  memset(&p, 0, sizeof p);
+  p.g = geometry_of(&sdr[0], &hdr[0]);
+  p.g.map_scale = 4;  // kMapDimensionScaleFactor, ultrahdr.h:213
+  p.g.map_width = p.g.width / 4;
+  p.g.map_height = p.g.height / 4;
+  p.sdr_k = yuv_coefs(sdr_is_601 ? 1 : sdr[0].colorGamut);
+  p.hdr_k = yuv_coefs(hdr[0].colorGamut);
+  p.luma = luma_coefs(sdr[0].colorGamut);
+  p.gamut = gamut_matrix(sdr[0].colorGamut, hdr[0].colorGamut);
+  p.use_gamut = sdr[0].colorGamut != hdr[0].colorGamut;
+  p.hdr_tf = hdr_tf;
+  p.hdr_white_nits = hdr_tf == UHDRB200_TF_PQ ? 10000.0f : 1000.0f;
+  static thread_local Planes host_planes[UHDRB200_NOALLOC_MAX_IMAGES];  // fixed storage: no heap either
+  bool vec = true;
+  for (int i = 0; i < n; i++) {
+    fill_metadata(&md[i], hdr_tf);
+    fill_map_desc(&dest[i], (size_t)p.g.map_width, (size_t)p.g.map_height);
+    memset(&host_planes[i], 0, sizeof(Planes));
+    set_sdr_planes(host_planes[i], sdr[i]);
+    host_planes[i].hdr_y = hdr[i].data;
+    host_planes[i].hdr_uv = hdr[i].chroma_data;
+    host_planes[i].out = dest[i].data;
+    vec = vec && generate_vec_ok(p.g, host_planes[i]);
+  }
+  p.gc = gain_code_of(md[0].minContentBoost, md[0].maxContentBoost);
+  // the n descriptors overwrite the head of the shared array (nothing in it has to start at zero; entries beyond n keep
+  // the previous call's contents and are never read: the grid's z extent is n). Pageable source: the runtime has staged
+  // the bytes when this returns, so host_planes may be reused by the next call.
+  CU(cudaMemcpyAsync(scratch, host_planes, sizeof(Planes) * (size_t)n, cudaMemcpyHostToDevice, s));
+  p.batch = scratch;
+  cudaError_t e = launch_generate_impl(p, n, vec, s);
+  if (e != cudaSuccess) return fail(e, "generate kernel launch (no-alloc)");
+  g_launches++;
+  return UHDRB200_NO_ERROR;
+}
+
+}  // namespace
+
 // ================================================================ host-pointer staging helpers
 namespace {
 
@@ -1154,6 +1245,10 @@ int uhdrb200_generate_gainmap_batch_dev(int n, const uhdrb200_image* yuv420, con
                                         uhdrb200_metadata* metadata, uhdrb200_image* dest, int sdr_is_601,
                                         void* stream) {
   return generate_core(n, yuv420, p010, hdr_tf, metadata, dest, sdr_is_601, (cudaStream_t)stream);
+}
+int uhdrb200_generate_gainmap_batch_dev_noalloc(int n, const uhdrb200_image* yuv420, const uhdrb200_image* p010, int hdr_tf,
+                                                uhdrb200_metadata* metadata, uhdrb200_image* dest, int sdr_is_601, void* stream) {
+  return generate_noalloc(n, yuv420, p010, hdr_tf, metadata, dest, sdr_is_601, (cudaStream_t)stream);
 }
 int uhdrb200_apply_gainmap_host(const uhdrb200_image* yuv420, const uhdrb200_image* gainmap,
                                 const uhdrb200_metadata* metadata, int output_format, float max_display_boost,
