@@ -370,7 +370,8 @@ __global__ void __launch_bounds__(kQThreads, LTAB ? UHDR_APPLYQ_L_MIN_BLOCKS : U
 
       const float d2 = e2 - e1, d3 = e3 - e1, d4 = e4 - e1, exb = fmaf(e1, p.Aq, p.Bq);
       const bool interior = dx && !last;
-      const bool satcell = interior && e1 == 255.0f && d2 == 0.0f && d3 == 0.0f && d4 == 0.0f;  // ApplyFastParams::vsat
+      const bool satcell = e1 == 255.0f && d2 == 0.0f && d3 == 0.0f && d4 == 0.0f;  // ApplyFastParams::vsat
+      const int sat_t = interior ? 0 : (dx ? 2 : (last ? 3 : 1));                   // which IDW table the cell uses
 
 #pragma unroll
       for (int qr = 0; qr < 2; qr++) {
@@ -414,7 +415,7 @@ __global__ void __launch_bounds__(kQThreads, LTAB ? UHDR_APPLYQ_L_MIN_BLOCKS : U
           }
         }
         quad_row_eval<PACK, MASK, LTAB, NORM>(hiP, yw[2 * qr], yw[2 * qr + 1], uw[qr], vw[qr], f, orow + (size_t)(2 * qr) * ostride, ostride, plane_bytes,
-                                              0xffffffffu, satcell, p.vsat + qr * 8, p.rsat + qr * 8);
+                                              0xffffffffu, satcell, p.vsat[sat_t] + qr * 8, p.rsat[sat_t] + qr * 8);
       }
       e1 = e2;
       e3 = e4;

@@ -550,14 +550,17 @@ __device__ __forceinline__ void quad_row_eval(const uint32_t hiP, const uint32_t
 #else
         const bool toe = fminf(fmaf(ym0, KP, om0), fmaf(ym1, KP, om1)) <= kPhiToe;
 #endif
+#ifndef UHDR_SAT_VARIANT
+#define UHDR_SAT_VARIANT 0  // 1: a third instantiation of the packed path for saturated cells without toe channels (more code, spills)
+#endif
         if constexpr (PACK == kPack1010102 && !MASK && UHDR_APPLYQ_F32X2) {
-          // three instantiations of the packed path: plain, + exact codes of saturated cells, + toe select as well
+          // the packed path, and one special path that serves both the toe channels and the exact codes of saturated cells
           const bool t = VOTE ? __any_sync(vote_mask, toe) : toe;
           const bool sc = VOTE ? __any_sync(vote_mask, satcell) : satcell;
-          if (t) {
+          if (UHDR_SAT_VARIANT ? t : (t || sc)) {
             if constexpr (VOTE) q_rows_paired<true, true>(hiP, oR, oG, oB, yf, f, orow, ostride, satcell, vs8);
             else q_rows<PACK, MASK, true, LTAB, NORM>(hiP, uq, vq, oR, oG, oB, yf, f, orow, ostride, plane_bytes, satcell, vs8, rs8);
-          } else if (sc) {
+          } else if (UHDR_SAT_VARIANT && sc) {
             q_rows_paired<false, true>(hiP, oR, oG, oB, yf, f, orow, ostride, satcell, vs8);
           } else {
             q_rows_paired<false, false>(hiP, oR, oG, oB, yf, f, orow, ostride);

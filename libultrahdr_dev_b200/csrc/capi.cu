@@ -320,15 +320,19 @@ int get_apply_tables(int device, ApplyTables* out) {
 // are 255: sampleMap (gainmapmath.cpp:700-719, e = 255 / 255.0f = 1, left-to-right float sum of the four weights),
 // applyGain (:550-555, double log2 / exp2 narrowed to float), `/ display_boost` (ultrahdr.cpp:451), srgbInvOetf(1)
 // (:149-155), hlgOetf / pqOetf (:259-267, 309-314, double) and the truncating `* 1023.0f` (:722-727).
-void fill_sat_cell(ApplyFastParams& f, const float w[16][4], float mn, float mx, float db, int fmt) {
+void fill_sat_cell(ApplyFastParams& f, float mn, float mx, float db, int fmt) {
   const float lin1 = (float)pow((double)((1.0f + 0.055f) / 1.055f), 2.4);
-  for (int i = 0; i < 16; i++) {
+  const int inc[4][2] = {{1, 1}, {0, 1}, {1, 0}, {0, 0}};  // mWeights, NR, NB, C (gainmapmath.h:184-228)
+  for (int t = 0; t < 4; t++) {
+   float w[16][4];
+   idw_fill(&w[0][0], 4, inc[t][0], inc[t][1]);
+   for (int i = 0; i < 16; i++) {
     const float e = 255.0f / 255.0f;
     const float gain = e * w[i][0] + e * w[i][1] + e * w[i][2] + e * w[i][3];
     const float log_boost = (float)(log2((double)mn) * (double)(1.0f - gain) + log2((double)mx) * (double)gain);
     const float gf = (float)exp2((double)(log_boost * db / mx));
     const float r = (lin1 * gf) / db;
-    f.rsat[i] = r;
+    f.rsat[t][i] = r;
     float o = r;
     if (fmt == UHDRB200_OUTPUT_HDR_HLG) {
       const float A = 0.17883277f, B = 0.28466892f, C = (float)0.55991073;
@@ -339,7 +343,8 @@ void fill_sat_cell(ApplyFastParams& f, const float w[16][4], float mn, float mx,
       const double pw = pow((double)r, (double)m1);
       o = r <= 0.0f ? 0.0f : (float)pow(((double)c1 + (double)c2 * pw) / (1 + (double)c3 * pw), (double)m2);
     }
-    f.vsat[i] = (float)(uint32_t)(o * 1023.0f) + 0.5f;
+    f.vsat[t][i] = (float)(uint32_t)(o * 1023.0f) + 0.5f;
+   }
   }
 }
 
@@ -610,7 +615,7 @@ int apply_core(int n, const uhdrb200_image* sdr, const uhdrb200_image* map, cons
     f.s_bias = 0x4B000000u << 3;
     f.need_mask = fmax > 1.0005 ? 1 : 0;  // at f <= 1.0005 no 10-bit code can reach 1024
     idw_fill(&f.w[0][0], 4, 1, 1);  // ShepardsIDW::mWeights for scale 4 ...
-    fill_sat_cell(f, f.w, md->minContentBoost, md->maxContentBoost, p.display_boost, fmt);
+    fill_sat_cell(f, md->minContentBoost, md->maxContentBoost, p.display_boost, fmt);
     for (int i = 0; i < 16; i++)
       for (int c = 0; c < 4; c++) f.w[i][c] = (float)((double)f.w[i][c] * A);  // ... pre-multiplied by A
     f.Aq = (float)(A / 2.4 / 255.0);  // the q kernel keeps the map samples as 0..255 floats

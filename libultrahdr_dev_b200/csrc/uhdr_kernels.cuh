@@ -119,12 +119,12 @@ struct ApplyFastParams {
   int scale_special;       // 1 / 2: compile-time specialisation of apply_qs_kernel (map planes aligned to 4 / 2 bytes), else 0
   int pipe;                // 1: apply_pipe_kernel (TMA-fed per-warp pipeline, apply_pipe.cu) instead of apply_q_kernel
   int pdl;                 // 1: launch with programmatic stream serialization (the kernels call griddepcontrol.*)
-  // A channel clamped to c = 1 (ultrahdr.cpp:430-431 -> clampPixelFloat) inside an interior cell whose four map samples
-  // are all 255 (blown highlight under a saturated map: gain = the weight sum, 1 or 1 - 1..2 ulp) lands exactly on a code
-  // boundary of the reference's float chain, finer than the q domain resolves; the host evaluates that chain exactly
-  // (capi.cu: fill_sat_cell) per pixel position [oy * 4 + ox]:
-  float vsat[16];          // RGBA1010102: the reference's 10-bit code (before `& 0x3ff`) + 0.5
-  float rsat[16];          // linear outputs: the reference's value f * srgbInvOetf(1) / displayBoost
+  // A channel clamped to c = 1 (ultrahdr.cpp:430-431 -> clampPixelFloat) inside a cell whose four map samples are all 255
+  // (blown highlight under a saturated map: gain = the weight sum, 1 or 1 - 1..2 ulp) lands exactly on a code boundary of
+  // the reference's float chain, finer than the q domain resolves; the host evaluates that chain exactly (capi.cu:
+  // fill_sat_cell) per IDW table (0 interior, 1 NR, 2 NB, 3 C, gainmapmath.cpp:710-716) and pixel position [oy * 4 + ox]:
+  float vsat[4][16];       // RGBA1010102: the reference's 10-bit code (before `& 0x3ff`) + 0.5
+  float rsat[4][16];       // linear outputs: the reference's value f * srgbInvOetf(1) / displayBoost
   float w2[4][4];          // ShepardsIDW::mWeights of scale 2, [oy * 2 + ox][k]
   // Aq x interior IDW weights of corners 2..4 (they include the 1/255 of the map samples), [corner - 2][oy * 4 + ox]:
   // horizontally adjacent pixels are one 8-byte pair for FFMA2
