@@ -22,6 +22,8 @@
 //     the blocks are persistent (grid = SMs x resident blocks, grid-stride over tiles).
 //   * the gain factor 2^(logBoost * displayBoost / maxContentBoost) / displayBoost (gainmapmath.cpp:550-555,
 //     ultrahdr.cpp:451) is three FFMA (FFMA2 on pixel pairs) + one MUFU.EX2 per pixel.
+#include <mutex>
+
 #include "apply_q_common.cuh"
 
 namespace uhdr {
@@ -585,11 +587,13 @@ bool aligned(const void* q, size_t a) { return (reinterpret_cast<uintptr_t>(q) &
 template <int PACK, bool MASK>
 cudaError_t launch(const ApplyFastParams& p, cudaStream_t s) {
   const size_t smem = PACK == kPack1010102 ? 0 : kSEntriesHi * sizeof(float2);
-  static int sms_of[64], per_sm_of[64];  // per device, filled on first use (benign race: same values)
+  static int sms_of[64], per_sm_of[64];  // per device, filled on first use under the lock (host threads launch concurrently)
+  static std::mutex mu;
   int dev = 0;
   cudaError_t e = cudaGetDevice(&dev);
   if (e != cudaSuccess) return e;
   dev &= 63;
+  std::unique_lock<std::mutex> lk(mu);
   if (per_sm_of[dev] == 0) {
     int n_sm = 0, n = 0;
     if ((e = cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev)) != cudaSuccess) return e;
@@ -599,6 +603,7 @@ cudaError_t launch(const ApplyFastParams& p, cudaStream_t s) {
     per_sm_of[dev] = n > 0 ? n : 1;
   }
   const int sms = sms_of[dev], per_sm = per_sm_of[dev];
+  lk.unlock();
   const int grid = p.n_tiles < sms * per_sm ? p.n_tiles : sms * per_sm;
   apply_fast_kernel<PACK, MASK><<<grid, kThreads, smem, s>>>(p);
   return cudaGetLastError();
@@ -625,11 +630,13 @@ int pick_cells(int tiles_x, int map_height, int n_img, int cap) {
 
 template <int PACK, bool MASK, bool BATCH, bool LTAB, bool NORM>
 cudaError_t launch_q(const ApplyFastParams& p0, cudaStream_t s) {
-  static int sms_of[64], per_sm_of[64], smem_of[64];
+  static int sms_of[64], per_sm_of[64], smem_of[64];  // per device, filled on first use under the lock
+  static std::mutex mu;
   int dev = 0;
   cudaError_t e = cudaGetDevice(&dev);
   if (e != cudaSuccess) return e;
   dev &= 63;
+  std::unique_lock<std::mutex> lk(mu);
   if (per_sm_of[dev] == 0) {
     int n_sm = 0, n = 0, reserved = 0;
     cudaFuncAttributes fa;
@@ -647,13 +654,14 @@ cudaError_t launch_q(const ApplyFastParams& p0, cudaStream_t s) {
   }
   ApplyFastParams p = p0;
   const int n_img = p.n_tiles / (p.tiles_x * p.tiles_y);
-  const int cap = sms_of[dev] * per_sm_of[dev];
+  const int cap = sms_of[dev] * per_sm_of[dev], smem_bytes = smem_of[dev];
+  lk.unlock();
   p.cells = pick_cells(p.tiles_x, p.g.map_height, n_img, cap);
   const int kQTileRows = (kQThreads / 32) * p.cells;
   p.tiles_y = (p.g.map_height + kQTileRows - 1) / kQTileRows;  // this kernel's tiles are kQTileRows cell rows tall
   p.n_tiles = p.tiles_x * p.tiles_y * n_img;
   const int grid = p.n_tiles < cap ? p.n_tiles : cap;
-  apply_q_kernel<PACK, MASK, BATCH, LTAB, NORM><<<grid, kQThreads, (size_t)smem_of[dev], s>>>(p);
+  apply_q_kernel<PACK, MASK, BATCH, LTAB, NORM><<<grid, kQThreads, (size_t)smem_bytes, s>>>(p);
   return cudaGetLastError();
 }
 
@@ -669,11 +677,13 @@ cudaError_t launch_q(const ApplyFastParams& p, cudaStream_t s) {
 
 template <int PACK, bool MASK, bool BATCH, bool LTAB, bool NORM, int SCALE>
 cudaError_t launch_qs(const ApplyFastParams& p0, cudaStream_t s) {
-  static int sms_of[64], per_sm_of[64], smem_of[64];
+  static int sms_of[64], per_sm_of[64], smem_of[64];  // per device, filled on first use under the lock
+  static std::mutex mu;
   int dev = 0;
   cudaError_t e = cudaGetDevice(&dev);
   if (e != cudaSuccess) return e;
   dev &= 63;
+  std::unique_lock<std::mutex> lk(mu);
   if (per_sm_of[dev] == 0) {
     int n_sm = 0, n = 0, reserved = 0;
     cudaFuncAttributes fa;
@@ -689,9 +699,10 @@ cudaError_t launch_qs(const ApplyFastParams& p0, cudaStream_t s) {
     smem_of[dev] = smem;
     per_sm_of[dev] = n > 0 ? n : 1;
   }
-  const int cap = sms_of[dev] * per_sm_of[dev];
+  const int cap = sms_of[dev] * per_sm_of[dev], smem_bytes = smem_of[dev];
+  lk.unlock();
   const int grid = p0.n_tiles < cap ? p0.n_tiles : cap;
-  apply_qs_kernel<PACK, MASK, BATCH, LTAB, NORM, SCALE><<<grid, kThreads, (size_t)smem_of[dev], s>>>(p0);
+  apply_qs_kernel<PACK, MASK, BATCH, LTAB, NORM, SCALE><<<grid, kThreads, (size_t)smem_bytes, s>>>(p0);
   return cudaGetLastError();
 }
 

@@ -59,9 +59,56 @@ struct Ctx {
   DevBuf buf[8];  // staging planes of the *_host entry points
   BatchSlot ring[kRing];
   int ring_next = 0;
+  int ring_device = -1;  // device the ring slots were allocated on (the *_batch_dev entry points follow the caller's device)
   std::string err;
+  void release_ring();
+  void release();
+  // A host thread that used the library owns a stream, events, page-locked chunks and device staging buffers; they go
+  // away with the thread (or with uhdrb200_shutdown). At process exit the CUDA runtime may already be unloading: every
+  // call below then fails harmlessly and is ignored.
+  ~Ctx() { release(); }
 };
 thread_local Ctx t_ctx;
+
+void Ctx::release_ring() {
+  for (auto& s : ring) {
+    if (s.done) cudaEventSynchronize(s.done);
+    if (s.host) cudaFreeHost(s.host);
+    if (s.dev) cudaFree(s.dev);
+    if (s.done) cudaEventDestroy(s.done);
+    s = BatchSlot();
+  }
+  ring_next = 0;
+  ring_device = -1;
+  cudaGetLastError();
+}
+void Ctx::release() {
+  int cur = -1;
+  const bool have_cur = cudaGetDevice(&cur) == cudaSuccess;
+  if (ring_device >= 0 && cudaSetDevice(ring_device) == cudaSuccess) release_ring();
+  if (ready && cudaSetDevice(device) == cudaSuccess) {
+    if (stream) cudaStreamSynchronize(stream);
+    for (auto& b : buf) {
+      if (b.p) cudaFree(b.p);
+      b = DevBuf();
+    }
+    for (int i = 0; i < kSlots; i++) {
+      if (pin[i]) cudaFreeHost(pin[i]);
+      if (pin_ev[i]) cudaEventDestroy(pin_ev[i]);
+      pin[i] = nullptr;
+      pin_ev[i] = nullptr;
+      pin_busy[i] = false;
+    }
+    pin_next = 0;
+    if (stream) cudaStreamDestroy(stream);
+    if (sync_ev) cudaEventDestroy(sync_ev);
+  }
+  stream = nullptr;
+  sync_ev = nullptr;
+  ready = false;
+  if (have_cur && cur >= 0) cudaSetDevice(cur);
+  cudaGetLastError();
+}
 
 int fail(cudaError_t e, const char* what) {
   char msg[256];
@@ -98,6 +145,19 @@ int ensure_ctx() {
   CU(cudaStreamCreateWithFlags(&c.stream, cudaStreamNonBlocking));
   CU(cudaEventCreateWithFlags(&c.sync_ev, cudaEventBlockingSync | cudaEventDisableTiming));
   c.ready = true;
+  return 0;
+}
+
+// The *_dev and *_batch_dev entry points run on the caller's stream and device pointers: they follow the caller's CURRENT
+// device (never switch it) and key the cached IDW / transfer-function tables and the descriptor ring on it. The *_host
+// entry points bind the thread to its uhdrb200_init device first (ensure_ctx), so both agree there.
+int core_device(int* dev) {
+  cudaError_t e = cudaGetDevice(dev);
+  if (e != cudaSuccess) {
+    t_ctx.err = std::string("no CUDA device: ") + cudaGetErrorString(e);
+    cudaGetLastError();
+    return UHDRB200_ERROR_INSUFFICIENT_RESOURCE;
+  }
   return 0;
 }
 
@@ -353,6 +413,16 @@ void fill_sat_cell(ApplyFastParams& f, float mn, float mx, float db, int fmt) {
 // come from a ring guarded by events so an async caller can have kRing launches in flight.
 int stage_batch(const std::vector<Planes>& v, cudaStream_t s, const Planes** dev, BatchSlot** slot_out) {
   Ctx& c = t_ctx;
+  int cur = 0;
+  CU(cudaGetDevice(&cur));
+  if (c.ring_device != cur) {  // first use, or the calling thread moved to another GPU: the slots belong to one device
+    if (c.ring_device >= 0) {
+      CU(cudaSetDevice(c.ring_device));
+      c.release_ring();
+      CU(cudaSetDevice(cur));
+    }
+    c.ring_device = cur;
+  }
   BatchSlot& sl = c.ring[c.ring_next];
   c.ring_next = (c.ring_next + 1) % kRing;
   if (sl.done) CU(cudaEventSynchronize(sl.done));
@@ -500,7 +570,8 @@ int generate_core(int n, const uhdrb200_image* sdr, const uhdrb200_image* hdr, i
   }
   if (!fits_int(sdr[0].width) || !fits_int(sdr[0].height) || !fits_int(sdr[0].luma_stride) || !fits_int(hdr[0].luma_stride))
     return UHDRB200_ERROR_UNSUPPORTED_WIDTH_HEIGHT;
-  int st = ensure_ctx();
+  int dev = 0;
+  int st = core_device(&dev);
   if (st) return st;
   GenerateParams p;
   memset(&p, 0, sizeof p);
@@ -563,7 +634,8 @@ int apply_core(int n, const uhdrb200_image* sdr, const uhdrb200_image* map, cons
   if (fmt != UHDRB200_OUTPUT_HDR_LINEAR && fmt != UHDRB200_OUTPUT_HDR_PQ && fmt != UHDRB200_OUTPUT_HDR_HLG &&
       fmt != UHDRB200_OUTPUT_HDR_LINEAR_RGB_10BIT)
     return UHDRB200_NO_ERROR;  // ultrahdr.cpp:491-493: nothing is written, NO_ERROR
-  int st = ensure_ctx();
+  int dev = 0;
+  int st = core_device(&dev);
   if (st) return st;
   ApplyParams p;
   memset(&p, 0, sizeof p);
@@ -577,7 +649,7 @@ int apply_core(int n, const uhdrb200_image* sdr, const uhdrb200_image* map, cons
   p.max_boost = md->maxContentBoost;
   p.display_boost = max_display_boost < md->maxContentBoost ? max_display_boost : md->maxContentBoost;  // :415
   p.inv_display_boost = 1.0f / p.display_boost;
-  if ((st = get_idw(t_ctx.device, p.g.map_scale, &p.idw))) return st;
+  if ((st = get_idw(dev, p.g.map_scale, &p.idw))) return st;
   std::vector<Planes> v(n);
   bool vec = true;
   for (int i = 0; i < n; i++) {
@@ -641,7 +713,7 @@ int apply_core(int n, const uhdrb200_image* sdr, const uhdrb200_image* map, cons
     for (int i = 0; i < 16; i++)
       for (int c = 1; c < 4; c++) f.wq[c - 1][i] = (float)((double)f.w[i][c] / 2.4 / 255.0);
     f.idw = p.idw;
-    if ((st = get_apply_tables(t_ctx.device, &f.tab))) return st;
+    if ((st = get_apply_tables(dev, &f.tab))) return st;
     f.single = v[0];
     f.batch = batch;
     e = launch_apply_fast_impl(f, n, s);
@@ -668,7 +740,8 @@ int tonemap_core(int n, const uhdrb200_image* src, uhdrb200_image* dest, cudaStr
   }
   if (!fits_int(src[0].width) || !fits_int(src[0].height) || !fits_int(src[0].luma_stride) || !fits_int(dest[0].luma_stride))
     return UHDRB200_ERROR_UNSUPPORTED_WIDTH_HEIGHT;
-  int st = ensure_ctx();
+  int dev = 0;
+  int st = core_device(&dev);
   if (st) return st;
   ToneMapParams p;
   memset(&p, 0, sizeof p);
@@ -716,7 +789,8 @@ int convert_yuv_core(uhdrb200_image* im, int src_enc, int dst_enc, cudaStream_t 
   if (src_enc < 0 || src_enc > 2 || dst_enc < 0 || dst_enc > 2) return UHDRB200_ERROR_INVALID_COLORGAMUT;
   if (src_enc == dst_enc) return UHDRB200_NO_ERROR;
   if (!im->data || !im->chroma_data) return UHDRB200_ERROR_BAD_PTR;
-  int st = ensure_ctx();
+  int dev = 0;
+  int st = core_device(&dev);
   if (st) return st;
   ConvertYuvParams p;
   memset(&p, 0, sizeof p);
@@ -742,7 +816,8 @@ int sdr_pack_core(int n, const uhdrb200_image* sdr, uhdrb200_image* dest, cudaSt
   }
   if (!fits_int(sdr[0].width) || !fits_int(sdr[0].height) || !fits_int(sdr[0].luma_stride) || !fits_int(dest[0].luma_stride))
     return UHDRB200_ERROR_UNSUPPORTED_WIDTH_HEIGHT;
-  int st = ensure_ctx();
+  int dev = 0;
+  int st = core_device(&dev);
   if (st) return st;
   SdrPackParams p;
   memset(&p, 0, sizeof p);
@@ -777,7 +852,8 @@ int copy_yuv420_core(const uhdrb200_image* src, uhdrb200_image* dst, cudaStream_
     return UHDRB200_ERROR_INVALID_STRIDE;
   if (!fits_int(src->width) || !fits_int(src->height) || !fits_int(src->luma_stride) || !fits_int(dst->luma_stride))
     return UHDRB200_ERROR_UNSUPPORTED_WIDTH_HEIGHT;
-  int st = ensure_ctx();
+  int dev = 0;
+  int st = core_device(&dev);
   if (st) return st;
   SdrPackParams p;
   memset(&p, 0, sizeof p);
@@ -1131,7 +1207,10 @@ int api0_host(const uhdrb200_image* hdr, int hdr_tf, int sdr_to_601, uhdrb200_im
   if (!map_buf || map_buf_bytes < mbytes) return -20004;  // ERROR_ULTRAHDR_BUFFER_TOO_SMALL
   if ((st = ensure_ctx())) return st;
   Ctx& c = t_ctx;
-  const size_t ly = hdr->height ? 2 * (hdr->luma_stride * (hdr->height - 1) + hdr->width) : 0;
+  // toneMap reads the luma stride as given (ultrahdr.cpp:527), generateGainMap reads 0 as `width` (gainmapmath.cpp:585):
+  // stage whichever extent is larger
+  const size_t ly_lit = hdr->height ? 2 * (hdr->luma_stride * (hdr->height - 1) + hdr->width) : 0;
+  const size_t ly = ly_lit > p010_luma_bytes(*hdr) ? ly_lit : p010_luma_bytes(*hdr);
   const size_t dl = sdr->luma_stride * sdr->height, dc = 2 * (sdr->chroma_stride * (sdr->height / 2));
   if ((st = upload(c.buf[2], hdr->data, ly, c.stream))) return st;
   if ((st = upload(c.buf[3], hdr->chroma_data, p010_chroma_bytes(*hdr), c.stream))) return st;
@@ -1165,41 +1244,11 @@ int uhdrb200_device_count(void) {
 }
 int uhdrb200_init(int device) {
   Ctx& c = t_ctx;
-  if (c.ready && c.device != device) {  // rebind: drop the old stream, keep it simple
-    cudaSetDevice(c.device);
-    for (auto& b : c.buf) { if (b.p) cudaFree(b.p); b = DevBuf(); }
-    if (c.stream) cudaStreamDestroy(c.stream);
-    c.stream = nullptr;
-    c.ready = false;
-  }
+  if (c.ready && c.device != device) c.release();  // rebind: everything the old device owns goes (stream, events, pins, buffers, ring)
   c.device = device;
   return ensure_ctx();
 }
-void uhdrb200_shutdown(void) {
-  Ctx& c = t_ctx;
-  if (!c.ready) return;
-  cudaSetDevice(c.device);
-  cudaStreamSynchronize(c.stream);
-  for (auto& b : c.buf) { if (b.p) cudaFree(b.p); b = DevBuf(); }
-  for (auto& s : c.ring) {
-    if (s.host) cudaFreeHost(s.host);
-    if (s.dev) cudaFree(s.dev);
-    if (s.done) cudaEventDestroy(s.done);
-    s = BatchSlot();
-  }
-  for (int i = 0; i < Ctx::kSlots; i++) {
-    if (c.pin[i]) cudaFreeHost(c.pin[i]);
-    if (c.pin_ev[i]) cudaEventDestroy(c.pin_ev[i]);
-    c.pin[i] = nullptr;
-    c.pin_ev[i] = nullptr;
-    c.pin_busy[i] = false;
-  }
-  cudaStreamDestroy(c.stream);
-  if (c.sync_ev) cudaEventDestroy(c.sync_ev);
-  c.sync_ev = nullptr;
-  c.stream = nullptr;
-  c.ready = false;
-}
+void uhdrb200_shutdown(void) { t_ctx.release(); }
 const char* uhdrb200_last_error(void) { return t_ctx.err.c_str(); }
 void* uhdrb200_host_alloc(size_t bytes) {
   void* p = nullptr;
@@ -1218,10 +1267,11 @@ int uhdrb200_test_set_apply_mode(int mode) {
 int uhdrb200_test_eval(int fn, const float* in_dev, float* out_dev, size_t n, void* stream) {
   if (fn < 0 || fn >= UHDRB200_FN_COUNT) return UHDRB200_ERROR_UNSUPPORTED_FEATURE;
   if (n && (!in_dev || !out_dev)) return UHDRB200_ERROR_BAD_PTR;
-  int st = ensure_ctx();
+  int dev = 0;
+  int st = core_device(&dev);
   if (st) return st;
   ApplyTables tab;
-  if ((st = get_apply_tables(t_ctx.device, &tab))) return st;
+  if ((st = get_apply_tables(dev, &tab))) return st;
   const GainCode gc = gain_code_of(1.0f, 1000.0f / 203.0f);  // what generateGainMap writes for HLG (ultrahdr.cpp:250-257)
   cudaError_t e = launch_kat_impl(fn, in_dev, out_dev, n, tab, gc, (cudaStream_t)stream);
   if (e != cudaSuccess) return fail(e, "test_eval kernel launch");
