@@ -211,7 +211,7 @@ def main():
     ap.add_argument("--e2e-images", type=int, default=64, help="4K pairs per e2e step per GPU (host planes)")
     ap.add_argument("--e2e-threads", type=int, default=4, help="host threads calling the synchronous host-pointer API concurrently")
     ap.add_argument("--e2e-join", default="auto", choices=["auto", "spin", "blocking"], help="how the host entry points wait (uhdrb200_set_sync_mode)")
-    ap.add_argument("--e2e-host-memory", default="pinned", choices=["pinned", "pageable"],
+    ap.add_argument("--e2e-host-memory", default="pageable", choices=["pinned", "pageable"],
                     help="host planes of the e2e leg: uhdrb200_host_alloc (page-locked) or plain malloc'ed numpy buffers")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-other-stages", action="store_true", help="skip the per-kernel rooflines of the other stages")
@@ -285,6 +285,24 @@ def main():
     dev = torch.device("cuda", local)
     uh = api.JpegR(lib)
     assert lib.uhdrb200_init(local) == 0, lib.uhdrb200_last_error()
+
+    # N > 1: keep this rank's host threads (and the library's staging helpers) on the cores next to its GPU
+    numa_cores = None
+    if world > 1:
+        try:
+            import pynvml
+
+            pynvml.nvmlInit()
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            phys = int(vis.split(",")[local]) if vis and all(v.strip().isdigit() for v in vis.split(",")) else local
+            ncpu = os.cpu_count() or 1
+            words = pynvml.nvmlDeviceGetCpuAffinity(pynvml.nvmlDeviceGetHandleByIndex(phys), (ncpu + 63) // 64)
+            near = {i for i in range(ncpu) if (words[i // 64] >> (i % 64)) & 1} & os.sched_getaffinity(0)
+            if near:
+                os.sched_setaffinity(0, near)
+                numa_cores = len(near)
+        except Exception:
+            numa_cores = None
 
     # ---- CPU baseline first (rank 0, N=1 only), before the GPU is busy
     cpu_info = None
@@ -626,22 +644,25 @@ def main():
     e2e_s = time.perf_counter() - te0
     h2d = E * (sdr_len + hdr_len * 2 + sdr_len + MW * MH)  # generate: SDR+HDR planes; apply: SDR planes + map
     d2h = E * (MW * MH + PIX * 4)
-    # the same leg with pageable planes (what an unmodified libultrahdr caller passes): the library stages them through
-    # per-thread page-locked chunks (capi.cu copy_h2d / copy_d2h). Reported beside the pinned number, N = 1 only.
-    pageable_mpix = None
-    if world == 1 and not a.no_e2e and a.e2e_host_memory == "pinned":
-        cur_bufs[0] = make_bufs("pageable")
+    # the same leg with the OTHER kind of host memory, reported beside the headline: page-locked planes
+    # (uhdrb200_host_alloc: what a caller that adopts the library's allocator gets) when the headline is pageable
+    other_kind = "pinned" if a.e2e_host_memory == "pageable" else "pageable"
+    other_mpix = None
+    if not a.no_e2e:
+        cur_bufs[0] = make_bufs(other_kind)
         e2e_step()
+        barrier()
         tp0 = time.perf_counter()
         for _ in range(2):
             e2e_step()
-        pageable_mpix = 2 * E * PIX / (time.perf_counter() - tp0) / 1e6
+        barrier()
+        other_s = time.perf_counter() - tp0
         cur_bufs[0] = host_bufs
 
-    # what the PCIe link of this box gives (rank 0, N = 1): pinned <-> device copies of 256 MB alone and in both directions
-    # at once, in the e2e traffic ratio. The e2e rate is judged against these, not against HBM.
-    pcie = None
-    if world == 1 and not a.no_e2e:
+    # what the host <-> device links of this box give with ALL ranks copying at once (every N): pinned <-> device copies of
+    # 256 MB alone and in both directions together. The e2e rate is judged against these, not against HBM.
+    pcie_rates = [0.0, 0.0, 0.0]
+    if not a.no_e2e:
         nb = 256 << 20
         h_a = torch.empty(nb, dtype=torch.uint8).pin_memory()
         h_b = torch.empty(nb, dtype=torch.uint8).pin_memory()
@@ -650,7 +671,7 @@ def main():
         s1, s2 = torch.cuda.Stream(), torch.cuda.Stream()
 
         def copy_rate(up, down, reps=4):
-            torch.cuda.synchronize()
+            barrier()
             t = time.perf_counter()
             for _ in range(reps):
                 if up:
@@ -659,18 +680,24 @@ def main():
                 if down:
                     with torch.cuda.stream(s2):
                         h_b.copy_(d_b, non_blocking=True)
-            torch.cuda.synchronize()
+            barrier()
             return reps * nb / (time.perf_counter() - t) / 1e9
 
         copy_rate(True, True, 1)
-        pcie = {"h2d_alone_gbs": copy_rate(True, False), "d2h_alone_gbs": copy_rate(False, True),
-                "each_direction_when_both_gbs": copy_rate(True, True)}
+        pcie_rates = [copy_rate(True, False), copy_rate(False, True), copy_rate(True, True)]
         del h_a, h_b, d_a, d_b
 
-    times = torch.tensor([total_ms, e2e_s * 1e3, gen_ms, app_ms], dtype=torch.float64, device=dev)
+    times = torch.tensor([total_ms, e2e_s * 1e3, gen_ms, app_ms, (other_s if not a.no_e2e else 0.0) * 1e3], dtype=torch.float64, device=dev)
+    rates = torch.tensor(pcie_rates, dtype=torch.float64, device=dev)
     if dist is not None:
         dist.all_reduce(times, op=dist.ReduceOp.MAX)
-    total_ms, e2e_ms, gen_ms, app_ms = [float(x) for x in times.tolist()]
+        dist.all_reduce(rates, op=dist.ReduceOp.SUM)  # every rank timed the same barrier-to-barrier window: the sum is the box aggregate
+    total_ms, e2e_ms, gen_ms, app_ms, other_ms = [float(x) for x in times.tolist()]
+    pcie = None
+    if not a.no_e2e:
+        r_up, r_down, r_both = [float(x) for x in rates.tolist()]
+        pcie = {"ranks_copying_at_once": world, "h2d_alone_gbs": r_up, "d2h_alone_gbs": r_down, "each_direction_when_both_gbs": r_both}
+        other_mpix = world * 2 * E * PIX / (other_ms * 1e-3) / 1e6
     if clocks:
         clocks.stop()
     if dist is not None:
@@ -717,8 +744,9 @@ def main():
         "stage_mpix_s": {"generate": B * PIX / gen_ms / 1e3, "apply": B * PIX / app_ms / 1e3},
         "e2e": {"value": world * E * PIX * e2e_steps / (e2e_ms * 1e-3) / 1e6 if e2e_steps else None, "unit": UNIT, "h2d_bytes_per_step": h2d,
                 "d2h_bytes_per_step": d2h, "images_per_step_per_gpu": E, "steps": e2e_steps,
-                "host_threads": T, "join": "blocking" if blocking else "spin", "pcie_measured": pcie, "host_memory": a.e2e_host_memory, "pageable_callers_mpix_s": pageable_mpix,
-                "api": "uhdrb200_generate_gainmap_host_into + uhdrb200_apply_gainmap_host (synchronous, reference-style), pinned host planes"},
+                "host_threads": T, "numa_local_cores": numa_cores, "join": "blocking" if blocking else "spin", "pcie_measured": pcie, "host_memory": a.e2e_host_memory, other_kind + "_planes_mpix_s": other_mpix,
+                "api": "uhdrb200_generate_gainmap_host_into + uhdrb200_apply_gainmap_host (synchronous, reference-style); " +
+                       ("pageable host planes, as an unmodified libultrahdr caller passes them" if a.e2e_host_memory == "pageable" else "page-locked host planes")},
         "other_stages": {k: dict(v, frac_of_hbm_peak=v["achieved_gbs"] / peak) for k, v in other.items()},
         "gpu_launches": int(launches),
         "clocks": clk,
@@ -727,6 +755,11 @@ def main():
         ips = out["e2e"]["value"] * 1e6 / PIX / world  # images per second per GPU
         out["e2e"]["h2d_gbs_per_gpu"] = ips * h2d / E / 1e9
         out["e2e"]["d2h_gbs_per_gpu"] = ips * d2h / E / 1e9
+        if pcie and pcie["each_direction_when_both_gbs"] > 0:
+            # ceiling of this traffic mix on the measured links: both directions busy, the up direction carries more bytes
+            ceil_ips = pcie["each_direction_when_both_gbs"] * 1e9 / max(h2d / E, d2h / E)
+            out["e2e"]["link_ceiling_mpix_s"] = ceil_ips * PIX / 1e6
+            out["e2e"]["frac_of_link_ceiling"] = out["e2e"]["value"] / out["e2e"]["link_ceiling_mpix_s"]
     if cpu_info:
         out["cpu_baseline"] = cpu_info
     print(json.dumps(out))

@@ -253,7 +253,9 @@ template <int PACK, bool MASK, bool BATCH, bool LTAB, bool NORM>
 __global__ void __launch_bounds__(kQThreads, LTAB ? UHDR_APPLYQ_L_MIN_BLOCKS : UHDR_APPLYQ_MIN_BLOCKS) apply_q_kernel(const __grid_constant__ ApplyFastParams p) {
   const uint32_t kQCells = (uint32_t)p.cells, kQTileRows = (kQThreads / 32) * kQCells;  // cell rows per tile: warps x CELLS
   const int tid = threadIdx.x;
-  const uint32_t hiP = stage_q_table<PACK, LTAB>(p, tid);
+  pdl_trigger();
+  const uint32_t hiP = stage_q_table<PACK, LTAB>(p, tid);  // constants only: may overlap the previous kernel's tail
+  pdl_wait();
 
   const Geometry& g = p.g;
   const uint32_t mw = g.map_width, mh = g.map_height;
@@ -287,6 +289,11 @@ __global__ void __launch_bounds__(kQThreads, LTAB ? UHDR_APPLYQ_L_MIN_BLOCKS : U
     ty += dty;
     if (ty >= tiles_y) { ty -= tiles_y; z++; }
     z += dz;
+#ifndef UHDR_APPLYQ_VOTE
+#define UHDR_APPLYQ_VOTE 1  // a quad-row with a toe channel in ANY lane sends the whole warp down the packed toe-select path
+#endif
+    // the lanes of a warp share cy and kmax (a warp is one row of 32 cells), so those inside the map walk in lock step
+    const unsigned amask = __ballot_sync(0xffffffffu, cx < mw && cy < mh);
     if (cx >= mw || cy >= mh) continue;
     const uint8_t *sdr_y, *sdr_u, *sdr_v, *map;
     uint8_t* outp;
@@ -339,7 +346,7 @@ __global__ void __launch_bounds__(kQThreads, LTAB ? UHDR_APPLYQ_L_MIN_BLOCKS : U
     };
     fetch(cy);
 #endif
-#pragma unroll 1
+#pragma unroll kQUnroll
     for (uint32_t k = 0; k < kmax; k++, cy++) {
       uint32_t yw[4], uw[2], vw[2];
 #if UHDR_APPLYQ_PREFETCH
@@ -416,8 +423,8 @@ __global__ void __launch_bounds__(kQThreads, LTAB ? UHDR_APPLYQ_L_MIN_BLOCKS : U
             f[i] = ex2_fast(fmaf(gain, p.Aq, p.Bq));
           }
         }
-        quad_row_eval<PACK, MASK, LTAB, NORM>(hiP, yw[2 * qr], yw[2 * qr + 1], uw[qr], vw[qr], f, orow + (size_t)(2 * qr) * ostride, ostride, plane_bytes,
-                                              0xffffffffu, satcell, p.vsat[sat_t] + qr * 8, p.rsat[sat_t] + qr * 8);
+        quad_row_eval<PACK, MASK, LTAB, NORM, UHDR_APPLYQ_VOTE != 0>(hiP, yw[2 * qr], yw[2 * qr + 1], uw[qr], vw[qr], f, orow + (size_t)(2 * qr) * ostride,
+                                                                     ostride, plane_bytes, amask, satcell, p.vsat[sat_t] + qr * 8, p.rsat[sat_t] + qr * 8);
       }
       e1 = e2;
       e3 = e4;
@@ -437,7 +444,9 @@ __global__ void __launch_bounds__(kQThreads, LTAB ? UHDR_APPLYQ_L_MIN_BLOCKS : U
 template <int PACK, bool MASK, bool BATCH, bool LTAB, bool NORM, int SCALE>
 __global__ void __launch_bounds__(kThreads, 3) apply_qs_kernel(const __grid_constant__ ApplyFastParams p) {
   const int tid = threadIdx.x;
-  const uint32_t hiP = stage_q_table<PACK, LTAB>(p, tid);
+  pdl_trigger();
+  const uint32_t hiP = stage_q_table<PACK, LTAB>(p, tid);  // constants only: may overlap the previous kernel's tail
+  pdl_wait();
   const Geometry& g = p.g;
   const uint32_t mw = g.map_width, mh = g.map_height, sc = (uint32_t)g.map_scale, magic = p.scale_magic;
   const uint32_t bw = (uint32_t)g.width >> 2, bh = (uint32_t)g.height >> 2;  // 4x4 pixel blocks
@@ -661,8 +670,7 @@ cudaError_t launch_q(const ApplyFastParams& p0, cudaStream_t s) {
   p.tiles_y = (p.g.map_height + kQTileRows - 1) / kQTileRows;  // this kernel's tiles are kQTileRows cell rows tall
   p.n_tiles = p.tiles_x * p.tiles_y * n_img;
   const int grid = p.n_tiles < cap ? p.n_tiles : cap;
-  apply_q_kernel<PACK, MASK, BATCH, LTAB, NORM><<<grid, kQThreads, (size_t)smem_bytes, s>>>(p);
-  return cudaGetLastError();
+  return launch_pdl(apply_q_kernel<PACK, MASK, BATCH, LTAB, NORM>, dim3(grid), dim3(kQThreads), (size_t)smem_bytes, s, p.pdl != 0, p);
 }
 
 template <int PACK, bool MASK>
@@ -702,8 +710,7 @@ cudaError_t launch_qs(const ApplyFastParams& p0, cudaStream_t s) {
   const int cap = sms_of[dev] * per_sm_of[dev], smem_bytes = smem_of[dev];
   lk.unlock();
   const int grid = p0.n_tiles < cap ? p0.n_tiles : cap;
-  apply_qs_kernel<PACK, MASK, BATCH, LTAB, NORM, SCALE><<<grid, kThreads, (size_t)smem_bytes, s>>>(p0);
-  return cudaGetLastError();
+  return launch_pdl(apply_qs_kernel<PACK, MASK, BATCH, LTAB, NORM, SCALE>, dim3(grid), dim3(kThreads), (size_t)smem_bytes, s, p0.pdl != 0, p0);
 }
 
 template <int PACK, bool MASK, int SCALE>

@@ -103,7 +103,7 @@ template <int PACK, bool MASK, bool BATCH, bool LTAB, bool NORM>
 __global__ void __launch_bounds__(kPipeThreads, LTAB ? UHDR_PIPE_L_MIN_BLOCKS : UHDR_PIPE_MIN_BLOCKS) apply_pipe_kernel(const __grid_constant__ ApplyFastParams p) {
   // programmatic dependent launch: the next kernel of the stream may start its prologue now; its own griddepcontrol.wait
   // still orders its loads and stores behind this whole grid
-  asm volatile("griddepcontrol.launch_dependents;");
+  pdl_trigger();
   extern __shared__ __align__(16) uint8_t smem_dyn[];
   const int tid = threadIdx.x;
   const uint32_t lane = tid & 31, wid = tid >> 5;
@@ -123,7 +123,7 @@ __global__ void __launch_bounds__(kPipeThreads, LTAB ? UHDR_PIPE_L_MIN_BLOCKS : 
   __syncwarp();
   const uint32_t hiP = stage_q_table<PACK, LTAB>(p, tid);
   // everything above touches only constants; the planes below may be the previous kernel's output
-  asm volatile("griddepcontrol.wait;" ::: "memory");
+  pdl_wait();
 
   const Geometry& g = p.g;
   const uint32_t mw = g.map_width, mh = g.map_height, cells = (uint32_t)p.cells;
@@ -364,18 +364,7 @@ cudaError_t launch_pipe(const ApplyFastParams& p0, int n_img, cudaStream_t s) {
   const int grid = blocks_needed < li.sms * li.per_sm ? blocks_needed : li.sms * li.per_sm;
   // programmatic dependent launch: this kernel's start-up (table staging, barrier set-up) may overlap the tail of the
   // previous kernel in the stream; its griddepcontrol.wait orders everything else
-  cudaLaunchConfig_t cfg;
-  memset(&cfg, 0, sizeof cfg);
-  cfg.gridDim = dim3((unsigned)grid);
-  cfg.blockDim = dim3(kPipeThreads);
-  cfg.dynamicSmemBytes = (size_t)li.smem;
-  cfg.stream = s;
-  cudaLaunchAttribute at[1];
-  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-  at[0].val.programmaticStreamSerializationAllowed = 1;
-  cfg.attrs = at;
-  cfg.numAttrs = p0.pdl ? 1 : 0;
-  return cudaLaunchKernelEx(&cfg, apply_pipe_kernel<PACK, MASK, BATCH, LTAB, NORM>, p);
+  return launch_pdl(apply_pipe_kernel<PACK, MASK, BATCH, LTAB, NORM>, dim3((unsigned)grid), dim3(kPipeThreads), (size_t)li.smem, s, p0.pdl != 0, p);
 }
 
 template <int PACK, bool MASK>

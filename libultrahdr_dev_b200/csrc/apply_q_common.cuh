@@ -26,6 +26,10 @@ constexpr int kThreads = 256;
 #endif
 constexpr int kQThreads = UHDR_APPLYQ_THREADS;  // block size of apply_q_kernel (its tile is kQThreads / 32 warps x CELLS cell rows tall)
 constexpr int kTileCellsX = 32, kTileCellsY = 8;
+#ifndef UHDR_APPLYQ_UNROLL
+#define UHDR_APPLYQ_UNROLL 1  // unroll factor of apply_q_kernel's cell walk
+#endif
+constexpr int kQUnroll = UHDR_APPLYQ_UNROLL;
 
 enum { kPack1010102 = 0, kPackF16 = 1, kPackPlanar10 = 2 };
 

@@ -6,6 +6,9 @@
 // There is NO CPU fallback: without a usable CUDA device every compute entry point returns
 // UHDRB200_ERROR_INSUFFICIENT_RESOURCE and uhdrb200_last_error() says why.
 #include <atomic>
+#include <condition_variable>
+#include <deque>
+#include <thread>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -31,6 +34,14 @@ std::atomic<int> g_sync_mode{-1};  // -1: from the environment (UHDRB200_BLOCKIN
 // test hook (include/uhdr_b200_test.h), per calling thread: 0 auto, 1 analytic kernel, 2 two-table kernel, 3 the TMA-fed
 // pipeline variant of the q-domain kernel
 thread_local int t_apply_mode = 0;
+// programmatic dependent launch of the generate / apply kernels (uhdr_io.cuh); UHDRB200_NO_PDL=1 turns it off
+bool pdl_enabled() {
+  static const bool on = [] {
+    const char* e = getenv("UHDRB200_NO_PDL");
+    return !(e && e[0] == '1');
+  }();
+  return on;
+}
 
 // ---------------------------------------------------------------- per-thread context
 struct DevBuf {
@@ -222,6 +233,91 @@ void stage_copy(uint8_t* dst, const uint8_t* src, size_t n) {
   memcpy(dst, src, n);
 #endif
 }
+// The reference spends up to four host threads on one call (ultrahdr.cpp:304, 500); for a caller with pageable planes the
+// host-side cost here is the copy into / out of the page-locked chunks, so that copy gets the same budget: a chunk is cut
+// into slices which the calling thread and up to three helpers of a process-wide pool move concurrently (one core's copy
+// rate, ~10 GB/s, is a fifth of what the PCIe link takes). UHDRB200_STAGE_THREADS sets the pool size (0 = caller only).
+class StagePool {
+ public:
+  static StagePool& get() {
+    static StagePool* p = new StagePool();  // never destroyed: its threads sleep on the queue until the process exits
+    return *p;
+  }
+  // copies n bytes; `nt` = streaming stores (dst 16-byte aligned, only read by the copy engine afterwards)
+  void copy(uint8_t* dst, const uint8_t* src, size_t n, bool nt) {
+    const size_t kSlice = size_t(1) << 20;
+    if (workers_ == 0 || n < 2 * kSlice) {
+      move(dst, src, n, nt);
+      return;
+    }
+    const int parts = (int)((n + kSlice - 1) / kSlice < (size_t)kPerCall ? (n + kSlice - 1) / kSlice : (size_t)kPerCall);
+    const size_t per = ((n / parts) + 63) & ~size_t(63);
+    std::atomic<int> pending{parts - 1};
+    {
+      std::lock_guard<std::mutex> lk(mu_);
+      for (int i = 1; i < parts; i++) {
+        const size_t off = per * i, len = i == parts - 1 ? n - off : per;
+        q_.push_back(Task{dst + off, src + off, len, nt, &pending});
+      }
+    }
+    cv_.notify_all();
+    move(dst, src, per, nt);
+    Task t;
+    while (pending.load(std::memory_order_acquire) > 0) {  // help with whatever is queued (mine or another caller's), then wait
+      if (pop(&t)) run(t);
+      else std::this_thread::yield();
+    }
+  }
+
+ private:
+  static constexpr int kPerCall = 4;
+  struct Task {
+    uint8_t* dst;
+    const uint8_t* src;
+    size_t n;
+    bool nt;
+    std::atomic<int>* pending;
+  };
+  StagePool() {
+    int n = (int)std::thread::hardware_concurrency() / 2;
+    n = n < 2 ? 2 : (n > 12 ? 12 : n);
+    if (const char* e = getenv("UHDRB200_STAGE_THREADS")) n = atoi(e);
+    workers_ = n < 0 ? 0 : n;
+    for (int i = 0; i < workers_; i++) std::thread([this] { loop(); }).detach();
+  }
+  static void move(uint8_t* dst, const uint8_t* src, size_t n, bool nt) {
+    if (nt) stage_copy(dst, src, n);
+    else memcpy(dst, src, n);
+  }
+  static void run(const Task& t) {
+    move(t.dst, t.src, t.n, t.nt);
+    t.pending->fetch_sub(1, std::memory_order_release);
+  }
+  bool pop(Task* t) {
+    std::lock_guard<std::mutex> lk(mu_);
+    if (q_.empty()) return false;
+    *t = q_.front();
+    q_.pop_front();
+    return true;
+  }
+  void loop() {
+    for (;;) {
+      Task t;
+      {
+        std::unique_lock<std::mutex> lk(mu_);
+        cv_.wait(lk, [this] { return !q_.empty(); });
+        t = q_.front();
+        q_.pop_front();
+      }
+      run(t);
+    }
+  }
+  std::mutex mu_;
+  std::condition_variable cv_;
+  std::deque<Task> q_;
+  int workers_ = 0;
+};
+
 int copy_h2d(Ctx& c, void* dst, const void* src, size_t bytes) {
   if (!bytes) return 0;
   if (!is_pageable(src)) {
@@ -235,7 +331,7 @@ int copy_h2d(Ctx& c, void* dst, const void* src, size_t bytes) {
     const int k = c.pin_next;
     c.pin_next = (k + 1) % Ctx::kSlots;
     if (c.pin_busy[k]) CU(cudaEventSynchronize(c.pin_ev[k]));  // the chunk's previous DMA has drained
-    stage_copy(c.pin[k], (const uint8_t*)src + off, n);
+    StagePool::get().copy(c.pin[k], (const uint8_t*)src + off, n, true);
     CU(cudaMemcpyAsync((uint8_t*)dst + off, c.pin[k], n, cudaMemcpyHostToDevice, c.stream));
     CU(cudaEventRecord(c.pin_ev[k], c.stream));
     c.pin_busy[k] = true;
@@ -269,7 +365,7 @@ int copy_d2h(Ctx& c, void* dst, const void* src, size_t bytes) {
     const int k = slot_of[done % Ctx::kSlots];
     const size_t off = done * Ctx::kChunk, n = bytes - off < Ctx::kChunk ? bytes - off : Ctx::kChunk;
     CU(cudaEventSynchronize(c.pin_ev[k]));
-    memcpy((uint8_t*)dst + off, c.pin[k], n);
+    StagePool::get().copy((uint8_t*)dst + off, c.pin[k], n, false);
     c.pin_busy[k] = false;
     done++;
   }
@@ -599,6 +695,7 @@ int generate_core(int n, const uhdrb200_image* sdr, const uhdrb200_image* hdr, i
     vec = vec && generate_vec_ok(p.g, v[i]);
   }
   p.gc = gain_code_of(md[0].minContentBoost, md[0].maxContentBoost);
+  p.pdl = pdl_enabled() ? 1 : 0;
   if (conv) {
     p.convert = 1;
     memcpy(p.conv, conv, sizeof p.conv);
@@ -696,7 +793,7 @@ int apply_core(int n, const uhdrb200_image* sdr, const uhdrb200_image* map, cons
     f.two_table = t_apply_mode == 2;
     f.pipe = (t_apply_mode == 3 && !any_scale) ? 1 : 0;
     for (int i = 0; i < n && f.pipe; i++) f.pipe = apply_pipe_ok(p.g, v[i]) ? 1 : 0;
-    f.pdl = 1;
+    f.pdl = pdl_enabled() ? 1 : 0;
     f.any_scale = any_scale ? 1 : 0;
     if (any_scale && (p.g.map_scale == 1 || p.g.map_scale == 2)) {
       bool al = true;  // the specialised kernels read the map as 32-bit (scale 1) / 16-bit (scale 2) words

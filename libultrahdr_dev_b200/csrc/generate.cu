@@ -25,10 +25,12 @@ namespace {
 // transformYuv420 gainmapmath.cpp:483-520) while the gain computation keeps the un-converted samples.
 template <bool VEC, bool FUSED, bool CONVERT = false>
 __global__ void __launch_bounds__(256) generate_kernel(GenerateParams p) {
+  pdl_trigger();
   const Geometry& g = p.g;
   const int mx = blockIdx.x * 32 + threadIdx.x;
   const int my = blockIdx.y * 8 + threadIdx.y;
   if (mx >= g.map_width || my >= g.map_height) return;
+  pdl_wait();  // planes (and the descriptor array) may come from the previous kernel of the stream
   const Planes pl = p.batch ? p.batch[blockIdx.z] : p.single;
 
   // ---- gather the raw samples of the 4x4 block as packed words (all loads first) ----
@@ -179,9 +181,8 @@ cudaError_t launch_generate_impl(const GenerateParams& p, int n, bool vec, cudaS
   if (p.g.map_width == 0 || p.g.map_height == 0 || n == 0) return cudaSuccess;
   dim3 block(32, 8, 1);
   dim3 grid((p.g.map_width + 31) / 32, (p.g.map_height + 7) / 8, n);
-  if (vec) generate_kernel<true, false><<<grid, block, 0, s>>>(p);
-  else generate_kernel<false, false><<<grid, block, 0, s>>>(p);
-  return cudaGetLastError();
+  if (vec) return launch_pdl(generate_kernel<true, false, false>, grid, block, 0, s, p.pdl != 0, p);
+  return launch_pdl(generate_kernel<false, false, false>, grid, block, 0, s, p.pdl != 0, p);
 }
 
 // API-0 fused toneMap + generateGainMap: the sdr_* planes of `Planes` are OUTPUTS here.
@@ -192,9 +193,8 @@ cudaError_t launch_api0_fused_impl(const GenerateParams& p, int n, cudaStream_t 
   if (p.g.map_width == 0 || p.g.map_height == 0 || n == 0) return cudaSuccess;
   dim3 block(32, 8, 1);
   dim3 grid((p.g.map_width + 31) / 32, (p.g.map_height + 7) / 8, n);
-  if (p.convert) generate_kernel<true, true, true><<<grid, block, 0, s>>>(p);
-  else generate_kernel<true, true, false><<<grid, block, 0, s>>>(p);
-  return cudaGetLastError();
+  if (p.convert) return launch_pdl(generate_kernel<true, true, true>, grid, block, 0, s, p.pdl != 0, p);
+  return launch_pdl(generate_kernel<true, true, false>, grid, block, 0, s, p.pdl != 0, p);
 }
 
 }  // namespace uhdr

@@ -40,6 +40,7 @@ struct GenerateParams {
   int hdr_tf;       // 0 linear, 1 HLG, 2 PQ
   float hdr_white_nits;
   GainCode gc;      // encodeGain constants (uhdr_math.cuh), filled by the host
+  int pdl;          // 1: launch with programmatic stream serialization (uhdr_io.cuh: launch_pdl)
   int convert;                   // fused API-0 only: 1 = the SDR planes are written re-encoded with `conv` (row N1, jpegr.cpp:223-225)
   float conv[9];                 // YUV->YUV matrix, gainmapmath.cpp:447-481
   Planes single;

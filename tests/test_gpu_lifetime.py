@@ -46,13 +46,14 @@ def test_thread_exit_releases_its_context(uh):
             t.start()
             t.join()
 
-    run(2)
+    run(4)
     torch.cuda.synchronize()
     free0, _ = torch.cuda.mem_get_info()
     run(24)
     torch.cuda.synchronize()
     free1, _ = torch.cuda.mem_get_info()
-    assert free0 - free1 < (8 << 20), f"device memory shrank by {(free0 - free1) >> 20} MB over 24 thread lifetimes"
+    # a leaked context would cost ~25 MB of device staging per thread (600 MB here); the driver's own pools may grow a little
+    assert free0 - free1 < (64 << 20), f"device memory shrank by {(free0 - free1) >> 20} MB over 24 thread lifetimes"
     assert all(np.array_equal(results[i], results[i % 2]) for i in range(len(results)))
 
 
