@@ -243,6 +243,26 @@ int uhdrb200_yuv420_to_rgba8888_batch_dev(int n, const uhdrb200_image* yuv420, u
 int uhdrb200_copy_yuv420_host(const uhdrb200_image* src, uhdrb200_image* dest);
 int uhdrb200_copy_yuv420_dev(const uhdrb200_image* src, uhdrb200_image* dest, void* stream);
 
+/* ---- N4 (first slice): the coefficient-domain back half of the JPEG decode that feeds applyGainMap ----
+ * JpegDecoderHelper::decompressImage with raw_data_out = TRUE and dct_method = JDCT_ISLOW
+ * (lib/src/jpegdecoderhelper.cpp:291-307, 380-435, called from jpegr.cpp:693 for the primary image and :732 for the gain
+ * map): dequantise + 8x8 integer inverse DCT (IJG "islow", jidctint.c) + range-limit, into the planar Y | U | V / grey
+ * planes. Entropy decoding stays on the host: `coeffs` is what libjpeg's jpeg_read_coefficients() / access_virt_barray
+ * hands out per component (blocks in raster order, 64 int16 each in natural order, whole MCUs), `quant` the component's
+ * 64 quantisation steps in natural order (quant_tbl_ptrs[...]->quantval). Rows beyond `height` and columns beyond `width`
+ * (the MCU padding) are not written. libjpeg-turbo's source is not part of the reference tree: parity is pinned on its
+ * OUTPUT for the reference's JPEG fixtures (tests/test_jpeg_idct.py). Up to 4 components per call (_host: up to 3);
+ * `coeffs` must be 16-byte aligned. _dev: every pointer is device memory, asynchronous on `stream`. */
+typedef struct uhdrb200_jpeg_component {
+  const int16_t* coeffs;
+  const uint16_t* quant;
+  size_t blocks_w, blocks_h;
+  void* plane;
+  size_t width, height, stride;
+} uhdrb200_jpeg_component;
+int uhdrb200_jpeg_idct_host(int n_components, const uhdrb200_jpeg_component* comps);
+int uhdrb200_jpeg_idct_dev(int n_components, const uhdrb200_jpeg_component* comps, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

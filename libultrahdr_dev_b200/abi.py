@@ -74,6 +74,21 @@ class Metadata(C.Structure):
         return d
 
 
+class JpegComponent(C.Structure):
+    """uhdrb200_jpeg_component (row N4): one colour component in the coefficient domain and its output plane."""
+
+    _fields_ = [
+        ("coeffs", C.c_void_p),
+        ("quant", C.c_void_p),
+        ("blocks_w", C.c_size_t),
+        ("blocks_h", C.c_size_t),
+        ("plane", C.c_void_p),
+        ("width", C.c_size_t),
+        ("height", C.c_size_t),
+        ("stride", C.c_size_t),
+    ]
+
+
 def default_metadata(max_boost, min_boost=1.0):
     """What generateGainMap writes (ultrahdr.cpp:250-257)."""
     m = Metadata()

@@ -51,6 +51,8 @@ SYMBOLS = {
     "uhdrb200_yuv420_to_rgba8888_host": (C.c_int, [P_IMG, P_IMG]),
     "uhdrb200_yuv420_to_rgba8888_dev": (C.c_int, [P_IMG, P_IMG, C.c_void_p]),
     "uhdrb200_yuv420_to_rgba8888_batch_dev": (C.c_int, [C.c_int, P_IMG, P_IMG, C.c_void_p]),
+    "uhdrb200_jpeg_idct_host": (C.c_int, [C.c_int, C.POINTER(abi.JpegComponent)]),
+    "uhdrb200_jpeg_idct_dev": (C.c_int, [C.c_int, C.POINTER(abi.JpegComponent), C.c_void_p]),
     "uhdrb200_copy_yuv420_host": (C.c_int, [P_IMG, P_IMG]),
     "uhdrb200_copy_yuv420_dev": (C.c_int, [P_IMG, P_IMG, C.c_void_p]),
 }

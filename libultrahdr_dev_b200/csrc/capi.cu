@@ -1330,6 +1330,81 @@ int api0_host(const uhdrb200_image* hdr, int hdr_tf, int sdr_to_601, uhdrb200_im
 
 }  // namespace
 
+// ================================================================ row N4: JPEG coefficient planes -> sample planes
+namespace {
+
+int validate_jpeg(int n, const uhdrb200_jpeg_component* comps, int max_n) {
+  if (n <= 0) return UHDRB200_NO_ERROR;
+  if (!comps) return UHDRB200_ERROR_BAD_PTR;
+  if (n > max_n) return UHDRB200_ERROR_UNSUPPORTED_FEATURE;
+  for (int i = 0; i < n; i++) {
+    const uhdrb200_jpeg_component& c = comps[i];
+    if (c.blocks_w == 0 || c.blocks_h == 0) continue;
+    if (!c.coeffs || !c.quant || !c.plane) return UHDRB200_ERROR_BAD_PTR;
+    if (c.width > c.blocks_w * 8 || c.height > c.blocks_h * 8) return UHDRB200_ERROR_RESOLUTION_MISMATCH;
+    if (c.stride < c.width) return UHDRB200_ERROR_INVALID_STRIDE;
+    if (!fits_int(c.blocks_w * 8) || !fits_int(c.blocks_h * 8)) return UHDRB200_ERROR_UNSUPPORTED_WIDTH_HEIGHT;
+  }
+  return UHDRB200_NO_ERROR;
+}
+
+int jpeg_idct_core(int n, const uhdrb200_jpeg_component* comps, cudaStream_t s) {
+  int st = validate_jpeg(n, comps, 4);
+  if (st || n <= 0) return st;
+  int dev = 0;
+  if ((st = core_device(&dev))) return st;
+  JpegIdctParams p;
+  memset(&p, 0, sizeof p);
+  p.n_components = n;
+  for (int i = 0; i < n; i++) {
+    if ((reinterpret_cast<uintptr_t>(comps[i].coeffs) & 15) != 0) {
+      t_ctx.err = "uhdrb200_jpeg_idct: coeffs must be 16-byte aligned";
+      return UHDRB200_ERROR_UNSUPPORTED_FEATURE;
+    }
+    p.comp[i] = JpegIdctComponent{comps[i].coeffs, comps[i].quant, comps[i].blocks_w, comps[i].blocks_h, (uint8_t*)comps[i].plane,
+                                  comps[i].width, comps[i].height, comps[i].stride};
+  }
+  cudaError_t e = launch_jpeg_idct_impl(p, s);
+  if (e != cudaSuccess) return fail(e, "jpeg_idct kernel launch");
+  g_launches++;
+  return UHDRB200_NO_ERROR;
+}
+
+int jpeg_idct_host(int n, const uhdrb200_jpeg_component* comps) {
+  int st = validate_jpeg(n, comps, 3);
+  if (st || n <= 0) return st;
+  if ((st = ensure_ctx())) return st;
+  Ctx& c = t_ctx;
+  uhdrb200_jpeg_component d[3];
+  if ((st = reserve(c.buf[3], 3 * 64 * sizeof(uint16_t)))) return st;
+  for (int i = 0; i < n; i++) {
+    d[i] = comps[i];
+    const size_t cb = comps[i].blocks_w * comps[i].blocks_h * 64 * sizeof(int16_t);
+    const size_t pb = comps[i].height ? comps[i].stride * (comps[i].height - 1) + comps[i].width : 0;
+    if (cb == 0) continue;
+    if ((st = upload(c.buf[i], comps[i].coeffs, cb, c.stream))) return st;
+    if ((st = copy_h2d(c, (uint8_t*)c.buf[3].p + i * 128, comps[i].quant, 128))) return st;
+    if ((st = reserve(c.buf[4 + i], pb ? pb : 1))) return st;
+    d[i].coeffs = (const int16_t*)c.buf[i].p;
+    d[i].quant = (const uint16_t*)((uint8_t*)c.buf[3].p + i * 128);
+    d[i].plane = c.buf[4 + i].p;
+  }
+  if ((st = jpeg_idct_core(n, d, c.stream))) return st;
+  for (int i = 0; i < n; i++) {
+    const uhdrb200_jpeg_component& h = comps[i];
+    if (h.blocks_w == 0 || h.blocks_h == 0 || h.height == 0 || h.width == 0) continue;
+    if (h.stride == h.width) {
+      if ((st = copy_d2h(c, h.plane, d[i].plane, h.stride * (h.height - 1) + h.width))) return st;
+    } else {  // only the samples: bytes between width and the stride stay the caller's
+      CU(cudaMemcpy2DAsync(h.plane, h.stride, d[i].plane, h.stride, h.width, h.height, cudaMemcpyDeviceToHost, c.stream));
+    }
+  }
+  CU(join_stream(c));
+  return UHDRB200_NO_ERROR;
+}
+
+}  // namespace
+
 // ================================================================ extern "C"
 extern "C" {
 
@@ -1451,6 +1526,10 @@ int uhdrb200_yuv420_to_rgba8888_dev(const uhdrb200_image* yuv420, uhdrb200_image
 }
 int uhdrb200_yuv420_to_rgba8888_batch_dev(int n, const uhdrb200_image* yuv420, uhdrb200_image* dest, void* stream) {
   return sdr_pack_core(n, yuv420, dest, (cudaStream_t)stream);
+}
+int uhdrb200_jpeg_idct_host(int n_components, const uhdrb200_jpeg_component* comps) { return jpeg_idct_host(n_components, comps); }
+int uhdrb200_jpeg_idct_dev(int n_components, const uhdrb200_jpeg_component* comps, void* stream) {
+  return jpeg_idct_core(n_components, comps, (cudaStream_t)stream);
 }
 int uhdrb200_copy_yuv420_host(const uhdrb200_image* src, uhdrb200_image* dest) { return copy_yuv420_host(src, dest); }
 int uhdrb200_copy_yuv420_dev(const uhdrb200_image* src, uhdrb200_image* dest, void* stream) {

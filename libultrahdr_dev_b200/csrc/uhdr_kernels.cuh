@@ -157,6 +157,20 @@ struct SdrPackParams {   // row N3: yuv420 -> RGBA8888 (out = packed pixels, dst
   const Planes* batch;
 };
 
+// row N4 (jpeg_idct.cu): one colour component of a JPEG in the coefficient domain -> its u8 plane
+struct JpegIdctComponent {
+  const int16_t* coeffs;      // blocks_h x blocks_w blocks of 64 quantised coefficients, natural (row-major) order, 16-byte aligned
+  const uint16_t* quant;      // 64 quantisation steps, natural order
+  size_t blocks_w, blocks_h;  // geometry of the coefficient array (whole MCUs, as jpeg_read_coefficients stores it)
+  uint8_t* plane;             // output samples
+  size_t width, height, stride;  // visible samples and the plane's row stride in bytes
+};
+struct JpegIdctParams {
+  int n_components;
+  JpegIdctComponent comp[4];
+};
+cudaError_t launch_jpeg_idct_impl(const JpegIdctParams& p, cudaStream_t s);
+
 // *_vec_ok: true when the planes/strides of an image allow the 128-bit vector path (the caller
 // ANDs it over a batch). launch_*_impl return the cudaError_t of the launch; `n` = images (grid.z).
 bool generate_vec_ok(const Geometry& g, const Planes& pl);

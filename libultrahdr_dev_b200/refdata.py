@@ -21,12 +21,24 @@ FILES = {"p010": ("raw_p010_image.p010", 1280, 720), "yuv420": ("raw_yuv420_imag
          "minnie": ("minnie-320x240.yu12", 320, 240)}
 
 
+# baseline JPEG fixtures of the reference's codec tests (row N4): 4:2:0 colour 1280x720 and 320x240, and a grey one
+JPEGS = ["jpeg_image.jpg", "minnie-320x240-yuv.jpg", "minnie-320x240-y.jpg"]
+
+
+def jpeg_path(name):
+    for d in (LOCAL, REF):
+        p = os.path.join(d, name)
+        if os.path.exists(p):
+            return p
+    return None
+
+
 def stage():
     """Copy the fixtures next to the tests (build time, only where the reference tree exists)."""
     if not os.path.isdir(REF):
         return False
     os.makedirs(LOCAL, exist_ok=True)
-    for name, _, _ in FILES.values():
+    for name in [f[0] for f in FILES.values()] + JPEGS:
         dst = os.path.join(LOCAL, name)
         if not os.path.exists(dst):
             shutil.copyfile(os.path.join(REF, name), dst)

@@ -588,3 +588,63 @@ int orc_copy_yuv420(const uhdrb200_image* src, uhdrb200_image* dst) {
   dst->colorGamut = src->colorGamut;
   return UHDRB200_NO_ERROR;
 }
+
+/* ------------------------------------------------------------------------------------------------------------------
+ * Row N4: dequantise + 8x8 inverse DCT + range-limit of JPEG coefficient planes, what libjpeg-turbo does inside
+ * jpeg_read_raw_data for the reference's JpegDecoderHelper (lib/src/jpegdecoderhelper.cpp:291-307: raw_data_out,
+ * dct_method = JDCT_ISLOW). libjpeg-turbo (tag 3.0.1, fetched at configure time, CMakeLists.txt:254-256) is NOT in
+ * /root/reference: this restates the published IJG algorithm (jidctint.c, jpeg_idct_islow: CONST_BITS 13, PASS1_BITS 2;
+ * jdmaster.c prepare_range_limit_table). Pinned empirically: tests/test_jpeg_idct.py compares it bit for bit with
+ * libjpeg-turbo's own luma output (through Pillow) on the reference's JPEG fixtures. */
+static void islow_1d(const int32_t* in, int stride_in, int32_t* out, int stride_out, int shift) {
+  int32_t z1, z2, z3, z4, z5, tmp0, tmp1, tmp2, tmp3, tmp10, tmp11, tmp12, tmp13;
+  z2 = in[2 * stride_in]; z3 = in[6 * stride_in];
+  z1 = (z2 + z3) * 4433;            /* FIX_0_541196100 */
+  tmp2 = z1 + z3 * (-15137);        /* FIX_1_847759065 */
+  tmp3 = z1 + z2 * 6270;            /* FIX_0_765366865 */
+  z2 = in[0]; z3 = in[4 * stride_in];
+  tmp0 = (int32_t)((uint32_t)(z2 + z3) << 13);
+  tmp1 = (int32_t)((uint32_t)(z2 - z3) << 13);
+  tmp10 = tmp0 + tmp3; tmp13 = tmp0 - tmp3; tmp11 = tmp1 + tmp2; tmp12 = tmp1 - tmp2;
+  tmp0 = in[7 * stride_in]; tmp1 = in[5 * stride_in]; tmp2 = in[3 * stride_in]; tmp3 = in[1 * stride_in];
+  z1 = tmp0 + tmp3; z2 = tmp1 + tmp2; z3 = tmp0 + tmp2; z4 = tmp1 + tmp3;
+  z5 = (z3 + z4) * 9633;            /* FIX_1_175875602 */
+  tmp0 *= 2446; tmp1 *= 16819; tmp2 *= 25172; tmp3 *= 12299; /* 0.298631336 2.053119869 3.072711026 1.501321110 */
+  z1 *= -7373; z2 *= -20995; z3 *= -16069; z4 *= -3196;      /* 0.899976223 2.562915447 1.961570560 0.390180644 */
+  z3 += z5; z4 += z5;
+  tmp0 += z1 + z3; tmp1 += z2 + z4; tmp2 += z2 + z3; tmp3 += z1 + z4;
+  const int32_t rnd = (int32_t)1 << (shift - 1);
+  out[0 * stride_out] = (tmp10 + tmp3 + rnd) >> shift; out[7 * stride_out] = (tmp10 - tmp3 + rnd) >> shift;
+  out[1 * stride_out] = (tmp11 + tmp2 + rnd) >> shift; out[6 * stride_out] = (tmp11 - tmp2 + rnd) >> shift;
+  out[2 * stride_out] = (tmp12 + tmp1 + rnd) >> shift; out[5 * stride_out] = (tmp12 - tmp1 + rnd) >> shift;
+  out[3 * stride_out] = (tmp13 + tmp0 + rnd) >> shift; out[4 * stride_out] = (tmp13 - tmp0 + rnd) >> shift;
+}
+static uint8_t jpeg_range_limit(int32_t x) { /* table index x & RANGE_MASK (1023), centred on 128 */
+  int i = (int)(x & 1023);
+  return (uint8_t)(i < 128 ? i + 128 : (i < 512 ? 255 : (i < 896 ? 0 : i - 896)));
+}
+/* one block: 64 coefficients (natural order) x 64 quantisation steps -> 8x8 samples */
+void orc_jpeg_idct_islow_block(const int16_t* coef, const uint16_t* quant, uint8_t* out8x8) {
+  int32_t ws[64], in[64], row[8];
+  for (int i = 0; i < 64; i++) in[i] = (int32_t)coef[i] * (int32_t)quant[i];
+  for (int c = 0; c < 8; c++) islow_1d(in + c, 8, ws + c, 8, 13 - 2);
+  for (int r = 0; r < 8; r++) {
+    islow_1d(ws + r * 8, 1, row, 1, 13 + 2 + 3);
+    for (int c = 0; c < 8; c++) out8x8[r * 8 + c] = jpeg_range_limit(row[c]);
+  }
+}
+/* a whole component: blocks in raster order; only the visible width x height samples are written */
+int orc_jpeg_idct_plane(const int16_t* coeffs, const uint16_t* quant, size_t blocks_w, size_t blocks_h, uint8_t* plane,
+                        size_t width, size_t height, size_t stride) {
+  if (!coeffs || !quant || !plane) return UHDRB200_ERROR_BAD_PTR;
+  if (width > blocks_w * 8 || height > blocks_h * 8) return UHDRB200_ERROR_RESOLUTION_MISMATCH;
+  uint8_t blk[64];
+  for (size_t by = 0; by < blocks_h; by++)
+    for (size_t bx = 0; bx < blocks_w; bx++) {
+      orc_jpeg_idct_islow_block(coeffs + (by * blocks_w + bx) * 64, quant, blk);
+      for (int r = 0; r < 8; r++)
+        for (int c = 0; c < 8; c++)
+          if (by * 8 + r < height && bx * 8 + c < width) plane[(by * 8 + r) * stride + bx * 8 + c] = blk[r * 8 + c];
+    }
+  return UHDRB200_NO_ERROR;
+}
