@@ -252,7 +252,7 @@ int uhdrb200_copy_yuv420_dev(const uhdrb200_image* src, uhdrb200_image* dest, vo
  * 64 quantisation steps in natural order (quant_tbl_ptrs[...]->quantval). Rows beyond `height` and columns beyond `width`
  * (the MCU padding) are not written. libjpeg-turbo's source is not part of the reference tree: parity is pinned on its
  * OUTPUT for the reference's JPEG fixtures (tests/test_jpeg_idct.py). Up to 4 components per call (_host: up to 3);
- * `coeffs` must be 16-byte aligned. _dev: every pointer is device memory, asynchronous on `stream`. */
+ * _dev: every pointer is device memory, asynchronous on `stream`. */
 typedef struct uhdrb200_jpeg_component {
   const int16_t* coeffs;
   const uint16_t* quant;

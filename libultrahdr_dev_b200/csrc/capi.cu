@@ -1357,8 +1357,8 @@ int jpeg_idct_core(int n, const uhdrb200_jpeg_component* comps, cudaStream_t s) 
   memset(&p, 0, sizeof p);
   p.n_components = n;
   for (int i = 0; i < n; i++) {
-    if ((reinterpret_cast<uintptr_t>(comps[i].coeffs) & 15) != 0) {
-      t_ctx.err = "uhdrb200_jpeg_idct: coeffs must be 16-byte aligned";
+    if ((reinterpret_cast<uintptr_t>(comps[i].coeffs) & 1) != 0 || (reinterpret_cast<uintptr_t>(comps[i].quant) & 1) != 0) {
+      t_ctx.err = "uhdrb200_jpeg_idct: coeffs and quant must be 2-byte aligned";
       return UHDRB200_ERROR_UNSUPPORTED_FEATURE;
     }
     p.comp[i] = JpegIdctComponent{comps[i].coeffs, comps[i].quant, comps[i].blocks_w, comps[i].blocks_h, (uint8_t*)comps[i].plane,

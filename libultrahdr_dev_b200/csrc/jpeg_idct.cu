@@ -10,10 +10,10 @@
 // restated from its published description; parity is anchored on libjpeg-turbo's own output for the reference's JPEG
 // fixtures, obtained through Pillow in tests/test_jpeg_idct.py (luma planes, bit for bit).
 //
-// Mapping: 8 lanes per 8x8 block, 4 blocks per warp, 8 warps per CTA. Lane r of a block loads coefficient row r as one
-// 16-byte vector and dequantises it into a padded shared-memory workspace, runs the column pass on column r, then the
-// row pass on row r, and stores 8 output bytes (one 8-byte store; a block row is contiguous in the plane). HBM traffic:
-// 128 B of coefficients in, 64 B of samples out per block = 3 B per sample.
+// Mapping: 8 lanes per 8x8 block, 4 blocks per warp, 8 warps per CTA = 32 consecutive blocks of one block row. Lane r of
+// a block reads coefficient column r, dequantises, runs the column pass, passes the block through a padded shared-memory
+// workspace once, runs the row pass on row r and stores 8 output bytes (one 8-byte store; a block row is contiguous in
+// the plane). HBM traffic: 128 B of coefficients in, 64 B of samples out per block = 3 B per sample.
 #include <cstring>
 
 #include "uhdr_io.cuh"
@@ -74,73 +74,78 @@ __device__ __forceinline__ void idct_1d(const int (&in)[8], int (&out)[8]) {
   out[4] = (tmp13 - tmp0 + kRound) >> SHIFT;
 }
 
-// libjpeg's range_limit table (jdmaster.c prepare_range_limit_table) indexed with `x & RANGE_MASK` (1023): x + 128
-// clamped to 0..255 for -512 <= x < 512, and its documented wrap-around for corrupt data beyond that
-__device__ __forceinline__ uint32_t range_limit(int x) {
-  const int i = x & 1023;
-  return (uint32_t)(i < 128 ? i + 128 : (i < 512 ? 255 : (i < 896 ? 0 : i - 896)));
+// libjpeg's range_limit table (jdmaster.c prepare_range_limit_table) indexed with `x & RANGE_MASK` (1023) is x + 128
+// clamped to 0..255 for -512 <= x < 512 plus a documented wrap-around for corrupt data beyond that; both together are
+// clamp(sext10(x) + 128, 0, 255). Two samples per saturating pack.
+__device__ __forceinline__ int sext10(int x) {
+  int r;
+  asm("bfe.s32 %0, %1, 0, 10;" : "=r"(r) : "r"(x));
+  return r;
+}
+__device__ __forceinline__ uint32_t pack4_u8_sat(int a, int b, int c, int d) {  // bytes: a | b << 8 | c << 16 | d << 24
+  uint32_t hi, r;  // cvt.pack d, x, y, z = sat(y) | sat(x) << 8 | z << 16
+  asm("cvt.pack.sat.u8.s32.b32 %0, %1, %2, 0;" : "=r"(hi) : "r"(d), "r"(c));
+  asm("cvt.pack.sat.u8.s32.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(b), "r"(a), "r"(hi));
+  return r;
 }
 
 constexpr int kIdctThreads = 256, kBlocksPerCta = kIdctThreads / 8;
 constexpr int kWsStride = 8 * 9 + 1;  // words per block in shared memory: rows padded to 9, blocks staggered by 1 (bank spread)
 
+// CTA = a strip of 32 block columns walked kRowsPerCta block rows down (grid.x strips, grid.y row groups, grid.z
+// components); 8 lanes per block. Lane r reads coefficient COLUMN r (eight 2-byte loads; the eight lanes of a block cover
+// each 16-byte row together), dequantises with the column's eight quantisation steps held in registers, runs the column
+// pass, hands the block over through shared memory once, runs the row pass on row r and stores its eight samples.
+constexpr int kRowsPerCta = 8;  // block rows a CTA walks down its strip of 32 block columns
+
 __global__ void __launch_bounds__(kIdctThreads) jpeg_idct_kernel(const __grid_constant__ JpegIdctParams p) {
   __shared__ int ws[kBlocksPerCta * kWsStride];
-  __shared__ int sq[64];
-  const JpegIdctComponent& c = p.comp[blockIdx.y];
-  const int tid = threadIdx.x, r = tid & 7, lb = tid >> 3;
-  if (tid < 64) sq[tid] = (int)c.quant[tid];
-  __syncthreads();
-  const size_t n_blocks = c.blocks_w * c.blocks_h;
+  const JpegIdctComponent& c = p.comp[blockIdx.z];
+  const uint32_t tid = threadIdx.x, r = tid & 7, lb = tid >> 3;
+  const uint32_t bw = (uint32_t)c.blocks_w, bh = (uint32_t)c.blocks_h, bx = blockIdx.x * kBlocksPerCta + lb;
+  const uint32_t by0 = blockIdx.y * kRowsPerCta;
+  if (by0 >= bh || bx >= bw) return;  // the components of one launch differ in size; a warp's four blocks may straddle the right edge
+  const uint32_t by1 = by0 + kRowsPerCta < bh ? by0 + kRowsPerCta : bh;
+  const unsigned lanes = __activemask();  // the lanes of this warp that own a block column (uniform over the walk)
   int* w = ws + lb * kWsStride;
-  for (size_t b0 = (size_t)blockIdx.x * kBlocksPerCta; b0 < n_blocks; b0 += (size_t)gridDim.x * kBlocksPerCta) {
-    const size_t b = b0 + lb;
-    const bool live = b < n_blocks;
+  int q[8];
+#pragma unroll
+  for (int k = 0; k < 8; k++) q[k] = (int)__ldg(c.quant + 8 * k + r);  // the quantisation steps of column r
+  const size_t row_step = (size_t)bw * 64;
+  const int16_t* cp = c.coeffs + ((size_t)by0 * bw + bx) * 64 + r;
+  int nv[8];
+#pragma unroll
+  for (int k = 0; k < 8; k++) nv[k] = (int)__ldg(cp + 8 * k);
+  const size_t x = (size_t)bx * 8;
+  const bool wide = x + 8 <= c.width;
+  for (uint32_t by = by0; by < by1; by++) {
     int v[8], o[8];
-    if (live) {  // coefficient row r, dequantised (DEQUANTIZE(coef, quantval) = coef * quantval)
-      const uint4 q = ldg16(c.coeffs + b * 64 + r * 8);
-      const uint32_t qw[4] = {q.x, q.y, q.z, q.w};
 #pragma unroll
-      for (int i = 0; i < 4; i++) {
-        w[r * 9 + 2 * i] = (int)(short)(qw[i] & 0xffff) * sq[r * 8 + 2 * i];
-        w[r * 9 + 2 * i + 1] = (int)(short)(qw[i] >> 16) * sq[r * 8 + 2 * i + 1];
-      }
+    for (int k = 0; k < 8; k++) v[k] = nv[k] * q[k];  // DEQUANTIZE(coef, quantval)
+    cp += row_step;
+    if (by + 1 < by1) {  // the next block's coefficients are in flight while this one is transformed
+#pragma unroll
+      for (int k = 0; k < 8; k++) nv[k] = (int)__ldg(cp + 8 * k);
     }
-    __syncwarp();
-    if (live) {  // pass 1: column r
+    idct_1d<kConstBits - kPass1Bits>(v, o);  // pass 1: column r
 #pragma unroll
-      for (int k = 0; k < 8; k++) v[k] = w[k * 9 + r];
-      idct_1d<kConstBits - kPass1Bits>(v, o);
+    for (int k = 0; k < 8; k++) w[k * 9 + r] = o[k];
+    __syncwarp(lanes);
+#pragma unroll
+    for (int k = 0; k < 8; k++) v[k] = w[r * 9 + k];
+    __syncwarp(lanes);  // the workspace is rewritten by the next block row
+    idct_1d<kConstBits + kPass1Bits + 3>(v, o);  // pass 2: row r
+    const size_t y = (size_t)by * 8 + r;
+    if (y >= c.height || x >= c.width) continue;
+    const uint32_t lo = pack4_u8_sat(sext10(o[0]) + 128, sext10(o[1]) + 128, sext10(o[2]) + 128, sext10(o[3]) + 128);
+    const uint32_t hi = pack4_u8_sat(sext10(o[4]) + 128, sext10(o[5]) + 128, sext10(o[6]) + 128, sext10(o[7]) + 128);
+    uint8_t* dst = c.plane + y * c.stride + x;
+    if (wide && ((reinterpret_cast<uintptr_t>(dst) & 7) == 0)) {
+      stg8(dst, make_uint2(lo, hi));
+    } else {  // ragged right edge or an unaligned plane: byte stores
+      const size_t n = c.width - x < 8 ? c.width - x : 8;
+      for (size_t k = 0; k < n; k++) dst[k] = (uint8_t)((k < 4 ? lo >> (8 * k) : hi >> (8 * (k - 4))) & 0xff);
     }
-    __syncwarp();
-    if (live) {
-#pragma unroll
-      for (int k = 0; k < 8; k++) w[k * 9 + r] = o[k];
-    }
-    __syncwarp();
-    if (live) {  // pass 2: row r, range-limit, store the visible part of the row
-#pragma unroll
-      for (int k = 0; k < 8; k++) v[k] = w[r * 9 + k];
-      idct_1d<kConstBits + kPass1Bits + 3>(v, o);
-      const size_t by = b / c.blocks_w, bx = b - by * c.blocks_w;
-      const size_t y = by * 8 + r, x = bx * 8;
-      if (y < c.height && x < c.width) {
-        uint32_t lo = 0, hi = 0;
-#pragma unroll
-        for (int k = 0; k < 4; k++) {
-          lo |= range_limit(o[k]) << (8 * k);
-          hi |= range_limit(o[k + 4]) << (8 * k);
-        }
-        uint8_t* dst = c.plane + y * c.stride + x;
-        if (x + 8 <= c.width && ((reinterpret_cast<uintptr_t>(dst) & 7) == 0)) {
-          stg8(dst, make_uint2(lo, hi));
-        } else {  // ragged right edge or an unaligned plane: byte stores
-          const size_t n = c.width - x < 8 ? c.width - x : 8;
-          for (size_t k = 0; k < n; k++) dst[k] = (uint8_t)((k < 4 ? lo >> (8 * k) : hi >> (8 * (k - 4))) & 0xff);
-        }
-      }
-    }
-    __syncwarp();
   }
 }
 
@@ -148,15 +153,15 @@ __global__ void __launch_bounds__(kIdctThreads) jpeg_idct_kernel(const __grid_co
 
 cudaError_t launch_jpeg_idct_impl(const JpegIdctParams& p, cudaStream_t s) {
   if (p.n_components <= 0) return cudaSuccess;
-  size_t most = 0;
+  size_t bw = 0, bh = 0;
   for (int i = 0; i < p.n_components; i++) {
-    const size_t n = p.comp[i].blocks_w * p.comp[i].blocks_h;
-    most = n > most ? n : most;
+    bw = p.comp[i].blocks_w > bw ? p.comp[i].blocks_w : bw;
+    bh = p.comp[i].blocks_h > bh ? p.comp[i].blocks_h : bh;
   }
-  if (most == 0) return cudaSuccess;
-  size_t ctas = (most + kBlocksPerCta - 1) / kBlocksPerCta;
-  if (ctas > 148 * 16) ctas = 148 * 16;  // grid-stride beyond 16 resident-CTA waves per SM
-  jpeg_idct_kernel<<<dim3((unsigned)ctas, (unsigned)p.n_components), kIdctThreads, 0, s>>>(p);
+  if (bw == 0 || bh == 0) return cudaSuccess;
+  if (bh > 65535u * kRowsPerCta) return cudaErrorInvalidValue;  // far beyond any JPEG (65 535 x 65 535 samples)
+  const dim3 grid((unsigned)((bw + kBlocksPerCta - 1) / kBlocksPerCta), (unsigned)((bh + kRowsPerCta - 1) / kRowsPerCta), (unsigned)p.n_components);
+  jpeg_idct_kernel<<<grid, kIdctThreads, 0, s>>>(p);
   return cudaGetLastError();
 }
 

@@ -159,7 +159,7 @@ struct SdrPackParams {   // row N3: yuv420 -> RGBA8888 (out = packed pixels, dst
 
 // row N4 (jpeg_idct.cu): one colour component of a JPEG in the coefficient domain -> its u8 plane
 struct JpegIdctComponent {
-  const int16_t* coeffs;      // blocks_h x blocks_w blocks of 64 quantised coefficients, natural (row-major) order, 16-byte aligned
+  const int16_t* coeffs;      // blocks_h x blocks_w blocks of 64 quantised coefficients, natural (row-major) order
   const uint16_t* quant;      // 64 quantisation steps, natural order
   size_t blocks_w, blocks_h;  // geometry of the coefficient array (whole MCUs, as jpeg_read_coefficients stores it)
   uint8_t* plane;             // output samples
