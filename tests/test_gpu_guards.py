@@ -112,3 +112,51 @@ def test_other_stages_write_inside(uh, t, w, h):
     assert uh.yuv420ToRgba8888Device(_sdr_img(g_sdr, w, h), o, st) == 0
     g_rgba.check("SDR pack")
     g_hdr.check("P010 input")
+
+
+@pytest.mark.parametrize("w,h", [(64, 8), (128, 36), (192, 68), (1024, 20), (960, 540)])
+def test_pipeline_variant_writes_stay_inside(uh, t, w, h):
+    """The TMA-fed variant of the scale-4 kernel (test hook Q_PIPE; layouts with width % 64 == 0): outputs between guard
+    bands, partial strips (16 of 32 cells), short walks, and byte-identical to the default kernel."""
+    sdr_b, _ = synth.natural_pair(w, h, 15)
+    g_sdr = Guarded(t, sdr_b.size, sdr_b)
+    mp = synth.natural_map(w // 4, h // 4, 16)
+    g_map = Guarded(t, mp.size, mp)
+    m_img = abi.Image()
+    m_img.data, m_img.width, m_img.height, m_img.luma_stride = g_map.ptr, w // 4, h // 4, w // 4
+    m_img.pixelFormat = abi.PIX_FMT_MONOCHROME
+    md = abi.default_metadata(4.926108)
+    st = t.cuda.current_stream().cuda_stream
+    for fmt in (abi.OUTPUT_HDR_LINEAR, abi.OUTPUT_HDR_HLG, abi.OUTPUT_HDR_LINEAR_RGB_10BIT):
+        outs = []
+        for mode in (abi.APPLY_Q_PIPE, abi.APPLY_AUTO):
+            assert uh.lib.uhdrb200_test_set_apply_mode(mode) == 0
+            g_out = Guarded(t, w * h * abi.out_bytes_per_pixel(fmt))
+            o = abi.Image()
+            o.data = g_out.ptr
+            assert uh.applyGainMapDevice(_sdr_img(g_sdr, w, h), m_img, md, fmt, FLT_MAX, o, st) == 0
+            g_out.check(f"apply mode={mode} fmt={fmt} {w}x{h}")
+            outs.append(g_out.payload())
+        assert uh.lib.uhdrb200_test_set_apply_mode(abi.APPLY_AUTO) == 0
+        assert np.array_equal(outs[0], outs[1]), f"pipeline variant differs from the default kernel, fmt={fmt} {w}x{h}"
+
+
+@pytest.mark.parametrize("w,h", [(8, 8), (17, 9), (250, 130), (264, 7)])
+def test_jpeg_idct_writes_stay_inside(uh, t, w, h):
+    """Row N4 through the device entry point: ragged widths / heights inside whole-MCU coefficient arrays, planes between
+    guard bands, padded stride bytes untouched."""
+    rng = np.random.Generator(np.random.PCG64(w + h))
+    bw, bh = -(-w // 16) * 2, -(-h // 16) * 2  # whole 16x16 MCUs
+    co = (rng.integers(-200, 200, (bh, bw, 64)) * (rng.random((bh, bw, 64)) < 0.2)).astype(np.int16)
+    q = rng.integers(1, 40, 64).astype(np.uint16)
+    stride = w + 5
+    n = stride * (h - 1) + w
+    g_plane = Guarded(t, n, np.full(n, 0x5A, np.uint8))
+    d_co, d_q = t.from_numpy(co).cuda(), t.from_numpy(q.astype(np.int16)).cuda()
+    c = (abi.JpegComponent * 1)()
+    c[0].coeffs, c[0].quant, c[0].blocks_w, c[0].blocks_h = d_co.data_ptr(), d_q.data_ptr(), bw, bh
+    c[0].plane, c[0].width, c[0].height, c[0].stride = g_plane.ptr, w, h, stride
+    assert uh.lib.uhdrb200_jpeg_idct_dev(1, c, t.cuda.current_stream().cuda_stream) == 0
+    g_plane.check(f"jpeg idct {w}x{h}")
+    got = np.concatenate([g_plane.payload(), np.full(stride - w, 0x5A, np.uint8)]).reshape(h, stride)
+    assert (got[:, w:] == 0x5A).all() and (got[:, :w] != 0x5A).any()
