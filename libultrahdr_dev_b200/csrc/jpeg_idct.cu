@@ -90,7 +90,10 @@ __device__ __forceinline__ uint32_t pack4_u8_sat(int a, int b, int c, int d) {  
 }
 
 constexpr int kIdctThreads = 256, kBlocksPerCta = kIdctThreads / 8;
-constexpr int kWsStride = 8 * 9 + 1;  // words per block in shared memory: rows padded to 9, blocks staggered by 1 (bank spread)
+// shared-memory workspace per WARP: the four 8x8 blocks side by side as one 8 x 32 matrix with rows padded to 33 words:
+// a column-pass write (row k, lanes = 32 consecutive columns) and a row-pass read (lane (block b, row r) reads word
+// r * 33 + 8 b + k: bank r + 8 b + k, all 32 different) are both free of bank conflicts
+constexpr int kWsRow = 33, kWsWarp = 8 * kWsRow;
 
 // CTA = a strip of 32 block columns walked kRowsPerCta block rows down (grid.x strips, grid.y row groups, grid.z
 // components); 8 lanes per block. Lane r reads coefficient COLUMN r (eight 2-byte loads; the eight lanes of a block cover
@@ -99,7 +102,7 @@ constexpr int kWsStride = 8 * 9 + 1;  // words per block in shared memory: rows 
 constexpr int kRowsPerCta = 8;  // block rows a CTA walks down its strip of 32 block columns
 
 __global__ void __launch_bounds__(kIdctThreads) jpeg_idct_kernel(const __grid_constant__ JpegIdctParams p) {
-  __shared__ int ws[kBlocksPerCta * kWsStride];
+  __shared__ int ws[(kIdctThreads / 32) * kWsWarp];
   const JpegIdctComponent& c = p.comp[blockIdx.z];
   const uint32_t tid = threadIdx.x, r = tid & 7, lb = tid >> 3;
   const uint32_t bw = (uint32_t)c.blocks_w, bh = (uint32_t)c.blocks_h, bx = blockIdx.x * kBlocksPerCta + lb;
@@ -107,7 +110,7 @@ __global__ void __launch_bounds__(kIdctThreads) jpeg_idct_kernel(const __grid_co
   if (by0 >= bh || bx >= bw) return;  // the components of one launch differ in size; a warp's four blocks may straddle the right edge
   const uint32_t by1 = by0 + kRowsPerCta < bh ? by0 + kRowsPerCta : bh;
   const unsigned lanes = __activemask();  // the lanes of this warp that own a block column (uniform over the walk)
-  int* w = ws + lb * kWsStride;
+  int* w = ws + (tid >> 5) * kWsWarp + (lb & 3) * 8;  // this block's eight columns inside its warp's matrix
   int q[8];
 #pragma unroll
   for (int k = 0; k < 8; k++) q[k] = (int)__ldg(c.quant + 8 * k + r);  // the quantisation steps of column r
@@ -129,10 +132,10 @@ __global__ void __launch_bounds__(kIdctThreads) jpeg_idct_kernel(const __grid_co
     }
     idct_1d<kConstBits - kPass1Bits>(v, o);  // pass 1: column r
 #pragma unroll
-    for (int k = 0; k < 8; k++) w[k * 9 + r] = o[k];
+    for (int k = 0; k < 8; k++) w[k * kWsRow + r] = o[k];
     __syncwarp(lanes);
 #pragma unroll
-    for (int k = 0; k < 8; k++) v[k] = w[r * 9 + k];
+    for (int k = 0; k < 8; k++) v[k] = w[r * kWsRow + k];
     __syncwarp(lanes);  // the workspace is rewritten by the next block row
     idct_1d<kConstBits + kPass1Bits + 3>(v, o);  // pass 2: row r
     const size_t y = (size_t)by * 8 + r;
