@@ -22,6 +22,7 @@
 //     the blocks are persistent (grid = SMs x resident blocks, grid-stride over tiles).
 //   * the gain factor 2^(logBoost * displayBoost / maxContentBoost) / displayBoost (gainmapmath.cpp:550-555,
 //     ultrahdr.cpp:451) is three FFMA (FFMA2 on pixel pairs) + one MUFU.EX2 per pixel.
+#include <cstdlib>
 #include <mutex>
 
 #include "apply_q_common.cuh"
@@ -666,6 +667,13 @@ cudaError_t launch_q(const ApplyFastParams& p0, cudaStream_t s) {
   const int cap = sms_of[dev] * per_sm_of[dev], smem_bytes = smem_of[dev];
   lk.unlock();
   p.cells = pick_cells(p.tiles_x, p.g.map_height, n_img, cap);
+  {
+    static const int forced = [] {  // experiments: UHDRB200_Q_CELLS=1..16 overrides the tile height
+      const char* e = getenv("UHDRB200_Q_CELLS");
+      return e ? atoi(e) : 0;
+    }();
+    if (forced >= 1 && forced <= 16) p.cells = forced;
+  }
   const int kQTileRows = (kQThreads / 32) * p.cells;
   p.tiles_y = (p.g.map_height + kQTileRows - 1) / kQTileRows;  // this kernel's tiles are kQTileRows cell rows tall
   p.n_tiles = p.tiles_x * p.tiles_y * n_img;
