@@ -533,6 +533,14 @@ def main():
         assert lib.uhdrb200_test_set_apply_mode(abi.APPLY_GENERIC) == 0
         other["apply_1010102_hlg_generic_kernel"] = timed(lambda: uh.applyGainMapBatch(Bo, sdrs, maps, md, abi.OUTPUT_HDR_HLG, FLT_MAX, bigs, stream), APPLY_BPP, 2)
         assert lib.uhdrb200_test_set_apply_mode(abi.APPLY_AUTO) == 0
+        # LUT numeric mode (UHDRB200_MODE_LUT, byte-identical to the reference's -DUSE_*_LUT=1 build): the per-pixel kernels
+        # with the reference's nearest-entry tables and float order
+        assert lib.uhdrb200_set_numeric_mode(abi.MODE_LUT) == 0
+        other["lut_mode_generate"] = timed(lambda: uh.generateGainMapBatch(Bo, sdrs, hdrs, abi.TF_HLG, mds, maps, False, stream), GEN_BPP, 4)
+        other["lut_mode_apply_1010102_hlg"] = timed(lambda: uh.applyGainMapBatch(Bo, sdrs, maps, md, abi.OUTPUT_HDR_HLG, FLT_MAX, bigs, stream), APPLY_BPP, 2)
+        other["lut_mode_apply_rgba_f16_linear"] = timed(lambda: uh.applyGainMapBatch(Bo, sdrs, maps, md, abi.OUTPUT_HDR_LINEAR, FLT_MAX, bigs, stream), 9.5625, 2)
+        assert lib.uhdrb200_set_numeric_mode(abi.MODE_ANALYTIC) == 0
+        assert uh.generateGainMapBatch(Bo, sdrs, hdrs, abi.TF_HLG, mds, maps, False, stream) == 0  # restore the analytic maps
         # ---- N4: dequantise + ISLOW IDCT + range-limit of 4:2:0 coefficient planes (3 B per sample: 2 in, 1 out): one 8160x6144
         # image per call (150 MB of coefficients), four distinct images in rotation
         jw, jh = 8160, 6144

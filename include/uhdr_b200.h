@@ -118,8 +118,17 @@ typedef struct uhdrb200_metadata {
 enum {
   /* default: follows the reference AS BUILT (analytic transfer functions; the USE_*_LUT macros
    * of jpegr.cpp:33-38 are invisible to ultrahdr.cpp). */
-  UHDRB200_MODE_ANALYTIC = 0
+  UHDRB200_MODE_ANALYTIC = 0,
+  /* the reference's -DUSE_SRGB_INVOETF_LUT=1 ... -DUSE_APPLY_GAIN_LUT=1 build (what jpegr.cpp:33-38 intends): nearest-entry
+   * tables for srgbInvOetf (1024), hlg/pqInvOetf (4096), hlg/pqOetf (65 536) and the gain factor (1024), gainmapmath.cpp:
+   * 21-64, gainmapmath.h:150-183. In this mode the kernels follow the reference's float arithmetic operation by operation
+   * (tables built on the host by the same g++ / glibc expressions), so the output is byte-identical to that build. */
+  UHDRB200_MODE_LUT = 1
 };
+/* Numeric mode of the CALLING THREAD for its following generate / apply / API-0 calls (toneMap, convertYuv and the packers
+ * are integer or mode-free). Default UHDRB200_MODE_ANALYTIC. Returns ERROR_UNSUPPORTED_FEATURE for an unknown mode. */
+int uhdrb200_set_numeric_mode(int mode);
+int uhdrb200_get_numeric_mode(void);
 
 /* ---- library / device management ---- */
 int uhdrb200_abi_version(void);

@@ -34,6 +34,7 @@ APPLY_AUTO, APPLY_GENERIC, APPLY_TWO_TABLE, APPLY_Q_PIPE = 0, 1, 2, 3  # uhdrb20
 # uhdrb200_test_eval function selectors (include/uhdr_b200_test.h)
 (FN_SRGB_INV_OETF, FN_HLG_OETF, FN_HLG_INV_OETF, FN_PQ_OETF, FN_PQ_INV_OETF, FN_FLOAT_TO_HALF, FN_TO_10BIT, FN_P_HLG, FN_P_PQ,
  FN_L_POW, FN_TOE_FIX, FN_ENCODE_GAIN) = range(12)
+MODE_ANALYTIC, MODE_LUT = 0, 1  # uhdrb200_set_numeric_mode
 SYNC_SPIN, SYNC_BLOCKING = 0, 1  # uhdrb200_set_sync_mode
 MAP_SCALE = 4  # kMapDimensionScaleFactor, ultrahdr.h:213
 SDR_WHITE_NITS, HLG_MAX_NITS, PQ_MAX_NITS = 203.0, 1000.0, 10000.0  # gainmapmath.h:34-36

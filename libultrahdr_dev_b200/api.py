@@ -32,6 +32,8 @@ SYMBOLS = {
     "uhdrb200_free": (None, [C.c_void_p]),
     "uhdrb200_launch_count": (C.c_uint64, []),
     "uhdrb200_set_sync_mode": (C.c_int, [C.c_int]),
+    "uhdrb200_set_numeric_mode": (C.c_int, [C.c_int]),
+    "uhdrb200_get_numeric_mode": (C.c_int, []),
     "uhdrb200_generate_gainmap_host": (C.c_int, [P_IMG, P_IMG, C.c_int, P_MD, P_IMG, C.c_int]),
     "uhdrb200_generate_gainmap_host_into": (C.c_int, [P_IMG, P_IMG, C.c_int, P_MD, P_IMG, C.c_int, C.c_void_p, C.c_size_t]),
     "uhdrb200_generate_gainmap_dev": (C.c_int, [P_IMG, P_IMG, C.c_int, P_MD, P_IMG, C.c_int, C.c_void_p]),

@@ -51,11 +51,19 @@ __device__ __forceinline__ float sample_map(const uint8_t* __restrict__ map, int
   return e1 * w.x + e2 * w.y + e3 * w.z + e4 * w.w;
 }
 
-// one pixel: ultrahdr.cpp:429-451
+// one pixel: ultrahdr.cpp:429-451. LUT (numeric mode LUT, the reference's -DUSE_*_LUT=1 build): srgbInvOetfLUT (:433-434),
+// applyGainLUT (:446-447, gainmapmath.cpp:557-560) from the two 1024-entry tables in shared memory, then the correctly
+// rounded `/ display_boost` (:451).
+template <bool LUT>
 __device__ __forceinline__ Color3 recover(const ApplyParams& p, const YuvCoefs& k601, uint32_t Y, uint32_t U,
-                                          uint32_t V, float gain) {
+                                          uint32_t V, float gain, const float* s_srgb, const float* s_gain) {
   Color3 yuv = {(float)Y * (1 / 255.0f), (float)((int)U - 128) * (1 / 255.0f), (float)((int)V - 128) * (1 / 255.0f)};
   Color3 rgb = yuv_to_rgb(k601, yuv);
+  if (LUT) {
+    const float f = s_gain[lut_index(gain, kLutGain)];
+    const Color3 lin = {s_srgb[lut_index(rgb.r, kLutSrgbInv)], s_srgb[lut_index(rgb.g, kLutSrgbInv)], s_srgb[lut_index(rgb.b, kLutSrgbInv)]};
+    return {__fdiv_rn(lin.r * f, p.display_boost), __fdiv_rn(lin.g * f, p.display_boost), __fdiv_rn(lin.b * f, p.display_boost)};
+  }
   Color3 lin = {srgb_inv_oetf(rgb.r), srgb_inv_oetf(rgb.g), srgb_inv_oetf(rgb.b)};
   // applyGain(e, gain, metadata, displayBoost), gainmapmath.cpp:550-555
   float log_boost = p.log2_min * (1.0f - gain) + p.log2_max * gain;
@@ -67,18 +75,24 @@ __device__ __forceinline__ uint32_t pack1010102(Color3 e) {
   return to_10bit(e.r) | (to_10bit(e.g) << 10) | (to_10bit(e.b) << 20) | 0xC0000000u;
 }
 
-template <bool VEC>
+template <bool VEC, bool LUT>
 __global__ void __launch_bounds__(256) apply_kernel(ApplyParams p) {
-  extern __shared__ float s_idw[];
+  extern __shared__ float s_idw[];  // [IDW tables when they fit][LUT: srgbInvOetf table | gain table]
   const Geometry& g = p.g;
   const int s = g.map_scale;
   const float* tabs = p.idw;
-  if (s <= kMaxSmemScale) {
-    const int n = 16 * s * s;
-    for (int i = threadIdx.y * 32 + threadIdx.x; i < n; i += 256) s_idw[i] = p.idw[i];
-    __syncthreads();
+  const int n_idw = s <= kMaxSmemScale ? 16 * s * s : 0;
+  const float* s_srgb = s_idw + n_idw;
+  const float* s_gain = s_srgb + kLutSrgbInv;
+  if (n_idw) {
+    for (int i = threadIdx.y * 32 + threadIdx.x; i < n_idw; i += 256) s_idw[i] = p.idw[i];
     tabs = s_idw;
   }
+  if (LUT) {
+    for (int i = threadIdx.y * 32 + threadIdx.x; i < kLutSrgbInv; i += 256) s_idw[n_idw + i] = p.lt.srgb_inv[i];
+    for (int i = threadIdx.y * 32 + threadIdx.x; i < kLutGain; i += 256) s_idw[n_idw + kLutSrgbInv + i] = p.gain_lut[i];
+  }
+  if (n_idw || LUT) __syncthreads();
   const int x0 = (blockIdx.x * 32 + threadIdx.x) * 4;
   const int y0 = (blockIdx.y * 8 + threadIdx.y) * 2;
   if (x0 >= g.width || y0 >= g.height) return;
@@ -115,7 +129,7 @@ __global__ void __launch_bounds__(256) apply_kernel(ApplyParams p) {
     for (int i = 0; i < 4; i++) {
       const int x = min(x0 + i, g.width - 1);
       float gain = sample_map(map, g.map_width, g.map_height, s, x, y, tabs);
-      e[i] = recover(p, k601, Y[r][i], U[i >> 1], V[i >> 1], gain);
+      e[i] = recover<LUT>(p, k601, Y[r][i], U[i >> 1], V[i >> 1], gain, s_srgb, s_gain);
     }
     const size_t pix = (size_t)y * g.width + x0;
     switch (p.output_format) {
@@ -152,8 +166,14 @@ __global__ void __launch_bounds__(256) apply_kernel(ApplyParams p) {
         uint32_t w[4];
 #pragma unroll
         for (int i = 0; i < 4; i++) {
-          Color3 q = p.output_format == 3 ? Color3{hlg_oetf(e[i].r), hlg_oetf(e[i].g), hlg_oetf(e[i].b)}
-                                          : Color3{pq_oetf(e[i].r), pq_oetf(e[i].g), pq_oetf(e[i].b)};
+          Color3 q;
+          if (LUT) {  // hlgOetfLUT / pqOetfLUT, 65 536 entries each (ultrahdr.cpp:470-485): L1 / L2 resident
+            const float* t = p.output_format == 3 ? p.lt.hlg_oetf : p.lt.pq_oetf;
+            q = {__ldg(t + lut_index(e[i].r, kLutHlgOetf)), __ldg(t + lut_index(e[i].g, kLutHlgOetf)), __ldg(t + lut_index(e[i].b, kLutHlgOetf))};
+          } else {
+            q = p.output_format == 3 ? Color3{hlg_oetf(e[i].r), hlg_oetf(e[i].g), hlg_oetf(e[i].b)}
+                                     : Color3{pq_oetf(e[i].r), pq_oetf(e[i].g), pq_oetf(e[i].b)};
+          }
           w[i] = pack1010102(q);
         }
         uint32_t* o = (uint32_t*)pl.out + pix;
@@ -180,8 +200,14 @@ cudaError_t launch_apply_impl(const ApplyParams& p, int n, bool vec, cudaStream_
   dim3 block(32, 8, 1);
   dim3 grid((p.g.width + 127) / 128, (p.g.height + 15) / 16, n);
   size_t smem = p.g.map_scale <= kMaxSmemScale ? sizeof(float) * 16 * p.g.map_scale * p.g.map_scale : 0;
-  if (vec) apply_kernel<true><<<grid, block, smem, s>>>(p);
-  else apply_kernel<false><<<grid, block, smem, s>>>(p);
+  if (p.lut) {
+    smem += sizeof(float) * (kLutSrgbInv + kLutGain);
+    if (vec) apply_kernel<true, true><<<grid, block, smem, s>>>(p);
+    else apply_kernel<false, true><<<grid, block, smem, s>>>(p);
+    return cudaGetLastError();
+  }
+  if (vec) apply_kernel<true, false><<<grid, block, smem, s>>>(p);
+  else apply_kernel<false, false><<<grid, block, smem, s>>>(p);
   return cudaGetLastError();
 }
 

@@ -19,6 +19,7 @@
 #include <map>
 #include <mutex>
 #include <string>
+#include <tuple>
 #include <vector>
 
 #include "../../include/uhdr_b200.h"
@@ -34,6 +35,9 @@ std::atomic<int> g_sync_mode{-1};  // -1: from the environment (UHDRB200_BLOCKIN
 // test hook (include/uhdr_b200_test.h), per calling thread: 0 auto, 1 analytic kernel, 2 two-table kernel, 3 the TMA-fed
 // pipeline variant of the q-domain kernel
 thread_local int t_apply_mode = 0;
+// numeric mode of the calling thread (include/uhdr_b200.h): UHDRB200_MODE_ANALYTIC (the reference as built) or
+// UHDRB200_MODE_LUT (the reference's -DUSE_*_LUT=1 build, jpegr.cpp:33-38)
+thread_local int t_numeric_mode = UHDRB200_MODE_ANALYTIC;
 // programmatic dependent launch of the generate / apply kernels (uhdr_io.cuh); UHDRB200_NO_PDL=1 turns it off
 bool pdl_enabled() {
   static const bool on = [] {
@@ -471,6 +475,84 @@ int get_apply_tables(int device, ApplyTables* out) {
   return 0;
 }
 
+// ---------------------------------------------------------------- LUT numeric mode: device copies of the reference's tables
+std::map<int, LutTables> g_lut_tables;  // device -> the five transfer-function tables (guarded by g_idw_mu)
+
+int get_lut_tables(int device, LutTables* out) {
+  std::lock_guard<std::mutex> lk(g_idw_mu);
+  auto it = g_lut_tables.find(device);
+  if (it != g_lut_tables.end()) {
+    *out = it->second;
+    return 0;
+  }
+  const size_t n = (size_t)kLutSrgbInv + kLutHlgInv + kLutPqInv + kLutHlgOetf + kLutPqOetf;
+  std::vector<float> h(n);
+  float* h_srgb = h.data();
+  float* h_hlg_inv = h_srgb + kLutSrgbInv;
+  float* h_pq_inv = h_hlg_inv + kLutHlgInv;
+  float* h_hlg = h_pq_inv + kLutPqInv;
+  float* h_pq = h_hlg + kLutHlgOetf;
+  build_lut_tables(h_srgb, h_hlg_inv, h_pq_inv, h_hlg, h_pq);
+  float* d = nullptr;
+  CU(cudaMalloc((void**)&d, n * sizeof(float)));
+  CU(cudaMemcpy(d, h.data(), n * sizeof(float), cudaMemcpyHostToDevice));
+  LutTables t;
+  t.srgb_inv = d;
+  t.hlg_inv = t.srgb_inv + kLutSrgbInv;
+  t.pq_inv = t.hlg_inv + kLutHlgInv;
+  t.hlg_oetf = t.pq_inv + kLutPqInv;
+  t.pq_oetf = t.hlg_oetf + kLutHlgOetf;
+  g_lut_tables[device] = t;
+  *out = t;
+  return 0;
+}
+
+// GainLUT (gainmapmath.h:150-183) depends on the metadata and the display boost of the call: one 4 KB device table per
+// distinct (device, minContentBoost, maxContentBoost, displayBoost), built once with the reference's own host arithmetic
+// and kept (a decoder sees a handful of distinct boosts). The cache is bounded: beyond kGainLutMax tables the device is
+// drained and the tables are dropped before the new one is built, so no kernel in flight can lose its table.
+struct GainLutKey {
+  int device;
+  uint32_t mn, mx, db;  // the floats' bit patterns
+  bool operator<(const GainLutKey& o) const { return std::tie(device, mn, mx, db) < std::tie(o.device, o.mn, o.mx, o.db); }
+};
+constexpr size_t kGainLutMax = 256;
+std::map<GainLutKey, float*> g_gain_luts;  // guarded by g_idw_mu
+
+int get_gain_lut(int device, float mn, float mx, float db, const float** out) {
+  GainLutKey key;
+  key.device = device;
+  memcpy(&key.mn, &mn, 4);
+  memcpy(&key.mx, &mx, 4);
+  memcpy(&key.db, &db, 4);
+  std::lock_guard<std::mutex> lk(g_idw_mu);
+  auto it = g_gain_luts.find(key);
+  if (it != g_gain_luts.end()) {
+    *out = it->second;
+    return 0;
+  }
+  if (g_gain_luts.size() >= kGainLutMax) {
+    int cur = 0;
+    CU(cudaGetDevice(&cur));
+    for (auto& kv : g_gain_luts) {
+      if (cudaSetDevice(kv.first.device) == cudaSuccess) {
+        cudaDeviceSynchronize();
+        cudaFree(kv.second);
+      }
+    }
+    g_gain_luts.clear();
+    CU(cudaSetDevice(cur));
+  }
+  float h[kLutGain];
+  build_gain_lut(h, mn, mx, db);
+  float* d = nullptr;
+  CU(cudaMalloc((void**)&d, sizeof h));
+  CU(cudaMemcpy(d, h, sizeof h, cudaMemcpyHostToDevice));
+  g_gain_luts[key] = d;
+  *out = d;
+  return 0;
+}
+
 // ---------------------------------------------------------------- saturated-white pixels under a saturated map
 // The reference's own float / double chain for a channel with c == 1 in an interior scale-4 cell whose four map samples
 // are 255: sampleMap (gainmapmath.cpp:700-719, e = 255 / 255.0f = 1, left-to-right float sum of the four weights),
@@ -623,6 +705,7 @@ GainCode gain_code_of(float min_boost, float max_boost) {
   k.max_boost = max_boost;
   k.log2_min = (float)log2((double)min_boost);
   const float log2_max = (float)log2((double)max_boost);
+  k.log2_max = log2_max;
   const double den = (double)(log2_max - k.log2_min);
   k.code_at_min = (int)(uint8_t)((log2((double)min_boost) - (double)k.log2_min) / den * 255.0);
   k.code_at_max = (int)(uint8_t)((log2((double)max_boost) - (double)k.log2_min) / den * 255.0);
@@ -696,6 +779,10 @@ int generate_core(int n, const uhdrb200_image* sdr, const uhdrb200_image* hdr, i
   }
   p.gc = gain_code_of(md[0].minContentBoost, md[0].maxContentBoost);
   p.pdl = pdl_enabled() ? 1 : 0;
+  if (t_numeric_mode == UHDRB200_MODE_LUT) {
+    p.lut = 1;
+    if ((st = get_lut_tables(dev, &p.lt))) return st;
+  }
   if (conv) {
     p.convert = 1;
     memcpy(p.conv, conv, sizeof p.conv);
@@ -758,10 +845,16 @@ int apply_core(int n, const uhdrb200_image* sdr, const uhdrb200_image* map, cons
   }
   // Fast path (apply_fast.cu): map scale 4, 4-aligned planes, and a gain factor
   // f = 2^(gain*A + B) (gain in [0,1]) small enough for the OETF table range.
-  bool fast = t_apply_mode != 1;
+  const bool lut = t_numeric_mode == UHDRB200_MODE_LUT;  // LUT mode: the per-pixel kernel with the reference's tables
+  if (lut) {
+    p.lut = 1;
+    if ((st = get_lut_tables(dev, &p.lt))) return st;
+    if ((st = get_gain_lut(dev, md->minContentBoost, md->maxContentBoost, p.display_boost, &p.gain_lut))) return st;
+  }
+  bool fast = t_apply_mode != 1 && !lut;
   for (int i = 0; i < n && fast; i++) fast = apply_fast_ok(p.g, v[i]);
   // other integer scale factors (or scale 4 with a ragged map) keep the q-domain tables through apply_qs_kernel
-  bool any_scale = !fast && (t_apply_mode == 0 || t_apply_mode == 3);
+  bool any_scale = !fast && !lut && (t_apply_mode == 0 || t_apply_mode == 3);
   for (int i = 0; i < n && any_scale; i++) any_scale = apply_qs_ok(p.g, v[i]);
   fast = fast || any_scale;
   const double k = (double)p.display_boost / (double)p.max_boost;
@@ -1049,6 +1142,10 @@ int generate_noalloc(int n, const uhdrb200_image* sdr, const uhdrb200_image* hdr
     snprintf(msg, sizeof msg, "uhdrb200_generate_gainmap_batch_dev_noalloc: n = %d exceeds UHDRB200_NOALLOC_MAX_IMAGES (%d)", n,
              UHDRB200_NOALLOC_MAX_IMAGES);
     t_ctx.err = msg;
+    return UHDRB200_ERROR_UNSUPPORTED_FEATURE;
+  }
+  if (t_numeric_mode != UHDRB200_MODE_ANALYTIC) {  // the LUT mode's tables live in allocated device memory
+    t_ctx.err = "uhdrb200_generate_gainmap_batch_dev_noalloc: only UHDRB200_MODE_ANALYTIC is supported";
     return UHDRB200_ERROR_UNSUPPORTED_FEATURE;
   }
   if (!sdr || !hdr || !md || !dest) return UHDRB200_ERROR_BAD_PTR;
@@ -1449,6 +1546,12 @@ int uhdrb200_test_eval(int fn, const float* in_dev, float* out_dev, size_t n, vo
   if (e != cudaSuccess) return fail(e, "test_eval kernel launch");
   return UHDRB200_NO_ERROR;
 }
+int uhdrb200_set_numeric_mode(int mode) {
+  if (mode != UHDRB200_MODE_ANALYTIC && mode != UHDRB200_MODE_LUT) return UHDRB200_ERROR_UNSUPPORTED_FEATURE;
+  t_numeric_mode = mode;
+  return UHDRB200_NO_ERROR;
+}
+int uhdrb200_get_numeric_mode(void) { return t_numeric_mode; }
 int uhdrb200_set_sync_mode(int mode) {
   if (mode != UHDRB200_SYNC_SPIN && mode != UHDRB200_SYNC_BLOCKING) return UHDRB200_ERROR_UNSUPPORTED_FEATURE;
   g_sync_mode = mode;

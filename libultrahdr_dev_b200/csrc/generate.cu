@@ -23,7 +23,10 @@ namespace {
 // once and nothing is re-read (4.5625 B/px instead of 4.5 + 4.5625). Requires width, height % 4 == 0.
 // CONVERT (with FUSED): the SDR block is stored re-encoded by convertYuv (row N1, jpegr.cpp:223-225,
 // transformYuv420 gainmapmath.cpp:483-520) while the gain computation keeps the un-converted samples.
-template <bool VEC, bool FUSED, bool CONVERT = false>
+// LUT = the LUT numeric mode (graded against the reference's -DUSE_*_LUT=1 build): after the same gather the thread
+// follows the reference's float arithmetic operation by operation (sequential box sum, unfused YUV matrix, nearest-entry
+// tables, double log2 in encodeGain) instead of the fp32 fast chain.
+template <bool VEC, bool FUSED, bool CONVERT = false, bool LUT = false>
 __global__ void __launch_bounds__(256) generate_kernel(GenerateParams p) {
   pdl_trigger();
   const Geometry& g = p.g;
@@ -125,6 +128,41 @@ __global__ void __launch_bounds__(256) generate_kernel(GenerateParams p) {
   // far inside the +-1 LSB contract (measured exact-match fraction in tests/ and DESIGN.md),
   // and it removes ~300 unpack/convert/add instructions per map pixel from an issue-bound kernel.
   // Each chroma sample covers 4 of the 16 pixels, so chroma averages are sums of 4 samples / 4.
+  if (LUT) {
+    Color3 s = {0.0f, 0.0f, 0.0f}, h = {0.0f, 0.0f, 0.0f};
+#pragma unroll
+    for (int r = 0; r < 4; r++)  // samplePixels: dy-major, sequential float sums of the per-pixel conversions
+#pragma unroll
+      for (int i = 0; i < 4; i++) {
+        const int y8 = (int)((sy[r] >> (8 * i)) & 0xFFu);  // getYuv420Pixel, gainmapmath.cpp:562-581
+        const int u8 = (int)((su[r >> 1] >> (8 * (i >> 1))) & 0xFFu), v8 = (int)((sv[r >> 1] >> (8 * (i >> 1))) & 0xFFu);
+        s.r += (float)y8 * (1 / 255.0f);
+        s.g += (float)(u8 - 128) * (1 / 255.0f);
+        s.b += (float)(v8 - 128) * (1 / 255.0f);
+        const uint32_t yw = i < 2 ? hy[r].x : hy[r].y, cw = i < 2 ? huv[r >> 1].x : huv[r >> 1].y;
+        const int y10 = (int)(((yw >> (16 * (i & 1))) & 0xFFFFu) >> 6);  // getP010Pixel, :583-601
+        const int u10 = (int)((cw & 0xFFFFu) >> 6), v10 = (int)(cw >> 22);
+        h.r += (float)(y10 - 64) * (1 / 876.0f);
+        h.g += (float)(u10 - 64) * (1 / 896.0f) - 0.5f;
+        h.b += (float)(v10 - 64) * (1 / 896.0f) - 0.5f;
+      }
+    s = {s.r / 16.0f, s.g / 16.0f, s.b / 16.0f};
+    h = {h.r / 16.0f, h.g / 16.0f, h.b / 16.0f};
+    const Color3 sg = yuv_to_rgb(p.sdr_k, s);  // ultrahdr.cpp:316-324 with srgbInvOetfLUT
+    const Color3 sl = {__ldg(p.lt.srgb_inv + lut_index(sg.r, kLutSrgbInv)), __ldg(p.lt.srgb_inv + lut_index(sg.g, kLutSrgbInv)),
+                       __ldg(p.lt.srgb_inv + lut_index(sg.b, kLutSrgbInv))};
+    const float sdr_nits = luminance(p.luma, sl) * 203.0f;
+    const Color3 hg = yuv_to_rgb(p.hdr_k, h);  // :326-330 with hlgInvOetfLUT / pqInvOetfLUT
+    Color3 hl = hg;
+    if (p.hdr_tf == 1 || p.hdr_tf == 2) {
+      const float* t = p.hdr_tf == 1 ? p.lt.hlg_inv : p.lt.pq_inv;  // both tables have 4096 entries
+      hl = {__ldg(t + lut_index(hg.r, kLutHlgInv)), __ldg(t + lut_index(hg.g, kLutHlgInv)), __ldg(t + lut_index(hg.b, kLutHlgInv))};
+    }
+    if (p.use_gamut) hl = mat3_apply(p.gamut, hl);
+    const float hdr_nits = luminance(p.luma, hl) * p.hdr_white_nits;
+    ((uint8_t*)pl.out)[(size_t)my * g.map_width + mx] = (uint8_t)encode_gain_exact(sdr_nits, hdr_nits, p.gc);
+    return;
+  }
   uint32_t ys = 0, us, vs, yh = 0, uh = 0, vh = 0;
 #pragma unroll
   for (int r = 0; r < 4; r++) {
@@ -181,6 +219,10 @@ cudaError_t launch_generate_impl(const GenerateParams& p, int n, bool vec, cudaS
   if (p.g.map_width == 0 || p.g.map_height == 0 || n == 0) return cudaSuccess;
   dim3 block(32, 8, 1);
   dim3 grid((p.g.map_width + 31) / 32, (p.g.map_height + 7) / 8, n);
+  if (p.lut) {
+    if (vec) return launch_pdl(generate_kernel<true, false, false, true>, grid, block, 0, s, p.pdl != 0, p);
+    return launch_pdl(generate_kernel<false, false, false, true>, grid, block, 0, s, p.pdl != 0, p);
+  }
   if (vec) return launch_pdl(generate_kernel<true, false, false>, grid, block, 0, s, p.pdl != 0, p);
   return launch_pdl(generate_kernel<false, false, false>, grid, block, 0, s, p.pdl != 0, p);
 }
@@ -193,6 +235,10 @@ cudaError_t launch_api0_fused_impl(const GenerateParams& p, int n, cudaStream_t 
   if (p.g.map_width == 0 || p.g.map_height == 0 || n == 0) return cudaSuccess;
   dim3 block(32, 8, 1);
   dim3 grid((p.g.map_width + 31) / 32, (p.g.map_height + 7) / 8, n);
+  if (p.lut) {
+    if (p.convert) return launch_pdl(generate_kernel<true, true, true, true>, grid, block, 0, s, p.pdl != 0, p);
+    return launch_pdl(generate_kernel<true, true, false, true>, grid, block, 0, s, p.pdl != 0, p);
+  }
   if (p.convert) return launch_pdl(generate_kernel<true, true, true>, grid, block, 0, s, p.pdl != 0, p);
   return launch_pdl(generate_kernel<true, true, false>, grid, block, 0, s, p.pdl != 0, p);
 }

@@ -99,4 +99,59 @@ void build_apply_tables(float2* s, float2* s_hi, float2* o_hlg, float2* o_pq, fl
   for (int i = 0; i < 256; i++) e255[i] = (float)i / 255.0f;  // gainmapmath.cpp:700-703
 }
 
+// ---------------------------------------------------------------- LUT numeric mode
+// The nearest-entry tables of the reference's -DUSE_*_LUT=1 build (gainmapmath.cpp:21-64): entry i holds the analytic
+// function at (float)i / (float)(N - 1), evaluated the way g++ / glibc evaluate the reference's expressions: float operands,
+// the transcendental in double (pow / exp / log take the double overload because one operand is a double literal or the
+// float is promoted), narrowed to float on return. This file is host code compiled by the same g++ / glibc.
+namespace {
+float ref_srgb_inv(float x) {  // gainmapmath.cpp:149-155
+  if (x <= 0.04045f) return x / 12.92f;
+  return (float)pow((double)((x + 0.055f) / 1.055f), 2.4);
+}
+const float kHlgA = 0.17883277f, kHlgB = 0.28466892f, kHlgC = 0.55991073f;  // gainmapmath.cpp:257
+float ref_hlg_oetf(float e) {  // :259-265
+  if (e <= 1.0f / 12.0f) return sqrtf(3.0f * e);
+  return (float)((double)kHlgA * log((double)(12.0f * e - kHlgB)) + (double)kHlgC);
+}
+float ref_hlg_inv(float x) {  // :280-286
+  if (x <= 0.5f) return (float)(pow((double)x, 2.0) / (double)3.0f);
+  return (float)((exp((double)((x - kHlgC) / kHlgA)) + (double)kHlgB) / (double)12.0f);
+}
+const float kPqM1 = 2610.0f / 16384.0f, kPqM2 = 2523.0f / 4096.0f * 128.0f;  // :305-307
+const float kPqC1 = 3424.0f / 4096.0f, kPqC2 = 2413.0f / 4096.0f * 32.0f, kPqC3 = 2392.0f / 4096.0f * 32.0f;
+float ref_pq_oetf(float e) {  // :309-312
+  if (e <= 0.0f) return 0.0f;
+  const double p = pow((double)e, (double)kPqM1);
+  return (float)pow(((double)kPqC1 + (double)kPqC2 * p) / (1 + (double)kPqC3 * p), (double)kPqM2);
+}
+float ref_pq_inv(float x) {  // :327-338
+  if (x <= 0.0001f) return 0.0f;
+  const double p = pow((double)x, (double)0.0126833f);
+  return (float)pow(((double)128.0f * p - (double)107.0f) / ((double)2413.0f - (double)2392.0f * p), (double)6.2773946361f);
+}
+void fill_lut(float* t, int n, float (*fn)(float)) {
+  for (int i = 0; i < n; i++) t[i] = fn((float)i / (float)(n - 1));
+}
+}  // namespace
+
+void build_lut_tables(float* srgb_inv, float* hlg_inv, float* pq_inv, float* hlg_oetf, float* pq_oetf) {
+  fill_lut(srgb_inv, kLutSrgbInv, ref_srgb_inv);
+  fill_lut(hlg_inv, kLutHlgInv, ref_hlg_inv);
+  fill_lut(pq_inv, kLutPqInv, ref_pq_inv);
+  fill_lut(hlg_oetf, kLutHlgOetf, ref_hlg_oetf);
+  fill_lut(pq_oetf, kLutPqOetf, ref_pq_oetf);
+}
+
+// GainLUT(metadata, displayBoost), gainmapmath.h:161-169: log2 of the float boosts in double, the blend narrowed to
+// float, `logBoost * boostFactor` in float, exp2 in double narrowed to float.
+void build_gain_lut(float* tab, float min_boost, float max_boost, float display_boost) {
+  const float boost_factor = display_boost > 0 ? display_boost / max_boost : 1.0f;
+  for (int i = 0; i < kLutGain; i++) {
+    const float v = (float)i / (float)(kLutGain - 1);
+    const float log_boost = (float)(log2((double)min_boost) * (double)(1.0f - v) + log2((double)max_boost) * (double)v);
+    tab[i] = (float)exp2((double)(log_boost * boost_factor));
+  }
+}
+
 }  // namespace uhdr

@@ -30,8 +30,26 @@ struct Geometry {
   int map_width, map_height, map_scale;
 };
 
+// ---- LUT numeric mode (lut tables of the reference's -DUSE_*_LUT=1 build, gainmapmath.cpp:21-64) ----
+// Nearest-entry tables over [0, 1]: index = uint32(x * (N - 1) + 0.5) clipped to N - 1 (gainmapmath.cpp:162-167, 269-275,
+// 292-298, 316-322, 344-350); sizes gainmapmath.h:268-269, 329-330, 342-343, 355-356, 368-369. Built on the host with the
+// reference's own float / double arithmetic (tables.cu), one device copy per GPU (capi.cu: get_lut_tables).
+constexpr int kLutSrgbInv = 1024, kLutHlgInv = 4096, kLutPqInv = 4096, kLutHlgOetf = 65536, kLutPqOetf = 65536;
+constexpr int kLutGain = 1024;  // GainLUT, gainmapmath.h:150-183 (one table per metadata / display boost)
+struct LutTables {
+  const float* srgb_inv;
+  const float* hlg_inv;
+  const float* pq_inv;
+  const float* hlg_oetf;
+  const float* pq_oetf;
+};
+void build_lut_tables(float* srgb_inv, float* hlg_inv, float* pq_inv, float* hlg_oetf, float* pq_oetf);
+void build_gain_lut(float* tab, float min_boost, float max_boost, float display_boost);
+
 struct GenerateParams {
   Geometry g;
+  int lut;          // 1: LUT numeric mode (nearest-entry tables, the reference's float order, exact encodeGain)
+  LutTables lt;
   YuvCoefs sdr_k;   // YUV matrix of the SDR image (BT.601 when sdr_is_601, ultrahdr.cpp:284-286)
   YuvCoefs hdr_k;   // YUV matrix of the HDR image (ultrahdr.cpp:288-302)
   LumaCoefs luma;   // luminance weights of the SDR gamut, used for BOTH images (ultrahdr.cpp:265-283)
@@ -49,6 +67,9 @@ struct GenerateParams {
 
 struct ApplyParams {
   Geometry g;
+  int lut;                // 1: LUT numeric mode: srgbInvOetfLUT, applyGainLUT, hlg/pqOetfLUT (ultrahdr.cpp:433-485)
+  LutTables lt;
+  const float* gain_lut;  // device, kLutGain floats
   int output_format;      // UHDRB200_OUTPUT_*
   float log2_min, log2_max;
   float max_boost;        // maxContentBoost (gainmapmath.cpp:553: logBoost * displayBoost / maxContentBoost)

@@ -166,6 +166,7 @@ __device__ __forceinline__ Color3 mat3_apply(const Mat3& k, Color3 e) {
 // computes it exactly as the reference does (capi.cu: gain_code_of).
 struct GainCode {
   float min_boost, max_boost, log2_min;
+  float log2_max;                // LUT numeric mode only (encode_gain_exact)
   float code_scale;              // 255 / (log2_max - log2_min), the float difference like the reference, in double
   int code_at_min, code_at_max;  // encodeGain of a gain clamped to min / max
 };
@@ -177,6 +178,26 @@ __device__ __forceinline__ uint32_t encode_gain(float sdr_nits, float hdr_nits, 
   if (gain <= k.min_boost) code = (uint32_t)k.code_at_min;
   if (gain >= k.max_boost) code = (uint32_t)k.code_at_max;
   return code;
+}
+
+// LUT numeric mode: the reference's own chain, float quotient, clamp, then double log2 / quotient / * 255 and a
+// truncating cast (gainmapmath.cpp:529-541). libdevice's double log2 is within 1 ulp of glibc's, so the truncated code
+// can differ only when the double product sits within ~1e-16 of an integer.
+__device__ __forceinline__ uint32_t encode_gain_exact(float sdr_nits, float hdr_nits, const GainCode& k) {
+  float gain = 1.0f;
+  if (sdr_nits > 0.0f) gain = __fdiv_rn(hdr_nits, sdr_nits);
+  if (gain < k.min_boost) gain = k.min_boost;
+  if (gain > k.max_boost) gain = k.max_boost;
+  const double v = (log2((double)gain) - (double)k.log2_min) / (double)(k.log2_max - k.log2_min) * 255.0;
+  return (uint32_t)(uint8_t)(int)v;
+}
+// nearest-entry LUT index, `static_cast<uint32_t>(x * (N - 1) + 0.5)` then CLIP3 (gainmapmath.cpp:162-167): the float
+// product, + 0.5 in double (exact for a product below 2^23), truncation. x >= 0 here (clamped colours, IDW gains).
+__device__ __forceinline__ uint32_t lut_index(float x, int n) {
+  const float pos = x * (float)(n - 1);
+  const float fl = truncf(pos);
+  uint32_t idx = __float2uint_rz(fl) + ((pos - fl) >= 0.5f ? 1u : 0u);
+  return idx > (uint32_t)(n - 1) ? (uint32_t)(n - 1) : idx;
 }
 
 // ---- packers ----
