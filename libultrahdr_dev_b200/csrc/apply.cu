@@ -31,24 +31,32 @@ __device__ __forceinline__ void stg8(void* p, uint2 v) {
   asm volatile("st.global.L1::no_allocate.v2.u32 [%0], {%1,%2};" ::"l"(p), "r"(v.x), "r"(v.y) : "memory");
 }
 
-// sampleMap with the IDW tables, gainmapmath.cpp:686-720 (the map is addressed with its width).
-__device__ __forceinline__ float sample_map(const uint8_t* __restrict__ map, int mw, int mh, int s, int x, int y,
-                                            const float* __restrict__ tabs) {
-  int xl = x / s, yl = y / s;
-  int ox = x - xl * s, oy = y - yl * s;
-  int xu = min(xl + 1, mw - 1), yu = min(yl + 1, mh - 1);
+// sampleMap with the IDW tables, gainmapmath.cpp:686-720 (the map is addressed with its width), split in two so that
+// neighbouring pixels of one map cell share the four samples: `MapCell` holds e1..e4 = sample / 255.0f (the correctly
+// rounded quotients come from a 256-entry shared-memory table, built on the host as (float)i / 255.0f) and the weight
+// table the cell selects; `cell_gain` is the left-to-right float sum of gainmapmath.cpp:718-719.
+struct MapCell {
+  float e1, e2, e3, e4;
+  int t;  // 0 mWeights, 1 mWeightsNR, 2 mWeightsNB, 3 mWeightsC
+};
+__device__ __forceinline__ MapCell load_cell(const uint8_t* __restrict__ map, int mw, int mh, int xl, int yl, const float* e255) {
+  const int xu = min(xl + 1, mw - 1), yu = min(yl + 1, mh - 1);
   xl = min(xl, mw - 1);
   yl = min(yl, mh - 1);
-  float e1 = __fdiv_rn((float)__ldg(map + xl + yl * mw), 255.0f);
-  float e2 = __fdiv_rn((float)__ldg(map + xl + yu * mw), 255.0f);
-  float e3 = __fdiv_rn((float)__ldg(map + xu + yl * mw), 255.0f);
-  float e4 = __fdiv_rn((float)__ldg(map + xu + yu * mw), 255.0f);
-  int t = 0;  // mWeights
-  if (xl == xu && yl == yu) t = 3;       // mWeightsC
-  else if (xl == xu) t = 1;              // mWeightsNR
-  else if (yl == yu) t = 2;              // mWeightsNB
-  const float4 w = *reinterpret_cast<const float4*>(tabs + ((t * s + oy) * s + ox) * 4);
-  return e1 * w.x + e2 * w.y + e3 * w.z + e4 * w.w;
+  MapCell c;
+  c.e1 = e255[__ldg(map + xl + yl * mw)];
+  c.e2 = e255[__ldg(map + xl + yu * mw)];
+  c.e3 = e255[__ldg(map + xu + yl * mw)];
+  c.e4 = e255[__ldg(map + xu + yu * mw)];
+  c.t = 0;
+  if (xl == xu && yl == yu) c.t = 3;
+  else if (xl == xu) c.t = 1;
+  else if (yl == yu) c.t = 2;
+  return c;
+}
+__device__ __forceinline__ float cell_gain(const MapCell& c, int s, int ox, int oy, const float* __restrict__ tabs) {
+  const float4 w = *reinterpret_cast<const float4*>(tabs + ((c.t * s + oy) * s + ox) * 4);
+  return c.e1 * w.x + c.e2 * w.y + c.e3 * w.z + c.e4 * w.w;
 }
 
 // one pixel: ultrahdr.cpp:429-451. LUT (numeric mode LUT, the reference's -DUSE_*_LUT=1 build): srgbInvOetfLUT (:433-434),
@@ -77,22 +85,25 @@ __device__ __forceinline__ uint32_t pack1010102(Color3 e) {
 
 template <bool VEC, bool LUT>
 __global__ void __launch_bounds__(256) apply_kernel(ApplyParams p) {
-  extern __shared__ float s_idw[];  // [IDW tables when they fit][LUT: srgbInvOetf table | gain table]
+  extern __shared__ float s_idw[];  // [IDW tables when they fit][i / 255.0f][LUT: srgbInvOetf table | gain table]
   const Geometry& g = p.g;
   const int s = g.map_scale;
   const float* tabs = p.idw;
   const int n_idw = s <= kMaxSmemScale ? 16 * s * s : 0;
-  const float* s_srgb = s_idw + n_idw;
+  const float* s_e255 = s_idw + n_idw;
+  const float* s_srgb = s_e255 + 256;
   const float* s_gain = s_srgb + kLutSrgbInv;
+  const int tid = threadIdx.y * 32 + threadIdx.x;
   if (n_idw) {
-    for (int i = threadIdx.y * 32 + threadIdx.x; i < n_idw; i += 256) s_idw[i] = p.idw[i];
+    for (int i = tid; i < n_idw; i += 256) s_idw[i] = p.idw[i];
     tabs = s_idw;
   }
+  s_idw[n_idw + tid] = p.e255[tid];
   if (LUT) {
-    for (int i = threadIdx.y * 32 + threadIdx.x; i < kLutSrgbInv; i += 256) s_idw[n_idw + i] = p.lt.srgb_inv[i];
-    for (int i = threadIdx.y * 32 + threadIdx.x; i < kLutGain; i += 256) s_idw[n_idw + kLutSrgbInv + i] = p.gain_lut[i];
+    for (int i = tid; i < kLutSrgbInv; i += 256) s_idw[n_idw + 256 + i] = p.lt.srgb_inv[i];
+    for (int i = tid; i < kLutGain; i += 256) s_idw[n_idw + 256 + kLutSrgbInv + i] = p.gain_lut[i];
   }
-  if (n_idw || LUT) __syncthreads();
+  __syncthreads();
   const int x0 = (blockIdx.x * 32 + threadIdx.x) * 4;
   const int y0 = (blockIdx.y * 8 + threadIdx.y) * 2;
   if (x0 >= g.width || y0 >= g.height) return;
@@ -120,16 +131,29 @@ __global__ void __launch_bounds__(256) apply_kernel(ApplyParams p) {
     for (int i = 0; i < 2; i++) { U[i] = (2 * i < nx) ? up[i] : 128; V[i] = (2 * i < nx) ? vp[i] : 128; }
   }
 
+  // map cell of the thread's first pixel: the only two integer divisions; the other seven pixels step from it
+  const int xl0 = x0 / s, yl0 = y0 / s;
+  const int ox0 = x0 - xl0 * s;
+  int yl = yl0, oy = y0 - yl0 * s;
 #pragma unroll
   for (int r = 0; r < 2; r++) {
     if (!VEC && r >= ny) break;
     const int y = y0 + r;
     Color3 e[4];
+    int xl = xl0, ox = ox0;
+    MapCell cell = load_cell(map, g.map_width, g.map_height, xl, yl, s_e255);
 #pragma unroll
     for (int i = 0; i < 4; i++) {
-      const int x = min(x0 + i, g.width - 1);
-      float gain = sample_map(map, g.map_width, g.map_height, s, x, y, tabs);
+      const float gain = cell_gain(cell, s, ox, oy, tabs);
       e[i] = recover<LUT>(p, k601, Y[r][i], U[i >> 1], V[i >> 1], gain, s_srgb, s_gain);
+      if (i < 3 && ++ox == s) {  // the next pixel starts a new cell (columns past the right edge are never stored)
+        ox = 0;
+        cell = load_cell(map, g.map_width, g.map_height, ++xl, yl, s_e255);
+      }
+    }
+    if (++oy == s) {
+      oy = 0;
+      ++yl;
     }
     const size_t pix = (size_t)y * g.width + x0;
     switch (p.output_format) {
@@ -199,7 +223,7 @@ cudaError_t launch_apply_impl(const ApplyParams& p, int n, bool vec, cudaStream_
   if (p.g.width == 0 || p.g.height == 0 || n == 0) return cudaSuccess;
   dim3 block(32, 8, 1);
   dim3 grid((p.g.width + 127) / 128, (p.g.height + 15) / 16, n);
-  size_t smem = p.g.map_scale <= kMaxSmemScale ? sizeof(float) * 16 * p.g.map_scale * p.g.map_scale : 0;
+  size_t smem = (p.g.map_scale <= kMaxSmemScale ? sizeof(float) * 16 * p.g.map_scale * p.g.map_scale : 0) + sizeof(float) * 256;
   if (p.lut) {
     smem += sizeof(float) * (kLutSrgbInv + kLutGain);
     if (vec) apply_kernel<true, true><<<grid, block, smem, s>>>(p);

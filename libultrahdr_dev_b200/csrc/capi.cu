@@ -834,6 +834,9 @@ int apply_core(int n, const uhdrb200_image* sdr, const uhdrb200_image* map, cons
   p.display_boost = max_display_boost < md->maxContentBoost ? max_display_boost : md->maxContentBoost;  // :415
   p.inv_display_boost = 1.0f / p.display_boost;
   if ((st = get_idw(dev, p.g.map_scale, &p.idw))) return st;
+  ApplyTables tabs;
+  if ((st = get_apply_tables(dev, &tabs))) return st;
+  p.e255 = tabs.e255;
   std::vector<Planes> v(n);
   bool vec = true;
   for (int i = 0; i < n; i++) {
@@ -903,7 +906,7 @@ int apply_core(int n, const uhdrb200_image* sdr, const uhdrb200_image* map, cons
     for (int i = 0; i < 16; i++)
       for (int c = 1; c < 4; c++) f.wq[c - 1][i] = (float)((double)f.w[i][c] / 2.4 / 255.0);
     f.idw = p.idw;
-    if ((st = get_apply_tables(dev, &f.tab))) return st;
+    f.tab = tabs;
     f.single = v[0];
     f.batch = batch;
     e = launch_apply_fast_impl(f, n, s);

@@ -76,6 +76,7 @@ struct ApplyParams {
   float inv_display_boost;
   float display_boost;
   const float* idw;       // device: 4 tables x scale^2 x 4 floats (mWeights, NR, NB, C)
+  const float* e255;      // device: 256 floats, i / 255.0f correctly rounded (ApplyTables::e255)
   Planes single;
   const Planes* batch;
 };
