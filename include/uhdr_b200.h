@@ -76,6 +76,7 @@ enum {
   UHDRB200_ERROR_RESOLUTION_MISMATCH = -10006,
   UHDRB200_ERROR_INVALID_OUTPUT_FORMAT = -10009,
   UHDRB200_ERROR_BAD_METADATA = -10010,
+  UHDRB200_ERROR_DECODE = -20002, /* ERROR_ULTRAHDR_DECODE_ERROR: not a JPEG / corrupt header (row N4) */
   UHDRB200_ERROR_UNSUPPORTED_MAP_SCALE_FACTOR = -20008,
   UHDRB200_ERROR_INSUFFICIENT_RESOURCE = -20009, /* also: no CUDA device / CUDA failure */
   UHDRB200_ERROR_UNSUPPORTED_FEATURE = -30000
@@ -271,6 +272,28 @@ typedef struct uhdrb200_jpeg_component {
 } uhdrb200_jpeg_component;
 int uhdrb200_jpeg_idct_host(int n_components, const uhdrb200_jpeg_component* comps);
 int uhdrb200_jpeg_idct_dev(int n_components, const uhdrb200_jpeg_component* comps, void* stream);
+
+/* ---- N4 (second slice): the whole baseline-JPEG decode, entropy decoding included, on the device ----
+ * JpegDecoderHelper::decompressImage(image, length, DECODE_TO_YCBCR) + getDecompressedImagePtr / Width / Height
+ * (lib/src/jpegdecoderhelper.cpp:190-320, 380-470; jpegr.cpp:693 primary image, :732 gain map): a 4:2:0 YCbCr JPEG becomes
+ * packed planar Y | U | V (strides width and width / 2), a greyscale JPEG one plane; like the reference, other samplings
+ * and images above 8192 x 8192 are refused. Handled on the device: baseline / sequential Huffman, 8-bit, one interleaved
+ * scan, no restart intervals (what libjpeg-turbo and JpegEncoderHelper write by default). Progressive, arithmetic-coded,
+ * 12-bit, multi-scan and restart-interval streams return UHDRB200_ERROR_UNSUPPORTED_FEATURE with the reason in
+ * uhdrb200_last_error() so the caller can fall back to libjpeg; a stream that is not a JPEG returns UHDRB200_ERROR_DECODE.
+ * The host parses the markers and removes the byte stuffing; only the compressed bytes are copied to the GPU, where the
+ * Huffman stream is decoded in parallel (csrc/jpeg_huff.cu) and transformed by the N4 IDCT kernel, ISLOW like the reference
+ * (jpegdecoderhelper.cpp:305): the planes are byte-identical to libjpeg-turbo's.
+ *   uhdrb200_jpeg_get_info     getCompressedImageParameters (:339): size and UHDRB200_PIX_FMT_YUV420 / _MONOCHROME, no GPU work.
+ *   uhdrb200_jpeg_decode_host  `jpeg` and dest->data are host memory; dest->data holds width * height * 3 / 2 (grey:
+ *                              width * height) bytes; width, height, strides, chroma_data and pixelFormat are filled in.
+ *   uhdrb200_jpeg_decode_dev   `jpeg` is host memory, dest->data DEVICE memory of the same size on the calling thread's
+ *                              uhdrb200_init device: the planes stay on the GPU for uhdrb200_apply_gainmap_dev. Runs on
+ *                              `stream` (0: the thread's own) and returns when the planes are complete.
+ * Both are synchronous and use scratch buffers owned by the calling thread. */
+int uhdrb200_jpeg_get_info(const void* jpeg, size_t bytes, size_t* width, size_t* height, int* pixel_format);
+int uhdrb200_jpeg_decode_host(const void* jpeg, size_t bytes, uhdrb200_image* dest);
+int uhdrb200_jpeg_decode_dev(const void* jpeg, size_t bytes, uhdrb200_image* dest, void* stream);
 
 #ifdef __cplusplus
 }

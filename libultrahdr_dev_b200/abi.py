@@ -25,6 +25,7 @@ ERROR_INVALID_STRIDE = -10004
 ERROR_INVALID_TRANS_FUNC = -10005
 ERROR_RESOLUTION_MISMATCH = -10006
 ERROR_BAD_METADATA = -10010
+ERROR_DECODE = -20002
 ERROR_UNSUPPORTED_MAP_SCALE_FACTOR = -20008
 ERROR_INSUFFICIENT_RESOURCE = -20009
 ERROR_UNSUPPORTED_FEATURE = -30000

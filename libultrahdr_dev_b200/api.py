@@ -55,6 +55,9 @@ SYMBOLS = {
     "uhdrb200_yuv420_to_rgba8888_batch_dev": (C.c_int, [C.c_int, P_IMG, P_IMG, C.c_void_p]),
     "uhdrb200_jpeg_idct_host": (C.c_int, [C.c_int, C.POINTER(abi.JpegComponent)]),
     "uhdrb200_jpeg_idct_dev": (C.c_int, [C.c_int, C.POINTER(abi.JpegComponent), C.c_void_p]),
+    "uhdrb200_jpeg_get_info": (C.c_int, [C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t), C.POINTER(C.c_size_t), C.POINTER(C.c_int)]),
+    "uhdrb200_jpeg_decode_host": (C.c_int, [C.c_void_p, C.c_size_t, P_IMG]),
+    "uhdrb200_jpeg_decode_dev": (C.c_int, [C.c_void_p, C.c_size_t, P_IMG, C.c_void_p]),
     "uhdrb200_copy_yuv420_host": (C.c_int, [P_IMG, P_IMG]),
     "uhdrb200_copy_yuv420_dev": (C.c_int, [P_IMG, P_IMG, C.c_void_p]),
 }

@@ -6,6 +6,7 @@
 // There is NO CPU fallback: without a usable CUDA device every compute entry point returns
 // UHDRB200_ERROR_INSUFFICIENT_RESOURCE and uhdrb200_last_error() says why.
 #include <atomic>
+#include <chrono>
 #include <condition_variable>
 #include <deque>
 #include <thread>
@@ -558,7 +559,44 @@ int get_gain_lut(int device, float mn, float mx, float db, const float** out) {
 // are 255: sampleMap (gainmapmath.cpp:700-719, e = 255 / 255.0f = 1, left-to-right float sum of the four weights),
 // applyGain (:550-555, double log2 / exp2 narrowed to float), `/ display_boost` (ultrahdr.cpp:451), srgbInvOetf(1)
 // (:149-155), hlgOetf / pqOetf (:259-267, 309-314, double) and the truncating `* 1023.0f` (:722-727).
+// The 64 evaluations cost ~5 us of libm per call, a third of a single 4K image's kernel time: the last few (metadata,
+// display boost, format) combinations of the calling thread are kept (UHDRB200_NO_SATCACHE=1 turns the cache off).
+struct SatCellEntry {
+  uint32_t mn, mx, db;
+  int fmt;
+  bool valid;
+  float vsat[4][16], rsat[4][16];
+};
+thread_local SatCellEntry t_sat_cache[4];
+thread_local int t_sat_next = 0;
+
+void fill_sat_cell_uncached(ApplyFastParams& f, float mn, float mx, float db, int fmt);
 void fill_sat_cell(ApplyFastParams& f, float mn, float mx, float db, int fmt) {
+  static const bool off = [] {
+    const char* e = getenv("UHDRB200_NO_SATCACHE");
+    return e && e[0] == '1';
+  }();
+  if (off) return fill_sat_cell_uncached(f, mn, mx, db, fmt);
+  uint32_t k[3];
+  memcpy(&k[0], &mn, 4);
+  memcpy(&k[1], &mx, 4);
+  memcpy(&k[2], &db, 4);
+  for (auto& c : t_sat_cache)
+    if (c.valid && c.mn == k[0] && c.mx == k[1] && c.db == k[2] && c.fmt == fmt) {
+      memcpy(f.vsat, c.vsat, sizeof f.vsat);
+      memcpy(f.rsat, c.rsat, sizeof f.rsat);
+      return;
+    }
+  fill_sat_cell_uncached(f, mn, mx, db, fmt);
+  SatCellEntry& c = t_sat_cache[t_sat_next];
+  t_sat_next = (t_sat_next + 1) % 4;
+  c.mn = k[0]; c.mx = k[1]; c.db = k[2];
+  c.fmt = fmt;
+  memcpy(c.vsat, f.vsat, sizeof f.vsat);
+  memcpy(c.rsat, f.rsat, sizeof f.rsat);
+  c.valid = true;
+}
+void fill_sat_cell_uncached(ApplyFastParams& f, float mn, float mx, float db, int fmt) {
   const float lin1 = (float)pow((double)((1.0f + 0.055f) / 1.055f), 2.4);
   const int inc[4][2] = {{1, 1}, {0, 1}, {1, 0}, {0, 0}};  // mWeights, NR, NB, C (gainmapmath.h:184-228)
   for (int t = 0; t < 4; t++) {
@@ -1278,11 +1316,26 @@ int apply_host(const uhdrb200_image* sdr, const uhdrb200_image* map, const uhdrb
   if (!dest->data) return UHDRB200_ERROR_BAD_PTR;
   if ((st = ensure_ctx())) return st;
   Ctx& c = t_ctx;
-  if ((st = upload(c.buf[0], sdr->data, yuv420_luma_bytes(*sdr), c.stream))) return st;
-  if ((st = upload(c.buf[1], sdr->chroma_data, yuv420_chroma_bytes(*sdr), c.stream))) return st;
+  uhdrb200_image dsdr = *sdr, dmap = *map, ddst = *dest;
+  if ((sdr->luma_stride % 4 != 0 || sdr->chroma_stride % 2 != 0) && sdr->width % 4 == 0 && sdr->height % 4 == 0) {
+    // Row strides the table-driven kernels cannot take (they read 32-bit luma and 16-bit chroma words): the planes are
+    // re-strided by the copy engine on their way up, so the image still gets those kernels instead of the per-pixel one
+    const size_t w = sdr->width, h = sdr->height, ls2 = w, cs2 = w / 2;  // w % 4 == 0
+    if ((st = reserve(c.buf[0], ls2 * h))) return st;
+    if ((st = reserve(c.buf[1], cs2 * (h / 2) * 2))) return st;
+    const uint8_t* ch = (const uint8_t*)sdr->chroma_data;
+    CU(cudaMemcpy2DAsync(c.buf[0].p, ls2, sdr->data, sdr->luma_stride, w, h, cudaMemcpyHostToDevice, c.stream));
+    CU(cudaMemcpy2DAsync(c.buf[1].p, cs2, ch, sdr->chroma_stride, w / 2, h / 2, cudaMemcpyHostToDevice, c.stream));
+    CU(cudaMemcpy2DAsync((uint8_t*)c.buf[1].p + cs2 * (h / 2), cs2, ch + sdr->chroma_stride * (h / 2), sdr->chroma_stride, w / 2, h / 2,
+                         cudaMemcpyHostToDevice, c.stream));
+    dsdr.luma_stride = ls2;
+    dsdr.chroma_stride = cs2;
+  } else {
+    if ((st = upload(c.buf[0], sdr->data, yuv420_luma_bytes(*sdr), c.stream))) return st;
+    if ((st = upload(c.buf[1], sdr->chroma_data, yuv420_chroma_bytes(*sdr), c.stream))) return st;
+  }
   if ((st = upload(c.buf[5], map->data, map->width * map->height, c.stream))) return st;
   if ((st = reserve(c.buf[4], obytes))) return st;
-  uhdrb200_image dsdr = *sdr, dmap = *map, ddst = *dest;
   dsdr.data = c.buf[0].p; dsdr.chroma_data = c.buf[1].p;
   dmap.data = c.buf[5].p;
   ddst.data = c.buf[4].p;
@@ -1503,6 +1556,205 @@ int jpeg_idct_host(int n, const uhdrb200_jpeg_component* comps) {
   return UHDRB200_NO_ERROR;
 }
 
+// ---------------------------------------------------------------- N4: whole baseline-JPEG decode (jpeg_huff.cu + jpeg_idct.cu)
+// JpegDecoderHelper::decompressImage(image, length, DECODE_TO_YCBCR) (lib/src/jpegdecoderhelper.cpp:190-320, 380-470):
+// 4:2:0 YCbCr -> planar Y | U | V (strides width and width / 2, floor), greyscale -> one plane; anything else is refused
+// there ("decoding to YUV only supports 4:2:0 subsampling") and here. Sizes above kMaxWidth / kMaxHeight = 8192 are
+// refused like jpegdecoderhelper.cpp:254-258.
+int jpeg_status(int parse_status, const char* why) {
+  if (parse_status == 0) return UHDRB200_NO_ERROR;
+  t_ctx.err = std::string("uhdrb200_jpeg: ") + why;
+  return parse_status == 2 ? UHDRB200_ERROR_UNSUPPORTED_FEATURE : UHDRB200_ERROR_DECODE;
+}
+int jpeg_check_layout(const JpegHeader& h) {
+  if (h.width > 8192 || h.height > 8192) {
+    t_ctx.err = "uhdrb200_jpeg: image larger than 8192 x 8192 (kMaxWidth / kMaxHeight)";
+    return UHDRB200_ERROR_UNSUPPORTED_WIDTH_HEIGHT;
+  }
+  if (h.n_comp == 3 && !(h.comp_h[0] == 2 && h.comp_v[0] == 2 && h.comp_h[1] == 1 && h.comp_v[1] == 1 && h.comp_h[2] == 1 && h.comp_v[2] == 1)) {
+    t_ctx.err = "uhdrb200_jpeg: decoding to YUV only supports 4:2:0 subsampling";  // jpegdecoderhelper.cpp:286-292
+    return UHDRB200_ERROR_UNSUPPORTED_FEATURE;
+  }
+  return UHDRB200_NO_ERROR;
+}
+
+// UHDRB200_JPEG_TIMING=1: wall-clock phase times of every decode on stderr (each phase joined; a debugging aid, not a mode)
+struct JpegPhaseTimer {
+  bool on;
+  cudaStream_t s = nullptr;
+  std::chrono::steady_clock::time_point t0;
+  std::string line;
+  JpegPhaseTimer() {
+    static const bool env = [] { const char* e = getenv("UHDRB200_JPEG_TIMING"); return e && e[0] == '1'; }();
+    on = env;
+    t0 = std::chrono::steady_clock::now();
+  }
+  void mark(const char* what) {
+    if (!on) return;
+    if (s) cudaStreamSynchronize(s);
+    const auto t1 = std::chrono::steady_clock::now();
+    char b[64];
+    snprintf(b, sizeof b, " %s %.0f us", what, std::chrono::duration<double, std::micro>(t1 - t0).count());
+    line += b;
+    t0 = t1;
+  }
+  ~JpegPhaseTimer() { if (on) fprintf(stderr, "[uhdrb200 jpeg]%s\n", line.c_str()); }
+};
+
+int jpeg_decode(const void* jpeg, size_t bytes, uhdrb200_image* dest, bool to_device, cudaStream_t user_stream) {
+  if (!jpeg || !dest || !dest->data) return UHDRB200_ERROR_BAD_PTR;
+  JpegPhaseTimer tm;
+  static thread_local JpegHeader h;  // 11 KB with its tables
+  const char* why = "";
+  const int parsed = jpeg_parse((const uint8_t*)jpeg, bytes, &h, &why);
+  int st = jpeg_status(parsed, why);
+  if (st) return st;
+  if ((st = jpeg_check_layout(h))) return st;
+  if ((st = ensure_ctx())) return st;
+  Ctx& c = t_ctx;
+  cudaStream_t s = to_device && user_stream ? user_stream : c.stream;
+  tm.s = s;
+  tm.mark("parse");
+  const size_t w = (size_t)h.width, ht = (size_t)h.height;
+  // ---- entropy-coded segment: stuffing removed on the host, zero padded to whole 32-bit words + slack for the bit reader
+  static thread_local std::vector<uint8_t> seg;
+  seg.resize(h.scan_end - h.scan_begin + 64);
+  int marker = 0;
+  const size_t nseg = jpeg_destuff((const uint8_t*)jpeg, h.scan_begin, h.scan_end, seg.data(), &marker);
+  if (marker >= 0xD0 && marker <= 0xD7) {
+    t_ctx.err = "uhdrb200_jpeg: restart markers";
+    return UHDRB200_ERROR_UNSUPPORTED_FEATURE;
+  }
+  const size_t padded = (nseg + 63) & ~(size_t)31;
+  memset(seg.data() + nseg, 0, padded - nseg);
+  tm.mark("destuff");
+  JpegScan sc;
+  memset(&sc, 0, sizeof sc);
+  sc.n_comp = h.n_comp;
+  sc.total_bits = (uint64_t)nseg * 8;
+  sc.n_subseq = (uint32_t)((sc.total_bits + kJpegSubseqBits - 1) / kJpegSubseqBits);
+  if (h.n_comp == 1) {  // a single-component scan is not interleaved: one block per MCU whatever the sampling factors say (A.2.2)
+    sc.blocks_per_mcu = 1;
+    sc.mcus_x = (uint32_t)((w + 7) / 8);
+    sc.mcus_y = (uint32_t)((ht + 7) / 8);
+    sc.comp_h[0] = sc.comp_v[0] = 1;
+    sc.comp_dc[0] = (uint8_t)h.comp_td[0];
+    sc.comp_ac[0] = (uint8_t)h.comp_ta[0];
+  } else {
+    sc.mcus_x = (uint32_t)((w + 8 * h.hmax - 1) / (8 * h.hmax));
+    sc.mcus_y = (uint32_t)((ht + 8 * h.vmax - 1) / (8 * h.vmax));
+    int b = 0;
+    for (int ci = 0; ci < h.n_comp; ci++) {
+      sc.comp_h[ci] = (uint8_t)h.comp_h[ci];
+      sc.comp_v[ci] = (uint8_t)h.comp_v[ci];
+      sc.comp_dc[ci] = (uint8_t)h.comp_td[ci];
+      sc.comp_ac[ci] = (uint8_t)h.comp_ta[ci];
+      for (int y = 0; y < h.comp_v[ci]; y++)
+        for (int x = 0; x < h.comp_h[ci]; x++, b++) {
+          sc.blk_comp[b] = (uint8_t)ci;
+          sc.blk_dx[b] = (uint8_t)x;
+          sc.blk_dy[b] = (uint8_t)y;
+        }
+    }
+    sc.blocks_per_mcu = b;
+  }
+  for (int b = 0; b < sc.blocks_per_mcu; b++) {
+    sc.dc_mask |= (uint32_t)sc.comp_dc[sc.blk_comp[b]] << b;
+    sc.ac_mask |= (uint32_t)sc.comp_ac[sc.blk_comp[b]] << b;
+  }
+  sc.total_blocks = sc.mcus_x * sc.mcus_y * (uint32_t)sc.blocks_per_mcu;
+  size_t coeff_off[4] = {0, 0, 0, 0}, coeff_bytes = 0;
+  for (int ci = 0; ci < h.n_comp; ci++) {
+    sc.comp_blocks_w[ci] = sc.mcus_x * sc.comp_h[ci];
+    sc.comp_blocks_h[ci] = sc.mcus_y * sc.comp_v[ci];
+    coeff_off[ci] = coeff_bytes;
+    coeff_bytes += (size_t)sc.comp_blocks_w[ci] * sc.comp_blocks_h[ci] * 64 * sizeof(int16_t);
+  }
+  // ---- device buffers of the calling thread: segment, tables, workspace, coefficients (+ planes for the host variant)
+  if ((st = upload(c.buf[0], seg.data(), padded, s))) return st;
+  if ((st = upload(c.buf[1], &h.tables, sizeof h.tables, s))) return st;
+  if ((st = reserve(c.buf[2], jpeg_huff_workspace_bytes(sc.n_subseq)))) return st;
+  if ((st = reserve(c.buf[3], coeff_bytes))) return st;
+  CU(cudaMemsetAsync(c.buf[3].p, 0, coeff_bytes, s));
+  sc.data = (const uint32_t*)c.buf[0].p;
+  sc.tables = (const JpegDeviceTables*)c.buf[1].p;
+  for (int ci = 0; ci < h.n_comp; ci++) sc.coeffs[ci] = (int16_t*)((uint8_t*)c.buf[3].p + coeff_off[ci]);
+  tm.mark("upload+memset");
+  int iters = 0;
+  cudaError_t e = jpeg_huff_decode(sc, c.buf[2].p, s, &iters);
+  if (e != cudaSuccess) return fail(e, "jpeg entropy decode");
+  tm.mark("huffman");
+  g_launches += 6 + (uint64_t)iters;
+  // ---- planes: Y w x h, then U and V (w / 2) x (h / 2), packed (decompressYUV, jpegdecoderhelper.cpp:380-399)
+  const size_t cw = w / 2, chh = ht / 2;
+  const size_t plane_bytes = h.n_comp == 1 ? w * ht : w * ht + 2 * cw * chh;
+  uint8_t* planes = (uint8_t*)dest->data;
+  if (!to_device) {
+    if ((st = reserve(c.buf[4], plane_bytes))) return st;
+    planes = (uint8_t*)c.buf[4].p;
+  }
+  uhdrb200_jpeg_component comp[3];
+  const JpegDeviceTables* dt = sc.tables;
+  for (int ci = 0; ci < h.n_comp; ci++) {
+    comp[ci].coeffs = sc.coeffs[ci];
+    comp[ci].quant = dt->quant[h.comp_tq[ci]];
+    comp[ci].blocks_w = sc.comp_blocks_w[ci];
+    comp[ci].blocks_h = sc.comp_blocks_h[ci];
+    comp[ci].plane = ci == 0 ? planes : planes + w * ht + (size_t)(ci - 1) * cw * chh;
+    comp[ci].width = ci == 0 ? w : cw;
+    comp[ci].height = ci == 0 ? ht : chh;
+    comp[ci].stride = comp[ci].width;
+  }
+  if (h.n_comp == 3 && (cw == 0 || chh == 0)) {
+    t_ctx.err = "uhdrb200_jpeg: 4:2:0 image narrower or lower than 2 pixels";
+    return UHDRB200_ERROR_UNSUPPORTED_WIDTH_HEIGHT;
+  }
+  {
+    JpegIdctParams p;
+    memset(&p, 0, sizeof p);
+    p.n_components = h.n_comp;
+    for (int i = 0; i < h.n_comp; i++)
+      p.comp[i] = JpegIdctComponent{comp[i].coeffs, comp[i].quant, comp[i].blocks_w, comp[i].blocks_h, (uint8_t*)comp[i].plane,
+                                    comp[i].width, comp[i].height, comp[i].stride};
+    if ((e = launch_jpeg_idct_impl(p, s)) != cudaSuccess) return fail(e, "jpeg_idct kernel launch");
+    g_launches++;
+  }
+  if (!to_device) {
+    if ((st = copy_d2h(c, dest->data, planes, plane_bytes))) return st;
+    CU(join_stream(c));
+  } else {
+    CU(cudaStreamSynchronize(s));  // the scratch buffers above belong to the calling thread: nothing may still read them
+  }
+  tm.mark("idct+join");
+  dest->width = w;
+  dest->height = ht;
+  dest->luma_stride = w;
+  dest->colorGamut = UHDRB200_COLORGAMUT_UNSPECIFIED;
+  if (h.n_comp == 1) {
+    dest->pixelFormat = UHDRB200_PIX_FMT_MONOCHROME;
+    dest->chroma_data = nullptr;
+    dest->chroma_stride = 0;
+  } else {
+    dest->pixelFormat = UHDRB200_PIX_FMT_YUV420;
+    dest->chroma_data = (uint8_t*)dest->data + w * ht;
+    dest->chroma_stride = cw;
+  }
+  return UHDRB200_NO_ERROR;
+}
+
+int jpeg_get_info(const void* jpeg, size_t bytes, size_t* width, size_t* height, int* pixel_format) {
+  if (!jpeg) return UHDRB200_ERROR_BAD_PTR;
+  static thread_local JpegHeader h;
+  const char* why = "";
+  const int parsed = jpeg_parse((const uint8_t*)jpeg, bytes, &h, &why);
+  int st = jpeg_status(parsed, why);
+  if (st) return st;
+  if (width) *width = (size_t)h.width;
+  if (height) *height = (size_t)h.height;
+  if (pixel_format) *pixel_format = h.n_comp == 1 ? UHDRB200_PIX_FMT_MONOCHROME : UHDRB200_PIX_FMT_YUV420;
+  return jpeg_check_layout(h);
+}
+
 }  // namespace
 
 // ================================================================ extern "C"
@@ -1636,6 +1888,13 @@ int uhdrb200_yuv420_to_rgba8888_batch_dev(int n, const uhdrb200_image* yuv420, u
 int uhdrb200_jpeg_idct_host(int n_components, const uhdrb200_jpeg_component* comps) { return jpeg_idct_host(n_components, comps); }
 int uhdrb200_jpeg_idct_dev(int n_components, const uhdrb200_jpeg_component* comps, void* stream) {
   return jpeg_idct_core(n_components, comps, (cudaStream_t)stream);
+}
+int uhdrb200_jpeg_get_info(const void* jpeg, size_t bytes, size_t* width, size_t* height, int* pixel_format) {
+  return jpeg_get_info(jpeg, bytes, width, height, pixel_format);
+}
+int uhdrb200_jpeg_decode_host(const void* jpeg, size_t bytes, uhdrb200_image* dest) { return jpeg_decode(jpeg, bytes, dest, false, nullptr); }
+int uhdrb200_jpeg_decode_dev(const void* jpeg, size_t bytes, uhdrb200_image* dest, void* stream) {
+  return jpeg_decode(jpeg, bytes, dest, true, (cudaStream_t)stream);
 }
 int uhdrb200_copy_yuv420_host(const uhdrb200_image* src, uhdrb200_image* dest) { return copy_yuv420_host(src, dest); }
 int uhdrb200_copy_yuv420_dev(const uhdrb200_image* src, uhdrb200_image* dest, void* stream) {

@@ -193,6 +193,58 @@ struct JpegIdctParams {
 };
 cudaError_t launch_jpeg_idct_impl(const JpegIdctParams& p, cudaStream_t s);
 
+// row N4 (jpeg_huff.cu): baseline JPEG entropy decoding on the device. The host parses the markers (jpeg_parse), removes the
+// byte stuffing and uploads the entropy-coded segment; the device decodes it with one thread per kJpegSubseqBits-bit
+// subsequence (self-synchronising parallel Huffman decoding) into the coefficient arrays jpeg_idct_kernel reads.
+#ifndef UHDR_JPEG_SUBSEQ_BITS
+#define UHDR_JPEG_SUBSEQ_BITS 1024
+#endif
+constexpr int kJpegSubseqBits = UHDR_JPEG_SUBSEQ_BITS;   // bits of entropy-coded data one thread owns (a multiple of 32)
+constexpr int kJpegLookBits = 10;       // first-level Huffman look-up: codes of up to 10 bits in one shared-memory load
+struct JpegHuffTable {                  // one DC or AC table (ITU-T T.81 Annex C / F.2.2.3), built by jpeg_parse
+  // first level, indexed by the next kJpegLookBits bits: code length | size << 5 | run << 9 | (length + size) << 13 for a
+  // code of up to kJpegLookBits bits (size = SSSS extra bits, run = RRRR, 0 in a DC table); 0 = a longer code
+  uint32_t fast[1 << kJpegLookBits];
+  int32_t maxcode[18];                  // largest code of each length 1..16 (-1: none); [17] = sentinel
+  int32_t valoff[18];                   // index into vals of the first code of each length minus that code
+  uint8_t vals[256];
+};
+struct JpegDeviceTables {               // one upload per decode
+  JpegHuffTable dc[2], ac[2];           // baseline: table ids 0 and 1
+  uint16_t quant[4][64];                // natural (row-major) order
+};
+struct JpegScan {                       // passed by value to the kernels
+  int n_comp, blocks_per_mcu;
+  uint32_t mcus_x, mcus_y, total_blocks;
+  uint8_t blk_comp[10], blk_dx[10], blk_dy[10];  // block i of an MCU: component, block offset inside the MCU
+  uint8_t comp_h[4], comp_v[4], comp_dc[4], comp_ac[4];
+  uint32_t dc_mask, ac_mask;            // bit i: DC / AC table id (0 or 1) of block i of an MCU
+  uint32_t comp_blocks_w[4], comp_blocks_h[4];   // coefficient array geometry (whole MCUs)
+  int16_t* coeffs[4];                   // device, zero-filled before the write pass
+  const uint32_t* data;                 // device: the entropy-coded segment without byte stuffing, zero padded
+  uint64_t total_bits;
+  uint32_t n_subseq;
+  const JpegDeviceTables* tables;       // device
+};
+struct JpegHeader {                     // host-side result of jpeg_parse
+  int width, height, n_comp;
+  int comp_id[4], comp_h[4], comp_v[4], comp_tq[4], comp_td[4], comp_ta[4];
+  int hmax, vmax, restart_interval;
+  size_t scan_begin, scan_end;          // byte range of the entropy-coded segment inside the file
+  JpegDeviceTables tables;
+};
+// status: 0 ok, 1 not a JPEG / corrupt header, 2 a JPEG this decoder does not handle (progressive, arithmetic, 12-bit,
+// restart intervals, several scans); `why` receives a short reason
+int jpeg_parse(const uint8_t* data, size_t len, JpegHeader* h, const char** why);
+// copies the entropy-coded segment that starts at `begin` into dst (capacity end - begin) without its byte stuffing
+// (FF 00 -> FF) up to the first marker, which it reports (0: the data ran out); returns the number of bytes
+size_t jpeg_destuff(const uint8_t* data, size_t begin, size_t end, uint8_t* dst, int* marker);
+// workspace per subsequence: 2 x u32 exit state (ping-pong), u32 block count, u32 scanned count, 2 x u8 dirty flags
+size_t jpeg_huff_workspace_bytes(uint32_t n_subseq);
+// the whole entropy decode on stream s; synchronises the stream while iterating to the fixed point. `iters` (optional)
+// receives the number of synchronisation passes.
+cudaError_t jpeg_huff_decode(const JpegScan& sc, void* workspace, cudaStream_t s, int* iters);
+
 // *_vec_ok: true when the planes/strides of an image allow the 128-bit vector path (the caller
 // ANDs it over a batch). launch_*_impl return the cudaError_t of the launch; `n` = images (grid.z).
 bool generate_vec_ok(const Geometry& g, const Planes& pl);

@@ -28,10 +28,13 @@ def worker():
                      ("generate_us", lambda i: uh.generateGainMapDevice(sdrs[i], hdrs[i], abi.TF_HLG, md, maps[i], False, st))):
         for i in range(8): fn(i)
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        torch.cuda.synchronize(); e0.record()
+        import time
+        torch.cuda.synchronize(); e0.record(); t0 = time.perf_counter()
         for i in range(96): fn(i % B)
+        t1 = time.perf_counter()  # host side only: what the calling thread spends per call (python + ctypes + C ABI + launch)
         e1.record(); torch.cuda.synchronize()
         res[name] = round(e0.elapsed_time(e1) / 96 * 1e3, 2)
+        res[name.replace("_us", "_host_us")] = round((t1 - t0) / 96 * 1e6, 2)
     print(json.dumps(res))
 
 

@@ -1,0 +1,85 @@
+"""Row N4, host side of the device JPEG decoder (no GPU): uhdrb200_jpeg_get_info = the marker parser of csrc/jpeg_huff.cu,
+mirroring JpegDecoderHelper::getCompressedImageParameters and the layout checks of decompressImage
+(lib/src/jpegdecoderhelper.cpp:254-258, 286-292, 339): sizes and formats of the reference's fixtures, and a clear refusal
+(never a wrong decode) of everything the device decoder does not handle."""
+import ctypes as C
+import io
+
+import numpy as np
+import pytest
+
+from libultrahdr_dev_b200 import abi, refdata
+from libultrahdr_dev_b200.api import load_library
+
+PIL = pytest.importorskip("PIL.Image")
+
+
+def info(lib, data):
+    w, h, f = C.c_size_t(0), C.c_size_t(0), C.c_int(-7)
+    buf = (C.c_ubyte * max(1, len(data))).from_buffer_copy(bytes(data) or b"\0")
+    st = lib.uhdrb200_jpeg_get_info(buf, len(data), C.byref(w), C.byref(h), C.byref(f))
+    return st, w.value, h.value, f.value
+
+
+def encode(arr, **kw):
+    b = io.BytesIO()
+    PIL.fromarray(arr).save(b, "JPEG", **kw)
+    return b.getvalue()
+
+
+@pytest.fixture(scope="module")
+def lib():
+    return load_library()
+
+
+@pytest.mark.skipif(not all(refdata.jpeg_path(n) for n in refdata.JPEGS), reason="JPEG fixtures not staged")
+def test_fixture_parameters(lib):
+    want = {"jpeg_image.jpg": (1280, 720, abi.PIX_FMT_YUV420), "minnie-320x240-yuv.jpg": (320, 240, abi.PIX_FMT_YUV420),
+            "minnie-320x240-y.jpg": (320, 240, abi.PIX_FMT_MONOCHROME)}
+    for name, (w, h, f) in want.items():
+        assert info(lib, open(refdata.jpeg_path(name), "rb").read()) == (0, w, h, f)
+
+
+def test_generated_streams(lib):
+    rng = np.random.Generator(np.random.PCG64(3))
+    rgb = rng.integers(0, 256, (48, 64, 3), dtype=np.uint8)
+    assert info(lib, encode(rgb, quality=90, subsampling=2)) == (0, 64, 48, abi.PIX_FMT_YUV420)
+    assert info(lib, encode(rgb, quality=90, subsampling=2, optimize=True)) == (0, 64, 48, abi.PIX_FMT_YUV420)
+    assert info(lib, encode(rgb[..., 0], quality=50)) == (0, 64, 48, abi.PIX_FMT_MONOCHROME)
+    # what decompressImage refuses, or what the device decoder leaves to libjpeg
+    st, *_ = info(lib, encode(rgb, quality=90, subsampling=0))  # 4:4:4: "decoding to YUV only supports 4:2:0 subsampling"
+    assert st == abi.ERROR_UNSUPPORTED_FEATURE and b"4:2:0" in lib.uhdrb200_last_error()
+    st, *_ = info(lib, encode(rgb, quality=90, subsampling=1))  # 4:2:2
+    assert st == abi.ERROR_UNSUPPORTED_FEATURE
+    st, *_ = info(lib, encode(rgb, quality=90, subsampling=2, progressive=True))
+    assert st == abi.ERROR_UNSUPPORTED_FEATURE and b"progressive" in lib.uhdrb200_last_error()
+    st, *_ = info(lib, encode(rgb, quality=90, subsampling=2, restart_marker_rows=1))
+    assert st == abi.ERROR_UNSUPPORTED_FEATURE and b"restart" in lib.uhdrb200_last_error()
+
+
+def test_not_a_jpeg(lib):
+    good = encode(np.zeros((16, 16, 3), np.uint8), quality=90, subsampling=2)
+    assert info(lib, b"")[0] == abi.ERROR_DECODE
+    assert info(lib, b"\x89PNG\r\n\x1a\n" + bytes(64))[0] == abi.ERROR_DECODE
+    assert info(lib, good[:20])[0] == abi.ERROR_DECODE          # cut inside the headers
+    assert info(lib, good[:2] + b"\xff\xe0\xff\xff" + good[2:])[0] == abi.ERROR_DECODE  # segment longer than the file
+    assert lib.uhdrb200_jpeg_get_info(None, 10, None, None, None) == abi.ERROR_BAD_PTR
+    buf = (C.c_ubyte * len(good)).from_buffer_copy(good)
+    assert lib.uhdrb200_jpeg_get_info(buf, len(good), None, None, None) == 0  # outputs are optional
+
+
+def test_size_limit(lib):
+    big = encode(np.zeros((8, 8200), np.uint8), quality=50)  # wider than kMaxWidth = 8192 (jpegdecoderhelper.cpp:254-258)
+    assert info(lib, big)[0] == abi.ERROR_UNSUPPORTED_WIDTH_HEIGHT
+
+
+@pytest.mark.skipif(not refdata.jpeg_path("minnie-320x240-yuv.jpg"), reason="JPEG fixtures not staged")
+def test_progressive_fixture_is_refused(lib):
+    import os
+
+    p = os.path.join(os.path.dirname(refdata.jpeg_path("minnie-320x240-yuv.jpg")), "minnie-320x240-yuv-icc.jpg")
+    if not os.path.exists(p):
+        p = "/root/reference/tests/data/minnie-320x240-yuv-icc.jpg"
+    if not os.path.exists(p):
+        pytest.skip("progressive fixture not available")
+    assert info(lib, open(p, "rb").read())[0] == abi.ERROR_UNSUPPORTED_FEATURE  # SOF2
