@@ -396,6 +396,7 @@ def main():
 
     # ---- the other kernels of the path (not part of `value`): per-kernel roofline on the same batch, rank 0 only
     other = {}
+    jpeg_stage = None
     if rank == 0 and not a.no_other_stages:
         Bo = min(B, 64)
         d_tm = torch.zeros((Bo, sdr_len), dtype=torch.uint8, device=dev)
@@ -565,6 +566,62 @@ def main():
         r.update(mpix_s=r["mpix_s"] * scale, achieved_gbs=r["achieved_gbs"] * scale, images_per_launch=1, image="8160x6144 4:2:0")
         other["jpeg_idct_420_50mp"] = r
         del d_co, d_pl
+        # ---- N4, whole decode: 4K 4:2:0 baseline JPEGs (quality 90, libjpeg-turbo's default tables, made here through
+        # Pillow from the natural SDR planes + sensor-like noise) -> planes in device memory. Host parse and byte-stuffing
+        # removal, upload of the compressed bytes, parallel Huffman decode and IDCT, wall clock per synchronous call; one
+        # calling thread and four (each with its own context and stream). Latency-bound, not HBM-bound: no roofline.
+        try:
+            import io
+            import threading
+
+            from PIL import Image
+
+            jp = []
+            for i in range(4):
+                hp = d_sdr[i % K].cpu().numpy()
+                yy = hp[: W * H].reshape(H, W)
+                uu = hp[W * H: W * H * 5 // 4].reshape(H // 2, W // 2).repeat(2, 0).repeat(2, 1)
+                vv = hp[W * H * 5 // 4:].reshape(H // 2, W // 2).repeat(2, 0).repeat(2, 1)
+                rr = np.random.Generator(np.random.PCG64(i))
+                yy = np.clip(yy.astype(np.int16) + rr.integers(-6, 7, yy.shape), 0, 255).astype(np.uint8)
+                bio = io.BytesIO()
+                Image.fromarray(np.stack([yy, uu, vv], -1), "YCbCr").save(bio, "JPEG", quality=90, subsampling=2)
+                jp.append(bio.getvalue())
+            jbufs = [(C.c_ubyte * len(b)).from_buffer_copy(b) for b in jp]
+
+            def decode_loop(tid, iters, out):
+                torch.cuda.set_device(dev)
+                d_pl = torch.zeros(W * H * 3 // 2, dtype=torch.uint8, device=dev)
+                im = abi.Image()
+                im.data = d_pl.data_ptr()
+                for k in range(2):
+                    assert lib.uhdrb200_jpeg_decode_dev(jbufs[k % 4], len(jp[k % 4]), C.byref(im), None) == 0, lib.uhdrb200_last_error()
+                t0 = time.perf_counter()
+                for k in range(iters):
+                    lib.uhdrb200_jpeg_decode_dev(jbufs[(k + tid) % 4], len(jp[(k + tid) % 4]), C.byref(im), None)
+                out[tid] = (time.perf_counter() - t0) / iters
+
+            res1 = {}
+            decode_loop(0, 12, res1)
+            res4 = {}
+            ths = [threading.Thread(target=decode_loop, args=(t, 12, res4)) for t in range(4)]
+            for t in ths:
+                t.start()
+            for t in ths:
+                t.join()
+            t0 = time.perf_counter()
+            for k in range(2):
+                im = Image.open(io.BytesIO(jp[k]))
+                im.draft("YCbCr", (W, H))
+                im.load()
+            cpu_ms = (time.perf_counter() - t0) / 2 * 1e3
+            jpeg_stage = {"mpix_s": PIX / res1[0] / 1e6, "ms_per_image": res1[0] * 1e3, "images_per_launch": 1,
+                          "mpix_s_4_host_threads": 4 * PIX / (sum(res4.values()) / 4) / 1e6, "jpeg_bytes": int(np.mean([len(b) for b in jp])),
+                          "libjpeg_turbo_1_core_mpix_s": PIX / cpu_ms / 1e3, "libjpeg_turbo_1_core_ms": cpu_ms,
+                          "content": "natural SDR planes + noise, quality 90, 4:2:0, through Pillow / libjpeg-turbo's encoder",
+                          "bound": "latency (sequential synchronisation chains of the parallel Huffman decode), not HBM"}
+        except ImportError:
+            pass
         # ---- real image content: the reference's own fixtures (tests/data, staged by build() into tests/_ref_data):
         # the 1280x720 raw P010 + YUV420 pair of ProfileGainMapFuncs (tests/jpegr_test.cpp:2250-2304) tiled 3 x 3 to 4K,
         # and the only photograph in the tree (minnie-320x240.yu12) tiled 12 x 9; every slot a different cyclic shift
@@ -779,7 +836,8 @@ def main():
                 "host_threads": T, "numa_local_cores": numa_cores, "join": "blocking" if blocking else "spin", "pcie_measured": pcie, "host_memory": a.e2e_host_memory, other_kind + "_planes_mpix_s": other_mpix,
                 "api": "uhdrb200_generate_gainmap_host_into + uhdrb200_apply_gainmap_host (synchronous, reference-style); " +
                        ("pageable host planes, as an unmodified libultrahdr caller passes them" if a.e2e_host_memory == "pageable" else "page-locked host planes")},
-        "other_stages": {k: dict(v, frac_of_hbm_peak=v["achieved_gbs"] / peak) for k, v in other.items()},
+        "other_stages": dict({k: dict(v, frac_of_hbm_peak=v["achieved_gbs"] / peak) for k, v in other.items()},
+                             **({"jpeg_decode_4k_q90_to_device_planes": jpeg_stage} if jpeg_stage else {})),
         "gpu_launches": int(launches),
         "clocks": clk,
     }
