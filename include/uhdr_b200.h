@@ -278,8 +278,8 @@ int uhdrb200_jpeg_idct_dev(int n_components, const uhdrb200_jpeg_component* comp
  * (lib/src/jpegdecoderhelper.cpp:190-320, 380-470; jpegr.cpp:693 primary image, :732 gain map): a 4:2:0 YCbCr JPEG becomes
  * packed planar Y | U | V (strides width and width / 2), a greyscale JPEG one plane; like the reference, other samplings
  * and images above 8192 x 8192 are refused. Handled on the device: baseline / sequential Huffman, 8-bit, one interleaved
- * scan, no restart intervals (what libjpeg-turbo and JpegEncoderHelper write by default). Progressive, arithmetic-coded,
- * 12-bit, multi-scan and restart-interval streams return UHDRB200_ERROR_UNSUPPORTED_FEATURE with the reason in
+ * scan, with or without restart intervals (libjpeg-turbo and JpegEncoderHelper write none by default). Progressive,
+ * arithmetic-coded, 12-bit and multi-scan streams return UHDRB200_ERROR_UNSUPPORTED_FEATURE with the reason in
  * uhdrb200_last_error() so the caller can fall back to libjpeg; a stream that is not a JPEG returns UHDRB200_ERROR_DECODE.
  * The host parses the markers and removes the byte stuffing; only the compressed bytes are copied to the GPU, where the
  * Huffman stream is decoded in parallel (csrc/jpeg_huff.cu) and transformed by the N4 IDCT kernel, ISLOW like the reference

@@ -1618,12 +1618,21 @@ int jpeg_decode(const void* jpeg, size_t bytes, uhdrb200_image* dest, bool to_de
   const size_t w = (size_t)h.width, ht = (size_t)h.height;
   // ---- entropy-coded segment: stuffing removed on the host, zero padded to whole 32-bit words + slack for the bit reader
   static thread_local std::vector<uint8_t> seg;
-  seg.resize(h.scan_end - h.scan_begin + 64);
+  static thread_local std::vector<uint32_t> ivals;  // [interval_first (n_intervals) | interval_of (n_subseq)] once laid out
+  const uint64_t total_mcus = h.n_comp == 1 ? (uint64_t)((w + 7) / 8) * ((ht + 7) / 8)
+                                            : (uint64_t)((w + 8 * h.hmax - 1) / (8 * h.hmax)) * ((ht + 8 * h.vmax - 1) / (8 * h.vmax));
+  uint32_t ri = (uint32_t)h.restart_interval;
+  if (ri >= total_mcus) ri = 0;  // one interval: the prediction never restarts
+  const uint32_t max_intervals = ri ? (uint32_t)((total_mcus + ri - 1) / ri) : 1;
+  constexpr size_t kSubBytes = kJpegSubseqBits / 8;
+  seg.resize(h.scan_end - h.scan_begin + (size_t)max_intervals * kSubBytes + 64);
+  ivals.resize(max_intervals);
   int marker = 0;
-  const size_t nseg = jpeg_destuff((const uint8_t*)jpeg, h.scan_begin, h.scan_end, seg.data(), &marker);
+  uint32_t n_intervals = 1;
+  const size_t nseg = jpeg_destuff((const uint8_t*)jpeg, h.scan_begin, h.scan_end, seg.data(), &marker, max_intervals, ivals.data(), &n_intervals);
   if (marker >= 0xD0 && marker <= 0xD7) {
-    t_ctx.err = "uhdrb200_jpeg: restart markers";
-    return UHDRB200_ERROR_UNSUPPORTED_FEATURE;
+    t_ctx.err = ri ? "uhdrb200_jpeg: more restart markers than restart intervals" : "uhdrb200_jpeg: restart markers without a restart interval (DRI)";
+    return UHDRB200_ERROR_DECODE;
   }
   const size_t padded = (nseg + 63) & ~(size_t)31;
   memset(seg.data() + nseg, 0, padded - nseg);
@@ -1633,6 +1642,16 @@ int jpeg_decode(const void* jpeg, size_t bytes, uhdrb200_image* dest, bool to_de
   sc.n_comp = h.n_comp;
   sc.total_bits = (uint64_t)nseg * 8;
   sc.n_subseq = (uint32_t)((sc.total_bits + kJpegSubseqBits - 1) / kJpegSubseqBits);
+  sc.restart_interval = ri;
+  sc.n_intervals = n_intervals;
+  if (ri) {  // interval_first in subsequences, then interval_of per subsequence
+    ivals.resize((size_t)n_intervals + sc.n_subseq);
+    for (uint32_t i = 0; i < n_intervals; i++) ivals[i] = (uint32_t)(ivals[i] / kSubBytes);
+    for (uint32_t i = 0; i < n_intervals; i++) {
+      const uint32_t t0 = ivals[i], t1 = i + 1 < n_intervals ? ivals[i + 1] : sc.n_subseq;
+      for (uint32_t t = t0; t < t1 && t < sc.n_subseq; t++) ivals[n_intervals + t] = i;
+    }
+  }
   if (h.n_comp == 1) {  // a single-component scan is not interleaved: one block per MCU whatever the sampling factors say (A.2.2)
     sc.blocks_per_mcu = 1;
     sc.mcus_x = (uint32_t)((w + 7) / 8);
@@ -1673,6 +1692,11 @@ int jpeg_decode(const void* jpeg, size_t bytes, uhdrb200_image* dest, bool to_de
   // ---- device buffers of the calling thread: segment, tables, workspace, coefficients (+ planes for the host variant)
   if ((st = upload(c.buf[0], seg.data(), padded, s))) return st;
   if ((st = upload(c.buf[1], &h.tables, sizeof h.tables, s))) return st;
+  if (ri) {
+    if ((st = upload(c.buf[5], ivals.data(), ivals.size() * sizeof(uint32_t), s))) return st;
+    sc.interval_first = (const uint32_t*)c.buf[5].p;
+    sc.interval_of = sc.interval_first + n_intervals;
+  }
   if ((st = reserve(c.buf[2], jpeg_huff_workspace_bytes(sc.n_subseq)))) return st;
   if ((st = reserve(c.buf[3], coeff_bytes))) return st;
   CU(cudaMemsetAsync(c.buf[3].p, 0, coeff_bytes, s));

@@ -161,7 +161,6 @@ int jpeg_parse(const uint8_t* d, size_t len, JpegHeader* h, const char** why) {
             return 1;
           }
         }
-        if (h->restart_interval != 0) { *why = "restart intervals"; return 2; }
         h->scan_begin = pos + ln;
         h->scan_end = len;  // jpeg_destuff finds the marker that ends the segment while it copies
         *why = "";
@@ -173,9 +172,13 @@ int jpeg_parse(const uint8_t* d, size_t len, JpegHeader* h, const char** why) {
   }
 }
 
-size_t jpeg_destuff(const uint8_t* d, size_t begin, size_t end, uint8_t* dst, int* marker) {
+size_t jpeg_destuff(const uint8_t* d, size_t begin, size_t end, uint8_t* dst, int* marker, uint32_t max_intervals,
+                    uint32_t* interval_start, uint32_t* n_intervals) {
+  constexpr size_t kAlign = kJpegSubseqBits / 8;
   size_t o = 0, i = begin;
   *marker = 0;
+  *n_intervals = 1;
+  interval_start[0] = 0;
   while (i < end) {
     const uint8_t* f = (const uint8_t*)memchr(d + i, 0xFF, end - i);
     const size_t run = f ? (size_t)(f - (d + i)) : end - i;
@@ -189,6 +192,12 @@ size_t jpeg_destuff(const uint8_t* d, size_t begin, size_t end, uint8_t* dst, in
       i += 2;
     } else if (m == 0xFF) {  // fill byte before a marker
       i++;
+    } else if (m >= 0xD0 && m <= 0xD7 && *n_intervals < max_intervals) {  // RSTn: the next interval starts byte aligned
+      const size_t padded = (o + kAlign - 1) / kAlign * kAlign;
+      memset(dst + o, 0, padded - o);
+      o = padded;
+      interval_start[(*n_intervals)++] = (uint32_t)o;
+      i += 2;
     } else {                 // EOI (or any other marker): the entropy-coded segment ends here
       *marker = m;
       break;
@@ -293,20 +302,20 @@ struct BlockCursor {
   }
 };
 
-// Decodes from bit p in state (c, k) until the first symbol that starts at or after p_end (or, when writing, until the
-// image's last block is complete). blk = scan-order index of the block in progress. Returns the exit state; `done`
+// Decodes from bit p in state (c, k) until the first symbol that starts at or after p_end (or, when writing, until block
+// blk_end - 1, the last one of the image or of the restart interval, is complete). blk = scan-order index of the block in progress. Returns the exit state; `done`
 // counts the blocks completed. The symbol-to-symbol dependency chain is: table entry (one shared-memory load indexed by
 // the window), its `length + size` field, the window shift; everything else hangs off it.
 template <bool WRITE>
 __device__ __forceinline__ uint32_t decode_span(const JpegScan& sc, const HuffSmem* sm, uint64_t p, const uint64_t p_end, uint32_t c, uint32_t k,
-                                                uint32_t blk, uint32_t& done) {
+                                                uint32_t blk, const uint32_t blk_end, uint32_t& done) {
   const uint32_t B = (uint32_t)sc.blocks_per_mcu, dc_sel = sc.dc_mask, ac_sel = sc.ac_mask;
   done = 0;
   if (p >= p_end) return pack_state(0, c, k);
   BlockCursor cur;
   int16_t* out = nullptr;
   if (WRITE) {
-    if (blk >= sc.total_blocks) return pack_state(0, c, k);
+    if (blk >= blk_end) return pack_state(0, c, k);
     cur.open(sc, blk);
     out = cur.addr(sc, c);
   }
@@ -336,13 +345,18 @@ __device__ __forceinline__ uint32_t decode_span(const JpegScan& sc, const HuffSm
       tac = &sm->ac[(ac_sel >> c) & 1u];
       if (WRITE) {
         cur.next(sc, c);
-        if (cur.blk >= sc.total_blocks) break;
+        if (cur.blk >= blk_end) break;  // the image's (or the restart interval's) last block is complete
         out = cur.addr(sc, c);
       }
     }
   }
   done = n;
   return pack_state((uint32_t)(left < 0 ? -left : 0), c, k);
+}
+
+// a subsequence whose entry state is known without decoding: the first one of the scan or of a restart interval
+__device__ __forceinline__ bool hard_start(const JpegScan& sc, uint32_t t) {
+  return t == 0 || (sc.interval_of != nullptr && __ldg(sc.interval_first + __ldg(sc.interval_of + t)) == t);
 }
 
 __device__ __forceinline__ void span_of(const JpegScan& sc, uint32_t t, uint64_t& b, uint64_t& e) {
@@ -372,21 +386,22 @@ __global__ void __launch_bounds__(kHuffThreads) huff_round_kernel(const __grid_c
   }
   load_tables(&sm, sc.tables);
   const bool live = t < sc.n_subseq;
+  const bool hard = live && hard_start(sc, t);  // entry state exact from the start: never decoded again
   uint64_t b = 0, e = 0;
   if (live) span_of(sc, t, b, e);
   uint32_t cur = 0, cnt = 0;
   bool ch = false;
   if (FIRST) {
-    if (live) cur = decode_span<false>(sc, &sm, b, e, 0, 0, 0, cnt);
+    if (live) cur = decode_span<false>(sc, &sm, b, e, 0, 0, 0, 0, cnt);
     ch = live;
   } else if (live) {
     cur = exit_state[t];
     cnt = count[t];
   }
   const uint32_t entry_exit = cur;  // this subsequence's exit state before the round
-  if (!FIRST && i == 0) {           // re-enter with the predecessor CTA's last exit state
+  if (!FIRST && i == 0 && !hard) {  // re-enter with the predecessor CTA's last exit state
     const uint32_t st = exit_state[t - 1];
-    const uint32_t now = decode_span<false>(sc, &sm, b + (st >> 16), e, (st >> 8) & 0xFFu, st & 0xFFu, 0, cnt);
+    const uint32_t now = decode_span<false>(sc, &sm, b + (st >> 16), e, (st >> 8) & 0xFFu, st & 0xFFu, 0, 0, cnt);
     ch = now != cur;
     cur = now;
   }
@@ -395,12 +410,12 @@ __global__ void __launch_bounds__(kHuffThreads) huff_round_kernel(const __grid_c
   int ph = 0;
   for (;;) {
     __syncthreads();
-    const bool work = live && i > 0 && dirty_s[ph][i - 1];
+    const bool work = live && i > 0 && !hard && dirty_s[ph][i - 1];
     const uint32_t st = work ? exit_s[i - 1] : 0;
     __syncthreads();  // every thread has read its neighbour before any thread publishes a new state
     ch = false;
     if (work) {
-      const uint32_t now = decode_span<false>(sc, &sm, b + (st >> 16), e, (st >> 8) & 0xFFu, st & 0xFFu, 0, cnt);
+      const uint32_t now = decode_span<false>(sc, &sm, b + (st >> 16), e, (st >> 8) & 0xFFu, st & 0xFFu, 0, 0, cnt);
       ch = now != cur;
       cur = now;
       exit_s[i] = now;
@@ -442,18 +457,29 @@ __global__ void __launch_bounds__(1024) huff_scan_kernel(const uint32_t* __restr
   }
 }
 
-// pass 4: decode from the exact entry states and write the coefficients (DC as differences)
+// pass 4: decode from the exact entry states and write the coefficients (DC as differences). With restart intervals the
+// block a subsequence starts in is counted from its interval's first block, which is known (interval * restart_interval MCUs).
 __global__ void __launch_bounds__(kHuffThreads) huff_write_kernel(const __grid_constant__ JpegScan sc, const uint32_t* __restrict__ exit_state,
                                                                   const uint32_t* __restrict__ first_block) {
   __shared__ HuffSmem sm;
   load_tables(&sm, sc.tables);
   const uint32_t t = blockIdx.x * kHuffThreads + threadIdx.x;
   if (t >= sc.n_subseq) return;
-  const uint32_t st = t ? exit_state[t - 1] : 0;
+  uint32_t blk = first_block[t], blk_end = sc.total_blocks;
+  bool hard = t == 0;
+  if (sc.interval_of != nullptr) {
+    const uint32_t iv = sc.interval_of[t], t0 = sc.interval_first[iv], per = sc.restart_interval * (uint32_t)sc.blocks_per_mcu;
+    const uint64_t base = (uint64_t)iv * per;
+    if (base >= sc.total_blocks) return;  // more intervals in the stream than the image has room for
+    blk = (uint32_t)base + (blk - first_block[t0]);
+    blk_end = (uint32_t)min((uint64_t)sc.total_blocks, base + per);
+    hard = t == t0;
+  }
+  const uint32_t st = hard ? 0 : exit_state[t - 1];
   uint64_t b, e;
   span_of(sc, t, b, e);
   uint32_t n;
-  decode_span<true>(sc, &sm, b + (st >> 16), e, (st >> 8) & 0xFFu, st & 0xFFu, first_block[t], n);
+  decode_span<true>(sc, &sm, b + (st >> 16), e, (st >> 8) & 0xFFu, st & 0xFFu, blk, blk_end, n);
 }
 
 // pass 5: DC prediction (F.2.2.1: DIFF + PRED) as a scan over one component's blocks in DECODING order: block j of the
@@ -521,6 +547,31 @@ __global__ void __launch_bounds__(kDcThreads) dc_apply_kernel(const __grid_const
   for (uint32_t i = 0; i < (uint32_t)kDcPer; i++) {
     run += d[i];
     if (j0 + i < n) dc_addr(sc, comp, j0 + i)[0] = (int16_t)run;
+  }
+}
+
+// DC prediction with restart intervals: the prediction restarts at every interval, i.e. every restart_interval * h * v
+// elements of a component's decoding-order sequence. One warp per (component, interval): a warp-wide scan, 32 elements a step.
+__global__ void __launch_bounds__(kDcThreads) dc_interval_kernel(const __grid_constant__ JpegScan sc) {
+  const uint32_t comp = blockIdx.y, n = comp_blocks(sc, comp), lane = threadIdx.x & 31;
+  const uint32_t seg = blockIdx.x * (kDcThreads / 32) + (threadIdx.x >> 5);
+  const uint32_t nb = sc.n_comp == 1 ? 1u : (uint32_t)sc.comp_h[comp] * sc.comp_v[comp], len = sc.restart_interval * nb;
+  const uint64_t j0 = (uint64_t)seg * len;
+  if (j0 >= n) return;  // warp-uniform
+  const uint32_t j1 = (uint32_t)min((uint64_t)n, j0 + len);
+  int carry = 0;
+  for (uint32_t j = (uint32_t)j0; j < j1; j += 32) {
+    const bool in = j + lane < j1;
+    int16_t* p = in ? dc_addr(sc, comp, j + lane) : nullptr;
+    int v = in ? (int)p[0] : 0;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const int o = __shfl_up_sync(0xffffffffu, v, d);
+      if (lane >= (uint32_t)d) v += o;
+    }
+    v += carry;
+    if (in) p[0] = (int16_t)v;
+    carry = __shfl_sync(0xffffffffu, v, 31);
   }
 }
 
@@ -594,6 +645,11 @@ cudaError_t jpeg_huff_decode(const JpegScan& sc, void* workspace, cudaStream_t s
   for (int c = 0; c < sc.n_comp; c++) {
     const uint32_t nb = sc.n_comp == 1 ? sc.total_blocks : sc.mcus_x * sc.mcus_y * sc.comp_h[c] * sc.comp_v[c];
     max_blocks = nb > max_blocks ? nb : max_blocks;
+  }
+  if (sc.restart_interval) {
+    const uint32_t segs = (sc.mcus_x * sc.mcus_y + sc.restart_interval - 1) / sc.restart_interval;
+    dc_interval_kernel<<<dim3((segs + kDcThreads / 32 - 1) / (kDcThreads / 32), sc.n_comp), kDcThreads, 0, s>>>(sc);
+    return cudaGetLastError();
   }
   const uint32_t chunks = (max_blocks + kDcChunk - 1) / kDcChunk;
   dc_partial_kernel<<<dim3(chunks, sc.n_comp), kDcThreads, 0, s>>>(sc, partial, chunks);

@@ -224,6 +224,12 @@ struct JpegScan {                       // passed by value to the kernels
   const uint32_t* data;                 // device: the entropy-coded segment without byte stuffing, zero padded
   uint64_t total_bits;
   uint32_t n_subseq;
+  // restart intervals (T.81 B.2.4.4, F.2.1.3.1): every interval starts at a subsequence boundary of `data` (the host pads),
+  // in a known state (block 0 of MCU interval * restart_interval, DC predictions zero)
+  uint32_t restart_interval;            // MCUs per interval, 0 = none (one interval)
+  uint32_t n_intervals;
+  const uint32_t* interval_of;          // device, per subsequence: its interval (nullptr without restart intervals)
+  const uint32_t* interval_first;       // device, per interval: its first subsequence
   const JpegDeviceTables* tables;       // device
 };
 struct JpegHeader {                     // host-side result of jpeg_parse
@@ -234,11 +240,15 @@ struct JpegHeader {                     // host-side result of jpeg_parse
   JpegDeviceTables tables;
 };
 // status: 0 ok, 1 not a JPEG / corrupt header, 2 a JPEG this decoder does not handle (progressive, arithmetic, 12-bit,
-// restart intervals, several scans); `why` receives a short reason
+// several scans); `why` receives a short reason
 int jpeg_parse(const uint8_t* data, size_t len, JpegHeader* h, const char** why);
-// copies the entropy-coded segment that starts at `begin` into dst (capacity end - begin) without its byte stuffing
-// (FF 00 -> FF) up to the first marker, which it reports (0: the data ran out); returns the number of bytes
-size_t jpeg_destuff(const uint8_t* data, size_t begin, size_t end, uint8_t* dst, int* marker);
+// copies the entropy-coded segment that starts at `begin` into dst without its byte stuffing (FF 00 -> FF) up to the
+// first marker that is not RSTn, which it reports (0: the data ran out); returns the number of bytes. At every RSTn (at
+// most max_intervals - 1 of them) the output is zero padded to a multiple of kJpegSubseqBits / 8 bytes and the byte offset
+// of the next interval is appended to interval_start (which starts as {0}). dst capacity: end - begin + max_intervals *
+// kJpegSubseqBits / 8.
+size_t jpeg_destuff(const uint8_t* data, size_t begin, size_t end, uint8_t* dst, int* marker, uint32_t max_intervals,
+                    uint32_t* interval_start, uint32_t* n_intervals);
 // workspace per subsequence: 2 x u32 exit state (ping-pong), u32 block count, u32 scanned count, 2 x u8 dirty flags
 size_t jpeg_huff_workspace_bytes(uint32_t n_subseq);
 // the whole entropy decode on stream s; synchronises the stream while iterating to the fixed point. `iters` (optional)

@@ -27,10 +27,10 @@ imgs = [ycc_image(i) for i in range(4)]
 d_yuv = torch.zeros((4, W * H * 3 // 2), dtype=torch.uint8, device=dev)
 st = torch.cuda.current_stream().cuda_stream
 out = []
-for q in (75, 90, 95, 100):
+for q, extra in ((75, {}), (90, {}), (95, {}), (100, {}), (90, {"restart_marker_rows": 1}), (100, {"restart_marker_rows": 1}), (90, {"restart_marker_blocks": 16})):
     datas = []
     for im in imgs:
-        b = io.BytesIO(); im.save(b, "JPEG", quality=q, subsampling=2); datas.append(b.getvalue())
+        b = io.BytesIO(); im.save(b, "JPEG", quality=q, subsampling=2, **extra); datas.append(b.getvalue())
     bufs = [(C.c_ubyte * len(d)).from_buffer_copy(d) for d in datas]
     dst = [abi.Image() for _ in range(4)]
     for k in range(4): dst[k].data = d_yuv[k].data_ptr()
@@ -48,7 +48,7 @@ for q in (75, 90, 95, 100):
     for k in range(4):
         im = Image.open(io.BytesIO(datas[k])); im.draft("YCbCr", (W, H)); im.load()
     dt_cpu = (time.perf_counter() - t0) / 4
-    out.append({"quality": q, "jpeg_bytes": int(np.mean([len(d) for d in datas])), "sync_passes": passes, "decode_dev_ms": round(dt * 1e3, 3),
+    out.append({"quality": q, "restart": extra or None, "jpeg_bytes": int(np.mean([len(d) for d in datas])), "sync_passes": passes, "decode_dev_ms": round(dt * 1e3, 3),
                 "mpix_s": round(W * H / dt / 1e6), "parse_only_ms": round(dt_parse * 1e3, 3), "libjpeg_turbo_pillow_1core_ms": round(dt_cpu * 1e3, 2),
                 "libjpeg_turbo_mpix_s": round(W * H / dt_cpu / 1e6)})
     print(json.dumps(out[-1]), flush=True)

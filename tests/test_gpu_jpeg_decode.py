@@ -129,6 +129,44 @@ def test_extreme_streams(uh, kind):
         assert np.array_equal(p, r)
 
 
+@pytest.mark.parametrize("w,h", [(64, 48), (642, 362), (1280, 720), (3840, 2160)])
+@pytest.mark.parametrize("restart", [dict(restart_marker_rows=1), dict(restart_marker_blocks=1), dict(restart_marker_blocks=7),
+                                     dict(restart_marker_rows=3), dict(restart_marker_blocks=100000)])
+def test_restart_intervals(uh, w, h, restart):
+    """DRI streams (T.81 B.2.4.4): an interval per MCU row, per MCU, every 7 MCUs (intervals that straddle MCU rows),
+    every 3 MCU rows, and an interval longer than the image (no marker is ever written). Every interval starts in a known
+    state, so the decoder needs no synchronisation across them; the DC prediction restarts with each."""
+    pytest.importorskip("PIL.Image")
+    data = encode(scene(w, h, w + 3), quality=88, subsampling=2, **restart)
+    n_rst = sum(data.count(bytes([0xFF, 0xD0 + k])) for k in range(8))
+    planes = decode_host(uh.lib, data)
+    for i, (p, r) in enumerate(zip(planes, libjpeg_planes(data))):
+        bad = int((p != r).sum())
+        assert bad == 0, f"plane {i}: {bad} of {p.size} samples differ ({w}x{h}, {restart}, ~{n_rst} markers)"
+
+
+def test_restart_intervals_grey_and_q100(uh):
+    pytest.importorskip("PIL.Image")
+    for arr, kw in ((scene(1283, 721, 4)[..., 0], dict(quality=90, restart_marker_rows=1)),
+                    (scene(640, 360, 6, noise=40.0), dict(quality=100, subsampling=2, restart_marker_blocks=3, optimize=True))):
+        data = encode(arr, **kw)
+        for p, r in zip(decode_host(uh.lib, data), libjpeg_planes(data)):
+            assert np.array_equal(p, r)
+
+
+def test_restart_marker_count_mismatch_is_an_error(uh):
+    """A stream with more RSTn markers than its DRI allows is refused (libjpeg would resynchronise and warn)."""
+    pytest.importorskip("PIL.Image")
+    data = bytearray(encode(scene(64, 48, 8), quality=90, subsampling=2, restart_marker_rows=1))
+    i = data.find(b"\xff\xdd")
+    data[i + 4: i + 6] = (60000).to_bytes(2, "big")  # the interval now covers the whole image: no marker may follow
+    img = abi.Image()
+    out = np.zeros(64 * 48 * 3, np.uint8)
+    img.data = out.ctypes.data
+    buf = (C.c_ubyte * len(data)).from_buffer_copy(bytes(data))
+    assert uh.lib.uhdrb200_jpeg_decode_host(buf, len(data), C.byref(img)) == abi.ERROR_DECODE
+
+
 def test_many_images_one_thread_reuses_scratch(uh):
     """The calling thread's scratch buffers shrink and grow between calls: large, small, large again."""
     pytest.importorskip("PIL.Image")
@@ -147,7 +185,7 @@ def test_refusals(uh):
     out = np.zeros(64 * 48 * 3, np.uint8)
     img.data = out.ctypes.data
     for kw, code in ((dict(subsampling=0), abi.ERROR_UNSUPPORTED_FEATURE), (dict(subsampling=2, progressive=True), abi.ERROR_UNSUPPORTED_FEATURE),
-                     (dict(subsampling=2, restart_marker_rows=1), abi.ERROR_UNSUPPORTED_FEATURE)):
+                     (dict(subsampling=1), abi.ERROR_UNSUPPORTED_FEATURE)):
         data = encode(rgb, quality=90, **kw)
         buf = (C.c_ubyte * len(data)).from_buffer_copy(data)
         assert lib.uhdrb200_jpeg_decode_host(buf, len(data), C.byref(img)) == code

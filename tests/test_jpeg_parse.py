@@ -53,8 +53,7 @@ def test_generated_streams(lib):
     assert st == abi.ERROR_UNSUPPORTED_FEATURE
     st, *_ = info(lib, encode(rgb, quality=90, subsampling=2, progressive=True))
     assert st == abi.ERROR_UNSUPPORTED_FEATURE and b"progressive" in lib.uhdrb200_last_error()
-    st, *_ = info(lib, encode(rgb, quality=90, subsampling=2, restart_marker_rows=1))
-    assert st == abi.ERROR_UNSUPPORTED_FEATURE and b"restart" in lib.uhdrb200_last_error()
+    assert info(lib, encode(rgb, quality=90, subsampling=2, restart_marker_rows=1)) == (0, 64, 48, abi.PIX_FMT_YUV420)  # DRI is handled
 
 
 def test_not_a_jpeg(lib):
