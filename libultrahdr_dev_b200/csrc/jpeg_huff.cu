@@ -233,20 +233,21 @@ __device__ __forceinline__ void load_tables(HuffSmem* sm, const JpegDeviceTables
 // (a symbol spans at most 16 + 15), the word after the window is already in flight (`next`) when the window is topped up,
 // so no load sits on the symbol-to-symbol dependency chain. The segment is zero padded: reads past its end are safe.
 struct BitWindow {
-  const uint32_t* __restrict__ data;
-  uint32_t hi, lo;  // the window, MSB first: hi = the next 32 bits, lo = the bits after them (`avail` - 32 valid)
-  uint32_t next, word;
+  const uint32_t* __restrict__ ptr;  // the word after `next_raw`
+  uint32_t hi, lo;    // the window, MSB first: hi = the next 32 bits, lo = the bits after them (`avail` - 32 valid)
+  uint32_t next_raw;  // the following word as loaded (little endian): swapped only when it enters the window, so that the
+                      // load issued at one top-up is not waited for before the next
   int avail;
   __device__ __forceinline__ static uint32_t be(uint32_t v) { return __byte_perm(v, 0, 0x0123); }
   __device__ __forceinline__ void open(const uint32_t* d, uint64_t p) {
-    data = d;
-    const uint32_t i = (uint32_t)(p >> 5), sh = (uint32_t)p & 31u;
-    const uint32_t w0 = be(__ldg(d + i)), w1 = be(__ldg(d + i + 1));
+    const uint32_t sh = (uint32_t)p & 31u;
+    ptr = d + (p >> 5);
+    const uint32_t w0 = be(__ldg(ptr)), w1 = be(__ldg(ptr + 1));
+    next_raw = __ldg(ptr + 2);
+    ptr += 3;
     hi = __funnelshift_l(w1, w0, sh);
     lo = w1 << sh;
     avail = 64 - (int)sh;
-    next = be(__ldg(d + i + 2));
-    word = i + 3;
   }
   __device__ __forceinline__ uint32_t peek() const { return hi; }
   __device__ __forceinline__ void skip(uint32_t n) {  // n <= 31
@@ -254,18 +255,20 @@ struct BitWindow {
     lo <<= n;
     avail -= (int)n;
     if (avail <= 32) {  // lo holds avail - 32 <= 0 valid bits: hi is short of 32 - avail bits at its low end
+      const uint32_t next = be(next_raw);
+      next_raw = __ldg(ptr++);
       const uint32_t sh = (uint32_t)(32 - avail);
       hi |= sh ? next >> (32 - sh) : 0u;
       lo = sh ? next << sh : next;
       avail += 32;
-      next = be(__ldg(data + word));
-      word++;
     }
   }
 };
 
 // codes of kJpegLookBits + 1 .. 16 bits: T.81 F.2.2.3 (Figure F.16), one length at a time; returns a first-level entry
-__device__ __noinline__ uint32_t huff_long_code(const JpegHuffTable& t, uint32_t bits, bool ac) {
+__device__ __noinline__ uint32_t huff_long_code(const HuffSmem* sm, uint32_t table, uint32_t bits) {  // table: 0, 1 = DC, 2, 3 = AC
+  const JpegHuffTable& t = table < 2 ? sm->dc[table] : sm->ac[table - 2];
+  const bool ac = table >= 2;
   for (uint32_t l = kJpegLookBits + 1; l <= 16; l++) {
     const int code = (int)(bits >> (32 - l));
     if (code <= t.maxcode[l]) {
@@ -319,8 +322,10 @@ __device__ __forceinline__ uint32_t decode_span(const JpegScan& sc, const HuffSm
     cur.open(sc, blk);
     out = cur.addr(sc, c);
   }
-  const JpegHuffTable* tdc = &sm->dc[(dc_sel >> c) & 1u];
-  const JpegHuffTable* tac = &sm->ac[(ac_sel >> c) & 1u];
+  // shared-memory byte addresses of the four first-level tables (HuffSmem = dc[0], dc[1], ac[0], ac[1])
+  const uint32_t sm0 = (uint32_t)__cvta_generic_to_shared(sm);
+  constexpr uint32_t kTab = (uint32_t)sizeof(JpegHuffTable);
+  uint32_t tdc = sm0 + ((dc_sel >> c) & 1u) * kTab, tac = sm0 + (2u + ((ac_sel >> c) & 1u)) * kTab;
   uint32_t n = 0;
   BitWindow bw;
   bw.open(sc.data, p);
@@ -328,9 +333,10 @@ __device__ __forceinline__ uint32_t decode_span(const JpegScan& sc, const HuffSm
   while (left > 0) {
     const uint32_t bits = bw.peek();
     const bool ac = k != 0;
-    const JpegHuffTable* t = ac ? tac : tdc;
-    uint32_t e = t->fast[bits >> (32 - kJpegLookBits)];
-    if (e == 0) e = huff_long_code(*t, bits, ac);
+    const uint32_t t = ac ? tac : tdc;
+    uint32_t e;
+    asm("ld.shared.u32 %0, [%1];" : "=r"(e) : "r"(t + ((bits >> (32 - kJpegLookBits)) << 2)));  // JpegHuffTable::fast comes first
+    if (e == 0) e = huff_long_code(sm, (t - sm0) / kTab, bits);
     const uint32_t used = e >> 13, s = (e >> 5) & 15u, r = (e >> 9) & 15u;
     const uint32_t kpos = k + r;  // zig-zag index of this coefficient (a DC entry has run 0)
     if (WRITE && s && kpos < 64) out[c_zigzag[kpos]] = (int16_t)extend((bits << (e & 31u)) >> (32 - s), s);
@@ -341,8 +347,8 @@ __device__ __forceinline__ uint32_t decode_span(const JpegScan& sc, const HuffSm
       k = 0;
       n++;
       if (++c == B) c = 0;
-      tdc = &sm->dc[(dc_sel >> c) & 1u];
-      tac = &sm->ac[(ac_sel >> c) & 1u];
+      tdc = sm0 + ((dc_sel >> c) & 1u) * kTab;
+      tac = sm0 + (2u + ((ac_sel >> c) & 1u)) * kTab;
       if (WRITE) {
         cur.next(sc, c);
         if (cur.blk >= blk_end) break;  // the image's (or the restart interval's) last block is complete
@@ -375,7 +381,8 @@ __device__ __forceinline__ void span_of(const JpegScan& sc, uint32_t t, uint64_t
 template <bool FIRST>
 __global__ void __launch_bounds__(kHuffThreads) huff_round_kernel(const __grid_constant__ JpegScan sc, uint32_t* __restrict__ exit_state,
                                                                   uint32_t* __restrict__ count, const uint8_t* __restrict__ cta_dirty_in,
-                                                                  uint8_t* __restrict__ cta_dirty_out, uint32_t* __restrict__ n_changed) {
+                                                                  uint8_t* __restrict__ cta_dirty_out, uint32_t* __restrict__ n_changed,
+                                                                  uint32_t* __restrict__ max_steps) {
   __shared__ HuffSmem sm;
   __shared__ uint32_t exit_s[kHuffThreads];
   __shared__ uint8_t dirty_s[2][kHuffThreads];
@@ -408,7 +415,9 @@ __global__ void __launch_bounds__(kHuffThreads) huff_round_kernel(const __grid_c
   exit_s[i] = cur;
   dirty_s[0][i] = ch ? 1 : 0;
   int ph = 0;
+  uint32_t steps = 0;
   for (;;) {
+    steps++;
     __syncthreads();
     const bool work = live && i > 0 && !hard && dirty_s[ph][i - 1];
     const uint32_t st = work ? exit_s[i - 1] : 0;
@@ -429,6 +438,7 @@ __global__ void __launch_bounds__(kHuffThreads) huff_round_kernel(const __grid_c
     count[t] = cnt;
   }
   const uint32_t last = min((blockIdx.x + 1) * kHuffThreads, sc.n_subseq) - 1;  // the CTA's last live subsequence
+  if (i == 0 && max_steps) atomicMax(max_steps, steps);  // UHDRB200_JPEG_TIMING: the longest in-CTA chain
   if (t == last) {
     const bool moved = FIRST || cur != entry_exit;
     cta_dirty_out[blockIdx.x] = moved ? 1 : 0;
@@ -603,7 +613,8 @@ cudaError_t jpeg_huff_decode(const JpegScan& sc, void* workspace, cudaStream_t s
     for (auto& x : ev) cudaEventCreate(&x);
     cudaEventRecord(ev[0], s);
   }
-  huff_round_kernel<true><<<grid, kHuffThreads, 0, s>>>(sc, exit_a, count, dirty_b, dirty_a, n_changed);
+  uint32_t* step_stat = timing ? n_changed + 62 : nullptr;  // slots 62, 63: longest chain of the first / the later rounds
+  huff_round_kernel<true><<<grid, kHuffThreads, 0, s>>>(sc, exit_a, count, dirty_b, dirty_a, n_changed, step_stat);
   if (timing) cudaEventRecord(ev[1], s);
   int pass = 0;
   uint8_t* din = dirty_a;
@@ -618,7 +629,7 @@ cudaError_t jpeg_huff_decode(const JpegScan& sc, void* workspace, cudaStream_t s
       if (pass % 64 == 0) {  // the 64 counters come round again; the previous pair has been read
         if ((e = cudaMemsetAsync(n_changed, 0, 256, s)) != cudaSuccess) return e;
       }
-      huff_round_kernel<false><<<grid, kHuffThreads, 0, s>>>(sc, exit_a, count, din, dout, n_changed + pass % 64);
+      huff_round_kernel<false><<<grid, kHuffThreads, 0, s>>>(sc, exit_a, count, din, dout, n_changed + pass % 64, timing ? step_stat + 1 : nullptr);
       uint8_t* td = din; din = dout; dout = td;
     }
     if ((e = cudaMemcpyAsync(&last_changed, n_changed + pass % 64, 4, cudaMemcpyDeviceToHost, s)) != cudaSuccess) return e;
@@ -637,8 +648,10 @@ cudaError_t jpeg_huff_decode(const JpegScan& sc, void* workspace, cudaStream_t s
     cudaEventElapsedTime(&a, ev[0], ev[1]);
     cudaEventElapsedTime(&b, ev[1], ev[2]);
     cudaEventElapsedTime(&c, ev[2], ev[3]);
-    fprintf(stderr, "[uhdrb200 jpeg huffman] %u subsequences: first round %.0f us, %d more rounds %.0f us, scan + write pass %.0f us\n", n, a * 1e3, pass,
-            b * 1e3, c * 1e3);
+    uint32_t st2[2] = {0, 0};
+    cudaMemcpy(st2, n_changed + 62, 8, cudaMemcpyDeviceToHost);
+    fprintf(stderr, "[uhdrb200 jpeg huffman] %u subsequences: first round %.0f us (longest chain %u steps), %d more rounds %.0f us (%u steps), scan + write pass %.0f us\n",
+            n, a * 1e3, st2[0], pass, b * 1e3, st2[1], c * 1e3);
     for (auto& x : ev) cudaEventDestroy(x);
   }
   uint32_t max_blocks = 0;
