@@ -523,6 +523,15 @@ def main():
             maps2[i].pixelFormat = abi.PIX_FMT_MONOCHROME
         other["apply_1010102_hlg_map_scale_2"] = timed(lambda: uh.applyGainMapBatch(Bo, sdrs, maps2, md, abi.OUTPUT_HDR_HLG, FLT_MAX, bigs, stream), 1.5 + 0.25 + 4.0)
         del d_map2
+        # map scale factor 8 (an eighth-resolution map): the block-inside-one-cell specialisation of the any-scale kernel
+        d_map8 = d_map[:Bo].view(Bo, MH, MW)[:, ::2, ::2].contiguous()
+        maps8 = (abi.Image * Bo)()
+        for i in range(Bo):
+            maps8[i].data = d_map8[i].data_ptr()
+            maps8[i].width, maps8[i].height, maps8[i].luma_stride = MW // 2, MH // 2, MW // 2
+            maps8[i].pixelFormat = abi.PIX_FMT_MONOCHROME
+        other["apply_1010102_hlg_map_scale_8"] = timed(lambda: uh.applyGainMapBatch(Bo, sdrs, maps8, md, abi.OUTPUT_HDR_HLG, FLT_MAX, bigs, stream), 1.5 + 1.0 / 64 + 4.0)
+        del d_map8
         d_map1 = d_map[:Bo].view(Bo, MH, MW).repeat_interleave(4, 1).repeat_interleave(4, 2).contiguous()  # full-resolution map
         maps1 = (abi.Image * Bo)()
         for i in range(Bo):

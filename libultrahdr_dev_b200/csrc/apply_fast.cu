@@ -4,7 +4,7 @@
 //   apply_q_kernel   map scale factor 4 (kMapDimensionScaleFactor: what every libultrahdr encode writes). The kernel
 //                    the benchmark measures. One thread = one gain-map cell = 4x4 pixels, a lane walks CELLS cells
 //                    downwards with the next cell's loads in flight; ONE look-up per channel in the q domain (below).
-//   apply_qs_kernel  any integer scale factor (specialised for 1 and 2): thread = 4x4 pixel block, general Shepard-IDW
+//   apply_qs_kernel  any integer scale factor (specialised for 1, 2 and the multiples of 4): thread = 4x4 pixel block, general Shepard-IDW
 //                    sampling, the same q-domain evaluation (stage_q_table, quad_row_eval are shared).
 //   apply_fast_kernel  the previous two-table design (srgbInvOetf table + OETF table), kept selectable for A/B runs and
 //                    for linear outputs whose values can leave the normal-half range.
@@ -526,6 +526,8 @@ __global__ void __launch_bounds__(kThreads, 3) apply_qs_kernel(const __grid_cons
         }
       }
     }
+    float E4[4] = {0.f, 0.f, 0.f, 0.f};
+    const float4* w4 = idw;
 #pragma unroll
     for (int qr = 0; qr < 2; qr++) {
       float f[8];
@@ -551,6 +553,32 @@ __global__ void __launch_bounds__(kThreads, 3) apply_qs_kernel(const __grid_cons
               gain = fmaf(e3, w[2], gain);
               gain = fmaf(e4, w[3], gain);
             }
+            f[rr * 4 + i] = ex2_fast(fmaf(gain, p.Aq, p.Bq));
+          }
+      } else if (SCALE == 4) {  // scale factor a multiple of 4 (8, 16, ...; 4 with unaligned map): the 4x4 block lies inside ONE
+                                // map cell, so its four map samples and its weight table are loaded once (at qr == 0)
+        if (qr == 0) {
+          const uint32_t yl = div_s(4u * by);
+          const bool xlast = xl0 + 1 >= mw, ylast = yl + 1 >= mh;
+          const uint8_t* m0 = map + yl * mw;
+          const uint8_t* m1 = ylast ? m0 : m0 + mw;
+          const uint32_t xu = xlast ? xl0 : xl0 + 1;
+          E4[0] = (float)__ldg(m0 + xl0);
+          E4[1] = (float)__ldg(m1 + xl0);
+          E4[2] = (float)__ldg(m0 + xu);
+          E4[3] = (float)__ldg(m1 + xu);
+          const uint32_t t = xlast ? (ylast ? 3u : 1u) : (ylast ? 2u : 0u);  // C / NR / NB / interior, gainmapmath.cpp:710-716
+          w4 = idw + t * ss + (4u * by - yl * sc) * sc + ox0;  // weight row of the block's first pixel row
+        }
+#pragma unroll
+        for (int rr = 0; rr < 2; rr++)
+#pragma unroll
+          for (int i = 0; i < 4; i++) {
+            const float4 w = __ldg(w4 + (2 * qr + rr) * sc + i);
+            float gain = E4[0] * w.x;
+            gain = fmaf(E4[1], w.y, gain);
+            gain = fmaf(E4[2], w.z, gain);
+            gain = fmaf(E4[3], w.w, gain);
             f[rr * 4 + i] = ex2_fast(fmaf(gain, p.Aq, p.Bq));
           }
       } else {
@@ -736,6 +764,7 @@ cudaError_t launch_qs(const ApplyFastParams& p, cudaStream_t s) {
   switch (p.scale_special) {  // 1 / 2 when the map planes are aligned for the specialised loads (capi.cu)
     case 1: return launch_qs<PACK, MASK, 1>(p, s);
     case 2: return launch_qs<PACK, MASK, 2>(p, s);
+    case 4: return launch_qs<PACK, MASK, 4>(p, s);  // any multiple of 4
     default: return launch_qs<PACK, MASK, 0>(p, s);
   }
 }

@@ -934,6 +934,8 @@ int apply_core(int n, const uhdrb200_image* sdr, const uhdrb200_image* map, cons
       for (int i = 0; i < n; i++) al = al && (reinterpret_cast<uintptr_t>(v[i].map_in) % (p.g.map_scale == 1 ? 4 : 2)) == 0;
       if (al) f.scale_special = p.g.map_scale;
       idw_fill(&f.w2[0][0], 2, 1, 1);
+    } else if (any_scale && p.g.map_scale % 4 == 0) {
+      f.scale_special = 4;  // a 4x4 pixel block never straddles a map cell: one set of map samples per block
     }
     // linear outputs: every non-toe channel has Phi > 0.0904, so q >= 0.0904 * f'min must reach the L table's first
     // octave, and q^2.4 must be a normal half with margin (the F16 kernel then skips the subnormal/flush checks)

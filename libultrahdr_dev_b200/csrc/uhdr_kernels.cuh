@@ -139,7 +139,8 @@ struct ApplyFastParams {
   int cells;               // apply_q_kernel: map cells a lane walks per tile (set by launch_q / pick_cells)
   int any_scale;           // 1: apply_qs_kernel (any integer map scale factor, thread = 4x4 pixels) instead of the scale-4 kernels
   uint32_t scale_magic;    // ceil(2^32 / map_scale), 0 for scale 1 (set by launch_apply_fast_impl)
-  int scale_special;       // 1 / 2: compile-time specialisation of apply_qs_kernel (map planes aligned to 4 / 2 bytes), else 0
+  int scale_special;       // 1 / 2: compile-time specialisation of apply_qs_kernel (map planes aligned to 4 / 2 bytes); 4: any
+                           // scale factor that is a multiple of 4 (a 4x4 block lies inside one map cell); else 0
   int pipe;                // 1: apply_pipe_kernel (TMA-fed per-warp pipeline, apply_pipe.cu) instead of apply_q_kernel
   int pdl;                 // 1: launch with programmatic stream serialization (the kernels call griddepcontrol.*)
   // A channel clamped to c = 1 (ultrahdr.cpp:430-431 -> clampPixelFloat) inside a cell whose four map samples are all 255
