@@ -74,9 +74,11 @@ enum {
   UHDRB200_ERROR_INVALID_STRIDE = -10004,
   UHDRB200_ERROR_INVALID_TRANS_FUNC = -10005,
   UHDRB200_ERROR_RESOLUTION_MISMATCH = -10006,
+  UHDRB200_ERROR_INVALID_QUALITY_FACTOR = -10007,
   UHDRB200_ERROR_INVALID_OUTPUT_FORMAT = -10009,
   UHDRB200_ERROR_BAD_METADATA = -10010,
   UHDRB200_ERROR_DECODE = -20002, /* ERROR_ULTRAHDR_DECODE_ERROR: not a JPEG / corrupt header (row N4) */
+  UHDRB200_ERROR_BUFFER_TOO_SMALL = -20004,
   UHDRB200_ERROR_UNSUPPORTED_MAP_SCALE_FACTOR = -20008,
   UHDRB200_ERROR_INSUFFICIENT_RESOURCE = -20009, /* also: no CUDA device / CUDA failure */
   UHDRB200_ERROR_UNSUPPORTED_FEATURE = -30000
@@ -294,6 +296,25 @@ int uhdrb200_jpeg_idct_dev(int n_components, const uhdrb200_jpeg_component* comp
 int uhdrb200_jpeg_get_info(const void* jpeg, size_t bytes, size_t* width, size_t* height, int* pixel_format);
 int uhdrb200_jpeg_decode_host(const void* jpeg, size_t bytes, uhdrb200_image* dest);
 int uhdrb200_jpeg_decode_dev(const void* jpeg, size_t bytes, uhdrb200_image* dest, void* stream);
+
+/* ---- N4 (third slice): the JPEG encode of the SDR image and of the gain map on the device ----
+ * JpegEncoderHelper::compressImage(yBuffer, uvBuffer, width, height, lumaStride, chromaStride, quality, iccBuffer, iccSize)
+ * + getCompressedImagePtr / Size (lib/src/jpegencoderhelper.cpp:35-58, 86-232; called from jpegr.cpp:234-239 for the SDR
+ * image and :1037-1050 for the gain map): raw planar 4:2:0 (Y, then U rows and V rows at chroma_stride * (height / 2), as
+ * uhdrb200_image describes a YUV420 image) or one grey plane (chroma_data == NULL or pixelFormat MONOCHROME) -> a baseline
+ * JFIF file with the settings the reference gives libjpeg: jpeg_set_quality(quality, TRUE), JDCT_ISLOW, 2x2 / 1x1 / 1x1
+ * sampling, the typical Huffman tables of T.81 Annex K, no restart intervals, samples beyond the image inside the last MCUs
+ * zero, the caller's ICC payload as one APP2 segment. Forward DCT, quantisation and Huffman coding run on the GPU
+ * (csrc/jpeg_enc.cu); the host writes the markers and the byte stuffing. The file is BYTE-IDENTICAL to the one
+ * libjpeg-turbo writes from the same samples (tests/test_gpu_jpeg_encode.py).
+ *   _host: image planes in host memory.   _dev: image planes in DEVICE memory on the calling thread's uhdrb200_init device
+ *   (what the fused API-0 kernel and generateGainMap leave there); `stream` orders the encode after the producer.
+ * `out` is host memory of `out_capacity` bytes in both; *out_bytes receives the file size. Synchronous.
+ * UHDRB200_ERROR_BUFFER_TOO_SMALL when the file does not fit (width * height * 3 always suffices for quality <= 100). */
+int uhdrb200_jpeg_encode_host(const uhdrb200_image* image, int quality, const void* icc, size_t icc_bytes, void* out,
+                              size_t out_capacity, size_t* out_bytes);
+int uhdrb200_jpeg_encode_dev(const uhdrb200_image* image, int quality, const void* icc, size_t icc_bytes, void* out,
+                             size_t out_capacity, size_t* out_bytes, void* stream);
 
 #ifdef __cplusplus
 }

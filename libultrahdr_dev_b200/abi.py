@@ -25,7 +25,9 @@ ERROR_INVALID_STRIDE = -10004
 ERROR_INVALID_TRANS_FUNC = -10005
 ERROR_RESOLUTION_MISMATCH = -10006
 ERROR_BAD_METADATA = -10010
+ERROR_INVALID_QUALITY_FACTOR = -10007
 ERROR_DECODE = -20002
+ERROR_BUFFER_TOO_SMALL = -20004
 ERROR_UNSUPPORTED_MAP_SCALE_FACTOR = -20008
 ERROR_INSUFFICIENT_RESOURCE = -20009
 ERROR_UNSUPPORTED_FEATURE = -30000

@@ -58,6 +58,8 @@ SYMBOLS = {
     "uhdrb200_jpeg_get_info": (C.c_int, [C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t), C.POINTER(C.c_size_t), C.POINTER(C.c_int)]),
     "uhdrb200_jpeg_decode_host": (C.c_int, [C.c_void_p, C.c_size_t, P_IMG]),
     "uhdrb200_jpeg_decode_dev": (C.c_int, [C.c_void_p, C.c_size_t, P_IMG, C.c_void_p]),
+    "uhdrb200_jpeg_encode_host": (C.c_int, [P_IMG, C.c_int, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t)]),
+    "uhdrb200_jpeg_encode_dev": (C.c_int, [P_IMG, C.c_int, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t), C.c_void_p]),
     "uhdrb200_copy_yuv420_host": (C.c_int, [P_IMG, P_IMG]),
     "uhdrb200_copy_yuv420_dev": (C.c_int, [P_IMG, P_IMG, C.c_void_p]),
 }

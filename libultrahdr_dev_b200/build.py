@@ -6,7 +6,7 @@ import subprocess
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libuhdr_b200.so")
-SOURCES = ["capi.cu", "generate.cu", "apply.cu", "apply_fast.cu", "apply_pipe.cu", "kat.cu", "jpeg_idct.cu", "jpeg_huff.cu", "tables.cu", "tonemap.cu", "convert_yuv.cu", "sdr_pack.cu"]
+SOURCES = ["capi.cu", "generate.cu", "apply.cu", "apply_fast.cu", "apply_pipe.cu", "kat.cu", "jpeg_idct.cu", "jpeg_huff.cu", "jpeg_enc.cu", "tables.cu", "tonemap.cu", "convert_yuv.cu", "sdr_pack.cu"]
 HEADERS = ["uhdr_math.cuh", "uhdr_kernels.cuh", "uhdr_io.cuh", "uhdr_convert.cuh", "apply_q_common.cuh", os.path.join("..", "..", "include", "uhdr_b200.h"),
            os.path.join("..", "..", "include", "uhdr_b200_test.h")]
 # -fmad=false: plain a*b+c keeps the reference's two roundings (x86-64 baseline has no FMA

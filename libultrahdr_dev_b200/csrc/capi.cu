@@ -1701,6 +1701,7 @@ int jpeg_decode(const void* jpeg, size_t bytes, uhdrb200_image* dest, bool to_de
   }
   if ((st = reserve(c.buf[2], jpeg_huff_workspace_bytes(sc.n_subseq)))) return st;
   if ((st = reserve(c.buf[3], coeff_bytes))) return st;
+  if (s != c.stream) CU(cudaStreamSynchronize(c.stream));  // the uploads ran on the thread's own stream: done before `s` reads them
   CU(cudaMemsetAsync(c.buf[3].p, 0, coeff_bytes, s));
   sc.data = (const uint32_t*)c.buf[0].p;
   sc.tables = (const JpegDeviceTables*)c.buf[1].p;
@@ -1765,6 +1766,115 @@ int jpeg_decode(const void* jpeg, size_t bytes, uhdrb200_image* dest, bool to_de
     dest->chroma_data = (uint8_t*)dest->data + w * ht;
     dest->chroma_stride = cw;
   }
+  return UHDRB200_NO_ERROR;
+}
+
+// ---------------------------------------------------------------- N4: baseline-JPEG encode (jpeg_enc.cu)
+// JpegEncoderHelper::compressImage(yBuffer, uvBuffer, width, height, lumaStride, chromaStride, quality, iccBuffer, iccSize)
+// + getCompressedImagePtr / Size (lib/src/jpegencoderhelper.cpp:35-58, 86-130): uvBuffer == nullptr means greyscale.
+int jpeg_encode(const uhdrb200_image* img, int quality, const void* icc, size_t icc_bytes, void* out, size_t cap, size_t* out_bytes,
+                bool planes_on_device, cudaStream_t user_stream) {
+  if (!img || !img->data || !out || !out_bytes) return UHDRB200_ERROR_BAD_PTR;
+  *out_bytes = 0;
+  const bool grey = img->chroma_data == nullptr || img->pixelFormat == UHDRB200_PIX_FMT_MONOCHROME;
+  const size_t w = img->width, ht = img->height;
+  if (w == 0 || ht == 0 || w > 65500 || ht > 65500 || (!grey && (w < 2 || ht < 2))) return UHDRB200_ERROR_UNSUPPORTED_WIDTH_HEIGHT;  // JPEG_MAX_DIMENSION
+  if (quality < 0 || quality > 100) return UHDRB200_ERROR_INVALID_QUALITY_FACTOR;
+  const size_t ls = img->luma_stride ? img->luma_stride : w, cs = grey ? 0 : (img->chroma_stride ? img->chroma_stride : w / 2);
+  if (ls < w || (!grey && cs < w / 2)) return UHDRB200_ERROR_INVALID_STRIDE;
+  int st = ensure_ctx();
+  if (st) return st;
+  Ctx& c = t_ctx;
+  cudaStream_t s = planes_on_device && user_stream ? user_stream : c.stream;
+  static thread_local JpegEncTables tabs;
+  jpeg_enc_tables(quality, grey, &tabs);
+  // ---- geometry: MCUs of 16 x 16 (4:2:0) or 8 x 8 (grey) samples
+  JpegScan sc;
+  memset(&sc, 0, sizeof sc);
+  sc.n_comp = grey ? 1 : 3;
+  const uint32_t mcu = grey ? 8 : 16;
+  sc.mcus_x = (uint32_t)((w + mcu - 1) / mcu);
+  sc.mcus_y = (uint32_t)((ht + mcu - 1) / mcu);
+  int nb = 0;
+  for (int ci = 0; ci < sc.n_comp; ci++) {
+    const int hv = (!grey && ci == 0) ? 2 : 1;
+    sc.comp_h[ci] = sc.comp_v[ci] = (uint8_t)hv;
+    for (int y = 0; y < hv; y++)
+      for (int x = 0; x < hv; x++, nb++) {
+        sc.blk_comp[nb] = (uint8_t)ci;
+        sc.blk_dx[nb] = (uint8_t)x;
+        sc.blk_dy[nb] = (uint8_t)y;
+      }
+    sc.comp_blocks_w[ci] = sc.mcus_x * hv;
+    sc.comp_blocks_h[ci] = sc.mcus_y * hv;
+  }
+  sc.blocks_per_mcu = nb;
+  sc.total_blocks = sc.mcus_x * sc.mcus_y * (uint32_t)nb;
+  size_t coeff_off[3] = {0, 0, 0}, coeff_bytes = 0;
+  for (int ci = 0; ci < sc.n_comp; ci++) {
+    coeff_off[ci] = coeff_bytes;
+    coeff_bytes += (size_t)sc.comp_blocks_w[ci] * sc.comp_blocks_h[ci] * 64 * sizeof(int16_t);
+  }
+  // ---- planes: the caller's device memory, or staged copies of the host planes (U rows then V rows at chroma_stride * (h / 2))
+  const uint8_t* d_y = (const uint8_t*)img->data;
+  const uint8_t* d_u = (const uint8_t*)img->chroma_data;
+  const size_t cw = w / 2, chh = ht / 2;
+  if (!planes_on_device) {
+    if ((st = upload(c.buf[0], img->data, ls * (ht - 1) + w, s))) return st;
+    d_y = (const uint8_t*)c.buf[0].p;
+    if (!grey) {
+      if ((st = upload(c.buf[1], img->chroma_data, cs * (chh * 2 - 1) + cw, s))) return st;
+      d_u = (const uint8_t*)c.buf[1].p;
+    }
+  }
+  if ((st = upload(c.buf[5], &tabs, sizeof tabs, s))) return st;
+  if (s != c.stream) CU(cudaStreamSynchronize(c.stream));  // the uploads ran on the thread's own stream: done before `s` reads them
+  const JpegEncTables* d_tabs = (const JpegEncTables*)c.buf[5].p;
+  if ((st = reserve(c.buf[3], coeff_bytes))) return st;
+  if ((st = reserve(c.buf[2], jpeg_enc_workspace_bytes(sc.total_blocks)))) return st;
+  JpegEncParams ep;
+  memset(&ep, 0, sizeof ep);
+  ep.n_components = sc.n_comp;
+  for (int ci = 0; ci < sc.n_comp; ci++) {
+    sc.coeffs[ci] = (int16_t*)((uint8_t*)c.buf[3].p + coeff_off[ci]);
+    JpegEncComponent& e = ep.comp[ci];
+    e.plane = ci == 0 ? d_y : d_u + (size_t)(ci - 1) * cs * chh;  // compressYuv, jpegencoderhelper.cpp:134-138
+    e.width = ci == 0 ? w : cw;
+    e.height = ci == 0 ? ht : chh;
+    e.stride = ci == 0 ? ls : cs;
+    e.blocks_w = sc.comp_blocks_w[ci];
+    e.blocks_h = sc.comp_blocks_h[ci];
+    e.quant = d_tabs->quant[ci == 0 ? 0 : 1];
+    e.coeffs = sc.coeffs[ci];
+  }
+  cudaError_t e = launch_jpeg_fdct_impl(ep, s);
+  if (e != cudaSuccess) return fail(e, "jpeg fdct kernel launch");
+  uint32_t* d_total = (uint32_t*)((uint8_t*)c.buf[2].p + jpeg_enc_workspace_bytes(sc.total_blocks) - 64);
+  uint32_t* d_offsets = nullptr;
+  if ((e = jpeg_huff_encode(sc, d_tabs, c.buf[2].p, d_total, s, &d_offsets)) != cudaSuccess) return fail(e, "jpeg huffman sizing");
+  uint32_t total_bits = 0;
+  CU(cudaMemcpyAsync(&total_bits, d_total, 4, cudaMemcpyDeviceToHost, s));
+  CU(cudaStreamSynchronize(s));
+  const size_t nbytes = ((size_t)total_bits + 7) / 8, nwords = (nbytes + 3) / 4 + 1;
+  if ((st = reserve(c.buf[4], nwords * 4))) return st;
+  CU(cudaMemsetAsync(c.buf[4].p, 0, nwords * 4, s));
+  if ((e = jpeg_huff_emit(sc, d_tabs, d_offsets, (uint32_t*)c.buf[4].p, s)) != cudaSuccess) return fail(e, "jpeg huffman emit");
+  g_launches += 6;
+  static thread_local std::vector<uint8_t> raw;
+  raw.resize(nbytes + 8);
+  if (s != c.stream) CU(cudaStreamSynchronize(s));  // the copy below runs on the thread's own stream
+  if ((st = copy_d2h(c, raw.data(), c.buf[4].p, nbytes))) return st;
+  CU(join_stream(c));
+  if (total_bits & 7u) raw[nbytes - 1] |= (uint8_t)(0xFFu >> (total_bits & 7u));  // flush_bits: the last byte is filled with ones
+  uint8_t* o = (uint8_t*)out;
+  size_t n = jpeg_write_headers(o, cap, (int)w, (int)ht, grey, tabs, icc, icc_bytes);
+  if (n == 0) return icc_bytes > 65533 ? UHDRB200_ERROR_UNSUPPORTED_FEATURE : UHDRB200_ERROR_BUFFER_TOO_SMALL;
+  const size_t body = jpeg_stuff(raw.data(), nbytes, o + n, cap - n);
+  if ((body == 0 && nbytes != 0) || n + body + 2 > cap) return UHDRB200_ERROR_BUFFER_TOO_SMALL;
+  n += body;
+  o[n++] = 0xFF;
+  o[n++] = 0xD9;
+  *out_bytes = n;
   return UHDRB200_NO_ERROR;
 }
 
@@ -1921,6 +2031,14 @@ int uhdrb200_jpeg_get_info(const void* jpeg, size_t bytes, size_t* width, size_t
 int uhdrb200_jpeg_decode_host(const void* jpeg, size_t bytes, uhdrb200_image* dest) { return jpeg_decode(jpeg, bytes, dest, false, nullptr); }
 int uhdrb200_jpeg_decode_dev(const void* jpeg, size_t bytes, uhdrb200_image* dest, void* stream) {
   return jpeg_decode(jpeg, bytes, dest, true, (cudaStream_t)stream);
+}
+int uhdrb200_jpeg_encode_host(const uhdrb200_image* image, int quality, const void* icc, size_t icc_bytes, void* out, size_t out_capacity,
+                              size_t* out_bytes) {
+  return jpeg_encode(image, quality, icc, icc_bytes, out, out_capacity, out_bytes, false, nullptr);
+}
+int uhdrb200_jpeg_encode_dev(const uhdrb200_image* image, int quality, const void* icc, size_t icc_bytes, void* out, size_t out_capacity,
+                             size_t* out_bytes, void* stream) {
+  return jpeg_encode(image, quality, icc, icc_bytes, out, out_capacity, out_bytes, true, (cudaStream_t)stream);
 }
 int uhdrb200_copy_yuv420_host(const uhdrb200_image* src, uhdrb200_image* dest) { return copy_yuv420_host(src, dest); }
 int uhdrb200_copy_yuv420_dev(const uhdrb200_image* src, uhdrb200_image* dest, void* stream) {

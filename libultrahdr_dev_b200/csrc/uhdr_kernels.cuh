@@ -276,6 +276,36 @@ cudaError_t launch_apply_pipe_impl(const ApplyFastParams& p, int n, cudaStream_t
 // host: fills the double-precision-built tables (tables.cu)
 void build_apply_tables(float2* s, float2* s_hi, float2* o_hlg, float2* o_pq, float2* p_hlg, float2* p_pq, float2* l_pow, float* e255);
 cudaError_t launch_tonemap_impl(const ToneMapParams& p, int n, bool vec, cudaStream_t s);
+// row N4 (jpeg_enc.cu): baseline JPEG encode of raw 4:2:0 / grey planes (JpegEncoderHelper::compressImage)
+struct JpegEncHuff {       // EHUFCO / EHUFSI of T.81 Annex C for one table
+  uint16_t code[256];
+  uint8_t len[256];
+};
+struct JpegEncTables {     // one upload per encode
+  uint16_t quant[2][64];   // natural order (the FDCT kernel), [0] luma, [1] chroma
+  uint8_t quant_zz[2][64]; // zig-zag order (the DQT segments)
+  JpegEncHuff dc[2], ac[2];
+};
+struct JpegEncComponent {
+  const uint8_t* plane;    // device
+  size_t width, height, stride;  // visible samples; beyond them the encoder sees zero samples
+  uint32_t blocks_w, blocks_h;   // whole MCUs
+  const uint16_t* quant;   // device, natural order
+  int16_t* coeffs;         // device: blocks_h x blocks_w records of 64 quantised coefficients in ZIG-ZAG order
+};
+struct JpegEncParams {
+  int n_components;
+  JpegEncComponent comp[3];
+};
+void jpeg_enc_tables(int quality, bool grey, JpegEncTables* t);
+size_t jpeg_write_headers(uint8_t* out, size_t cap, int width, int height, bool grey, const JpegEncTables& t, const void* icc, size_t icc_bytes);
+size_t jpeg_stuff(const uint8_t* src, size_t n, uint8_t* dst, size_t cap);
+cudaError_t launch_jpeg_fdct_impl(const JpegEncParams& p, cudaStream_t s);
+size_t jpeg_enc_workspace_bytes(uint32_t total_blocks);
+cudaError_t jpeg_huff_encode(const JpegScan& sc, const JpegEncTables* tables_dev, void* workspace, uint32_t* total_bits_dev, cudaStream_t s,
+                             uint32_t** offsets_out);
+cudaError_t jpeg_huff_emit(const JpegScan& sc, const JpegEncTables* tables_dev, const uint32_t* offsets, uint32_t* out_words, cudaStream_t s);
+
 // test hook (include/uhdr_b200_test.h): out[i] = fn(in[i]) with the device functions of uhdr_math.cuh / apply_q_common.cuh
 cudaError_t launch_kat_impl(int fn, const float* in, float* out, size_t n, const ApplyTables& tab, const GainCode& gc, cudaStream_t s);
 bool sdr_pack_vec_ok(const Geometry& g, const Planes& pl);
