@@ -396,7 +396,7 @@ def main():
 
     # ---- the other kernels of the path (not part of `value`): per-kernel roofline on the same batch, rank 0 only
     other = {}
-    jpeg_stage = None
+    jpeg_stage = jpeg_enc_stage = None
     if rank == 0 and not a.no_other_stages:
         Bo = min(B, 64)
         d_tm = torch.zeros((Bo, sdr_len), dtype=torch.uint8, device=dev)
@@ -585,7 +585,7 @@ def main():
 
             from PIL import Image
 
-            jp = []
+            jp, noisy = [], []
             for i in range(4):
                 hp = d_sdr[i % K].cpu().numpy()
                 yy = hp[: W * H].reshape(H, W)
@@ -593,6 +593,7 @@ def main():
                 vv = hp[W * H * 5 // 4:].reshape(H // 2, W // 2).repeat(2, 0).repeat(2, 1)
                 rr = np.random.Generator(np.random.PCG64(i))
                 yy = np.clip(yy.astype(np.int16) + rr.integers(-6, 7, yy.shape), 0, 255).astype(np.uint8)
+                noisy.append(np.concatenate([yy.ravel(), hp[W * H:]]))
                 bio = io.BytesIO()
                 Image.fromarray(np.stack([yy, uu, vv], -1), "YCbCr").save(bio, "JPEG", quality=90, subsampling=2)
                 jp.append(bio.getvalue())
@@ -629,6 +630,42 @@ def main():
                           "libjpeg_turbo_1_core_mpix_s": PIX / cpu_ms / 1e3, "libjpeg_turbo_1_core_ms": cpu_ms,
                           "content": "natural SDR planes + noise, quality 90, 4:2:0, through Pillow / libjpeg-turbo's encoder",
                           "bound": "latency (sequential synchronisation chains of the parallel Huffman decode), not HBM"}
+            # the encode direction: the same planes, resident in device memory (where API-0 leaves the SDR image), -> JFIF
+            # bytes in host memory at quality 90; forward DCT, quantisation and Huffman coding on the device
+            d_noisy = torch.stack([torch.from_numpy(x) for x in noisy]).to(dev)
+            e_src = (abi.Image * 4)()
+            for k in range(4):
+                eb = d_noisy[k].data_ptr()
+                e_src[k].data, e_src[k].chroma_data = eb, eb + W * H
+                e_src[k].width, e_src[k].height, e_src[k].luma_stride, e_src[k].chroma_stride, e_src[k].pixelFormat = W, H, W, W // 2, abi.PIX_FMT_YUV420
+
+            def encode_loop(tid, iters, out):
+                torch.cuda.set_device(dev)
+                ob = np.zeros(W * H * 3, np.uint8)
+                on = C.c_size_t(0)
+                for k in range(2):
+                    assert lib.uhdrb200_jpeg_encode_dev(C.byref(e_src[k % 4]), 90, None, 0, ob.ctypes.data, ob.size, C.byref(on), None) == 0, lib.uhdrb200_last_error()
+                t0 = time.perf_counter()
+                for k in range(iters):
+                    lib.uhdrb200_jpeg_encode_dev(C.byref(e_src[(k + tid) % 4]), 90, None, 0, ob.ctypes.data, ob.size, C.byref(on), None)
+                out[tid] = ((time.perf_counter() - t0) / iters, on.value)
+
+            enc1, enc4 = {}, {}
+            encode_loop(0, 12, enc1)
+            ths = [threading.Thread(target=encode_loop, args=(t, 12, enc4)) for t in range(4)]
+            for t in ths:
+                t.start()
+            for t in ths:
+                t.join()
+            t0 = time.perf_counter()
+            for k in range(2):
+                bio = io.BytesIO()
+                Image.open(io.BytesIO(jp[k])).save(bio, "JPEG", quality=90, subsampling=2)
+            enc_cpu_ms = (time.perf_counter() - t0) / 2 * 1e3 - cpu_ms  # decode + encode minus the decode measured above
+            jpeg_enc_stage = {"mpix_s": PIX / enc1[0][0] / 1e6, "ms_per_image": enc1[0][0] * 1e3, "images_per_launch": 1,
+                              "mpix_s_4_host_threads": 4 * PIX / (sum(v[0] for v in enc4.values()) / 4) / 1e6, "jpeg_bytes": int(enc1[0][1]),
+                              "libjpeg_turbo_1_core_mpix_s": PIX / max(enc_cpu_ms, 1e-3) / 1e3, "libjpeg_turbo_1_core_ms": enc_cpu_ms,
+                              "parity": "file byte-identical to libjpeg-turbo's (tests/test_gpu_jpeg_encode.py)"}
         except ImportError:
             pass
         # ---- real image content: the reference's own fixtures (tests/data, staged by build() into tests/_ref_data):
@@ -846,7 +883,8 @@ def main():
                 "api": "uhdrb200_generate_gainmap_host_into + uhdrb200_apply_gainmap_host (synchronous, reference-style); " +
                        ("pageable host planes, as an unmodified libultrahdr caller passes them" if a.e2e_host_memory == "pageable" else "page-locked host planes")},
         "other_stages": dict({k: dict(v, frac_of_hbm_peak=v["achieved_gbs"] / peak) for k, v in other.items()},
-                             **({"jpeg_decode_4k_q90_to_device_planes": jpeg_stage} if jpeg_stage else {})),
+                             **({"jpeg_decode_4k_q90_to_device_planes": jpeg_stage} if jpeg_stage else {}),
+                             **({"jpeg_encode_4k_q90_from_device_planes": jpeg_enc_stage} if jpeg_enc_stage else {})),
         "gpu_launches": int(launches),
         "clocks": clk,
     }

@@ -52,3 +52,30 @@ for q, extra in ((75, {}), (90, {}), (95, {}), (100, {}), (90, {"restart_marker_
                 "mpix_s": round(W * H / dt / 1e6), "parse_only_ms": round(dt_parse * 1e3, 3), "libjpeg_turbo_pillow_1core_ms": round(dt_cpu * 1e3, 2),
                 "libjpeg_turbo_mpix_s": round(W * H / dt_cpu / 1e6)})
     print(json.dumps(out[-1]), flush=True)
+
+# ---- encode: 4K planes already in device memory -> JFIF bytes in host memory, against libjpeg-turbo on one core
+planes = []
+for i in range(4):
+    sdr, _ = synth.natural_pair(W, H, i)
+    rng = np.random.Generator(np.random.PCG64(i))
+    sdr = sdr.copy(); sdr[: W * H] = np.clip(sdr[: W * H].astype(np.int16) + rng.integers(-6, 7, W * H), 0, 255).astype(np.uint8)
+    planes.append(sdr)
+d_pl = torch.stack([torch.from_numpy(p) for p in planes]).to(dev)
+src = [abi.Image() for _ in range(4)]
+for k in range(4):
+    b = d_pl[k].data_ptr()
+    src[k].data, src[k].chroma_data = b, b + W * H
+    src[k].width, src[k].height, src[k].luma_stride, src[k].chroma_stride, src[k].pixelFormat = W, H, W, W // 2, abi.PIX_FMT_YUV420
+outb = np.zeros(W * H * 3, np.uint8); nb = C.c_size_t(0)
+for q in (75, 90, 95, 100):
+    for k in range(4): assert lib.uhdrb200_jpeg_encode_dev(C.byref(src[k]), q, None, 0, outb.ctypes.data, outb.size, C.byref(nb), st) == 0, lib.uhdrb200_last_error()
+    iters = 16
+    t0 = time.perf_counter()
+    for k in range(iters): lib.uhdrb200_jpeg_encode_dev(C.byref(src[k % 4]), q, None, 0, outb.ctypes.data, outb.size, C.byref(nb), st)
+    dt = (time.perf_counter() - t0) / iters
+    t0 = time.perf_counter()
+    for k in range(2):
+        bio = io.BytesIO(); imgs[k].save(bio, "JPEG", quality=q, subsampling=2)
+    dt_cpu = (time.perf_counter() - t0) / 2
+    print(json.dumps({"encode_quality": q, "jpeg_bytes": int(nb.value), "encode_dev_ms": round(dt * 1e3, 3), "mpix_s": round(W * H / dt / 1e6),
+                      "libjpeg_turbo_pillow_1core_ms": round(dt_cpu * 1e3, 2), "libjpeg_turbo_mpix_s": round(W * H / dt_cpu / 1e6)}), flush=True)
