@@ -396,7 +396,7 @@ def main():
 
     # ---- the other kernels of the path (not part of `value`): per-kernel roofline on the same batch, rank 0 only
     other = {}
-    jpeg_stage = jpeg_enc_stage = None
+    jpeg_stage = jpeg_enc_stage = jpeg_flow_stage = None
     if rank == 0 and not a.no_other_stages:
         Bo = min(B, 64)
         d_tm = torch.zeros((Bo, sdr_len), dtype=torch.uint8, device=dev)
@@ -602,13 +602,15 @@ def main():
             def decode_loop(tid, iters, out):
                 torch.cuda.set_device(dev)
                 d_pl = torch.zeros(W * H * 3 // 2, dtype=torch.uint8, device=dev)
+                ts = torch.cuda.Stream(device=dev).cuda_stream  # one stream per calling thread
+                torch.cuda.synchronize()
                 im = abi.Image()
                 im.data = d_pl.data_ptr()
                 for k in range(2):
-                    assert lib.uhdrb200_jpeg_decode_dev(jbufs[k % 4], len(jp[k % 4]), C.byref(im), None) == 0, lib.uhdrb200_last_error()
+                    assert lib.uhdrb200_jpeg_decode_dev(jbufs[k % 4], len(jp[k % 4]), C.byref(im), ts) == 0, lib.uhdrb200_last_error()
                 t0 = time.perf_counter()
                 for k in range(iters):
-                    lib.uhdrb200_jpeg_decode_dev(jbufs[(k + tid) % 4], len(jp[(k + tid) % 4]), C.byref(im), None)
+                    lib.uhdrb200_jpeg_decode_dev(jbufs[(k + tid) % 4], len(jp[(k + tid) % 4]), C.byref(im), ts)
                 out[tid] = (time.perf_counter() - t0) / iters
 
             res1 = {}
@@ -643,11 +645,13 @@ def main():
                 torch.cuda.set_device(dev)
                 ob = np.zeros(W * H * 3, np.uint8)
                 on = C.c_size_t(0)
+                ts = torch.cuda.Stream(device=dev).cuda_stream  # one stream per calling thread
+                torch.cuda.synchronize()
                 for k in range(2):
-                    assert lib.uhdrb200_jpeg_encode_dev(C.byref(e_src[k % 4]), 90, None, 0, ob.ctypes.data, ob.size, C.byref(on), None) == 0, lib.uhdrb200_last_error()
+                    assert lib.uhdrb200_jpeg_encode_dev(C.byref(e_src[k % 4]), 90, None, 0, ob.ctypes.data, ob.size, C.byref(on), ts) == 0, lib.uhdrb200_last_error()
                 t0 = time.perf_counter()
                 for k in range(iters):
-                    lib.uhdrb200_jpeg_encode_dev(C.byref(e_src[(k + tid) % 4]), 90, None, 0, ob.ctypes.data, ob.size, C.byref(on), None)
+                    lib.uhdrb200_jpeg_encode_dev(C.byref(e_src[(k + tid) % 4]), 90, None, 0, ob.ctypes.data, ob.size, C.byref(on), ts)
                 out[tid] = ((time.perf_counter() - t0) / iters, on.value)
 
             enc1, enc4 = {}, {}
@@ -666,6 +670,62 @@ def main():
                               "mpix_s_4_host_threads": 4 * PIX / (sum(v[0] for v in enc4.values()) / 4) / 1e6, "jpeg_bytes": int(enc1[0][1]),
                               "libjpeg_turbo_1_core_mpix_s": PIX / max(enc_cpu_ms, 1e-3) / 1e3, "libjpeg_turbo_1_core_ms": enc_cpu_ms,
                               "parity": "file byte-identical to libjpeg-turbo's (tests/test_gpu_jpeg_encode.py)"}
+            # the pixel side of encodeJPEGR API-0 and of decodeJPEGR (jpegr.cpp:167-261, 693-801) per 4K image and host thread,
+            # wall clock: P010 in PAGEABLE host memory -> [upload, toneMap + generateGainMap + convertYuv in one kernel, JPEG
+            # encode of the SDR image (quality 95) and of the gain map (85)] -> two byte strings; then those bytes -> [two
+            # decodes, applyGainMap -> RGBA1010102 HLG, copy to pageable host memory]
+            h_hdr = [d_hdr[i % K].cpu().numpy().copy() for i in range(2)]
+            f_hdr = torch.empty(hdr_len, dtype=torch.int16, device=dev)
+            f_sdr = torch.zeros(sdr_len, dtype=torch.uint8, device=dev)
+            f_map = torch.zeros(MW * MH, dtype=torch.uint8, device=dev)
+            f_out = torch.zeros(PIX, dtype=torch.int32, device=dev)
+            h_out = np.zeros(PIX, np.int32)
+            fh, fs, fm, fo = abi.Image(), abi.Image(), abi.Image(), abi.Image()
+            C.memmove(C.byref(fh), C.byref(hdrs[0]), C.sizeof(abi.Image))
+            fh.data, fh.chroma_data = f_hdr.data_ptr(), f_hdr.data_ptr() + 2 * W * H
+            C.memmove(C.byref(fs), C.byref(sdrs[0]), C.sizeof(abi.Image))
+            fs.data, fs.chroma_data, fs.colorGamut = f_sdr.data_ptr(), f_sdr.data_ptr() + W * H, abi.COLORGAMUT_UNSPECIFIED
+            fm.data, fo.data = f_map.data_ptr(), f_out.data_ptr()
+            fmd = abi.Metadata()
+            ob1, ob2 = np.zeros(W * H * 3, np.uint8), np.zeros(W * H, np.uint8)
+            n1, n2 = C.c_size_t(0), C.c_size_t(0)
+
+            def encode_flow(i):
+                f_hdr.copy_(torch.from_numpy(h_hdr[i % 2]), non_blocking=True)
+                assert uh.toneMapGenerateGainMapDevice(fh, abi.TF_HLG, fs, fmd, fm, stream, True) == 0
+                assert lib.uhdrb200_jpeg_encode_dev(C.byref(fs), 95, None, 0, ob1.ctypes.data, ob1.size, C.byref(n1), stream) == 0
+                assert lib.uhdrb200_jpeg_encode_dev(C.byref(fm), 85, None, 0, ob2.ctypes.data, ob2.size, C.byref(n2), stream) == 0
+
+            def decode_flow(b1, b2, l1, l2):
+                ds, dm = abi.Image(), abi.Image()
+                ds.data, dm.data = f_sdr.data_ptr(), f_map.data_ptr()
+                assert lib.uhdrb200_jpeg_decode_dev(b1, l1, C.byref(ds), stream) == 0
+                assert lib.uhdrb200_jpeg_decode_dev(b2, l2, C.byref(dm), stream) == 0
+                ds.colorGamut = abi.COLORGAMUT_BT2100
+                assert lib.uhdrb200_apply_gainmap_dev(C.byref(ds), C.byref(dm), C.byref(fmd), abi.OUTPUT_HDR_HLG, FLT_MAX, C.byref(fo), stream) == 0
+                torch.from_numpy(h_out).copy_(f_out)
+
+            for i in range(2):
+                encode_flow(i)
+            t0 = time.perf_counter()
+            for i in range(8):
+                encode_flow(i)
+            enc_flow = (time.perf_counter() - t0) / 8
+            b1 = (C.c_ubyte * n1.value).from_buffer_copy(ob1[: n1.value].tobytes())
+            b2 = (C.c_ubyte * n2.value).from_buffer_copy(ob2[: n2.value].tobytes())
+            for i in range(2):
+                decode_flow(b1, b2, n1.value, n2.value)
+            t0 = time.perf_counter()
+            for i in range(8):
+                decode_flow(b1, b2, n1.value, n2.value)
+            dec_flow = (time.perf_counter() - t0) / 8
+            jpeg_flow_stage = {"encode_side_ms_per_image": enc_flow * 1e3, "encode_side_mpix_s": PIX / enc_flow / 1e6,
+                               "decode_side_ms_per_image": dec_flow * 1e3, "decode_side_mpix_s": PIX / dec_flow / 1e6,
+                               "mpix_s": PIX / (enc_flow + dec_flow) / 1e6, "images_per_launch": 1, "sdr_jpeg_bytes": int(n1.value),
+                               "map_jpeg_bytes": int(n2.value), "host_threads": 1,
+                               "what": "P010 (pageable host) -> fused toneMap + generateGainMap + convertYuv -> 2 JPEG encodes -> bytes; "
+                                       "bytes -> 2 JPEG decodes -> applyGainMap HLG -> pageable host; nothing but P010, JPEG bytes and the "
+                                       "final pixels crosses PCIe"}
         except ImportError:
             pass
         # ---- real image content: the reference's own fixtures (tests/data, staged by build() into tests/_ref_data):
@@ -884,7 +944,8 @@ def main():
                        ("pageable host planes, as an unmodified libultrahdr caller passes them" if a.e2e_host_memory == "pageable" else "page-locked host planes")},
         "other_stages": dict({k: dict(v, frac_of_hbm_peak=v["achieved_gbs"] / peak) for k, v in other.items()},
                              **({"jpeg_decode_4k_q90_to_device_planes": jpeg_stage} if jpeg_stage else {}),
-                             **({"jpeg_encode_4k_q90_from_device_planes": jpeg_enc_stage} if jpeg_enc_stage else {})),
+                             **({"jpeg_encode_4k_q90_from_device_planes": jpeg_enc_stage} if jpeg_enc_stage else {}),
+                             **({"jpegr_pixel_flow_4k_one_host_thread": jpeg_flow_stage} if jpeg_flow_stage else {})),
         "gpu_launches": int(launches),
         "clocks": clk,
     }

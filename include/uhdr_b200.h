@@ -291,7 +291,7 @@ int uhdrb200_jpeg_idct_dev(int n_components, const uhdrb200_jpeg_component* comp
  *                              width * height) bytes; width, height, strides, chroma_data and pixelFormat are filled in.
  *   uhdrb200_jpeg_decode_dev   `jpeg` is host memory, dest->data DEVICE memory of the same size on the calling thread's
  *                              uhdrb200_init device: the planes stay on the GPU for uhdrb200_apply_gainmap_dev. Runs on
- *                              `stream` (0: the thread's own) and returns when the planes are complete.
+ *                              `stream` (0: the default stream) and returns when the planes are complete.
  * Both are synchronous and use scratch buffers owned by the calling thread. */
 int uhdrb200_jpeg_get_info(const void* jpeg, size_t bytes, size_t* width, size_t* height, int* pixel_format);
 int uhdrb200_jpeg_decode_host(const void* jpeg, size_t bytes, uhdrb200_image* dest);

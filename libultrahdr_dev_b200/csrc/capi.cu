@@ -1614,7 +1614,7 @@ int jpeg_decode(const void* jpeg, size_t bytes, uhdrb200_image* dest, bool to_de
   if ((st = jpeg_check_layout(h))) return st;
   if ((st = ensure_ctx())) return st;
   Ctx& c = t_ctx;
-  cudaStream_t s = to_device && user_stream ? user_stream : c.stream;
+  cudaStream_t s = to_device ? user_stream : c.stream;  // _dev: the caller's stream (0 = the default stream), ordered after its producers
   tm.s = s;
   tm.mark("parse");
   const size_t w = (size_t)h.width, ht = (size_t)h.height;
@@ -1785,7 +1785,7 @@ int jpeg_encode(const uhdrb200_image* img, int quality, const void* icc, size_t 
   int st = ensure_ctx();
   if (st) return st;
   Ctx& c = t_ctx;
-  cudaStream_t s = planes_on_device && user_stream ? user_stream : c.stream;
+  cudaStream_t s = planes_on_device ? user_stream : c.stream;  // _dev: the caller's stream (0 = the default stream), ordered after the producer of the planes
   static thread_local JpegEncTables tabs;
   jpeg_enc_tables(quality, grey, &tabs);
   // ---- geometry: MCUs of 16 x 16 (4:2:0) or 8 x 8 (grey) samples
