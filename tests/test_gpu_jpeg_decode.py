@@ -257,3 +257,54 @@ def test_decode_dev_feeds_apply(uh, orc):
     _, want, _ = orc.apply_gainmap(abi.host_yuv420(sdr_b, w, h, abi.COLORGAMUT_BT709), abi.host_map(ref_m[0], w // 4, h // 4), md,
                                    abi.OUTPUT_HDR_HLG, FLT_MAX)
     parity.compare_output(abi.OUTPUT_HDR_HLG, got, want, w * h, "decode_dev -> apply", min_exact=0.995)
+
+
+def test_four_host_threads_decode_and_encode_concurrently(uh):
+    """Every calling thread owns its context, scratch buffers and stream: four threads decoding different images (and
+    encoding them again) at the same time get the results a single thread gets."""
+    pytest.importorskip("PIL.Image")
+    import threading
+
+    import torch as t
+
+    lib = uh.lib
+    jobs = []
+    for k in range(4):
+        w, h = 640 + 64 * k, 368 + 16 * k
+        data = encode(scene(w, h, 50 + k), quality=80 + 5 * k, subsampling=2)
+        jobs.append((w, h, data, np.concatenate([p.ravel() for p in libjpeg_planes(data)])))
+    errors = []
+
+    def worker(k):
+        try:
+            t.cuda.set_device(0)
+            w, h, data, want = jobs[k]
+            stream = t.cuda.Stream()
+            d = t.zeros(w * h * 3 // 2, dtype=t.uint8, device="cuda")
+            buf = (C.c_ubyte * len(data)).from_buffer_copy(data)
+            out = np.zeros(w * h * 3, np.uint8)
+            n = C.c_size_t(0)
+            for _ in range(6):
+                img = abi.Image()
+                img.data = d.data_ptr()
+                d.zero_()
+                t.cuda.current_stream().synchronize()
+                assert lib.uhdrb200_jpeg_decode_dev(buf, len(data), C.byref(img), stream.cuda_stream) == 0, lib.uhdrb200_last_error()
+                assert np.array_equal(d.cpu().numpy(), want)
+                assert lib.uhdrb200_jpeg_encode_dev(C.byref(img), 77, None, 0, out.ctypes.data, out.size, C.byref(n), stream.cuda_stream) == 0
+                again = bytes(out[: n.value])
+                assert again[:2] == b"\xff\xd8" and again[-2:] == b"\xff\xd9"
+                if k == 0:  # whole MCUs (640 x 368): the re-encoded file must be libjpeg-turbo's for the decoded planes
+                    from test_gpu_jpeg_encode import pillow_encode
+
+                    pl = [want[: w * h].reshape(h, w), want[w * h: w * h * 5 // 4].reshape(h // 2, w // 2), want[w * h * 5 // 4:].reshape(h // 2, w // 2)]
+                    assert again == pillow_encode(pl, 77)
+        except Exception as e:  # noqa: BLE001
+            errors.append((k, repr(e)))
+
+    ths = [threading.Thread(target=worker, args=(k,)) for k in range(4)]
+    for th in ths:
+        th.start()
+    for th in ths:
+        th.join()
+    assert not errors, errors
