@@ -21,6 +21,8 @@
 #include <cstdlib>
 #include <cstring>
 
+#include <emmintrin.h>
+
 #include "uhdr_io.cuh"
 #include "uhdr_kernels.cuh"
 
@@ -208,14 +210,26 @@ size_t jpeg_write_headers(uint8_t* out, size_t cap, int width, int height, bool 
 // copies the entropy-coded bytes inserting the stuffed zero after every FF (F.1.2.3); returns bytes written or 0
 size_t jpeg_stuff(const uint8_t* src, size_t n, uint8_t* dst, size_t cap) {
   size_t o = 0, i = 0;
+  const __m128i ff = _mm_set1_epi8((char)0xFF);
   while (i < n) {
-    const uint8_t* f = (const uint8_t*)memchr(src + i, 0xFF, n - i);
-    const size_t run = f ? (size_t)(f - (src + i)) + 1 : n - i;  // up to and including the FF
-    if (o + run + 1 > cap) return 0;
-    memcpy(dst + o, src + i, run);
-    o += run;
-    i += run;
-    if (f) dst[o++] = 0x00;
+    while (i + 16 <= n && o + 17 <= cap) {  // 16 bytes at a time while no FF is among them
+      const __m128i v = _mm_loadu_si128(reinterpret_cast<const __m128i*>(src + i));
+      const int mask = _mm_movemask_epi8(_mm_cmpeq_epi8(v, ff));
+      _mm_storeu_si128(reinterpret_cast<__m128i*>(dst + o), v);
+      if (mask) {  // keep the bytes in front of the first FF; the FF itself is handled below
+        const int k = __builtin_ctz((unsigned)mask);
+        o += (size_t)k;
+        i += (size_t)k;
+        break;
+      }
+      o += 16;
+      i += 16;
+    }
+    if (i >= n) break;
+    if (o + 2 > cap) return 0;
+    const uint8_t b = src[i++];
+    dst[o++] = b;
+    if (b == 0xFF) dst[o++] = 0x00;
   }
   return o;
 }

@@ -25,6 +25,8 @@
 #include <cstdlib>
 #include <cstring>
 
+#include <emmintrin.h>
+
 #include "uhdr_kernels.cuh"
 
 namespace uhdr {
@@ -37,9 +39,12 @@ const uint8_t kZigZag[64] = {0,  1,  8,  16, 9,  2,  3,  10, 17, 24, 32, 25, 18,
                              30, 37, 44, 51, 58, 59, 52, 45, 38, 31, 39, 46, 53, 60, 61, 54, 47, 55, 62, 63};
 
 // T.81 Annex C: canonical codes in order of increasing length; F.2.2.3: MAXCODE / VALPTR for the bit-serial decode
+// length | size << 5 | run << 9 | (length + size) << 13 | step << 18: `step` is what the symbol adds to the coefficient index
+// (run + 1; 16 for ZRL; 64 for EOB, which ends the block; 1 for a DC symbol)
 uint32_t fast_entry(int len, int sym, bool ac) {
   const int s = sym & 15, r = ac ? sym >> 4 : 0;
-  return (uint32_t)len | ((uint32_t)s << 5) | ((uint32_t)r << 9) | ((uint32_t)(len + s) << 13);
+  const int step = !ac ? 1 : (s ? r + 1 : (r == 15 ? 16 : 64));
+  return (uint32_t)len | ((uint32_t)s << 5) | ((uint32_t)r << 9) | ((uint32_t)(len + s) << 13) | ((uint32_t)step << 18);
 }
 bool build_huff(const uint8_t* bits, const uint8_t* vals, int nvals, bool ac, JpegHuffTable* t) {
   memset(t, 0, sizeof *t);
@@ -179,13 +184,26 @@ size_t jpeg_destuff(const uint8_t* d, size_t begin, size_t end, uint8_t* dst, in
   *marker = 0;
   *n_intervals = 1;
   interval_start[0] = 0;
+  const __m128i ff = _mm_set1_epi8((char)0xFF);
   while (i < end) {
-    const uint8_t* f = (const uint8_t*)memchr(d + i, 0xFF, end - i);
-    const size_t run = f ? (size_t)(f - (d + i)) : end - i;
-    memcpy(dst + o, d + i, run);
-    o += run;
-    i += run;
+    // 16 bytes at a time while no FF is among them (an FF comes along every ~256 bytes of entropy-coded data; memchr +
+    // memcpy per run cost ~50 ns each, three times the copy itself)
+    while (i + 16 <= end) {
+      const __m128i v = _mm_loadu_si128(reinterpret_cast<const __m128i*>(d + i));
+      const int mask = _mm_movemask_epi8(_mm_cmpeq_epi8(v, ff));
+      _mm_storeu_si128(reinterpret_cast<__m128i*>(dst + o), v);  // dst has the slack (capacity covers end - begin + padding)
+      if (mask) {
+        const int k = __builtin_ctz((unsigned)mask);  // bytes before the first FF
+        o += (size_t)k;
+        i += (size_t)k;
+        break;
+      }
+      o += 16;
+      i += 16;
+    }
+    while (i < end && d[i] != 0xFF && i + 16 > end) dst[o++] = d[i++];  // the last few bytes
     if (i >= end) break;
+    if (d[i] != 0xFF) continue;
     const int m = i + 1 < end ? d[i + 1] : 0xD9;  // a lone FF at the very end: treat as EOI
     if (m == 0x00) {         // stuffed byte: FF 00 -> FF
       dst[o++] = 0xFF;
@@ -210,6 +228,10 @@ size_t jpeg_destuff(const uint8_t* d, size_t begin, size_t end, uint8_t* dst, in
 namespace {
 
 constexpr int kHuffThreads = 128;  // subsequences per CTA
+#ifndef UHDR_JPEG_WARM
+#define UHDR_JPEG_WARM 32
+#endif
+constexpr int kHuffWarm = UHDR_JPEG_WARM;  // subsequences a CTA decodes in front of its own in the first round (a multiple of 32)
 __constant__ uint8_t c_zigzag[64] = {0,  1,  8,  16, 9,  2,  3,  10, 17, 24, 32, 25, 18, 11, 4,  5,  12, 19, 26, 33, 40, 48,
                                     41, 34, 27, 20, 13, 6,  7,  14, 21, 28, 35, 42, 49, 56, 57, 50, 43, 36, 29, 22, 15, 23,
                                     30, 37, 44, 51, 58, 59, 52, 45, 38, 31, 39, 46, 53, 60, 61, 54, 47, 55, 62, 63};  // T.81 Figure A.6
@@ -273,10 +295,11 @@ __device__ __noinline__ uint32_t huff_long_code(const HuffSmem* sm, uint32_t tab
     const int code = (int)(bits >> (32 - l));
     if (code <= t.maxcode[l]) {
       const uint32_t sym = t.vals[(t.valoff[l] + code) & 255], s = sym & 15u, r = ac ? sym >> 4 : 0u;
-      return l | (s << 5) | (r << 9) | ((l + s) << 13);
+      const uint32_t step = !ac ? 1u : (s ? r + 1u : (r == 15u ? 16u : 64u));
+      return l | (s << 5) | (r << 9) | ((l + s) << 13) | (step << 18);
     }
   }
-  return 16u | (16u << 13) | (ac ? 0u : 0u);  // no code (only while decoding from a guessed position): 16 bits, EOB / zero difference
+  return 16u | (16u << 13) | ((ac ? 64u : 1u) << 18);  // no code (only while decoding from a guessed position): 16 bits, EOB / zero difference
 }
 
 // EXTEND, T.81 F.2.2.1 (Figure F.12)
@@ -337,10 +360,12 @@ __device__ __forceinline__ uint32_t decode_span(const JpegScan& sc, const HuffSm
     uint32_t e;
     asm("ld.shared.u32 %0, [%1];" : "=r"(e) : "r"(t + ((bits >> (32 - kJpegLookBits)) << 2)));  // JpegHuffTable::fast comes first
     if (e == 0) e = huff_long_code(sm, (t - sm0) / kTab, bits);
-    const uint32_t used = e >> 13, s = (e >> 5) & 15u, r = (e >> 9) & 15u;
-    const uint32_t kpos = k + r;  // zig-zag index of this coefficient (a DC entry has run 0)
-    if (WRITE && s && kpos < 64) out[c_zigzag[kpos]] = (int16_t)extend((bits << (e & 31u)) >> (32 - s), s);
-    k = (ac && s == 0) ? (r == 15 ? k + 16 : 64) : kpos + 1;  // ZRL / EOB (F.2.2.2), else the next coefficient
+    const uint32_t used = (e >> 13) & 31u;
+    if (WRITE) {
+      const uint32_t s = (e >> 5) & 15u, kpos = k + ((e >> 9) & 15u);  // zig-zag index of this coefficient (a DC entry has run 0)
+      if (s && kpos < 64) out[c_zigzag[kpos]] = (int16_t)extend((bits << (e & 31u)) >> (32 - s), s);
+    }
+    k += e >> 18;  // run + 1, or 16 for ZRL, or 64 for EOB (F.2.2.2): the block is complete at k >= 64
     bw.skip(used);
     left -= (int)used;
     if (k >= 64) {  // block complete (k > 64 only for corrupt data or a guessed state)
@@ -378,21 +403,28 @@ __device__ __forceinline__ void span_of(const JpegScan& sc, uint32_t t, uint64_t
 // rounds: a CTA whose predecessor's LAST exit state changed in the previous round re-enters with it; all others have
 // nothing to do. A round in which no CTA's last exit state changes is the global fixed point (the host checks
 // n_changed). Steps cost one subsequence's decode latency each, not a kernel launch.
+// In the FIRST round a CTA additionally decodes the kHuffWarm subsequences BEFORE its own 128 (lanes 0 .. kHuffWarm - 1,
+// results not stored): the chain that starts at the guessed state of the first warm-up lane has fallen into step by the
+// time it reaches the CTA's own subsequences (for every stream whose synchronisation distance is below kHuffWarm
+// subsequences), so the later rounds find the CTA's exit states already exact and only verify them.
 template <bool FIRST>
-__global__ void __launch_bounds__(kHuffThreads) huff_round_kernel(const __grid_constant__ JpegScan sc, uint32_t* __restrict__ exit_state,
-                                                                  uint32_t* __restrict__ count, const uint8_t* __restrict__ cta_dirty_in,
-                                                                  uint8_t* __restrict__ cta_dirty_out, uint32_t* __restrict__ n_changed,
-                                                                  uint32_t* __restrict__ max_steps) {
+__global__ void __launch_bounds__(kHuffThreads + kHuffWarm) huff_round_kernel(const __grid_constant__ JpegScan sc, uint32_t* __restrict__ exit_state,
+                                                                              uint32_t* __restrict__ count, const uint8_t* __restrict__ cta_dirty_in,
+                                                                              uint8_t* __restrict__ cta_dirty_out, uint32_t* __restrict__ n_changed,
+                                                                              uint32_t* __restrict__ max_steps) {
   __shared__ HuffSmem sm;
-  __shared__ uint32_t exit_s[kHuffThreads];
-  __shared__ uint8_t dirty_s[2][kHuffThreads];
-  const uint32_t i = threadIdx.x, t = blockIdx.x * kHuffThreads + i;
+  __shared__ uint32_t exit_s[kHuffThreads + kHuffWarm];
+  __shared__ uint8_t dirty_s[2][kHuffThreads + kHuffWarm];
+  constexpr uint32_t kLead = FIRST ? kHuffWarm : 0;  // lanes in front of the CTA's own subsequences
+  const uint32_t i = threadIdx.x;
+  const int64_t tt = (int64_t)blockIdx.x * kHuffThreads + (int64_t)i - (int64_t)kLead;
+  const uint32_t t = tt < 0 ? 0u : (uint32_t)tt;
   if (!FIRST && (blockIdx.x == 0 || !cta_dirty_in[blockIdx.x - 1])) {  // CTA-uniform
     if (i == 0) cta_dirty_out[blockIdx.x] = 0;
     return;
   }
   load_tables(&sm, sc.tables);
-  const bool live = t < sc.n_subseq;
+  const bool live = tt >= 0 && t < sc.n_subseq, owned = i >= kLead;
   const bool hard = live && hard_start(sc, t);  // entry state exact from the start: never decoded again
   uint64_t b = 0, e = 0;
   if (live) span_of(sc, t, b, e);
@@ -433,13 +465,13 @@ __global__ void __launch_bounds__(kHuffThreads) huff_round_kernel(const __grid_c
     if (!__syncthreads_or(ch ? 1 : 0)) break;
     ph ^= 1;
   }
-  if (live) {
+  if (live && owned) {
     exit_state[t] = cur;
     count[t] = cnt;
   }
   const uint32_t last = min((blockIdx.x + 1) * kHuffThreads, sc.n_subseq) - 1;  // the CTA's last live subsequence
   if (i == 0 && max_steps) atomicMax(max_steps, steps);  // UHDRB200_JPEG_TIMING: the longest in-CTA chain
-  if (t == last) {
+  if (live && owned && t == last) {
     const bool moved = FIRST || cur != entry_exit;
     cta_dirty_out[blockIdx.x] = moved ? 1 : 0;
     if (moved) atomicAdd(n_changed, 1u);
@@ -614,7 +646,7 @@ cudaError_t jpeg_huff_decode(const JpegScan& sc, void* workspace, cudaStream_t s
     cudaEventRecord(ev[0], s);
   }
   uint32_t* step_stat = timing ? n_changed + 62 : nullptr;  // slots 62, 63: longest chain of the first / the later rounds
-  huff_round_kernel<true><<<grid, kHuffThreads, 0, s>>>(sc, exit_a, count, dirty_b, dirty_a, n_changed, step_stat);
+  huff_round_kernel<true><<<grid, kHuffThreads + kHuffWarm, 0, s>>>(sc, exit_a, count, dirty_b, dirty_a, n_changed, step_stat);
   if (timing) cudaEventRecord(ev[1], s);
   int pass = 0;
   uint8_t* din = dirty_a;

@@ -203,8 +203,9 @@ cudaError_t launch_jpeg_idct_impl(const JpegIdctParams& p, cudaStream_t s);
 constexpr int kJpegSubseqBits = UHDR_JPEG_SUBSEQ_BITS;   // bits of entropy-coded data one thread owns (a multiple of 32)
 constexpr int kJpegLookBits = 10;       // first-level Huffman look-up: codes of up to 10 bits in one shared-memory load
 struct JpegHuffTable {                  // one DC or AC table (ITU-T T.81 Annex C / F.2.2.3), built by jpeg_parse
-  // first level, indexed by the next kJpegLookBits bits: code length | size << 5 | run << 9 | (length + size) << 13 for a
-  // code of up to kJpegLookBits bits (size = SSSS extra bits, run = RRRR, 0 in a DC table); 0 = a longer code
+  // first level, indexed by the next kJpegLookBits bits: code length | size << 5 | run << 9 | (length + size) << 13 |
+  // step << 18 for a code of up to kJpegLookBits bits (size = SSSS extra bits, run = RRRR, 0 in a DC table; step = what the
+  // symbol adds to the coefficient index: run + 1, 16 for ZRL, 64 for EOB, 1 for DC); 0 = a longer code
   uint32_t fast[1 << kJpegLookBits];
   int32_t maxcode[18];                  // largest code of each length 1..16 (-1: none); [17] = sentinel
   int32_t valoff[18];                   // index into vals of the first code of each length minus that code
