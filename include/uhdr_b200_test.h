@@ -43,6 +43,13 @@ enum {
 };
 int uhdrb200_test_eval(int fn, const float* in_dev, float* out_dev, size_t n, void* stream);
 
+/* Host-only parts of the JPEG encoder (csrc/jpeg_enc.cu), callable without a GPU: everything uhdrb200_jpeg_encode_* writes in
+ * front of the entropy-coded segment (SOI, JFIF APP0, optional ICC APP2, DQT, SOF0, DHT, SOS) for the given quality and
+ * size, and the byte stuffing (FF -> FF 00) of an entropy-coded segment. Both return the bytes written, 0 when `cap` is
+ * too small. */
+size_t uhdrb200_test_jpeg_headers(int quality, int grey, int width, int height, const void* icc, size_t icc_bytes, void* out, size_t cap);
+size_t uhdrb200_test_jpeg_stuff(const void* src, size_t n, void* out, size_t cap);
+
 #ifdef __cplusplus
 }
 #endif

@@ -69,6 +69,8 @@ SYMBOLS = {
 TEST_SYMBOLS = {
     "uhdrb200_test_set_apply_mode": (C.c_int, [C.c_int]),
     "uhdrb200_test_eval": (C.c_int, [C.c_int, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
+    "uhdrb200_test_jpeg_headers": (C.c_size_t, [C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t]),
+    "uhdrb200_test_jpeg_stuff": (C.c_size_t, [C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t]),
 }
 
 

@@ -1937,6 +1937,12 @@ int uhdrb200_test_eval(int fn, const float* in_dev, float* out_dev, size_t n, vo
   if (e != cudaSuccess) return fail(e, "test_eval kernel launch");
   return UHDRB200_NO_ERROR;
 }
+size_t uhdrb200_test_jpeg_headers(int quality, int grey, int width, int height, const void* icc, size_t icc_bytes, void* out, size_t cap) {
+  JpegEncTables t;
+  jpeg_enc_tables(quality, grey != 0, &t);
+  return jpeg_write_headers((uint8_t*)out, cap, width, height, grey != 0, t, icc, icc_bytes);
+}
+size_t uhdrb200_test_jpeg_stuff(const void* src, size_t n, void* out, size_t cap) { return jpeg_stuff((const uint8_t*)src, n, (uint8_t*)out, cap); }
 int uhdrb200_set_numeric_mode(int mode) {
   if (mode != UHDRB200_MODE_ANALYTIC && mode != UHDRB200_MODE_LUT) return UHDRB200_ERROR_UNSUPPORTED_FEATURE;
   t_numeric_mode = mode;

@@ -82,3 +82,47 @@ def test_progressive_fixture_is_refused(lib):
     if not os.path.exists(p):
         pytest.skip("progressive fixture not available")
     assert info(lib, open(p, "rb").read())[0] == abi.ERROR_UNSUPPORTED_FEATURE  # SOF2
+
+
+# ------------------------------------------------------------------------------ host side of the encoder (no GPU)
+def _headers(lib, quality, grey, w, h, icc=b""):
+    out = (C.c_ubyte * 70000)()
+    icc_buf = (C.c_ubyte * len(icc)).from_buffer_copy(icc) if icc else None
+    n = lib.uhdrb200_test_jpeg_headers(quality, 1 if grey else 0, w, h, icc_buf, len(icc), out, len(out))
+    return bytes(out[:n])
+
+
+@pytest.mark.parametrize("quality", [1, 25, 50, 51, 75, 90, 95, 100])
+def test_encoder_headers_equal_libjpeg_turbo(lib, quality):
+    """Markers, quantisation tables (jpeg_set_quality(q, TRUE): the Annex K tables scaled and clamped to 1..255) and Huffman
+    tables (Annex K.3) in front of the scan: byte-identical to what libjpeg-turbo writes for the same settings."""
+    rgb = np.zeros((32, 48, 3), np.uint8)
+    for grey in (False, True):
+        want = encode(rgb[..., 0] if grey else rgb, quality=quality, **({} if grey else {"subsampling": 2}))
+        sos = want.find(b"\xff\xda")
+        head = want[: sos + 2 + ((want[sos + 2] << 8) | want[sos + 3])]
+        assert _headers(lib, quality, grey, 48, 32) == head
+
+
+def test_encoder_icc_segment_and_limits(lib):
+    plain = _headers(lib, 90, False, 64, 64)
+    icc = bytes(range(256)) * 10
+    tagged = _headers(lib, 90, False, 64, 64, icc)
+    assert tagged == plain[:20] + b"\xff\xe2" + (len(icc) + 2).to_bytes(2, "big") + icc + plain[20:]
+    out = (C.c_ubyte * 100)()
+    assert lib.uhdrb200_test_jpeg_headers(90, 0, 64, 64, None, 0, out, 100) == 0  # does not fit
+    assert _headers(lib, 90, False, 64, 64, bytes(65534)) == b""                  # one APP2 segment holds 65 533 bytes
+
+
+def test_encoder_byte_stuffing(lib):
+    rng = np.random.Generator(np.random.PCG64(4))
+    for n in (0, 1, 15, 16, 17, 1000, 65537):
+        src = rng.integers(0, 256, n, dtype=np.uint8)
+        src[rng.random(n) < 0.1] = 0xFF  # dense FF bytes, runs of them included
+        want = bytes(src).replace(b"\xff", b"\xff\x00")
+        out = (C.c_ubyte * (2 * n + 32))()
+        buf = (C.c_ubyte * max(1, n)).from_buffer_copy(bytes(src) or b"\0")
+        got = lib.uhdrb200_test_jpeg_stuff(buf, n, out, len(out))
+        assert bytes(out[:got]) == want
+        if n > 17:
+            assert lib.uhdrb200_test_jpeg_stuff(buf, n, out, len(want) - 1) == 0  # one byte short
