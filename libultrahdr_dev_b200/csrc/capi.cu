@@ -1878,6 +1878,17 @@ int jpeg_encode(const uhdrb200_image* img, int quality, const void* icc, size_t 
   return UHDRB200_NO_ERROR;
 }
 
+// the codec entry points size host vectors from the caller's data: an allocation failure must not unwind through the C ABI
+template <class F>
+int no_throw(F f) {
+  try {
+    return f();
+  } catch (const std::exception& e) {
+    t_ctx.err = std::string("uhdrb200_jpeg: ") + e.what();
+    return UHDRB200_ERROR_INSUFFICIENT_RESOURCE;
+  }
+}
+
 int jpeg_get_info(const void* jpeg, size_t bytes, size_t* width, size_t* height, int* pixel_format) {
   if (!jpeg) return UHDRB200_ERROR_BAD_PTR;
   static thread_local JpegHeader h;
@@ -2034,17 +2045,19 @@ int uhdrb200_jpeg_idct_dev(int n_components, const uhdrb200_jpeg_component* comp
 int uhdrb200_jpeg_get_info(const void* jpeg, size_t bytes, size_t* width, size_t* height, int* pixel_format) {
   return jpeg_get_info(jpeg, bytes, width, height, pixel_format);
 }
-int uhdrb200_jpeg_decode_host(const void* jpeg, size_t bytes, uhdrb200_image* dest) { return jpeg_decode(jpeg, bytes, dest, false, nullptr); }
+int uhdrb200_jpeg_decode_host(const void* jpeg, size_t bytes, uhdrb200_image* dest) {
+  return no_throw([&] { return jpeg_decode(jpeg, bytes, dest, false, nullptr); });
+}
 int uhdrb200_jpeg_decode_dev(const void* jpeg, size_t bytes, uhdrb200_image* dest, void* stream) {
-  return jpeg_decode(jpeg, bytes, dest, true, (cudaStream_t)stream);
+  return no_throw([&] { return jpeg_decode(jpeg, bytes, dest, true, (cudaStream_t)stream); });
 }
 int uhdrb200_jpeg_encode_host(const uhdrb200_image* image, int quality, const void* icc, size_t icc_bytes, void* out, size_t out_capacity,
                               size_t* out_bytes) {
-  return jpeg_encode(image, quality, icc, icc_bytes, out, out_capacity, out_bytes, false, nullptr);
+  return no_throw([&] { return jpeg_encode(image, quality, icc, icc_bytes, out, out_capacity, out_bytes, false, nullptr); });
 }
 int uhdrb200_jpeg_encode_dev(const uhdrb200_image* image, int quality, const void* icc, size_t icc_bytes, void* out, size_t out_capacity,
                              size_t* out_bytes, void* stream) {
-  return jpeg_encode(image, quality, icc, icc_bytes, out, out_capacity, out_bytes, true, (cudaStream_t)stream);
+  return no_throw([&] { return jpeg_encode(image, quality, icc, icc_bytes, out, out_capacity, out_bytes, true, (cudaStream_t)stream); });
 }
 int uhdrb200_copy_yuv420_host(const uhdrb200_image* src, uhdrb200_image* dest) { return copy_yuv420_host(src, dest); }
 int uhdrb200_copy_yuv420_dev(const uhdrb200_image* src, uhdrb200_image* dest, void* stream) {
