@@ -308,3 +308,29 @@ def test_four_host_threads_decode_and_encode_concurrently(uh):
     for th in ths:
         th.join()
     assert not errors, errors
+
+
+def test_limit_size_8192(uh):
+    """kMaxWidth x kMaxHeight (lib/include/ultrahdr/jpegr.h:31-32, jpegdecoderhelper.cpp:254-258): 8192 x 8192 4:2:0, the
+    largest image the reference's decoder admits; 100 M samples, 1.6 M blocks, the 32-bit bit offsets and block indices at
+    their largest. Encoded on the device, compared with libjpeg-turbo's file, decoded on the device, compared with
+    libjpeg-turbo's planes."""
+    pytest.importorskip("PIL.Image")
+    from test_gpu_jpeg_encode import device_encode, pillow_encode
+
+    w = h = 8192
+    rng = np.random.Generator(np.random.PCG64(8192))
+    yy, xx = np.mgrid[0:h, 0:w].astype(np.float32)
+    y = np.clip(128 + 100 * np.sin(xx / 37.0) * np.cos(yy / 29.0) + rng.normal(0, 4, (h, w)).astype(np.float32), 0, 255).astype(np.uint8)
+    del yy, xx
+    cy, cx = np.mgrid[0:h // 2, 0:w // 2].astype(np.float32)
+    u = np.clip(128 + 60 * np.sin(cx / 41.0), 0, 255).astype(np.uint8)
+    v = np.clip(128 + 60 * np.cos(cy / 33.0), 0, 255).astype(np.uint8)
+    del cy, cx
+    planes = [y, u, v]
+    data = device_encode(uh.lib, planes, 90)
+    assert data == pillow_encode(planes, 90)
+    got = decode_host(uh.lib, data)
+    for p, r in zip(got, libjpeg_planes(data)):
+        assert np.array_equal(p, r)
+    print(f"8192x8192 4:2:0 quality 90: {len(data)} bytes")
