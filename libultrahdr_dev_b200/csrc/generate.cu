@@ -26,8 +26,22 @@ namespace {
 // LUT = the LUT numeric mode (graded against the reference's -DUSE_*_LUT=1 build): after the same gather the thread
 // follows the reference's float arithmetic operation by operation (sequential box sum, unfused YUV matrix, nearest-entry
 // tables, double log2 in encodeGain) instead of the fp32 fast chain.
+// Occupancy bounds (blocks of 256 threads per SM), measured on B200 (scripts/api0_convert_variants.sh): the fused kernels
+// are bound by instruction issue and latency, not by HBM, and gain from more resident warps as long as nothing spills:
+// with convertYuv 54 registers / 4 blocks 0.60-0.67 of the HBM peak, 48 registers / 5 blocks 0.75, 40 registers / 6
+// blocks (52 B of spills) 0.72.
+#ifndef UHDR_API0_CONVERT_MIN_BLOCKS
+#define UHDR_API0_CONVERT_MIN_BLOCKS 5
+#endif
+#ifndef UHDR_API0_MIN_BLOCKS
+#define UHDR_API0_MIN_BLOCKS 5  // without convertYuv: 66 registers / 3 blocks 0.72, 4 blocks 0.81, 48 registers / 5 blocks 0.86 (same script)
+#endif
+#ifndef UHDR_GENERATE_MIN_BLOCKS
+#define UHDR_GENERATE_MIN_BLOCKS 1
+#endif
 template <bool VEC, bool FUSED, bool CONVERT = false, bool LUT = false>
-__global__ void __launch_bounds__(256) generate_kernel(GenerateParams p) {
+__global__ void __launch_bounds__(256, LUT ? 1 : (CONVERT ? UHDR_API0_CONVERT_MIN_BLOCKS : (FUSED ? UHDR_API0_MIN_BLOCKS : UHDR_GENERATE_MIN_BLOCKS)))
+    generate_kernel(GenerateParams p) {
   pdl_trigger();
   const Geometry& g = p.g;
   const int mx = blockIdx.x * 32 + threadIdx.x;
