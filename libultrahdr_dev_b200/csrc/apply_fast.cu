@@ -443,7 +443,10 @@ __global__ void __launch_bounds__(kQThreads, LTAB ? UHDR_APPLYQ_L_MIN_BLOCKS : U
 // interior weight rows from the constant bank at scale 2, same operation order as the general code, so the results are
 // identical); SCALE = 0 is the general run-time scale.
 template <int PACK, bool MASK, bool BATCH, bool LTAB, bool NORM, int SCALE>
-__global__ void __launch_bounds__(kThreads, 3) apply_qs_kernel(const __grid_constant__ ApplyFastParams p) {
+#ifndef UHDR_APPLYQS_MIN_BLOCKS
+#define UHDR_APPLYQS_MIN_BLOCKS 4  // 64 registers (0-8 B of spills): scale 1 0.59 -> 0.65, scale 2 0.49 -> 0.53 of the HBM peak against 3 blocks x 80 registers
+#endif
+__global__ void __launch_bounds__(kThreads, UHDR_APPLYQS_MIN_BLOCKS) apply_qs_kernel(const __grid_constant__ ApplyFastParams p) {
   const int tid = threadIdx.x;
   pdl_trigger();
   const uint32_t hiP = stage_q_table<PACK, LTAB>(p, tid);  // constants only: may overlap the previous kernel's tail
