@@ -72,6 +72,34 @@ def test_random_coefficients_ragged(uh, orc, w, h, pad):
         assert (g[:, c.width:] == 0x5A).all()
 
 
+@pytest.mark.parametrize("wide", [(True, False, False), (False, False, True), (True, True, True)])
+def test_sixteen_bit_quant_tables(uh, orc, wide):
+    """Quantisation steps above 255 (a 16-bit DQT, Pq = 1) in some or all components: the kernel's plain-multiply
+    dequantisation instead of its packed one; small coefficients keep the sums inside libjpeg's defined range."""
+    rng = np.random.Generator(np.random.PCG64(sum(wide) * 7 + wide[0]))
+    comps = []
+    for k in range(3):
+        c = Rnd()
+        cw, ch = (200, 120) if k == 0 else (100, 60)
+        bw, bh = -(-cw // 8), -(-ch // 8)
+        hi = 4000 if wide[k] else 256
+        q = rng.integers(1, hi, 64).astype(np.uint16)
+        if wide[k]:
+            q[rng.integers(0, 64)] = 65535
+        else:
+            q[rng.integers(0, 64)] = 255
+        co = (rng.integers(-3, 4, (bh, bw, 64)) * (rng.random((bh, bw, 64)) < 0.1)).astype(np.int16)
+        co[..., 0] = rng.integers(-1024, 1024, (bh, bw)) // np.maximum(1, q[0] // 8)
+        co[q[None, None, :].repeat(bh, 0).repeat(bw, 1) > 2000] = 0
+        c.coeffs, c.quant, c.width, c.height = co, q, cw, ch
+        comps.append(c)
+    want = oracle_planes(orc, comps)
+    got = host_idct(uh.lib, comps, [c.width for c in comps])
+    for g, wv in zip(got, want):
+        assert np.array_equal(g, wv)
+    assert len(np.unique(want[0])) > 16
+
+
 def test_error_codes(uh):
     lib = uh.lib
     assert lib.uhdrb200_jpeg_idct_host(0, None) == abi.NO_ERROR
