@@ -147,6 +147,7 @@ __device__ __forceinline__ IdctTile locate_tile(const JpegIdctParams& p, const u
   return r;
 }
 
+template <bool ALIGNED>  // every component's coefficient array is 16-byte aligned (the host looks at the pointers)
 __global__ void __launch_bounds__(kIdctBThreads, UHDR_IDCT_BLOCK_MIN_BLOCKS) jpeg_idct_kernel(const __grid_constant__ JpegIdctParams p) {
   __shared__ __align__(16) unsigned char tile[2][kIdctBThreads / 32][kTileBytes];
   __shared__ __align__(16) int qs[4][64], qp[4][32];  // steps in natural order; pairs packed for dp2a
@@ -166,7 +167,17 @@ __global__ void __launch_bounds__(kIdctBThreads, UHDR_IDCT_BLOCK_MIN_BLOCKS) jpe
 #pragma unroll
       for (int j = 0; j < 8; j++) {
         const uint32_t g = j * 32 + lane;  // 16-byte chunk g of the tile: block g / 8, coefficient row g % 8
-        if (g < it.count * 8) cp_async16(wt + (g >> 3) * kTileStride + (g & 7) * 16, src + (size_t)g * 16);
+        if (g >= it.count * 8) continue;
+        unsigned char* dst = wt + (g >> 3) * kTileStride + (g & 7) * 16;
+        if (ALIGNED) {
+          cp_async16(dst, src + (size_t)g * 16);
+        } else {  // a DEVICE-pointer caller's array that is only 2-byte aligned: plain loads, ordered by the __syncwarp below
+          const uint16_t* s2 = reinterpret_cast<const uint16_t*>(src + (size_t)g * 16);
+          uint32_t v[4];
+#pragma unroll
+          for (int k = 0; k < 4; k++) v[k] = ldg2(s2 + 2 * k) | ldg2(s2 + 2 * k + 1) << 16;
+          *reinterpret_cast<uint4*>(dst) = make_uint4(v[0], v[1], v[2], v[3]);
+        }
       }
     }
     cp_async_commit();
@@ -271,7 +282,9 @@ cudaError_t launch_jpeg_idct_impl(const JpegIdctParams& p, cudaStream_t s) {
   }
   if (bw == 0 || bh == 0) return cudaSuccess;
   size_t tiles = 0;
+  bool aligned = true;
   for (int i = 0; i < p.n_components; i++) {
+    aligned = aligned && (reinterpret_cast<uintptr_t>(p.comp[i].coeffs) & 15) == 0;
     const size_t nblk = p.comp[i].blocks_w * p.comp[i].blocks_h;
     if (nblk > 0x7fffffffu) return cudaErrorInvalidValue;  // jpeg_check_layout bounds the codec's images, this the raw entry point
     tiles += (nblk + 31) / 32;
@@ -286,15 +299,19 @@ cudaError_t launch_jpeg_idct_impl(const JpegIdctParams& p, cudaStream_t s) {
   if (per_sm_of[dev] == 0) {
     int n_sm = 0, n = 0;
     if ((e = cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev)) != cudaSuccess) return e;
-    if ((e = cudaFuncSetAttribute(jpeg_idct_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared)) != cudaSuccess) return e;
-    if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, jpeg_idct_kernel, kIdctBThreads, 0)) != cudaSuccess) return e;
+    if ((e = cudaFuncSetAttribute(jpeg_idct_kernel<true>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared)) != cudaSuccess ||
+        (e = cudaFuncSetAttribute(jpeg_idct_kernel<false>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared)) != cudaSuccess)
+      return e;
+    if ((e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, jpeg_idct_kernel<true>, kIdctBThreads, 0)) != cudaSuccess) return e;
     sms_of[dev] = n_sm;
     per_sm_of[dev] = n > 0 ? n : 1;
   }
   const size_t resident = (size_t)sms_of[dev] * per_sm_of[dev];
   lk.unlock();
   const size_t want = (tiles + kIdctBThreads / 32 - 1) / (kIdctBThreads / 32);
-  jpeg_idct_kernel<<<(unsigned)(want < resident ? want : resident), kIdctBThreads, 0, s>>>(p);
+  const unsigned grid = (unsigned)(want < resident ? want : resident);  // any grid is correct: every warp strides over the tiles
+  if (aligned) jpeg_idct_kernel<true><<<grid, kIdctBThreads, 0, s>>>(p);
+  else jpeg_idct_kernel<false><<<grid, kIdctBThreads, 0, s>>>(p);
   return cudaGetLastError();
 }
 

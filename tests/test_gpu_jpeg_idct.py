@@ -100,6 +100,39 @@ def test_sixteen_bit_quant_tables(uh, orc, wide):
     assert len(np.unique(want[0])) > 16
 
 
+@pytest.mark.parametrize("co_off,pl_off", [(1, 0), (3, 1), (0, 3)])
+def test_device_pointers_of_any_alignment(uh, orc, co_off, pl_off):
+    """Device-pointer callers: coefficient arrays that are only 2-byte aligned (the kernel's asynchronous 16-byte copies
+    need 16) and planes at odd addresses (byte stores instead of 8-byte ones): same samples."""
+    import torch as t
+
+    rng = np.random.Generator(np.random.PCG64(co_off * 10 + pl_off))
+    comps, arr, keep, outs = [], (abi.JpegComponent * 3)(), [], []
+    for k in range(3):
+        c = Rnd()
+        cw, ch = (333, 70) if k == 0 else (167, 35)
+        bw, bh = -(-cw // 8), -(-ch // 8)
+        co = (rng.integers(-200, 200, (bh, bw, 64)) * (rng.random((bh, bw, 64)) < 0.2)).astype(np.int16)
+        co[..., 0] = rng.integers(-900, 900, (bh, bw))
+        c.coeffs, c.quant, c.width, c.height = co, rng.integers(1, 40, 64).astype(np.uint16), cw, ch
+        comps.append(c)
+        dco = t.zeros(co.size + 8, dtype=t.int16, device="cuda")
+        dco[co_off: co_off + co.size] = t.from_numpy(co.ravel()).cuda()
+        dq = t.from_numpy(c.quant.astype(np.int16)).cuda()
+        dpl = t.full((cw * ch + 8,), 0x5A, dtype=t.uint8, device="cuda")
+        keep += [dco, dq]
+        outs.append(dpl)
+        arr[k].coeffs, arr[k].quant = dco.data_ptr() + 2 * co_off, dq.data_ptr()
+        arr[k].blocks_w, arr[k].blocks_h = bw, bh
+        arr[k].plane, arr[k].width, arr[k].height, arr[k].stride = dpl.data_ptr() + pl_off, cw, ch, cw
+    assert uh.lib.uhdrb200_jpeg_idct_dev(3, arr, t.cuda.current_stream().cuda_stream) == 0, uh.lib.uhdrb200_last_error()
+    t.cuda.synchronize()
+    for c, d, wv in zip(comps, outs, oracle_planes(orc, comps)):
+        g = d.cpu().numpy()
+        assert np.array_equal(g[pl_off: pl_off + c.width * c.height].reshape(c.height, c.width), wv)
+        assert (g[:pl_off] == 0x5A).all() and (g[pl_off + c.width * c.height:] == 0x5A).all()
+
+
 def test_error_codes(uh):
     lib = uh.lib
     assert lib.uhdrb200_jpeg_idct_host(0, None) == abi.NO_ERROR
