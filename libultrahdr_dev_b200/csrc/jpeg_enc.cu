@@ -278,57 +278,101 @@ __device__ __forceinline__ void fdct_1d(const int (&d)[8], int (&o)[8]) {
   o[1] = descale(t7 + z1 + z4, kShift);
 }
 
-__constant__ uint8_t c_enc_unzig[64] = {0,  1,  5,  6,  14, 15, 27, 28, 2,  4,  7,  13, 16, 26, 29, 42, 3,  8,  12, 17, 25, 30,
-                                        41, 43, 9,  11, 18, 24, 31, 40, 44, 53, 10, 19, 23, 32, 39, 45, 52, 54, 20, 22, 33, 38,
-                                        46, 51, 55, 60, 21, 34, 37, 47, 50, 56, 59, 61, 35, 36, 48, 49, 57, 58, 62, 63};  // natural index -> zig-zag position
+// zig-zag position -> natural index (jpeg_natural_order), folded at compile time in the unrolled store loop
+__device__ constexpr int zig_natural(int pos) {
+  constexpr int t[64] = {0,  1,  8,  16, 9,  2,  3,  10, 17, 24, 32, 25, 18, 11, 4,  5,  12, 19, 26, 33, 40, 48,
+                         41, 34, 27, 20, 13, 6,  7,  14, 21, 28, 35, 42, 49, 56, 57, 50, 43, 36, 29, 22, 15, 23,
+                         30, 37, 44, 51, 58, 59, 52, 45, 38, 31, 39, 46, 53, 60, 61, 54, 47, 55, 62, 63};
+  return t[pos];
+}
 
-constexpr int kFdctThreads = 256, kFdctBlocksPerCta = kFdctThreads / 8, kFdctWsRow = 33, kFdctWsWarp = 8 * kFdctWsRow;
+constexpr int kFdctThreads = 128, kFdctTileStride = 144;  // bytes per block record in the shared-memory tile (128 + 16 of padding)
 
-// grid (block columns / 32, block rows, components). 8 lanes per 8x8 block: lane r transforms sample row r (samples beyond
-// the image are ZERO, jpegencoderhelper.cpp:147-205, then centred like every sample), the block passes through a padded
-// per-warp workspace once, lane c transforms column c, quantises (jcdctmgr.c: (|x| + q/2) / q with q = 8 * step, sign
-// restored) and stores its eight coefficients at their zig-zag positions of the block's 64-entry record.
-__global__ void __launch_bounds__(kFdctThreads) fdct_quant_kernel(const __grid_constant__ JpegEncParams p) {
-  __shared__ int ws[(kFdctThreads / 32) * kFdctWsWarp];
+// One THREAD per 8x8 block, blocks in raster order over the component (grid.x chunks of 128 blocks, grid.z components): the
+// block lives in 64 registers, both passes run without a hand-over. Eight 8-byte loads fetch the samples (adjacent lanes
+// = adjacent blocks: 256 contiguous bytes per warp and row; samples beyond the image are ZERO, jpegencoderhelper.cpp:
+// 147-205, then centred like every sample). Quantisation (jcdctmgr.c: (|x| + q/2) / q with q = 8 * step, sign restored)
+// divides by multiplication: M = floor(2^32 / q) + 1 gives umulhi(n, M) == n / q for every n < 2^32 / q (q <= 2040, n <
+// 2^15 here). The 64 coefficients leave in zig-zag order: each lane writes its 128-byte record into a padded tile and the
+// warp stores its 32 consecutive records with coalesced 16-byte stores.
+__global__ void __launch_bounds__(kFdctThreads, 4) fdct_quant_kernel(const __grid_constant__ JpegEncParams p) {
+  __shared__ __align__(16) unsigned char tile[kFdctThreads * kFdctTileStride];
+  __shared__ __align__(8) uint2 qm[64];  // per natural index: q / 2 and the reciprocal M
   const JpegEncComponent& c = p.comp[blockIdx.z];
-  const uint32_t tid = threadIdx.x, r = tid & 7, lb = tid >> 3;
-  const uint32_t bx = blockIdx.x * kFdctBlocksPerCta + lb, by = blockIdx.y;
-  if (by >= c.blocks_h || bx >= c.blocks_w) return;
-  const unsigned lanes = __activemask();
-  int* w = ws + (tid >> 5) * kFdctWsWarp + (lb & 3) * 8;
-  int v[8], o[8];
-  const size_t x0 = (size_t)bx * 8, y = (size_t)by * 8 + r;
+  const uint32_t nblk = c.blocks_w * c.blocks_h, tid = threadIdx.x, lane = tid & 31;
+  if (blockIdx.x * kFdctThreads >= nblk) return;  // the components of one launch differ in size
+  if (tid < 64) {
+    const uint32_t q = (uint32_t)c.quant[tid] << 3;
+    qm[tid] = make_uint2(q >> 1, (uint32_t)(0x100000000ull / q) + 1);
+  }
+  __syncthreads();
+  const uint32_t first = blockIdx.x * kFdctThreads + (tid & ~31u);  // the warp's first block
+  if (first >= nblk) return;
+  const uint32_t in_warp = nblk - first < 32 ? nblk - first : 32;
+  const uint32_t i = first + lane < nblk ? first + lane : nblk - 1;  // idle lanes of the last warp repeat its last block
+  const uint32_t by = i / c.blocks_w, bx = i - by * c.blocks_w;
+  const size_t x0 = (size_t)bx * 8;
+  int w[64];
+  {
+    const uint8_t* src = c.plane + (size_t)by * 8 * c.stride + x0;
+    const bool vec = x0 + 8 <= c.width && ((reinterpret_cast<uintptr_t>(src) | c.stride) & 7) == 0;
+    uint2 raw[8];
 #pragma unroll
-  for (int k = 0; k < 8; k++) v[k] = -128;  // a zero sample, centred
-  if (y < c.height && x0 < c.width) {
-    const uint8_t* src = c.plane + y * c.stride + x0;
-    if (x0 + 8 <= c.width && ((reinterpret_cast<uintptr_t>(src) & 7) == 0)) {
-      const uint2 two = ldg8(src);
+    for (int r = 0; r < 8; r++) {
+      raw[r] = make_uint2(0, 0);  // zero samples
+      const size_t y = (size_t)by * 8 + r;
+      if (y < c.height && x0 < c.width) {
+        if (vec) {
+          raw[r] = ldg8(src + r * c.stride);
+        } else {
+          for (int k = 0; k < 8; k++)
+            if (x0 + k < c.width) (k < 4 ? raw[r].x : raw[r].y) |= (uint32_t)src[r * c.stride + k] << (8 * (k & 3));
+        }
+      }
+    }
+#pragma unroll
+    for (int r = 0; r < 8; r++) {  // pass 1: rows
+      int v[8], o[8];
+      const uint32_t lo = raw[r].x ^ 0x80808080u, hi = raw[r].y ^ 0x80808080u;  // sample - 128 as a signed byte
 #pragma unroll
       for (int k = 0; k < 4; k++) {
-        v[k] = (int)((two.x >> (8 * k)) & 0xff) - 128;
-        v[4 + k] = (int)((two.y >> (8 * k)) & 0xff) - 128;
+        v[k] = (int)(int8_t)(lo >> (8 * k));
+        v[4 + k] = (int)(int8_t)(hi >> (8 * k));
       }
-    } else {
+      fdct_1d<true>(v, o);
 #pragma unroll
-      for (int k = 0; k < 8; k++)
-        if (x0 + k < c.width) v[k] = (int)src[k] - 128;
+      for (int k = 0; k < 8; k++) w[8 * r + k] = o[k];
     }
   }
-  fdct_1d<true>(v, o);
 #pragma unroll
-  for (int k = 0; k < 8; k++) w[r * kFdctWsRow + k] = o[k];
-  __syncwarp(lanes);
+  for (int col = 0; col < 8; col++) {  // pass 2: columns, quantised as they are finished
+    int v[8], o[8];
 #pragma unroll
-  for (int k = 0; k < 8; k++) v[k] = w[k * kFdctWsRow + r];  // column r
-  fdct_1d<false>(v, o);
-  int16_t* dst = c.coeffs + ((size_t)by * c.blocks_w + bx) * 64;
+    for (int k = 0; k < 8; k++) v[k] = w[8 * k + col];
+    fdct_1d<false>(v, o);
 #pragma unroll
-  for (int k = 0; k < 8; k++) {
-    const int nat = k * 8 + (int)r, q = (int)c.quant[nat] << 3;
-    const int x = o[k], a = x < 0 ? -x : x;
-    const int m = (a + (q >> 1)) / q;
-    dst[c_enc_unzig[nat]] = (int16_t)(x < 0 ? -m : m);
+    for (int k = 0; k < 8; k++) {
+      const uint2 t = qm[8 * k + col];
+      const int x = o[k];
+      const int m = (int)__umulhi((uint32_t)(x < 0 ? -x : x) + t.x, t.y);
+      w[8 * k + col] = x < 0 ? -m : m;
+    }
+  }
+  unsigned char* wt = tile + (tid & ~31u) * kFdctTileStride;
+#pragma unroll
+  for (int j = 0; j < 8; j++) {  // the record in zig-zag order
+    uint32_t u[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++)
+      u[k] = ((uint32_t)w[zig_natural(8 * j + 2 * k)] & 0xffffu) | ((uint32_t)w[zig_natural(8 * j + 2 * k + 1)] << 16);
+    *reinterpret_cast<uint4*>(wt + lane * kFdctTileStride + j * 16) = make_uint4(u[0], u[1], u[2], u[3]);
+  }
+  __syncwarp();
+  unsigned char* dst = reinterpret_cast<unsigned char*>(c.coeffs + (size_t)first * 64);
+#pragma unroll
+  for (int j = 0; j < 8; j++) {
+    const uint32_t g = j * 32 + lane;  // 16-byte chunk g of the warp's records: block g / 8, chunk g % 8
+    if (g < in_warp * 8) stg16(dst + (size_t)g * 16, *reinterpret_cast<const uint4*>(wt + (g >> 3) * kFdctTileStride + (g & 7) * 16));
   }
 }
 
@@ -493,14 +537,14 @@ __global__ void __launch_bounds__(kScanThreads) scan_apply_kernel(const uint32_t
 }  // namespace
 
 cudaError_t launch_jpeg_fdct_impl(const JpegEncParams& p, cudaStream_t s) {
-  uint32_t bw = 0, bh = 0;
+  uint64_t most = 0;
   for (int i = 0; i < p.n_components; i++) {
-    bw = p.comp[i].blocks_w > bw ? p.comp[i].blocks_w : bw;
-    bh = p.comp[i].blocks_h > bh ? p.comp[i].blocks_h : bh;
+    const uint64_t nblk = (uint64_t)p.comp[i].blocks_w * p.comp[i].blocks_h;
+    if (nblk > 0x7fffffffu || (reinterpret_cast<uintptr_t>(p.comp[i].coeffs) & 15) != 0) return cudaErrorInvalidValue;  // 16-byte stores
+    most = nblk > most ? nblk : most;
   }
-  if (bw == 0 || bh == 0 || p.n_components <= 0) return cudaSuccess;
-  if (bh > 65535u) return cudaErrorInvalidValue;
-  fdct_quant_kernel<<<dim3((bw + kFdctBlocksPerCta - 1) / kFdctBlocksPerCta, bh, (unsigned)p.n_components), kFdctThreads, 0, s>>>(p);
+  if (most == 0 || p.n_components <= 0) return cudaSuccess;
+  fdct_quant_kernel<<<dim3((unsigned)((most + kFdctThreads - 1) / kFdctThreads), 1, (unsigned)p.n_components), kFdctThreads, 0, s>>>(p);
   return cudaGetLastError();
 }
 
