@@ -67,6 +67,55 @@ def test_not_a_jpeg(lib):
     assert lib.uhdrb200_jpeg_get_info(buf, len(good), None, None, None) == 0  # outputs are optional
 
 
+def test_mutated_headers_never_leave_the_buffer(lib):
+    """What the reference's decoder fuzzer does to the whole decoder (fuzzer/ultrahdr_dec_fuzzer.cpp), here for the marker
+    parser: byte flips, inserted bytes, cut files and over-long segment lengths in the header part of valid streams. Every
+    call returns one of the documented codes; a stream that is accepted has a sane size and format. The mutated copy sits
+    at the END of an exactly sized buffer followed by a guard page of different bytes, so a read past the end of the data
+    shows up as a changed answer between two guard patterns."""
+    rng = np.random.Generator(np.random.PCG64(99))
+    rgb = rng.integers(0, 256, (40, 56, 3), dtype=np.uint8)
+    seeds = [encode(rgb, quality=90, subsampling=2), encode(rgb, quality=60, subsampling=2, optimize=True),
+             encode(rgb[..., 0], quality=80), encode(rgb, quality=90, subsampling=2, restart_marker_rows=1)]
+    allowed = {0, abi.ERROR_DECODE, abi.ERROR_UNSUPPORTED_FEATURE, abi.ERROR_UNSUPPORTED_WIDTH_HEIGHT}
+    accepted = 0
+    for it in range(10000):
+        d = bytearray(seeds[it % len(seeds)])
+        head = min(len(d), 700)  # the markers live here
+        kind = it % 5
+        if kind == 0:
+            for _ in range(int(rng.integers(1, 4))):
+                d[int(rng.integers(2, head))] = int(rng.integers(0, 256))
+        elif kind == 1:
+            at = int(rng.integers(2, head))
+            d[at:at] = bytes(rng.integers(0, 256, int(rng.integers(1, 9)), dtype=np.uint8))
+        elif kind == 2:
+            del d[int(rng.integers(2, len(d))):]
+        elif kind == 3:  # a segment length that points far outside
+            at = d.find(b"\xff\xdb")
+            if at < 0:
+                at = 2
+            d[at + 2: at + 4] = bytes([int(rng.integers(0, 256)), int(rng.integers(0, 256))])
+        else:
+            at = int(rng.integers(2, head))
+            d[at] = 0xFF
+            d[at + 1] = int(rng.choice([0xC0, 0xC2, 0xC4, 0xDA, 0xDB, 0xDD, 0xD9, 0xE1]))
+        answers = []
+        for guard in (0x00, 0xFF):
+            n = len(d)
+            buf = (C.c_ubyte * (n + 4096)).from_buffer_copy(bytes(d) + bytes([guard]) * 4096)
+            w, h, f = C.c_size_t(0), C.c_size_t(0), C.c_int(-7)
+            st = lib.uhdrb200_jpeg_get_info(buf, n, C.byref(w), C.byref(h), C.byref(f))
+            assert st in allowed, (it, st)
+            answers.append((st, w.value, h.value, f.value))
+        assert answers[0] == answers[1], (it, answers)  # nothing behind the last byte took part
+        st, w, h, f = answers[0]
+        if st == 0:
+            accepted += 1
+            assert 1 <= w <= 8192 and 1 <= h <= 8192 and f in (abi.PIX_FMT_YUV420, abi.PIX_FMT_MONOCHROME)
+    assert 300 < accepted < 9700  # the mutations reach both sides
+
+
 def test_size_limit(lib):
     big = encode(np.zeros((8, 8200), np.uint8), quality=50)  # wider than kMaxWidth = 8192 (jpegdecoderhelper.cpp:254-258)
     assert info(lib, big)[0] == abi.ERROR_UNSUPPORTED_WIDTH_HEIGHT
