@@ -50,6 +50,16 @@ int uhdrb200_test_eval(int fn, const float* in_dev, float* out_dev, size_t n, vo
 size_t uhdrb200_test_jpeg_headers(int quality, int grey, int width, int height, const void* icc, size_t icc_bytes, void* out, size_t cap);
 size_t uhdrb200_test_jpeg_stuff(const void* src, size_t n, void* out, size_t cap);
 
+/* Host-only front end of the JPEG decoder (csrc/jpeg_huff.cu), callable without a GPU: the removal of the byte stuffing
+ * from an entropy-coded segment src[0, n) as uhdrb200_jpeg_decode_* does it before the upload. FF 00 -> FF, fill bytes
+ * (FF FF) dropped, every RSTn marker replaced by zero padding up to the next multiple of `uhdrb200_test_jpeg_subseq_bytes()`
+ * with the new interval's offset appended to interval_start (at most max_intervals entries, the first is 0), any other
+ * marker ends the segment and is returned in *marker (0 when the data ran out first). `out` needs n + max_intervals *
+ * subseq_bytes + 64 bytes. Returns the bytes written. */
+size_t uhdrb200_test_jpeg_destuff(const void* src, size_t n, void* out, int* marker, unsigned max_intervals, unsigned* interval_start,
+                                  unsigned* n_intervals);
+size_t uhdrb200_test_jpeg_subseq_bytes(void);
+
 #ifdef __cplusplus
 }
 #endif

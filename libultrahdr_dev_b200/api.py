@@ -71,6 +71,8 @@ TEST_SYMBOLS = {
     "uhdrb200_test_eval": (C.c_int, [C.c_int, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
     "uhdrb200_test_jpeg_headers": (C.c_size_t, [C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t]),
     "uhdrb200_test_jpeg_stuff": (C.c_size_t, [C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t]),
+    "uhdrb200_test_jpeg_destuff": (C.c_size_t, [C.c_void_p, C.c_size_t, C.c_void_p, C.POINTER(C.c_int), C.c_uint, C.POINTER(C.c_uint), C.POINTER(C.c_uint)]),
+    "uhdrb200_test_jpeg_subseq_bytes": (C.c_size_t, []),
 }
 
 

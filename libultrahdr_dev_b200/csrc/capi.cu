@@ -1954,6 +1954,12 @@ size_t uhdrb200_test_jpeg_headers(int quality, int grey, int width, int height, 
   return jpeg_write_headers((uint8_t*)out, cap, width, height, grey != 0, t, icc, icc_bytes);
 }
 size_t uhdrb200_test_jpeg_stuff(const void* src, size_t n, void* out, size_t cap) { return jpeg_stuff((const uint8_t*)src, n, (uint8_t*)out, cap); }
+size_t uhdrb200_test_jpeg_destuff(const void* src, size_t n, void* out, int* marker, unsigned max_intervals, unsigned* interval_start,
+                                  unsigned* n_intervals) {
+  if (!src || !out || !marker || !interval_start || !n_intervals || max_intervals == 0) return 0;
+  return jpeg_destuff((const uint8_t*)src, 0, n, (uint8_t*)out, marker, max_intervals, interval_start, n_intervals);
+}
+size_t uhdrb200_test_jpeg_subseq_bytes(void) { return kJpegSubseqBits / 8; }
 int uhdrb200_set_numeric_mode(int mode) {
   if (mode != UHDRB200_MODE_ANALYTIC && mode != UHDRB200_MODE_LUT) return UHDRB200_ERROR_UNSUPPORTED_FEATURE;
   t_numeric_mode = mode;

@@ -175,3 +175,68 @@ def test_encoder_byte_stuffing(lib):
         assert bytes(out[:got]) == want
         if n > 17:
             assert lib.uhdrb200_test_jpeg_stuff(buf, n, out, len(want) - 1) == 0  # one byte short
+
+
+def _destuff_model(src, align, max_intervals):
+    """The rules of jpeg_destuff, byte by byte."""
+    out, starts, marker, i, n = bytearray(), [0], 0, 0, len(src)
+    while i < n:
+        b = src[i]
+        if b != 0xFF:
+            out.append(b)
+            i += 1
+            continue
+        m = src[i + 1] if i + 1 < n else 0xD9
+        if m == 0x00:
+            out.append(0xFF)
+            i += 2
+        elif m == 0xFF:
+            i += 1
+        elif 0xD0 <= m <= 0xD7 and len(starts) < max_intervals:
+            out.extend(bytes(-len(out) % align))
+            starts.append(len(out))
+            i += 2
+        else:
+            marker = m
+            break
+    return bytes(out), starts, marker
+
+
+def _destuff(lib, src, max_intervals):
+    align = lib.uhdrb200_test_jpeg_subseq_bytes()
+    n = len(src)
+    out = (C.c_ubyte * (n + max_intervals * align + 64))()
+    buf = (C.c_ubyte * max(1, n)).from_buffer_copy(bytes(src) or b"\0")
+    marker, count = C.c_int(-1), C.c_uint(0)
+    starts = (C.c_uint * max_intervals)()
+    got = lib.uhdrb200_test_jpeg_destuff(buf, n, out, C.byref(marker), max_intervals, starts, C.byref(count))
+    return bytes(out[:got]), list(starts[: count.value]), marker.value
+
+
+def test_decoder_byte_stuffing_removal(lib):
+    """The SSE2 loop of the decoder's host front end against the rules written out byte by byte: stuffed bytes, fill
+    bytes, restart markers (padding to the subsequence size, interval offsets, more markers than intervals), the marker
+    that ends the segment, FF as the very last byte, every length around the 16-byte vector size."""
+    align = lib.uhdrb200_test_jpeg_subseq_bytes()
+    assert align >= 32 and align % 4 == 0
+    rng = np.random.Generator(np.random.PCG64(12))
+    for n in list(range(0, 40)) + [127, 128, 129, 1000, 4097, 70001]:
+        for dense in (0.0, 0.02, 0.3):
+            src = rng.integers(0, 255, n, dtype=np.uint8)  # no FF yet
+            at = np.nonzero(rng.random(n) < dense)[0]
+            src = bytearray(bytes(src))
+            for a in at:
+                src[a] = 0xFF
+                if a + 1 < n:  # mostly stuffing, some fill bytes and restart markers, never another marker
+                    src[a + 1] = int(rng.choice([0x00, 0x00, 0x00, 0xFF, 0xD0 + int(rng.integers(0, 8))]))
+            for max_intervals in (1, 3, 4096):
+                want = _destuff_model(src, align, max_intervals)
+                got = _destuff(lib, src, max_intervals)
+                assert got == want, (n, dense, max_intervals)
+    # a marker that is not RSTn ends the segment and is reported; so does an RSTn beyond the declared intervals
+    body = bytes([1, 2, 3, 0xFF, 0x00, 4]) * 5
+    for m in (0xD9, 0xC4, 0xDA, 0xE0):
+        out, starts, marker = _destuff(lib, body + bytes([0xFF, m]) + body, 8)
+        assert out == body.replace(b"\xff\x00", b"\xff") and marker == m and starts == [0]
+    out, starts, marker = _destuff(lib, body + b"\xff\xd0" + body + b"\xff\xd1" + body, 2)
+    assert marker == 0xD1 and starts == [0, align] and len(out) == align + len(body.replace(b"\xff\x00", b"\xff"))
