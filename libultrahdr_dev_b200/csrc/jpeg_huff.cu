@@ -227,6 +227,9 @@ size_t jpeg_destuff(const uint8_t* d, size_t begin, size_t end, uint8_t* dst, in
 // ================================================================ device: the decoder
 namespace {
 
+#ifndef UHDR_JPEG_HYP
+#define UHDR_JPEG_HYP 1  // phase hypotheses for interleaved scans (below); 0: guessed start + fixed-point rounds only
+#endif
 constexpr int kHuffThreads = 128;  // subsequences per CTA
 #ifndef UHDR_JPEG_WARM
 #define UHDR_JPEG_WARM 32
@@ -407,11 +410,15 @@ __device__ __forceinline__ void span_of(const JpegScan& sc, uint32_t t, uint64_t
 // results not stored): the chain that starts at the guessed state of the first warm-up lane has fallen into step by the
 // time it reaches the CTA's own subsequences (for every stream whose synchronisation distance is below kHuffWarm
 // subsequences), so the later rounds find the CTA's exit states already exact and only verify them.
-template <bool FIRST>
+// MODE 2 (after the phase-hypothesis passes below): every subsequence has an exit state already; all of them are decoded
+// once more from their left neighbour's state (the proof, and the repair where a hypothesis chain was broken).
+constexpr int kRoundLater = 0, kRoundFirst = 1, kRoundVerify = 2;
+template <int MODE>
 __global__ void __launch_bounds__(kHuffThreads + kHuffWarm) huff_round_kernel(const __grid_constant__ JpegScan sc, uint32_t* __restrict__ exit_state,
                                                                               uint32_t* __restrict__ count, const uint8_t* __restrict__ cta_dirty_in,
                                                                               uint8_t* __restrict__ cta_dirty_out, uint32_t* __restrict__ n_changed,
                                                                               uint32_t* __restrict__ max_steps) {
+  constexpr bool FIRST = MODE == kRoundFirst;
   __shared__ HuffSmem sm;
   __shared__ uint32_t exit_s[kHuffThreads + kHuffWarm];
   __shared__ uint8_t dirty_s[2][kHuffThreads + kHuffWarm];
@@ -419,7 +426,7 @@ __global__ void __launch_bounds__(kHuffThreads + kHuffWarm) huff_round_kernel(co
   const uint32_t i = threadIdx.x;
   const int64_t tt = (int64_t)blockIdx.x * kHuffThreads + (int64_t)i - (int64_t)kLead;
   const uint32_t t = tt < 0 ? 0u : (uint32_t)tt;
-  if (!FIRST && (blockIdx.x == 0 || !cta_dirty_in[blockIdx.x - 1])) {  // CTA-uniform
+  if (MODE == kRoundLater && (blockIdx.x == 0 || !cta_dirty_in[blockIdx.x - 1])) {  // CTA-uniform
     if (i == 0) cta_dirty_out[blockIdx.x] = 0;
     return;
   }
@@ -444,6 +451,7 @@ __global__ void __launch_bounds__(kHuffThreads + kHuffWarm) huff_round_kernel(co
     ch = now != cur;
     cur = now;
   }
+  if (MODE == kRoundVerify) ch = live;  // every lane decodes again from its neighbour's state in the first step
   exit_s[i] = cur;
   dirty_s[0][i] = ch ? 1 : 0;
   int ph = 0;
@@ -475,6 +483,103 @@ __global__ void __launch_bounds__(kHuffThreads + kHuffWarm) huff_round_kernel(co
     const bool moved = FIRST || cur != entry_exit;
     cta_dirty_out[blockIdx.x] = moved ? 1 : 0;
     if (moved) atomicAdd(n_changed, 1u);
+  }
+}
+
+// ---- phase hypotheses (interleaved scans: blocks_per_mcu = H > 1) ---------------------------------------------------------
+// Why the chains above are long: a decoder started at a subsequence border falls into step with the bit positions and the
+// coefficient index within ~100 bits, but which BLOCK OF THE MCU it is in (luma or chroma tables) only by luck; started
+// with the right block it is in step almost at once (scripts/huff_chain_sim.py: mean 0.09 subsequences against 1.5, longest
+// 2.7 against 10 in a stream of 1300). So every subsequence is decoded once per possible block-in-MCU (pass A: exit state
+// X[j][h], blocks N[j][h]), then once more from each of its left neighbour's H exit states (pass B: the EXACT exit state
+// Y[j][h] and block count M[j][h] of subsequence j given that the neighbour's true hypothesis is h, and the hypothesis of
+// j that left in the same state, Lnk[j][h]). The true hypotheses are then a composition of H -> H maps along the stream,
+// i.e. a scan (pass C), and one verification round (huff_round_kernel<kRoundVerify>) proves the result and repairs the few
+// places where no hypothesis of j left in the state Y[j][h] (a broken link: the chain continues with hypothesis 0).
+constexpr int kHypStride = 8;  // hypotheses per subsequence in the arrays (H <= 8: three bits per link)
+
+__global__ void __launch_bounds__(kHuffThreads) huff_hyp_kernel(const __grid_constant__ JpegScan sc, uint32_t* __restrict__ X, uint32_t* __restrict__ N) {
+  __shared__ HuffSmem sm;
+  load_tables(&sm, sc.tables);
+  const uint32_t H = (uint32_t)sc.blocks_per_mcu, g = blockIdx.x * kHuffThreads + threadIdx.x, j = g / H, h = g - j * H;
+  if (j >= sc.n_subseq) return;
+  uint64_t b, e;
+  span_of(sc, j, b, e);
+  uint32_t cnt = 0;
+  X[j * kHypStride + h] = decode_span<false>(sc, &sm, b, e, h, 0, 0, 0, cnt);
+  N[j * kHypStride + h] = cnt;
+}
+
+__global__ void __launch_bounds__(kHuffThreads) huff_link_kernel(const __grid_constant__ JpegScan sc, const uint32_t* __restrict__ X,
+                                                                 const uint32_t* __restrict__ N, uint32_t* __restrict__ Y, uint32_t* __restrict__ M,
+                                                                 uint8_t* __restrict__ Lnk) {
+  __shared__ HuffSmem sm;
+  load_tables(&sm, sc.tables);
+  const uint32_t H = (uint32_t)sc.blocks_per_mcu, g = blockIdx.x * kHuffThreads + threadIdx.x, j = g / H, h = g - j * H;
+  if (j >= sc.n_subseq) return;
+  uint32_t y, m, l = 0;
+  if (hard_start(sc, j)) {  // the entry state is known: block 0, coefficient 0 at the border itself = hypothesis 0
+    y = X[j * kHypStride];
+    m = N[j * kHypStride];
+  } else {
+    uint64_t b, e;
+    span_of(sc, j, b, e);
+    const uint32_t st = X[(j - 1) * kHypStride + h];
+    y = decode_span<false>(sc, &sm, b + (st >> 16), e, (st >> 8) & 0xFFu, st & 0xFFu, 0, 0, m);
+    // the hypothesis of j that leaves in this very state; failing that (none has fallen into step inside j) one that leaves
+    // in the same block of the MCU, which falls into step early in j + 1; failing that 0. A wrong choice costs steps of the
+    // verification round, never exactness.
+    bool exact = false;
+    for (uint32_t k = H; k-- > 0;) {
+      const uint32_t x = X[j * kHypStride + k];
+      if (x == y) {
+        l = k;
+        exact = true;
+      } else if (!exact && ((x ^ y) & 0xFF00u) == 0) {
+        l = k;
+      }
+    }
+  }
+  Y[j * kHypStride + h] = y;
+  M[j * kHypStride + h] = m;
+  Lnk[j * kHypStride + h] = (uint8_t)l;
+}
+
+// pass C: the true hypothesis of every subsequence = Lnk[j][true hypothesis of j - 1], a scan of H -> H maps (three bits per
+// entry in one word); one CTA, a chunk of consecutive subsequences per thread
+__device__ __forceinline__ uint32_t map_get(uint32_t f, uint32_t h) { return (f >> (3 * h)) & 7u; }
+__device__ __forceinline__ uint32_t map_then(uint32_t f, uint32_t g) {  // h -> g[f[h]]
+  uint32_t r = 0;
+#pragma unroll
+  for (uint32_t h = 0; h < (uint32_t)kHypStride; h++) r |= map_get(g, map_get(f, h)) << (3 * h);
+  return r;
+}
+__global__ void __launch_bounds__(1024) huff_select_kernel(const uint32_t* __restrict__ Y, const uint32_t* __restrict__ M, const uint8_t* __restrict__ Lnk,
+                                                           uint32_t* __restrict__ exit_state, uint32_t* __restrict__ count, uint32_t n) {
+  __shared__ uint32_t part[1024];
+  constexpr uint32_t kIdentity = 0u | 1u << 3 | 2u << 6 | 3u << 9 | 4u << 12 | 5u << 15 | 6u << 18 | 7u << 21;
+  const uint32_t per = (n + 1023) / 1024, lo = threadIdx.x * per, hi = min(lo + per, n);
+  uint32_t f = kIdentity;
+  for (uint32_t j = lo; j < hi; j++) {
+    uint32_t mj = 0;
+    const uint2 raw = *reinterpret_cast<const uint2*>(Lnk + (size_t)j * kHypStride);
+#pragma unroll
+    for (uint32_t h = 0; h < (uint32_t)kHypStride; h++) mj |= (((h < 4 ? raw.x >> (8 * h) : raw.y >> (8 * (h - 4))) & 7u)) << (3 * h);
+    f = map_then(f, mj);
+  }
+  part[threadIdx.x] = f;
+  __syncthreads();
+  for (uint32_t d = 1; d < 1024; d <<= 1) {  // Hillis-Steele inclusive scan under composition (earlier chunks first)
+    const uint32_t v = threadIdx.x >= d ? part[threadIdx.x - d] : kIdentity;
+    __syncthreads();
+    part[threadIdx.x] = map_then(v, part[threadIdx.x]);
+    __syncthreads();
+  }
+  uint32_t h = threadIdx.x ? map_get(part[threadIdx.x - 1], 0) : 0u;  // subsequence 0 is a hard start: whatever enters, 0 leaves
+  for (uint32_t j = lo; j < hi; j++) {
+    exit_state[j] = Y[(size_t)j * kHypStride + h];
+    count[j] = M[(size_t)j * kHypStride + h];
+    h = Lnk[(size_t)j * kHypStride + h] & 7u;
   }
 }
 
@@ -622,7 +727,7 @@ __global__ void __launch_bounds__(kDcThreads) dc_interval_kernel(const __grid_co
 size_t jpeg_huff_workspace_bytes(uint32_t n_subseq) {
   const size_t n = ((size_t)n_subseq + 63) & ~(size_t)63;
   const size_t dc_chunks = 3 * (((size_t)8192 * 8192 / 64 + kDcChunk - 1) / kDcChunk);  // largest image jpeg_parse admits: 65535^2 is clamped by the caller
-  return n * (3 * 4 + 2) + 256 + dc_chunks * 4;
+  return n * (3 * 4 + 2) + 256 + dc_chunks * 4 + 64 + n * kHypStride * (4 * 4 + 1);  // + X, N, Y, M, Lnk of the phase hypotheses
 }
 
 cudaError_t jpeg_huff_decode(const JpegScan& sc, void* workspace, cudaStream_t s, int* iters) {
@@ -646,28 +751,59 @@ cudaError_t jpeg_huff_decode(const JpegScan& sc, void* workspace, cudaStream_t s
     cudaEventRecord(ev[0], s);
   }
   uint32_t* step_stat = timing ? n_changed + 62 : nullptr;  // slots 62, 63: longest chain of the first / the later rounds
-  huff_round_kernel<true><<<grid, kHuffThreads + kHuffWarm, 0, s>>>(sc, exit_a, count, dirty_b, dirty_a, n_changed, step_stat);
-  if (timing) cudaEventRecord(ev[1], s);
+  const size_t dc_chunks = 3 * (((size_t)8192 * 8192 / 64 + kDcChunk - 1) / kDcChunk);  // as in jpeg_huff_workspace_bytes
+  uint32_t* hyp_x = (uint32_t*)(((uintptr_t)(partial + dc_chunks) + 63) & ~(uintptr_t)63);
+  uint32_t* hyp_n = hyp_x + np * kHypStride;
+  uint32_t* hyp_y = hyp_n + np * kHypStride;
+  uint32_t* hyp_m = hyp_y + np * kHypStride;
+  uint8_t* hyp_l = (uint8_t*)(hyp_m + np * kHypStride);
+  const uint32_t H = (uint32_t)sc.blocks_per_mcu;
+  // Where the hypotheses pay (4K, one host thread, same box): 0.49 -> 0.47 ms at quality 75, 1.32 -> 1.17 at 90, 1.47 -> 1.43 at
+  // 95, 1.36 -> 1.16 with a restart interval per MCU row. Where they do not: streams with few end-of-block codes (quality
+  // 100: 200 bits per block, 3.5 -> 3.9 ms), whose chains wait for the COEFFICIENT INDEX to fall into step, which no guess of
+  // the block helps, and short restart intervals, which bound every chain anyway (16 MCUs: 0.99 -> 1.02 ms).
+  const uint64_t bits_per_block = sc.total_bits / sc.total_blocks;
+  const bool short_intervals = sc.restart_interval != 0 && (uint64_t)n < 16ull * sc.n_intervals;
+  const bool hyp = UHDR_JPEG_HYP && H >= 2 && H <= (uint32_t)kHypStride && bits_per_block < 128 && !short_intervals;
   int pass = 0;
   uint8_t* din = dirty_a;
   uint8_t* dout = dirty_b;
+  bool settled = false;
+  if (hyp) {
+    const unsigned hgrid = (unsigned)(((uint64_t)n * H + kHuffThreads - 1) / kHuffThreads);
+    huff_hyp_kernel<<<hgrid, kHuffThreads, 0, s>>>(sc, hyp_x, hyp_n);
+    huff_link_kernel<<<hgrid, kHuffThreads, 0, s>>>(sc, hyp_x, hyp_n, hyp_y, hyp_m, hyp_l);
+    huff_select_kernel<<<1, 1024, 0, s>>>(hyp_y, hyp_m, hyp_l, exit_a, count, n);
+    huff_round_kernel<kRoundVerify><<<grid, kHuffThreads, 0, s>>>(sc, exit_a, count, dirty_b, dirty_a, n_changed, step_stat);
+    if (timing) cudaEventRecord(ev[1], s);
+    uint32_t moved = 0;
+    if ((e = cudaMemcpyAsync(&moved, n_changed, 4, cudaMemcpyDeviceToHost, s)) != cudaSuccess) return e;
+    if ((e = cudaStreamSynchronize(s)) != cudaSuccess) return e;
+    settled = moved == 0;  // no CTA's last exit state moved: every entry state is exact
+    pass = 3;              // launches so far beyond the first (for the caller's launch count)
+  } else {
+    huff_round_kernel<kRoundFirst><<<grid, kHuffThreads + kHuffWarm, 0, s>>>(sc, exit_a, count, dirty_b, dirty_a, n_changed, step_stat);
+    if (timing) cudaEventRecord(ev[1], s);
+  }
   // Rounds across CTAs, two per host round trip: after the first, every CTA has re-entered with its predecessor's exact
   // exit state (a CTA's LAST exit state is almost always right already, 128 subsequences after a guessed start); the
   // second finds nothing to do and proves the fixed point. A round that changes nothing costs a launch.
-  for (;;) {
+  int rounds = 0;
+  while (!settled) {
     uint32_t last_changed = 0;
     for (int k = 0; k < 2; k++) {
       pass++;
+      rounds++;
       if (pass % 64 == 0) {  // the 64 counters come round again; the previous pair has been read
         if ((e = cudaMemsetAsync(n_changed, 0, 256, s)) != cudaSuccess) return e;
       }
-      huff_round_kernel<false><<<grid, kHuffThreads, 0, s>>>(sc, exit_a, count, din, dout, n_changed + pass % 64, timing ? step_stat + 1 : nullptr);
+      huff_round_kernel<kRoundLater><<<grid, kHuffThreads, 0, s>>>(sc, exit_a, count, din, dout, n_changed + pass % 64, timing ? step_stat + 1 : nullptr);
       uint8_t* td = din; din = dout; dout = td;
     }
     if ((e = cudaMemcpyAsync(&last_changed, n_changed + pass % 64, 4, cudaMemcpyDeviceToHost, s)) != cudaSuccess) return e;
     if ((e = cudaStreamSynchronize(s)) != cudaSuccess) return e;
     if (last_changed == 0) break;           // nothing moved in the last round: every entry state is exact
-    if ((uint32_t)pass > grid + 4) break;   // cannot happen: exactness advances by at least one CTA per round
+    if ((uint32_t)rounds > grid + 4) break;   // cannot happen: exactness advances by at least one CTA per round
   }
   if (iters) *iters = pass;
   if (timing) cudaEventRecord(ev[2], s);
