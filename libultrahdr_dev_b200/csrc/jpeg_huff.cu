@@ -496,7 +496,8 @@ __global__ void __launch_bounds__(kHuffThreads + kHuffWarm) huff_round_kernel(co
 // j that left in the same state, Lnk[j][h]). The true hypotheses are then a composition of H -> H maps along the stream,
 // i.e. a scan (pass C), and one verification round (huff_round_kernel<kRoundVerify>) proves the result and repairs the few
 // places where no hypothesis of j left in the state Y[j][h] (a broken link: the chain continues with hypothesis 0).
-constexpr int kHypStride = 8;  // hypotheses per subsequence in the arrays (H <= 8: three bits per link)
+constexpr int kHypReal = 8;     // X, N: one slot per guessed block of the MCU (H <= 8)
+constexpr int kHypStride = 16;  // Y, M, Lnk: slots 0 .. 7 = "the neighbour's true hypothesis is h", 8 + h = the virtual hypothesis below
 
 __global__ void __launch_bounds__(kHuffThreads) huff_hyp_kernel(const __grid_constant__ JpegScan sc, uint32_t* __restrict__ X, uint32_t* __restrict__ N) {
   __shared__ HuffSmem sm;
@@ -506,10 +507,32 @@ __global__ void __launch_bounds__(kHuffThreads) huff_hyp_kernel(const __grid_con
   uint64_t b, e;
   span_of(sc, j, b, e);
   uint32_t cnt = 0;
-  X[j * kHypStride + h] = decode_span<false>(sc, &sm, b, e, h, 0, 0, 0, cnt);
-  N[j * kHypStride + h] = cnt;
+  X[j * kHypReal + h] = decode_span<false>(sc, &sm, b, e, h, 0, 0, 0, cnt);
+  N[j * kHypReal + h] = cnt;
 }
 
+// the hypothesis of subsequence j that leaves in state y; failing that (none has fallen into step inside j) one that leaves
+// in the same block of the MCU, which falls into step early in j + 1; failing that 0. A wrong choice costs steps of the
+// verification round, never exactness.
+__device__ __forceinline__ uint32_t link_of(const uint32_t* __restrict__ X, uint32_t j, uint32_t H, uint32_t y, bool& exact) {
+  uint32_t l = 0;
+  exact = false;
+  for (uint32_t k = H; k-- > 0;) {
+    const uint32_t x = X[j * kHypReal + k];
+    if (x == y) {
+      l = k;
+      exact = true;
+    } else if (!exact && ((x ^ y) & 0xFF00u) == 0) {
+      l = k;
+    }
+  }
+  return l;
+}
+
+// Thread (j, h): subsequence j decoded from the exit state of hypothesis h of j - 1. When no hypothesis of j leaves in the
+// resulting (exact) state y, the same thread goes on through j + 1 from y and looks for ITS exit state among the hypotheses
+// of j + 1: the pair is recorded as the virtual hypothesis 8 + h of j (slots 8 + h of j + 1 hold its exit state, block
+// count and link), which repairs every chain that falls into step within two subsequences.
 __global__ void __launch_bounds__(kHuffThreads) huff_link_kernel(const __grid_constant__ JpegScan sc, const uint32_t* __restrict__ X,
                                                                  const uint32_t* __restrict__ N, uint32_t* __restrict__ Y, uint32_t* __restrict__ M,
                                                                  uint8_t* __restrict__ Lnk) {
@@ -519,58 +542,59 @@ __global__ void __launch_bounds__(kHuffThreads) huff_link_kernel(const __grid_co
   if (j >= sc.n_subseq) return;
   uint32_t y, m, l = 0;
   if (hard_start(sc, j)) {  // the entry state is known: block 0, coefficient 0 at the border itself = hypothesis 0
-    y = X[j * kHypStride];
-    m = N[j * kHypStride];
+    y = X[j * kHypReal];
+    m = N[j * kHypReal];
   } else {
     uint64_t b, e;
     span_of(sc, j, b, e);
-    const uint32_t st = X[(j - 1) * kHypStride + h];
+    const uint32_t st = X[(j - 1) * kHypReal + h];
     y = decode_span<false>(sc, &sm, b + (st >> 16), e, (st >> 8) & 0xFFu, st & 0xFFu, 0, 0, m);
-    // the hypothesis of j that leaves in this very state; failing that (none has fallen into step inside j) one that leaves
-    // in the same block of the MCU, which falls into step early in j + 1; failing that 0. A wrong choice costs steps of the
-    // verification round, never exactness.
-    bool exact = false;
-    for (uint32_t k = H; k-- > 0;) {
-      const uint32_t x = X[j * kHypStride + k];
-      if (x == y) {
-        l = k;
-        exact = true;
-      } else if (!exact && ((x ^ y) & 0xFF00u) == 0) {
-        l = k;
-      }
+    bool exact;
+    l = link_of(X, j, H, y, exact);
+    if (!exact && j + 1 < sc.n_subseq && !hard_start(sc, j + 1)) {
+      span_of(sc, j + 1, b, e);
+      uint32_t m2;
+      const uint32_t y2 = decode_span<false>(sc, &sm, b + (y >> 16), e, (y >> 8) & 0xFFu, y & 0xFFu, 0, 0, m2);
+      bool exact2;
+      const uint32_t l2 = link_of(X, j + 1, H, y2, exact2);
+      const size_t v = (size_t)(j + 1) * kHypStride + 8 + h;
+      Y[v] = y2;
+      M[v] = m2;
+      Lnk[v] = (uint8_t)l2;
+      l = 8 + h;
     }
   }
-  Y[j * kHypStride + h] = y;
-  M[j * kHypStride + h] = m;
-  Lnk[j * kHypStride + h] = (uint8_t)l;
+  Y[(size_t)j * kHypStride + h] = y;
+  M[(size_t)j * kHypStride + h] = m;
+  Lnk[(size_t)j * kHypStride + h] = (uint8_t)l;
 }
 
-// pass C: the true hypothesis of every subsequence = Lnk[j][true hypothesis of j - 1], a scan of H -> H maps (three bits per
-// entry in one word); one CTA, a chunk of consecutive subsequences per thread
-__device__ __forceinline__ uint32_t map_get(uint32_t f, uint32_t h) { return (f >> (3 * h)) & 7u; }
-__device__ __forceinline__ uint32_t map_then(uint32_t f, uint32_t g) {  // h -> g[f[h]]
-  uint32_t r = 0;
+// pass C: the true hypothesis of every subsequence = Lnk[j][true hypothesis of j - 1], a scan of 16 -> 16 maps (four bits
+// per entry in one 64-bit word; slots nobody wrote hold arbitrary links, which only ever feed other unused slots); one CTA,
+// a chunk of consecutive subsequences per thread
+__device__ __forceinline__ uint32_t map_get(uint64_t f, uint32_t h) { return (uint32_t)(f >> (4 * h)) & 15u; }
+__device__ __forceinline__ uint64_t map_then(uint64_t f, uint64_t g) {  // h -> g[f[h]]
+  uint64_t r = 0;
 #pragma unroll
-  for (uint32_t h = 0; h < (uint32_t)kHypStride; h++) r |= map_get(g, map_get(f, h)) << (3 * h);
+  for (uint32_t h = 0; h < (uint32_t)kHypStride; h++) r |= (uint64_t)map_get(g, map_get(f, h)) << (4 * h);
   return r;
 }
 __global__ void __launch_bounds__(1024) huff_select_kernel(const uint32_t* __restrict__ Y, const uint32_t* __restrict__ M, const uint8_t* __restrict__ Lnk,
                                                            uint32_t* __restrict__ exit_state, uint32_t* __restrict__ count, uint32_t n) {
-  __shared__ uint32_t part[1024];
-  constexpr uint32_t kIdentity = 0u | 1u << 3 | 2u << 6 | 3u << 9 | 4u << 12 | 5u << 15 | 6u << 18 | 7u << 21;
+  __shared__ uint64_t part[1024];
+  constexpr uint64_t kIdentity = 0xFEDCBA9876543210ull;
   const uint32_t per = (n + 1023) / 1024, lo = threadIdx.x * per, hi = min(lo + per, n);
-  uint32_t f = kIdentity;
+  uint64_t f = kIdentity;
   for (uint32_t j = lo; j < hi; j++) {
-    uint32_t mj = 0;
-    const uint2 raw = *reinterpret_cast<const uint2*>(Lnk + (size_t)j * kHypStride);
+    uint64_t mj = 0;
 #pragma unroll
-    for (uint32_t h = 0; h < (uint32_t)kHypStride; h++) mj |= (((h < 4 ? raw.x >> (8 * h) : raw.y >> (8 * (h - 4))) & 7u)) << (3 * h);
+    for (uint32_t h = 0; h < (uint32_t)kHypStride; h++) mj |= (uint64_t)(Lnk[(size_t)j * kHypStride + h] & 15u) << (4 * h);
     f = map_then(f, mj);
   }
   part[threadIdx.x] = f;
   __syncthreads();
   for (uint32_t d = 1; d < 1024; d <<= 1) {  // Hillis-Steele inclusive scan under composition (earlier chunks first)
-    const uint32_t v = threadIdx.x >= d ? part[threadIdx.x - d] : kIdentity;
+    const uint64_t v = threadIdx.x >= d ? part[threadIdx.x - d] : kIdentity;
     __syncthreads();
     part[threadIdx.x] = map_then(v, part[threadIdx.x]);
     __syncthreads();
@@ -579,7 +603,7 @@ __global__ void __launch_bounds__(1024) huff_select_kernel(const uint32_t* __res
   for (uint32_t j = lo; j < hi; j++) {
     exit_state[j] = Y[(size_t)j * kHypStride + h];
     count[j] = M[(size_t)j * kHypStride + h];
-    h = Lnk[(size_t)j * kHypStride + h] & 7u;
+    h = Lnk[(size_t)j * kHypStride + h] & 15u;
   }
 }
 
@@ -727,7 +751,7 @@ __global__ void __launch_bounds__(kDcThreads) dc_interval_kernel(const __grid_co
 size_t jpeg_huff_workspace_bytes(uint32_t n_subseq) {
   const size_t n = ((size_t)n_subseq + 63) & ~(size_t)63;
   const size_t dc_chunks = 3 * (((size_t)8192 * 8192 / 64 + kDcChunk - 1) / kDcChunk);  // largest image jpeg_parse admits: 65535^2 is clamped by the caller
-  return n * (3 * 4 + 2) + 256 + dc_chunks * 4 + 64 + n * kHypStride * (4 * 4 + 1);  // + X, N, Y, M, Lnk of the phase hypotheses
+  return n * (3 * 4 + 2) + 256 + dc_chunks * 4 + 64 + n * (kHypReal * 8 + kHypStride * 9);  // + X, N | Y, M, Lnk of the phase hypotheses
 }
 
 cudaError_t jpeg_huff_decode(const JpegScan& sc, void* workspace, cudaStream_t s, int* iters) {
@@ -753,8 +777,8 @@ cudaError_t jpeg_huff_decode(const JpegScan& sc, void* workspace, cudaStream_t s
   uint32_t* step_stat = timing ? n_changed + 62 : nullptr;  // slots 62, 63: longest chain of the first / the later rounds
   const size_t dc_chunks = 3 * (((size_t)8192 * 8192 / 64 + kDcChunk - 1) / kDcChunk);  // as in jpeg_huff_workspace_bytes
   uint32_t* hyp_x = (uint32_t*)(((uintptr_t)(partial + dc_chunks) + 63) & ~(uintptr_t)63);
-  uint32_t* hyp_n = hyp_x + np * kHypStride;
-  uint32_t* hyp_y = hyp_n + np * kHypStride;
+  uint32_t* hyp_n = hyp_x + np * kHypReal;
+  uint32_t* hyp_y = hyp_n + np * kHypReal;
   uint32_t* hyp_m = hyp_y + np * kHypStride;
   uint8_t* hyp_l = (uint8_t*)(hyp_m + np * kHypStride);
   const uint32_t H = (uint32_t)sc.blocks_per_mcu;
@@ -764,7 +788,7 @@ cudaError_t jpeg_huff_decode(const JpegScan& sc, void* workspace, cudaStream_t s
   // the block helps, and short restart intervals, which bound every chain anyway (16 MCUs: 0.99 -> 1.02 ms).
   const uint64_t bits_per_block = sc.total_bits / sc.total_blocks;
   const bool short_intervals = sc.restart_interval != 0 && (uint64_t)n < 16ull * sc.n_intervals;
-  const bool hyp = UHDR_JPEG_HYP && H >= 2 && H <= (uint32_t)kHypStride && bits_per_block < 128 && !short_intervals;
+  const bool hyp = UHDR_JPEG_HYP && H >= 2 && H <= (uint32_t)kHypReal && bits_per_block < 128 && !short_intervals;
   int pass = 0;
   uint8_t* din = dirty_a;
   uint8_t* dout = dirty_b;

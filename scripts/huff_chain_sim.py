@@ -167,6 +167,56 @@ def main():
             need = max(need, best)
         return int(need)
 
+    # ---- the decoder as built (jpeg_huff.cu: huff_hyp_kernel, huff_link_kernel, huff_select_kernel) and two variants
+    def span(p, k, c, e):
+        while p < e and p < total:
+            p, k, c = step(p, k, c)
+        return (p, k, c)
+
+    def emulate(early=0, second_pass=False):
+        borders = [j * SUB for j in range(n_sub + 1)]
+        T = [None] * n_sub  # true exit states
+        st = (0, 0, 0)
+        for j in range(n_sub):
+            st = span(st[0], st[1], st[2], borders[j + 1])
+            T[j] = st
+        X = [[span(max(0, borders[j] - early), 0, h, borders[j + 1]) if not (early and j == 0) else span(0, 0, h, borders[1])
+              for h in range(B)] for j in range(n_sub)]
+        X[0] = [span(0, 0, 0, borders[1])] * B
+        exits, hyp, broken, repaired = [X[0][0]], 0, 0, 0
+        j = 1
+        while j < n_sub:
+            prev = X[j - 1][hyp] if exits[-1] == X[j - 1][hyp] else exits[-1]
+            y = span(X[j - 1][hyp][0], X[j - 1][hyp][1], X[j - 1][hyp][2], borders[j + 1])
+            match = [h for h in range(B) if X[j][h] == y]
+            if match:
+                hyp = match[0]
+            else:
+                broken += 1
+                same = [h for h in range(B) if X[j][h][2] == y[2]]
+                hyp = same[0] if same else 0
+                if second_pass and j + 1 < n_sub:  # the exact exit of j + 1 from the exact exit of j, linked there
+                    y2 = span(y[0], y[1], y[2], borders[j + 2])
+                    m2 = [h for h in range(B) if X[j + 1][h] == y2]
+                    if m2:
+                        exits += [y, y2]
+                        hyp = m2[0]
+                        repaired += 1
+                        j += 2
+                        continue
+            exits.append(y)
+            j += 1
+        wrong = [exits[j] != T[j] for j in range(n_sub)]
+        run = best = 0
+        for w in wrong:
+            run = run + 1 if w else 0
+            best = max(best, run)
+        return {"broken_links": broken, "second_pass_repairs": repaired, "wrong_exit_states": int(sum(wrong)), "longest_wrong_run": best}
+
+    as_built = emulate()
+    early_half = emulate(early=SUB // 2)
+    two_step = emulate(second_pass=True)
+
     print(json.dumps({"quality": quality, "image": f"{W}x{H} 4:2:0", "scan_bits": total, "subsequences": n_sub, "blocks_per_mcu": B,
                       "best_guess_minus_block_in_progress_mod_B": offs,
                       "guess_block_0": dict(row(d0), rounds=rounds(d0)),
@@ -174,7 +224,9 @@ def main():
                       "guess_block_in_progress": dict(row(d_same), rounds=rounds(d_same)),
                       "guess_block_after_it": dict(row(d_next), rounds=rounds(d_next)),
                       "better_of_those_two": dict(row(d_rule), rounds=rounds(d_rule)),
-                      "best_of_all_guesses_half_a_subsequence_early": dict(row(dh), rounds=rounds(dh))}))
+                      "best_of_all_guesses_half_a_subsequence_early": dict(row(dh), rounds=rounds(dh)),
+                      "decoder_as_built": as_built, "hypotheses_started_half_a_subsequence_early": early_half,
+                      "with_a_second_link_pass_over_two_subsequences": two_step}))
 
 
 if __name__ == "__main__":
